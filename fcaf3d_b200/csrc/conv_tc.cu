@@ -1,0 +1,340 @@
+// tcgen05 implicit-GEMM sparse convolution for sm_100a (bf16 operands, fp32 accumulators in TMEM).
+//
+// Output-stationary: one CTA owns a 128-row x BN-column output tile and walks the kernel offsets
+// that the tile actually uses (tile_mask).  For every (offset k, 64-channel slice) stage, four
+// producer warps gather the 128 neighbour rows (cp.async, 16 B per request, zero-fill for missing
+// neighbours) and the matching [BN x 64] slice of W_k^T into 128B-swizzled shared memory; a single
+// thread of warp 4 issues tcgen05.mma (M=128, N=BN, K=16) and releases the stage with
+// tcgen05.commit.  The accumulator never leaves TMEM until the fused epilogue
+// (bias, folded BatchNorm scale/shift, residual, ReLU/ELU), so there are no atomics, no scatter and
+// no intermediate [pairs x C] buffers as in MinkowskiEngine's gather-GEMM-scatter
+// (reference call sites: me_resnet.py:66-78 BasicBlock convs, fcaf3d_neck_with_head.py:52,60-69).
+#include "common.cuh"
+
+#define TC_BM 128
+#define TC_BK 64
+#define TC_LAG 2
+#define TC_PRODUCERS 128
+#define TC_THREADS 160
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(addr), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// K-major, 128-byte swizzle, 8-row atoms 1024 B apart (SBO); descriptor version 1 (sm_100)
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)1 << 16;             // leading byte offset (unused for swizzled K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;   // stride byte offset
+  d |= (uint64_t)1 << 46;             // version
+  d |= (uint64_t)2 << 61;             // SWIZZLE_128B
+  return d;
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+template <int BN>
+struct TcCfg {
+  static constexpr int STAGES = (BN == 64) ? 4 : 3;
+  static constexpr int A_BYTES = TC_BM * TC_BK * 2;
+  static constexpr int B_BYTES = BN * TC_BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+template <int BN, typename TOut>
+__global__ void __launch_bounds__(TC_THREADS)
+k_conv_tc(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict__ wt, const int* __restrict__ nbr, int ld,
+          const unsigned int* __restrict__ tile_mask, int n_out, int cin, int cout, int kvol,
+          const float* __restrict__ bias, const float* __restrict__ scale, const float* __restrict__ shift,
+          const TOut* __restrict__ residual, int act, int ch_mod, TOut* __restrict__ out) {
+  using Cfg = TcCfg<BN>;
+  constexpr int S = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S * Cfg::STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + S;
+  uint64_t* accum_bar = empty_bar + S;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int row0 = blockIdx.x * TC_BM, col0 = blockIdx.y * BN;
+  const unsigned int kmask = (nbr != nullptr) ? tile_mask[blockIdx.x] : 1u;
+  const int chunks = cin / TC_BK;
+  const int nstage = __popc(kmask & (kvol >= 32 ? 0xFFFFFFFFu : ((1u << kvol) - 1u))) * chunks;
+
+  if (tid == 0) {
+    for (int s = 0; s < S; ++s) {
+      mbar_init(&full_bar[s], TC_PRODUCERS / 32);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(accum_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 4) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"((uint32_t)(BN < 32 ? 32 : BN))
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp < 4) {
+    // ===================== producers: gather A rows + W_k^T slice ==========================
+    const int chunk16 = tid & 7, rsub = tid >> 3;  // 16 B chunk of the 128 B row, row inside a 16-row pass
+    int it = 0;
+    for (int k = 0; k < kvol; ++k) {
+      if (!((kmask >> k) & 1u)) continue;
+      int idx[TC_BM / 16];
+#pragma unroll
+      for (int p = 0; p < TC_BM / 16; ++p) {
+        const int r = p * 16 + rsub;
+        if (nbr != nullptr) {
+          idx[p] = __ldg(nbr + (long long)k * ld + row0 + r);
+        } else {
+          idx[p] = (row0 + r < n_out) ? row0 + r : -1;
+        }
+      }
+      for (int c = 0; c < chunks; ++c, ++it) {
+        const int s = it % S;
+        const uint32_t ph = (uint32_t)(it / S) & 1u;
+        mbar_wait(&empty_bar[s], ph ^ 1u);
+        const uint32_t a_base = smem_u32(smem + s * Cfg::STAGE_BYTES);
+        const uint32_t b_base = a_base + Cfg::A_BYTES;
+        const int ch0 = c * TC_BK + chunk16 * 8;
+#pragma unroll
+        for (int p = 0; p < TC_BM / 16; ++p) {
+          const int r = p * 16 + rsub;
+          const int src = idx[p];
+          const __nv_bfloat16* g = in + (src >= 0 ? ((long long)src * cin + ch0) : 0);
+          cp_async16(a_base + r * 128 + ((chunk16 ^ (r & 7)) << 4), g, src >= 0 ? 16u : 0u);
+        }
+        const __nv_bfloat16* wk = wt + ((long long)k * cout + col0) * cin + ch0;
+#pragma unroll
+        for (int p = 0; p < BN / 16; ++p) {
+          const int r = p * 16 + rsub;
+          cp_async16(b_base + r * 128 + ((chunk16 ^ (r & 7)) << 4), wk + (long long)r * cin, 16u);
+        }
+        cp_async_commit();
+        if (it >= TC_LAG) {
+          cp_async_wait<TC_LAG>();
+          fence_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&full_bar[(it - TC_LAG) % S]);
+        }
+      }
+    }
+    // drain the last TC_LAG groups
+    cp_async_wait<0>();
+    fence_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+      for (int j = (it > TC_LAG ? it - TC_LAG : 0); j < it; ++j) mbar_arrive(&full_bar[j % S]);
+    }
+
+    // ===================== epilogue: TMEM -> registers -> global ===========================
+    if (nstage > 0) {
+      mbar_wait(accum_bar, 0);
+      tc_fence_after();
+    }
+    const int r = warp * 32 + lane;
+    const int o = row0 + r;
+    for (int cc = 0; cc < BN; cc += 32) {
+      uint32_t v[32];
+      if (nstage > 0) {
+        tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)cc, v);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = 0u;
+      }
+      if (o < n_out) {
+        const long long base = (long long)o * cout + col0 + cc;
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int n = col0 + cc + j;
+          const int ch = ch_mod > 0 ? (n % ch_mod) : n;
+          float x = __uint_as_float(v[j]);
+          if (bias) x += __ldg(bias + ch);
+          if (scale) x = x * __ldg(scale + ch) + __ldg(shift + ch);
+          f[j] = x;
+        }
+        if (residual) {
+          if (sizeof(TOut) == 2) {
+            const uint4* rp = reinterpret_cast<const uint4*>(residual + base);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const uint4 u = __ldg(rp + q);
+              const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                f[q * 8 + e * 2] += __uint_as_float(w4[e] << 16);
+                f[q * 8 + e * 2 + 1] += __uint_as_float(w4[e] & 0xFFFF0000u);
+              }
+            }
+          } else {
+            const float4* rp = reinterpret_cast<const float4*>(residual + base);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              const float4 u = __ldg(rp + q);
+              f[q * 4] += u.x;
+              f[q * 4 + 1] += u.y;
+              f[q * 4 + 2] += u.z;
+              f[q * 4 + 3] += u.w;
+            }
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = b2_apply_act(f[j], act);
+        if (sizeof(TOut) == 2) {
+          uint4* op = reinterpret_cast<uint4*>(out + base);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            uint32_t w4[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const __nv_bfloat162 h = __floats2bfloat162_rn(f[q * 8 + e * 2], f[q * 8 + e * 2 + 1]);
+              w4[e] = *reinterpret_cast<const uint32_t*>(&h);
+            }
+            op[q] = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+          }
+        } else {
+          float4* op = reinterpret_cast<float4*>(out + base);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) op[q] = make_float4(f[q * 4], f[q * 4 + 1], f[q * 4 + 2], f[q * 4 + 3]);
+        }
+      }
+    }
+    tc_fence_before();
+  } else {
+    // ===================== MMA issuer (one thread) ==========================================
+    if (lane == 0 && nstage > 0) {
+      constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((128u >> 4) << 24);
+      for (int it = 0; it < nstage; ++it) {
+        const int s = it % S;
+        const uint32_t ph = (uint32_t)(it / S) & 1u;
+        mbar_wait(&full_bar[s], ph);
+        tc_fence_after();
+        const uint32_t a_base = smem_u32(smem + s * Cfg::STAGE_BYTES);
+        const uint32_t b_base = a_base + Cfg::A_BYTES;
+#pragma unroll
+        for (int kk = 0; kk < TC_BK / 16; ++kk) {
+          const uint64_t da = umma_desc_sw128(a_base + kk * 32);
+          const uint64_t db = umma_desc_sw128(b_base + kk * 32);
+          umma_bf16(tmem_base, da, db, idesc, (it > 0 || kk > 0) ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[s]);  // frees the smem stage once these MMAs have read it
+      }
+      umma_commit(accum_bar);
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                 "r"((uint32_t)(BN < 32 ? 32 : BN))
+                 : "memory");
+  }
+}
+
+template <int BN, typename TOut>
+static int launch_tc(const void* in, const void* wt, const int* nbr, long long ld, const unsigned int* tile_mask,
+                     long long n_out, int cin, int cout, int kvol, const float* bias, const float* scale,
+                     const float* shift, const void* residual, int act, int ch_mod, void* out, cudaStream_t st) {
+  using Cfg = TcCfg<BN>;
+  auto kern = k_conv_tc<BN, TOut>;
+  static bool configured = false;  // per template instance; attribute is per device function
+  if (!configured) {
+    B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
+    configured = true;
+  }
+  dim3 grid(b2_div_up(n_out, TC_BM), cout / BN);
+  kern<<<grid, TC_THREADS, Cfg::SMEM, st>>>((const __nv_bfloat16*)in, (const __nv_bfloat16*)wt, nbr, (int)ld, tile_mask,
+                                            (int)n_out, cin, cout, kvol, bias, scale, shift, (const TOut*)residual, act,
+                                            ch_mod, (TOut*)out);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+extern "C" int b2_conv_tc(const void* in_bf16, const void* wt_bf16, const int* nbr, long long ld,
+                          const unsigned int* tile_mask, long long n_out, int cin, int cout, int kvol, const float* bias,
+                          const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
+                          int out_dtype, void* stream) {
+  B2_CHECK_ARG(cin % TC_BK == 0 && cin > 0, "b2_conv_tc needs cin %% 64 == 0 (got %d)", cin);
+  B2_CHECK_ARG(cout % 64 == 0 && cout > 0, "b2_conv_tc needs cout %% 64 == 0 (got %d)", cout);
+  B2_CHECK_ARG(nbr != nullptr || kvol == 1, "identity map requires kernel volume 1");
+  B2_CHECK_ARG(nbr == nullptr || (tile_mask != nullptr && kvol <= 32 && ld % TC_BM == 0),
+               "neighbour table needs a tile mask, kvol <= 32 and ld %% 128 == 0");
+  B2_CHECK_ARG((scale == nullptr) == (shift == nullptr), "scale and shift come together");
+  if (n_out == 0) return B2_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool wide = (cout % 128 == 0);
+#define TC_GO(BN, T) \
+  return launch_tc<BN, T>(in_bf16, wt_bf16, nbr, ld, tile_mask, n_out, cin, cout, kvol, bias, scale, shift, residual, act, ch_mod, out, st)
+  if (out_dtype == 1) {
+    if (wide) TC_GO(128, __nv_bfloat16);
+    TC_GO(64, __nv_bfloat16);
+  } else {
+    if (wide) TC_GO(128, float);
+    TC_GO(64, float);
+  }
+#undef TC_GO
+}

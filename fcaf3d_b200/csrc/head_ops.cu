@@ -1,0 +1,394 @@
+// Head tail of the detector: trilinear score interpolation, per-scene top-k masks (pruning and
+// nms_pre), head post-processing (exp / scale / row max), box decoding and candidate assembly.
+//
+// Reference behaviour: mmdet3d/models/dense_heads/fcaf3d_neck_with_head.py
+//   _prune :110-126 (features_at_coordinates + per-scene topk mask), forward_single :256-279,
+//   _get_bboxes_single :227-253, _bbox_pred_to_bbox :281-330, _nms :332-374 (score threshold).
+#include "common.cuh"
+
+// ---------------------------------------------------------------------------
+// features_at_coordinates: 8-corner trilinear interpolation on the source grid
+// (ME v0.5.4 semantics): absent corners contribute 0.
+// ---------------------------------------------------------------------------
+__global__ void k_interp(const B2Slot* __restrict__ table, unsigned int cap_mask, const float* __restrict__ feats, int c,
+                         int ts, const float* __restrict__ query, int m, float* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  const float4 q = __ldg(reinterpret_cast<const float4*>(query) + i);
+  const int b = (int)q.x;
+  const float fts = (float)ts;
+  const int bx = (int)floorf(q.y / fts) * ts, by = (int)floorf(q.z / fts) * ts, bz = (int)floorf(q.w / fts) * ts;
+  int rows[8];
+  float wts[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int x = bx + ((k & 1) ? ts : 0), y = by + ((k & 2) ? ts : 0), z = bz + ((k & 4) ? ts : 0);
+    const float wx = 1.f - fabsf(q.y - (float)x) / fts;
+    const float wy = 1.f - fabsf(q.z - (float)y) / fts;
+    const float wz = 1.f - fabsf(q.w - (float)z) / fts;
+    wts[k] = wx * wy * wz;
+    int r = -1;
+    if (wts[k] != 0.f && b2_coord_in_range(b, x, y, z)) r = b2_table_find(table, cap_mask, b2_pack_key(b, x, y, z));
+    rows[k] = r;
+  }
+  for (int ch = 0; ch < c; ++ch) {
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      if (rows[k] >= 0) acc += wts[k] * feats[(long long)rows[k] * c + ch];
+    out[(long long)i * c + ch] = acc;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Per-segment top-k mask by radix select.  One CTA per segment (scene).
+// mask[i] = 1 for the k largest scores of the segment; ties at the threshold are
+// resolved towards the lowest row (torch.topk leaves this unspecified).
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ unsigned int f32_ordered(float v) {
+  const unsigned int u = __float_as_uint(v);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+__global__ void __launch_bounds__(1024) k_topk_mask(const float* __restrict__ scores, const int* __restrict__ seg_off,
+                                                    int k, uint8_t* __restrict__ mask) {
+  __shared__ unsigned int hist[256];
+  __shared__ unsigned int s_prefix, s_need;
+  __shared__ int s_warp[32];
+  __shared__ int s_run;
+  const int beg = seg_off[blockIdx.x], n = seg_off[blockIdx.x + 1] - beg;
+  if (n <= 0) return;
+  if (k >= n) {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) mask[beg + i] = 1;
+    return;
+  }
+  if (k <= 0) {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) mask[beg + i] = 0;
+    return;
+  }
+  unsigned int prefix = 0, need = (unsigned int)k;
+  for (int pass = 0; pass < 4; ++pass) {
+    const int shift = 24 - 8 * pass;
+    const unsigned int hi_mask = pass == 0 ? 0u : (0xFFFFFFFFu << (shift + 8));
+    if (threadIdx.x < 256) hist[threadIdx.x] = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const unsigned int u = f32_ordered(scores[beg + i]);
+      if ((u & hi_mask) == prefix) atomicAdd(&hist[(u >> shift) & 0xFF], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      unsigned int acc = 0;
+      int d = 255;
+      for (; d > 0; --d) {
+        if (acc + hist[d] >= need) break;
+        acc += hist[d];
+      }
+      s_prefix = prefix | ((unsigned int)d << shift);
+      s_need = need - acc;
+    }
+    __syncthreads();
+    prefix = s_prefix;
+    need = s_need;
+    __syncthreads();
+  }
+  // prefix == ordered bits of the k-th largest score; `need` of the rows equal to it are taken, lowest rows first
+  if (threadIdx.x == 0) s_run = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int base = 0; base < n; base += blockDim.x) {
+    const int i = base + threadIdx.x;
+    unsigned int u = 0;
+    bool eq = false;
+    if (i < n) {
+      u = f32_ordered(scores[beg + i]);
+      eq = (u == prefix);
+    }
+    const unsigned int bal = __ballot_sync(0xffffffffu, eq);
+    if (lane == 0) s_warp[warp] = __popc(bal);
+    __syncthreads();
+    int off = s_run;
+    for (int w = 0; w < warp; ++w) off += s_warp[w];
+    const int rank = off + __popc(bal & ((1u << lane) - 1u));
+    if (i < n) mask[beg + i] = (u > prefix || (eq && rank < (int)need)) ? 1 : 0;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int t = 0;
+      for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += s_warp[w];
+      s_run += t;
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Head post-processing on the fused head output feat[n, 1 + n_reg + n_cls]
+// (centerness | regression | class logits).  forward_single :257-269.
+// ---------------------------------------------------------------------------
+__global__ void k_head_post(const float* __restrict__ feat, int n, int n_reg, int n_cls,
+                            const float* __restrict__ scale_ptr,
+                            float* __restrict__ centerness, float* __restrict__ bbox_pred, float* __restrict__ cls,
+                            float* __restrict__ prune_score, float* __restrict__ max_score) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int c = 1 + n_reg + n_cls;
+  const float* f = feat + (long long)i * c;
+  const float ctr = f[0];
+  const float scale = scale_ptr ? __ldg(scale_ptr) : 1.f;
+  centerness[i] = ctr;
+  for (int r = 0; r < n_reg; ++r) {
+    const float v = f[1 + r];
+    bbox_pred[(long long)i * n_reg + r] = (r < 6) ? expf(scale * v) : v;
+  }
+  const float sc = 1.f / (1.f + expf(-ctr));
+  float mlogit = -INFINITY, mscore = -INFINITY;
+  for (int k = 0; k < n_cls; ++k) {
+    const float v = f[1 + n_reg + k];
+    cls[(long long)i * n_cls + k] = v;
+    mlogit = fmaxf(mlogit, v);
+    mscore = fmaxf(mscore, (1.f / (1.f + expf(-v))) * sc);
+  }
+  prune_score[i] = mlogit;
+  if (max_score) max_score[i] = mscore;
+}
+
+// distances -> box (_bbox_pred_to_bbox :281-330).  yaw_mode: 0 none(6), 1 naive, 2 sin-cos, 3 fcaf3d (Mobius)
+__device__ __forceinline__ void decode_box(const float* __restrict__ p, const float* __restrict__ bp, int n_reg,
+                                           int yaw_mode, float* __restrict__ o) {
+  const float xc = p[0] + (bp[1] - bp[0]) / 2;
+  const float yc = p[1] + (bp[3] - bp[2]) / 2;
+  const float zc = p[2] + (bp[5] - bp[4]) / 2;
+  o[0] = xc;
+  o[1] = yc;
+  o[2] = zc;
+  if (n_reg == 6 || yaw_mode == 0) {
+    o[3] = bp[0] + bp[1];
+    o[4] = bp[2] + bp[3];
+    o[5] = bp[4] + bp[5];
+    o[6] = 0.f;
+  } else if (yaw_mode == 1) {
+    o[3] = bp[0] + bp[1];
+    o[4] = bp[2] + bp[3];
+    o[5] = bp[4] + bp[5];
+    o[6] = bp[6];
+  } else if (yaw_mode == 2) {
+    const float norm = powf(powf(bp[6], 2.f) + powf(bp[7], 2.f), 0.5f);
+    o[3] = bp[0] + bp[1];
+    o[4] = bp[2] + bp[3];
+    o[5] = bp[4] + bp[5];
+    o[6] = atan2f(bp[6] / norm, bp[7] / norm);
+  } else {
+    const float scale = bp[0] + bp[1] + bp[2] + bp[3];
+    const float q = expf(sqrtf(bp[6] * bp[6] + bp[7] * bp[7]));
+    o[3] = scale / (1 + q);
+    o[4] = scale / (1 + q) * q;
+    o[5] = bp[5] + bp[4];
+    o[6] = 0.5f * atan2f(bp[6], bp[7]);
+  }
+}
+
+__global__ void k_decode_boxes(const float* __restrict__ points, const float* __restrict__ bbox_pred, int n, int n_reg,
+                               int yaw_mode, float* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  decode_box(points + (long long)i * 3, bbox_pred + (long long)i * n_reg, n_reg, yaw_mode, out + (long long)i * 7);
+}
+
+// Selected rows of one level -> the scene-major candidate arrays.
+// Row i (scene s) lands at dst_base[s] + (pos[i] - pos[seg_off[s]]).
+__global__ void k_emit_candidates(const int* __restrict__ coords, const float* __restrict__ centerness,
+                                  const float* __restrict__ bbox_pred, const float* __restrict__ cls,
+                                  const uint8_t* __restrict__ mask, const int* __restrict__ pos,
+                                  const int* __restrict__ seg_off, const int* __restrict__ dst_base, int n, int n_reg,
+                                  int n_cls, int yaw_mode, float voxel_size, float* __restrict__ cand_boxes,
+                                  float* __restrict__ cand_scores) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n || !mask[i]) return;
+  const int4 c = __ldg(reinterpret_cast<const int4*>(coords) + i);
+  const int s = c.x;
+  const int j = dst_base[s] + pos[i] - pos[seg_off[s]];
+  float p[3] = {(float)c.y * voxel_size, (float)c.z * voxel_size, (float)c.w * voxel_size};
+  decode_box(p, bbox_pred + (long long)i * n_reg, n_reg, yaw_mode, cand_boxes + (long long)j * 7);
+  const float sc = 1.f / (1.f + expf(-centerness[i]));
+  for (int k = 0; k < n_cls; ++k)
+    cand_scores[(long long)j * n_cls + k] = (1.f / (1.f + expf(-cls[(long long)i * n_cls + k]))) * sc;
+}
+
+// flags in (scene, class, candidate) order: flag[n_cls*cand_off[s] + c*M_s + j] = score[cand_off[s]+j][c] > thr
+__global__ void k_class_flags(const float* __restrict__ cand_scores, const int* __restrict__ cand_off, int nscene,
+                              int n_cls, float thr, int total, uint8_t* __restrict__ flags) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total * n_cls) return;
+  // find scene: n_cls*cand_off[s] <= t
+  int lo = 0, hi = nscene - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if ((long long)n_cls * cand_off[mid] <= t) lo = mid; else hi = mid - 1;
+  }
+  const int s = lo;
+  const int ms = cand_off[s + 1] - cand_off[s];
+  const int local = t - n_cls * cand_off[s];
+  const int c = local / ms, j = local - c * ms;
+  flags[t] = cand_scores[(long long)(cand_off[s] + j) * n_cls + c] > thr ? 1 : 0;
+}
+
+// compact the flagged (scene, class, candidate) triples into NMS segment arrays
+__global__ void k_class_compact(const float* __restrict__ cand_boxes, const float* __restrict__ cand_scores,
+                                const int* __restrict__ cand_off, int nscene, int n_cls, int total,
+                                const uint8_t* __restrict__ flags, const int* __restrict__ pos,
+                                float* __restrict__ seg_boxes, float* __restrict__ seg_scores, int* __restrict__ seg_src) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total * n_cls || !flags[t]) return;
+  int lo = 0, hi = nscene - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if ((long long)n_cls * cand_off[mid] <= t) lo = mid; else hi = mid - 1;
+  }
+  const int s = lo;
+  const int ms = cand_off[s + 1] - cand_off[s];
+  const int local = t - n_cls * cand_off[s];
+  const int c = local / ms, j = local - c * ms;
+  const int src = cand_off[s] + j;
+  const int d = pos[t];
+  const float* b = cand_boxes + (long long)src * 7;
+  float* o = seg_boxes + (long long)d * 7;
+#pragma unroll
+  for (int u = 0; u < 7; ++u) o[u] = b[u];
+  seg_scores[d] = cand_scores[(long long)src * n_cls + c];
+  seg_src[d] = src;
+}
+
+// segment offsets: seg_off[q] = pos[start_of_segment q] (q = s*n_cls + c), seg_off[nseg] = total kept
+__global__ void k_segment_offsets(const int* __restrict__ pos, const int* __restrict__ total_flagged,
+                                  const int* __restrict__ cand_off, int nscene, int n_cls, int total_flags,
+                                  int* __restrict__ seg_off) {
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nseg = nscene * n_cls;
+  if (q > nseg) return;
+  if (q == nseg) {
+    seg_off[q] = *total_flagged;
+    return;
+  }
+  const int s = q / n_cls, c = q - s * n_cls;
+  const int ms = cand_off[s + 1] - cand_off[s];
+  const long long start = (long long)n_cls * cand_off[s] + (long long)c * ms;
+  seg_off[q] = (start < total_flags) ? pos[start] : *total_flagged;
+}
+
+// kept entries (sorted order inside segments) -> final detections
+__global__ void k_collect_dets(const float* __restrict__ sorted_boxes, const float* __restrict__ seg_scores,
+                               const int* __restrict__ order, const int* __restrict__ seg_off, int nseg, int n_cls,
+                               const uint8_t* __restrict__ keep, const int* __restrict__ pos, int n,
+                               float* __restrict__ out_boxes, float* __restrict__ out_scores, int* __restrict__ out_labels,
+                               int* __restrict__ out_scene) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n || !keep[i]) return;
+  int lo = 0, hi = nseg - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (seg_off[mid] <= i) lo = mid; else hi = mid - 1;
+  }
+  const int q = lo;
+  const int d = pos[i];
+  const float* b = sorted_boxes + (long long)i * 7;
+  float* o = out_boxes + (long long)d * 7;
+#pragma unroll
+  for (int u = 0; u < 7; ++u) o[u] = b[u];
+  out_scores[d] = seg_scores[seg_off[q] + order[i]];
+  out_labels[d] = q % n_cls;
+  out_scene[d] = q / n_cls;
+}
+
+extern "C" {
+
+int b2_interp(const void* table, long long cap, const float* feats, int c, int tensor_stride, const float* query,
+              long long m, float* out, void* stream) {
+  B2_CHECK_ARG(tensor_stride > 0 && c > 0, "bad interpolation arguments");
+  if (m == 0) return B2_OK;
+  k_interp<<<b2_div_up(m, 128), 128, 0, (cudaStream_t)stream>>>((const B2Slot*)table, (unsigned)(cap - 1), feats, c,
+                                                              tensor_stride, query, (int)m, out);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_topk_mask(const float* scores, const int* seg_off, int nseg, int k, uint8_t* mask, void* stream) {
+  if (nseg == 0) return B2_OK;
+  k_topk_mask<<<nseg, 1024, 0, (cudaStream_t)stream>>>(scores, seg_off, k, mask);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_head_post(const float* feat, long long n, int n_reg, int n_cls, const float* scale, float* centerness,
+                 float* bbox_pred, float* cls, float* prune_score, float* max_score, void* stream) {
+  if (n == 0) return B2_OK;
+  k_head_post<<<b2_div_up(n, 256), 256, 0, (cudaStream_t)stream>>>(feat, (int)n, n_reg, n_cls, scale, centerness,
+                                                                 bbox_pred, cls, prune_score, max_score);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_decode_boxes(const float* points, const float* bbox_pred, long long n, int n_reg, int yaw_mode, float* out,
+                    void* stream) {
+  B2_CHECK_ARG(n_reg == 6 || n_reg == 7 || n_reg == 8, "n_reg must be 6, 7 or 8");
+  if (n == 0) return B2_OK;
+  k_decode_boxes<<<b2_div_up(n, 256), 256, 0, (cudaStream_t)stream>>>(points, bbox_pred, (int)n, n_reg, yaw_mode, out);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_emit_candidates(const int* coords, const float* centerness, const float* bbox_pred, const float* cls,
+                       const uint8_t* mask, const int* pos, const int* seg_off, const int* dst_base, long long n,
+                       int n_reg, int n_cls, int yaw_mode, float voxel_size, float* cand_boxes, float* cand_scores,
+                       void* stream) {
+  if (n == 0) return B2_OK;
+  k_emit_candidates<<<b2_div_up(n, 256), 256, 0, (cudaStream_t)stream>>>(coords, centerness, bbox_pred, cls, mask, pos,
+                                                                       seg_off, dst_base, (int)n, n_reg, n_cls, yaw_mode,
+                                                                       voxel_size, cand_boxes, cand_scores);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+// Builds the (scene, class) NMS segments from the scene-major candidate arrays.
+// flags/pos: scratch of total*n_cls entries; seg_* outputs sized total*n_cls; seg_off[nscene*n_cls + 1].
+int b2_class_segments(const float* cand_boxes, const float* cand_scores, const int* cand_off, int nscene, int n_cls,
+                      long long total, float score_thr, uint8_t* flags, int* pos, int* n_flagged, float* seg_boxes,
+                      float* seg_scores, int* seg_src, int* seg_off, void* ws, size_t ws_bytes, void* stream);
+
+int b2_collect_dets(const float* sorted_boxes, const float* seg_scores, const int* order, const int* seg_off, int nseg,
+                    int n_cls, const uint8_t* keep, const int* pos, long long n, float* out_boxes, float* out_scores,
+                    int* out_labels, int* out_scene, void* stream) {
+  if (n == 0) return B2_OK;
+  k_collect_dets<<<b2_div_up(n, 256), 256, 0, (cudaStream_t)stream>>>(sorted_boxes, seg_scores, order, seg_off, nseg,
+                                                                    n_cls, keep, pos, (int)n, out_boxes, out_scores,
+                                                                    out_labels, out_scene);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+}  // extern "C"
+
+int b2_scan_flags_launch(const uint8_t* flags, long long n, int* pos, int* total, void* ws, size_t ws_bytes,
+                         cudaStream_t st);
+
+extern "C" int b2_class_segments(const float* cand_boxes, const float* cand_scores, const int* cand_off, int nscene,
+                                 int n_cls, long long total, float score_thr, uint8_t* flags, int* pos, int* n_flagged,
+                                 float* seg_boxes, float* seg_scores, int* seg_src, int* seg_off, void* ws,
+                                 size_t ws_bytes, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long nf = total * n_cls;
+  const int nseg = nscene * n_cls;
+  if (nf > 0) {
+    k_class_flags<<<b2_div_up(nf, 256), 256, 0, st>>>(cand_scores, cand_off, nscene, n_cls, score_thr, (int)total, flags);
+    B2_LAUNCH_CHECK();
+  }
+  int rc = b2_scan_flags_launch(flags, nf, pos, n_flagged, ws, ws_bytes, st);
+  if (rc) return rc;
+  if (nf > 0) {
+    k_class_compact<<<b2_div_up(nf, 256), 256, 0, st>>>(cand_boxes, cand_scores, cand_off, nscene, n_cls, (int)total,
+                                                       flags, pos, seg_boxes, seg_scores, seg_src);
+    B2_LAUNCH_CHECK();
+  }
+  k_segment_offsets<<<b2_div_up(nseg + 1, 256), 256, 0, st>>>(pos, n_flagged, cand_off, nscene, n_cls, (int)nf, seg_off);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}

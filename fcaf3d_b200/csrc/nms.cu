@@ -1,0 +1,452 @@
+// Batched BEV NMS (rotated "nms_gpu" and axis-aligned "nms_normal_gpu" flavours).
+//
+// Same per-pair arithmetic as the reference's pcdet_nms extension
+// (mmdet3d/ops/pcdet_nms/src/iou3d_nms_kernel.cu:104-234 rotated BEV overlap / IoU,
+//  :314-325 axis-aligned BEV IoU, :267-372 64x64 suppression tiles,
+//  mmdet3d/ops/pcdet_nms/src/iou3d_nms.cpp:116-132 greedy reduce on the host),
+// restructured for B200: every (scene, class) segment of a batch goes through ONE launch per
+// stage, only upper-triangular tiles are evaluated, per-box trigonometry is hoisted out of the
+// pair loop, far-apart pairs are rejected by a bounding-circle test, and the greedy reduce runs
+// on the device (no cudaMalloc / D2H / host loop per class).
+#include "common.cuh"
+
+#define NMS_EPS 1e-8f
+#define NMS_TILE 64
+
+struct P2 {
+  float x, y;
+};
+
+__device__ __forceinline__ float cross3(const P2& p1, const P2& p2, const P2& p0) {
+  return (p1.x - p0.x) * (p2.y - p0.y) - (p2.x - p0.x) * (p1.y - p0.y);
+}
+__device__ __forceinline__ float cross2(const P2& a, const P2& b) { return a.x * b.y - a.y * b.x; }
+
+// per-box quantities that the reference recomputes for every pair
+struct BoxPrep {
+  float cx, cy, dx, dy;     // centre and full sizes
+  float cosm, sinm;         // cos(-heading), sin(-heading) used by the corner-in-box test
+  P2 c[4];                  // rotated corners
+  float rad;                // circumscribed radius (for the conservative far-apart rejection)
+};
+
+__device__ __forceinline__ void rotate_about(const P2& ctr, float ca, float sa, P2& p) {
+  const float nx = (p.x - ctr.x) * ca + (p.y - ctr.y) * (-sa) + ctr.x;
+  const float ny = (p.x - ctr.x) * sa + (p.y - ctr.y) * ca + ctr.y;
+  p.x = nx;
+  p.y = ny;
+}
+
+__device__ __forceinline__ void prep_box(const float* __restrict__ b, BoxPrep& o) {
+  const float ang = b[6];
+  const float hx = b[3] / 2, hy = b[4] / 2;
+  const float x1 = b[0] - hx, y1 = b[1] - hy, x2 = b[0] + hx, y2 = b[1] + hy;
+  P2 ctr;
+  ctr.x = b[0];
+  ctr.y = b[1];
+  o.cx = b[0];
+  o.cy = b[1];
+  o.dx = b[3];
+  o.dy = b[4];
+  o.c[0].x = x1; o.c[0].y = y1;
+  o.c[1].x = x2; o.c[1].y = y1;
+  o.c[2].x = x2; o.c[2].y = y2;
+  o.c[3].x = x1; o.c[3].y = y2;
+  const float ca = cosf(ang), sa = sinf(ang);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) rotate_about(ctr, ca, sa, o.c[k]);
+  o.cosm = cosf(-ang);
+  o.sinm = sinf(-ang);
+  o.rad = sqrtf(hx * hx + hy * hy);
+}
+
+__device__ __forceinline__ int seg_intersect(const P2& p1, const P2& p0, const P2& q1, const P2& q0, P2& ans) {
+  // bounding-rectangle rejection of the two segments
+  const int hit = fminf(p0.x, p1.x) <= fmaxf(q0.x, q1.x) && fminf(q0.x, q1.x) <= fmaxf(p0.x, p1.x) &&
+                  fminf(p0.y, p1.y) <= fmaxf(q0.y, q1.y) && fminf(q0.y, q1.y) <= fmaxf(p0.y, p1.y);
+  if (!hit) return 0;
+  const float s1 = cross3(q0, p1, p0);
+  const float s2 = cross3(p1, q1, p0);
+  const float s3 = cross3(p0, q1, q0);
+  const float s4 = cross3(q1, p1, q0);
+  if (!(s1 * s2 > 0 && s3 * s4 > 0)) return 0;
+  const float s5 = cross3(q1, p1, p0);
+  if (fabsf(s5 - s1) > NMS_EPS) {
+    ans.x = (s5 * q0.x - s1 * q1.x) / (s5 - s1);
+    ans.y = (s5 * q0.y - s1 * q1.y) / (s5 - s1);
+  } else {
+    const float a0 = p0.y - p1.y, b0 = p1.x - p0.x, c0 = p0.x * p1.y - p1.x * p0.y;
+    const float a1 = q0.y - q1.y, b1 = q1.x - q0.x, c1 = q0.x * q1.y - q1.x * q0.y;
+    const float D = a0 * b1 - a1 * b0;
+    ans.x = (b0 * c1 - b1 * c0) / D;
+    ans.y = (a1 * c0 - a0 * c1) / D;
+  }
+  return 1;
+}
+
+__device__ __forceinline__ int corner_in_box(const BoxPrep& box, const P2& p) {
+  const float MARGIN = 1e-2f;
+  const float rx = (p.x - box.cx) * box.cosm + (p.y - box.cy) * (-box.sinm);
+  const float ry = (p.x - box.cx) * box.sinm + (p.y - box.cy) * box.cosm;
+  return (fabsf(rx) < box.dx / 2 + MARGIN && fabsf(ry) < box.dy / 2 + MARGIN);
+}
+
+__device__ float bev_overlap(const BoxPrep& A, const BoxPrep& B) {
+  P2 pts[16];
+  P2 ctr;
+  ctr.x = 0.f;
+  ctr.y = 0.f;
+  int cnt = 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      P2 hit;
+      if (seg_intersect(A.c[(i + 1) & 3], A.c[i], B.c[(j + 1) & 3], B.c[j], hit)) {
+        pts[cnt] = hit;
+        ctr.x = ctr.x + hit.x;
+        ctr.y = ctr.y + hit.y;
+        cnt++;
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    if (corner_in_box(A, B.c[k])) {
+      ctr.x = ctr.x + B.c[k].x;
+      ctr.y = ctr.y + B.c[k].y;
+      pts[cnt] = B.c[k];
+      cnt++;
+    }
+    if (corner_in_box(B, A.c[k])) {
+      ctr.x = ctr.x + A.c[k].x;
+      ctr.y = ctr.y + A.c[k].y;
+      pts[cnt] = A.c[k];
+      cnt++;
+    }
+  }
+  ctr.x /= cnt;
+  ctr.y /= cnt;
+  // order the polygon vertices by angle around their mean (same exchange sort, same comparison)
+  for (int j = 0; j < cnt - 1; ++j) {
+    for (int i = 0; i < cnt - j - 1; ++i) {
+      if (atan2f(pts[i].y - ctr.y, pts[i].x - ctr.x) > atan2f(pts[i + 1].y - ctr.y, pts[i + 1].x - ctr.x)) {
+        const P2 t = pts[i];
+        pts[i] = pts[i + 1];
+        pts[i + 1] = t;
+      }
+    }
+  }
+  float area = 0.f;
+  for (int k = 0; k < cnt - 1; ++k) {
+    P2 u, v;
+    u.x = pts[k].x - pts[0].x;
+    u.y = pts[k].y - pts[0].y;
+    v.x = pts[k + 1].x - pts[0].x;
+    v.y = pts[k + 1].y - pts[0].y;
+    area += cross2(u, v);
+  }
+  return fabsf(area) / 2.0f;
+}
+
+__device__ __forceinline__ float iou_rotated(const BoxPrep& A, const BoxPrep& B) {
+  const float sa = A.dx * A.dy;
+  const float sb = B.dx * B.dy;
+  const float s = bev_overlap(A, B);
+  return s / fmaxf(sa + sb - s, NMS_EPS);
+}
+
+__device__ __forceinline__ float iou_aligned(const float* a, const float* b) {
+  const float left = fmaxf(a[0] - a[3] / 2, b[0] - b[3] / 2), right = fminf(a[0] + a[3] / 2, b[0] + b[3] / 2);
+  const float top = fmaxf(a[1] - a[4] / 2, b[1] - b[4] / 2), bottom = fminf(a[1] + a[4] / 2, b[1] + b[4] / 2);
+  const float width = fmaxf(right - left, 0.f), height = fmaxf(bottom - top, 0.f);
+  const float inter = width * height;
+  const float Sa = a[3] * a[4];
+  const float Sb = b[3] * b[4];
+  return inter / fmaxf(Sa + Sb - inter, NMS_EPS);
+}
+
+// ---------------------------------------------------------------------------
+// Stage 1: per-segment sort by score (descending; ties -> lower index first).
+// One CTA per segment, bitonic network in shared memory, <= 4096 entries.
+// ---------------------------------------------------------------------------
+#define SORT_MAX 4096
+
+__global__ void __launch_bounds__(1024) k_nms_sort(const float* __restrict__ boxes, const float* __restrict__ scores,
+                                                   const int* __restrict__ seg_off, float* __restrict__ sorted_boxes,
+                                                   int* __restrict__ order) {
+  __shared__ float s_key[SORT_MAX];
+  __shared__ int s_idx[SORT_MAX];
+  const int q = blockIdx.x;
+  const int beg = seg_off[q], n = seg_off[q + 1] - beg;
+  if (n <= 0) return;
+  int m = 1;
+  while (m < n) m <<= 1;
+  for (int i = threadIdx.x; i < m; i += blockDim.x) {
+    s_key[i] = (i < n) ? scores[beg + i] : -INFINITY;
+    s_idx[i] = (i < n) ? i : 0x7FFFFFFF;
+  }
+  __syncthreads();
+  for (int k = 2; k <= m; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = threadIdx.x; i < m; i += blockDim.x) {
+        const int ixj = i ^ j;
+        if (ixj > i) {
+          const float ka = s_key[i], kb = s_key[ixj];
+          const int ia = s_idx[i], ib = s_idx[ixj];
+          // "a before b" in the final order: higher score first, then lower index
+          const bool a_first = (ka > kb) || (ka == kb && ia < ib) || (kb != kb && ka == ka);
+          const bool up = ((i & k) == 0);
+          if (up ? !a_first : a_first) {
+            s_key[i] = kb;
+            s_key[ixj] = ka;
+            s_idx[i] = ib;
+            s_idx[ixj] = ia;
+          }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const int src = s_idx[i];
+    order[beg + i] = src;
+    const float* b = boxes + (long long)(beg + src) * 7;
+    float* o = sorted_boxes + (long long)(beg + i) * 7;
+#pragma unroll
+    for (int u = 0; u < 7; ++u) o[u] = b[u];
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Stage 2: suppression bit masks, upper-triangular 64x64 tiles of every segment.
+// tile_off[q] = first global tile id of segment q; mask_off[q] = first word of its
+// mask (n_q rows x T_q words).  256 threads: 4 threads per row, 16 columns each.
+// ---------------------------------------------------------------------------
+template <bool ROTATED>
+__global__ void __launch_bounds__(256) k_nms_mask(const float* __restrict__ boxes, const int* __restrict__ seg_off,
+                                                  const int* __restrict__ tile_off, const long long* __restrict__ mask_off,
+                                                  int nseg, int total_tiles, float thresh,
+                                                  unsigned long long* __restrict__ mask) {
+  __shared__ BoxPrep s_col[NMS_TILE];
+  __shared__ BoxPrep s_row[NMS_TILE];
+  __shared__ float s_colraw[NMS_TILE * 7];
+  __shared__ float s_rowraw[NMS_TILE * 7];
+  __shared__ unsigned long long s_bits[NMS_TILE];
+  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    // locate the segment (binary search) and the (row, col) tile inside its upper triangle
+    int lo = 0, hi = nseg - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (tile_off[mid] <= tile) lo = mid; else hi = mid - 1;
+    }
+    const int q = lo;
+    const int beg = seg_off[q], n = seg_off[q + 1] - beg;
+    const int T = (n + NMS_TILE - 1) / NMS_TILE;
+    int local = tile - tile_off[q];
+    int tr = 0;
+    while (local >= T - tr) {
+      local -= T - tr;
+      ++tr;
+    }
+    const int tc = tr + local;
+    const int row_n = min(n - tr * NMS_TILE, NMS_TILE), col_n = min(n - tc * NMS_TILE, NMS_TILE);
+
+    __syncthreads();
+    const int t = threadIdx.x;
+    if (t < NMS_TILE) {
+      s_bits[t] = 0ull;
+      if (t < col_n) {
+        const float* b = boxes + (long long)(beg + tc * NMS_TILE + t) * 7;
+#pragma unroll
+        for (int u = 0; u < 7; ++u) s_colraw[t * 7 + u] = b[u];
+        if (ROTATED) prep_box(b, s_col[t]);
+      }
+    } else if (t < 2 * NMS_TILE) {
+      const int r = t - NMS_TILE;
+      if (r < row_n) {
+        const float* b = boxes + (long long)(beg + tr * NMS_TILE + r) * 7;
+#pragma unroll
+        for (int u = 0; u < 7; ++u) s_rowraw[r * 7 + u] = b[u];
+        if (ROTATED) prep_box(b, s_row[r]);
+      }
+    }
+    __syncthreads();
+    const int r = t & 63, quarter = t >> 6;
+    if (r < row_n) {
+      unsigned long long bits = 0ull;
+      int c0 = quarter * 16, c1 = min(c0 + 16, col_n);
+      if (tr == tc) c0 = max(c0, r + 1);
+      for (int c = c0; c < c1; ++c) {
+        float iou;
+        if (ROTATED) {
+          const BoxPrep& A = s_row[r];
+          const BoxPrep& B = s_col[c];
+          const float ddx = A.cx - B.cx, ddy = A.cy - B.cy;
+          const float reach = A.rad + B.rad + 0.05f;
+          // far apart => the reference finds no vertex, overlap 0, IoU 0: bit stays clear (needs thresh >= 0)
+          if (thresh >= 0.f && ddx * ddx + ddy * ddy > reach * reach) continue;
+          iou = iou_rotated(A, B);
+        } else {
+          iou = iou_aligned(s_rowraw + r * 7, s_colraw + c * 7);
+        }
+        if (iou > thresh) bits |= 1ull << c;
+      }
+      if (bits) atomicOr(&s_bits[r], bits);
+    }
+    __syncthreads();
+    if (t < row_n) mask[mask_off[q] + (long long)(tr * NMS_TILE + t) * T + tc] = s_bits[t];
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Stage 3: greedy reduce on the device, one CTA per segment (same visiting order
+// as the reference's host loop).  keep[i] in sorted order; counts[q] = kept boxes.
+// ---------------------------------------------------------------------------
+#define RED_MAX_WORDS 1024
+
+__global__ void __launch_bounds__(128) k_nms_reduce(const unsigned long long* __restrict__ mask,
+                                                    const int* __restrict__ seg_off,
+                                                    const long long* __restrict__ mask_off, uint8_t* __restrict__ keep,
+                                                    int* __restrict__ counts) {
+  __shared__ unsigned long long s_remv[RED_MAX_WORDS];
+  __shared__ unsigned long long s_diag[NMS_TILE];
+  __shared__ unsigned long long s_keepw;
+  const int q = blockIdx.x;
+  const int beg = seg_off[q], n = seg_off[q + 1] - beg;
+  const int T = (n + NMS_TILE - 1) / NMS_TILE;
+  const unsigned long long* m = mask + mask_off[q];
+  for (int j = threadIdx.x; j < T; j += blockDim.x) s_remv[j] = 0ull;
+  int kept = 0;
+  __syncthreads();
+  for (int blk = 0; blk < T; ++blk) {
+    const int rows = min(n - blk * NMS_TILE, NMS_TILE);
+    if (threadIdx.x < NMS_TILE)
+      s_diag[threadIdx.x] = (threadIdx.x < rows) ? m[(long long)(blk * NMS_TILE + threadIdx.x) * T + blk] : 0ull;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      unsigned long long cur = s_remv[blk], kw = 0ull;
+      for (int i = 0; i < rows; ++i) {
+        if (!((cur >> i) & 1ull)) {
+          kw |= 1ull << i;
+          cur |= s_diag[i];
+        }
+      }
+      s_keepw = kw;
+    }
+    __syncthreads();
+    const unsigned long long kw = s_keepw;
+    kept += __popcll(kw);
+    for (int j = blk + 1 + threadIdx.x; j < T; j += blockDim.x) {
+      unsigned long long acc = 0ull, w = kw;
+      while (w) {
+        const int i = __ffsll((long long)w) - 1;
+        w &= w - 1;
+        acc |= m[(long long)(blk * NMS_TILE + i) * T + j];
+      }
+      s_remv[j] |= acc;
+    }
+    if (threadIdx.x < rows) keep[beg + blk * NMS_TILE + threadIdx.x] = (uint8_t)((kw >> threadIdx.x) & 1ull);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0 && counts) counts[q] = kept;
+}
+
+// pairwise BEV IoU / overlap matrices (reference: boxes_iou_bev_gpu / boxes_overlap_bev_gpu,
+// iou3d_nms_kernel.cu:236-265)
+__global__ void k_pair_matrix(const float* __restrict__ a, int na, const float* __restrict__ b, int nb, int mode,
+                              float* __restrict__ out) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = blockIdx.y * blockDim.y + threadIdx.y;
+  if (i >= na || j >= nb) return;
+  float v;
+  if (mode == 2) {
+    v = iou_aligned(a + (long long)i * 7, b + (long long)j * 7);
+  } else {
+    BoxPrep A, B;
+    prep_box(a + (long long)i * 7, A);
+    prep_box(b + (long long)j * 7, B);
+    v = (mode == 0) ? bev_overlap(A, B) : iou_rotated(A, B);
+  }
+  out[(long long)i * nb + j] = v;
+}
+
+// kept indices in order (compat with the reference's `keep` list)
+__global__ void k_keep_list(const uint8_t* __restrict__ keep, const int* __restrict__ pos, int n,
+                            long long* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && keep[i]) out[pos[i]] = i;
+}
+
+extern "C" {
+
+// Host-side helper: fills tile_off[nseg+1] (int32) and mask_off[nseg+1] (int64, in 8-byte words) from
+// host segment offsets; returns total mask words through *mask_words.
+int b2_nms_plan(const int* seg_off_host, int nseg, int* tile_off_host, long long* mask_off_host, long long* mask_words,
+                int* max_seg) {
+  long long words = 0;
+  int tiles = 0, mx = 0;
+  for (int q = 0; q < nseg; ++q) {
+    const int n = seg_off_host[q + 1] - seg_off_host[q];
+    B2_CHECK_ARG(n >= 0, "segment offsets must be non-decreasing");
+    const int T = (n + NMS_TILE - 1) / NMS_TILE;
+    tile_off_host[q] = tiles;
+    mask_off_host[q] = words;
+    tiles += T * (T + 1) / 2;
+    words += (long long)n * T;
+    if (n > mx) mx = n;
+  }
+  tile_off_host[nseg] = tiles;
+  mask_off_host[nseg] = words;
+  *mask_words = words;
+  *max_seg = mx;
+  return B2_OK;
+}
+
+// boxes [n,7] / scores [n] grouped in nseg segments (device seg_off[nseg+1]).
+// sort != 0: each segment is first ordered by descending score -> sorted_boxes, order (segment-local source index).
+// sort == 0: boxes are taken as already ordered (sorted_boxes may alias boxes, order unused).
+// keep[n] (uint8, in sorted order), counts[nseg].  mask: scratch of mask_words 8-byte words.
+int b2_nms_batched(const float* boxes, const float* scores, const int* seg_off, const int* tile_off,
+                   const long long* mask_off, int nseg, int total_tiles, int max_seg, float thresh, int rotated, int sort,
+                   float* sorted_boxes, int* order, unsigned long long* mask, uint8_t* keep, int* counts, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (nseg == 0) return B2_OK;
+  B2_CHECK_ARG(max_seg <= RED_MAX_WORDS * NMS_TILE, "segment too long for the device reduce (%d)", max_seg);
+  const float* sb = boxes;
+  if (sort) {
+    B2_CHECK_ARG(max_seg <= SORT_MAX, "segment longer than %d cannot be sorted in-kernel (%d)", SORT_MAX, max_seg);
+    k_nms_sort<<<nseg, 1024, 0, st>>>(boxes, scores, seg_off, sorted_boxes, order);
+    B2_LAUNCH_CHECK();
+    sb = sorted_boxes;
+  }
+  if (total_tiles > 0) {
+    const int grid = total_tiles < 148 * 8 ? total_tiles : 148 * 8;
+    if (rotated)
+      k_nms_mask<true><<<grid, 256, 0, st>>>(sb, seg_off, tile_off, mask_off, nseg, total_tiles, thresh, mask);
+    else
+      k_nms_mask<false><<<grid, 256, 0, st>>>(sb, seg_off, tile_off, mask_off, nseg, total_tiles, thresh, mask);
+    B2_LAUNCH_CHECK();
+  }
+  k_nms_reduce<<<nseg, 128, 0, st>>>(mask, seg_off, mask_off, keep, counts);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+// mode 0: rotated BEV overlap area, 1: rotated BEV IoU, 2: axis-aligned BEV IoU
+int b2_boxes_pair_matrix(const float* a, long long na, const float* b, long long nb, int mode, float* out, void* stream) {
+  if (na == 0 || nb == 0) return B2_OK;
+  dim3 block(16, 16), grid(b2_div_up(nb, 16), b2_div_up(na, 16));
+  k_pair_matrix<<<grid, block, 0, (cudaStream_t)stream>>>(a, (int)na, b, (int)nb, mode, out);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_keep_list(const uint8_t* keep, const int* pos, long long n, long long* out, void* stream) {
+  if (n == 0) return B2_OK;
+  k_keep_list<<<b2_div_up(n, 256), 256, 0, (cudaStream_t)stream>>>(keep, pos, (int)n, out);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+}  // extern "C"

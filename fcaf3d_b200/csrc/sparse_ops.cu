@@ -1,0 +1,405 @@
+// Kernel-map (neighbour table) construction, CUDA-core sparse convolution (fp32 accumulate),
+// max pooling, per-segment channel statistics and the fused affine/activation pass.
+//
+// Behavioural counterparts in the reference: MinkowskiConvolution / MinkowskiMaxPooling /
+// MinkowskiInstanceNorm / MinkowskiBatchNorm / MinkowskiReLU / MinkowskiELU as called from
+// mmdet3d/models/backbones/me_resnet.py:18-25,55-78 and
+// mmdet3d/models/dense_heads/fcaf3d_neck_with_head.py:49-72,83-85 (MinkowskiEngine v0.5.4, not vendored).
+#include "common.cuh"
+
+// ---------------------------------------------------------------------------
+// Neighbour table: nbr[k * ld + o] = input row at (coord_o + offset_k) or -1.
+// Offset order follows ME: x fastest (k = ix + KS*iy + KS*KS*iz); odd kernels are
+// centred, even kernels start at the voxel itself.  One CTA = one 128-row output
+// tile; tile_mask[tile] bit k says whether any row of the tile has neighbour k.
+// ---------------------------------------------------------------------------
+template <int KS>
+__global__ void __launch_bounds__(128) k_kernel_map(const B2Slot* __restrict__ table, unsigned int cap_mask,
+                                                    const int* __restrict__ out_coords, int n_out, int step,
+                                                    int* __restrict__ nbr, int ld, unsigned int* __restrict__ tile_mask) {
+  constexpr int K = KS * KS * KS;
+  const int o = blockIdx.x * 128 + threadIdx.x;
+  int res[K];
+  if (o < n_out) {
+    const int4 c = __ldg(reinterpret_cast<const int4*>(out_coords) + o);
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      const int ix = k % KS, iy = (k / KS) % KS, iz = k / (KS * KS);
+      const int base = (KS & 1) ? -(KS / 2) : 0;
+      const int x = c.y + (ix + base) * step, y = c.z + (iy + base) * step, z = c.w + (iz + base) * step;
+      int r = -1;
+      if (b2_coord_in_range(c.x, x, y, z)) r = b2_table_find(table, cap_mask, b2_pack_key(c.x, x, y, z));
+      res[k] = r;
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < K; ++k) res[k] = -1;
+  }
+  unsigned int m = 0;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    nbr[(long long)k * ld + o] = res[k];
+    if (__syncthreads_or(res[k] >= 0)) m |= (1u << k);
+  }
+  if (threadIdx.x == 0) tile_mask[blockIdx.x] = m;
+}
+
+// ---------------------------------------------------------------------------
+// CUDA-core implicit-GEMM sparse convolution (the fp32-parity path and the path
+// for narrow layers: Cin = 3 stem, Cout <= 32 heads).  Output-stationary:
+// a CTA owns a 128 x 64 output tile and accumulates over all kernel offsets, so
+// there are no atomics and no scatter.
+//   out[o, :] = act( (sum_k in[nbr[k][o], :] @ W[k] + bias) * scale + shift + residual[o, :] )
+// ---------------------------------------------------------------------------
+#define CV_TM 128
+#define CV_TN 64
+#define CV_TK 16
+
+template <typename T>
+__device__ __forceinline__ float to_f32(T v);
+template <>
+__device__ __forceinline__ float to_f32<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <typename T>
+__device__ __forceinline__ T from_f32(float v);
+template <>
+__device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16(v); }
+
+template <typename TIn, typename TOut>
+__global__ void __launch_bounds__(256) k_conv_cc(const TIn* __restrict__ in, const float* __restrict__ w,
+                                                 const int* __restrict__ nbr, int ld,
+                                                 const unsigned int* __restrict__ tile_mask, int n_out, int cin, int cout,
+                                                 int kvol, const float* __restrict__ bias, const float* __restrict__ scale,
+                                                 const float* __restrict__ shift, const TOut* __restrict__ residual,
+                                                 int act, int ch_mod, TOut* __restrict__ out) {
+  __shared__ __align__(16) float As[CV_TK][CV_TM + 4];
+  __shared__ __align__(16) float Bs[CV_TK][CV_TN + 4];
+  __shared__ int s_idx[CV_TM];
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;  // 16 x 16 threads; thread tile 8 rows x 4 cols
+  const int row0 = blockIdx.x * CV_TM, col0 = blockIdx.y * CV_TN;
+  const unsigned int tmask = (tile_mask != nullptr && nbr != nullptr) ? tile_mask[blockIdx.x] : 0xFFFFFFFFu;
+
+  float acc[8][4];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  for (int k = 0; k < kvol; ++k) {
+    if (kvol <= 32 && !((tmask >> k) & 1u)) continue;
+    __syncthreads();
+    if (tid < CV_TM) {
+      const int o = row0 + tid;
+      int r = -1;
+      if (o < n_out) r = nbr ? nbr[(long long)k * ld + o] : o;
+      s_idx[tid] = r;
+    }
+    __syncthreads();
+    const float* wk = w + (long long)k * cin * cout;
+    for (int c0 = 0; c0 < cin; c0 += CV_TK) {
+      // A tile: 128 rows x 16 channels; thread -> (row = tid/2, 8 channels)
+      {
+        const int r = tid >> 1, cb = (tid & 1) * 8;
+        const int src = s_idx[r];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int c = c0 + cb + u;
+          float v = 0.f;
+          if (src >= 0 && c < cin) v = to_f32<TIn>(in[(long long)src * cin + c]);
+          As[cb + u][r] = v;
+        }
+      }
+      // B tile: 16 x 64; thread -> (kk = tid/16, 4 cols)
+      {
+        const int kk = tid >> 4, nb = (tid & 15) * 4;
+        const int c = c0 + kk;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int n = col0 + nb + u;
+          float v = 0.f;
+          if (c < cin && n < cout) v = __ldg(wk + (long long)c * cout + n);
+          Bs[kk][nb + u] = v;
+        }
+      }
+      __syncthreads();
+#pragma unroll
+      for (int kk = 0; kk < CV_TK; ++kk) {
+        const float4 a0 = *reinterpret_cast<const float4*>(&As[kk][ty * 8]);
+        const float4 a1 = *reinterpret_cast<const float4*>(&As[kk][ty * 8 + 4]);
+        const float4 b = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
+        const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+        const float bb[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], bb[j], acc[i][j]);
+      }
+      __syncthreads();
+    }
+  }
+
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int o = row0 + ty * 8 + i;
+    if (o >= n_out) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = col0 + tx * 4 + j;
+      if (n >= cout) continue;
+      const int ch = ch_mod > 0 ? (n % ch_mod) : n;
+      float v = acc[i][j];
+      if (bias) v += bias[ch];
+      if (scale) v = v * scale[ch] + shift[ch];
+      if (residual) v += to_f32<TOut>(residual[(long long)o * cout + n]);
+      v = b2_apply_act(v, act);
+      out[(long long)o * cout + n] = from_f32<TOut>(v);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Max pooling over a neighbour table (2^3, stride 2): out[o, c] = max_k in[nbr[k][o], c]
+// ---------------------------------------------------------------------------
+template <typename T>
+__global__ void k_maxpool(const T* __restrict__ in, const int* __restrict__ nbr, int ld, int kvol, int n_out, int c,
+                          T* __restrict__ out, int* __restrict__ arg) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long long)n_out * c) return;
+  const int o = (int)(t / c), ch = (int)(t - (long long)o * c);
+  float best = -INFINITY;
+  int besti = -1;
+  for (int k = 0; k < kvol; ++k) {
+    const int r = nbr[(long long)k * ld + o];
+    if (r >= 0) {
+      const float v = to_f32<T>(in[(long long)r * c + ch]);
+      if (besti < 0 || v > best) {
+        best = v;
+        besti = r;
+      }
+    }
+  }
+  out[t] = from_f32<T>(besti >= 0 ? best : 0.f);
+  if (arg) arg[t] = besti;
+}
+
+// ---------------------------------------------------------------------------
+// Per-segment channel statistics (segments = contiguous row ranges: scenes for
+// InstanceNorm, the whole tensor for BatchNorm).  Deterministic two-level sum:
+// partial[s][chunk][c] then a final reduce; second pass centres on the mean.
+// ---------------------------------------------------------------------------
+#define ST_CHUNKS 64
+
+template <typename T, int POW>
+__global__ void __launch_bounds__(256) k_colsum_partial(const T* __restrict__ x, const int* __restrict__ seg_off, int c,
+                                                        const float* __restrict__ center, float* __restrict__ partial) {
+  const int s = blockIdx.y, chunk = blockIdx.x;
+  const int r0 = seg_off[s], r1 = seg_off[s + 1];
+  const int n = r1 - r0;
+  const int per = (n + ST_CHUNKS - 1) / ST_CHUNKS;
+  const int a = r0 + chunk * per;
+  const int b = min(a + per, r1);
+  // thread -> channel lane; 256 threads cover channels in a strided way, rows in y when c < 256
+  const int lanes_c = c < 256 ? c : 256;
+  const int rows_par = 256 / lanes_c;  // >= 1
+  const int cl = threadIdx.x % lanes_c, rl = threadIdx.x / lanes_c;
+  __shared__ float red[256];
+  for (int cb = 0; cb < c; cb += lanes_c) {
+    const int ch = cb + cl;
+    float acc = 0.f;
+    if (ch < c && rl < rows_par) {
+      const float m = center ? center[(long long)s * c + ch] : 0.f;
+      for (int r = a + rl; r < b; r += rows_par) {
+        float v = to_f32<T>(x[(long long)r * c + ch]) - m;
+        acc += (POW == 2) ? v * v : v;
+      }
+    }
+    red[threadIdx.x] = acc;
+    __syncthreads();
+    if (rl == 0 && ch < c) {
+      float t = 0.f;
+      for (int j = 0; j < rows_par; ++j) t += red[j * lanes_c + cl];
+      partial[((long long)s * ST_CHUNKS + chunk) * c + ch] = t;
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void k_colsum_final(const float* __restrict__ partial, const int* __restrict__ seg_off, int c, int nseg,
+                               float* __restrict__ out) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nseg * c) return;
+  const int s = t / c, ch = t - s * c;
+  float acc = 0.f;
+  for (int j = 0; j < ST_CHUNKS; ++j) acc += partial[((long long)s * ST_CHUNKS + j) * c + ch];
+  const int n = seg_off[s + 1] - seg_off[s];
+  out[t] = n > 0 ? acc / (float)n : 0.f;
+}
+
+// y = act(x * scale[s, c] + shift[s, c] + residual); s = batch index of the row (coords) or 0
+template <typename T>
+__global__ void k_affine_act(const T* __restrict__ x, const int* __restrict__ coords, long long n, int c,
+                             const float* __restrict__ scale, const float* __restrict__ shift,
+                             const T* __restrict__ residual, int act, T* __restrict__ y) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n * c) return;
+  const long long r = t / c;
+  const int ch = (int)(t - r * c);
+  const int s = coords ? coords[4 * r] : 0;
+  float v = to_f32<T>(x[t]);
+  if (scale) v = v * scale[(long long)s * c + ch] + shift[(long long)s * c + ch];
+  if (residual) v += to_f32<T>(residual[t]);
+  y[t] = from_f32<T>(b2_apply_act(v, act));
+}
+
+__global__ void k_f32_to_bf16(const float* __restrict__ x, long long n, __nv_bfloat16* __restrict__ y) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n) y[t] = __float2bfloat16(x[t]);
+}
+__global__ void k_bf16_to_f32(const __nv_bfloat16* __restrict__ x, long long n, float* __restrict__ y) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n) y[t] = __bfloat162float(x[t]);
+}
+
+// points [n, 3+F] fp32 -> coords (b, floor(xyz / voxel)) int32 [n, 4] and feats = rest / feat_div
+// (single_stage_sparse.py:34-36 + ME.utils.batch_sparse_collate)
+__global__ void k_quantize_points(const float* __restrict__ pts, int n, int dim, int batch, float voxel_size,
+                                  float feat_div, int row0, int* __restrict__ coords, float* __restrict__ feats) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float* p = pts + (long long)i * dim;
+  int4 c;
+  c.x = batch;
+  c.y = (int)floorf(p[0] / voxel_size);
+  c.z = (int)floorf(p[1] / voxel_size);
+  c.w = (int)floorf(p[2] / voxel_size);
+  reinterpret_cast<int4*>(coords)[row0 + i] = c;
+  for (int f = 3; f < dim; ++f) feats[(long long)(row0 + i) * (dim - 3) + (f - 3)] = p[f] / feat_div;
+}
+
+extern "C" {
+
+// ksize in {1,2,3}; step = input tensor stride * dilation; ld = n_out rounded up to 128
+int b2_kernel_map(const void* in_table, long long cap, const int* out_coords, long long n_out, int ksize, int step,
+                  int* nbr, long long ld, unsigned int* tile_mask, void* stream) {
+  B2_CHECK_ARG(ld % 128 == 0 && ld >= n_out, "ld must be n_out rounded up to 128");
+  B2_CHECK_ARG(ksize >= 1 && ksize <= 3, "kernel size %d unsupported (1..3)", ksize);
+  if (ld == 0) return B2_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int G = (int)(ld / 128);
+  const B2Slot* t = (const B2Slot*)in_table;
+  const unsigned m = (unsigned)(cap - 1);
+  if (ksize == 1) k_kernel_map<1><<<G, 128, 0, st>>>(t, m, out_coords, (int)n_out, step, nbr, (int)ld, tile_mask);
+  if (ksize == 2) k_kernel_map<2><<<G, 128, 0, st>>>(t, m, out_coords, (int)n_out, step, nbr, (int)ld, tile_mask);
+  if (ksize == 3) k_kernel_map<3><<<G, 128, 0, st>>>(t, m, out_coords, (int)n_out, step, nbr, (int)ld, tile_mask);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+// in_dtype/out_dtype: 0 = f32, 1 = bf16.  nbr == NULL means identity map (kvol must be 1).
+// ch_mod > 0: epilogue channel = col % ch_mod (generative transpose packs 8 kernels along columns).
+int b2_conv_cc(const void* in, int in_dtype, const float* w, const int* nbr, long long ld, const unsigned int* tile_mask,
+               long long n_out, int cin, int cout, int kvol, const float* bias, const float* scale, const float* shift,
+               const void* residual, int act, int ch_mod, void* out, int out_dtype, void* stream) {
+  B2_CHECK_ARG(nbr != nullptr || kvol == 1, "identity map requires kernel volume 1");
+  B2_CHECK_ARG((scale == nullptr) == (shift == nullptr), "scale and shift come together");
+  if (n_out == 0) return B2_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid(b2_div_up(n_out, CV_TM), b2_div_up(cout, CV_TN));
+#define CC_LAUNCH(TI, TO)                                                                                        \
+  k_conv_cc<TI, TO><<<grid, 256, 0, st>>>((const TI*)in, w, nbr, (int)ld, tile_mask, (int)n_out, cin, cout, kvol, bias, \
+                                          scale, shift, (const TO*)residual, act, ch_mod, (TO*)out)
+  if (in_dtype == 0 && out_dtype == 0) CC_LAUNCH(float, float);
+  else if (in_dtype == 0 && out_dtype == 1) CC_LAUNCH(float, __nv_bfloat16);
+  else if (in_dtype == 1 && out_dtype == 0) CC_LAUNCH(__nv_bfloat16, float);
+  else CC_LAUNCH(__nv_bfloat16, __nv_bfloat16);
+#undef CC_LAUNCH
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_maxpool(const void* in, int dtype, const int* nbr, long long ld, int kvol, long long n_out, int c, void* out,
+               int* argmax, void* stream) {
+  if (n_out == 0) return B2_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int G = b2_div_up(n_out * c, 256);
+  if (dtype == 0)
+    k_maxpool<float><<<G, 256, 0, st>>>((const float*)in, nbr, (int)ld, kvol, (int)n_out, c, (float*)out, argmax);
+  else
+    k_maxpool<__nv_bfloat16><<<G, 256, 0, st>>>((const __nv_bfloat16*)in, nbr, (int)ld, kvol, (int)n_out, c,
+                                                (__nv_bfloat16*)out, argmax);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+size_t b2_segment_stats_ws_bytes(int nseg, int c) { return (size_t)nseg * ST_CHUNKS * c * sizeof(float); }
+
+// mean[s, c], var[s, c] (biased) over rows seg_off[s]..seg_off[s+1]
+int b2_segment_stats(const void* x, int dtype, const int* seg_off, int nseg, int c, float* mean, float* var, void* ws,
+                     size_t ws_bytes, void* stream) {
+  B2_CHECK_ARG(nseg > 0 && c > 0, "bad shape");
+  if (ws_bytes < b2_segment_stats_ws_bytes(nseg, c)) {
+    b2_set_error("b2_segment_stats workspace too small");
+    return B2_ERR_WS;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  float* partial = (float*)ws;
+  dim3 grid(ST_CHUNKS, nseg);
+  const int GF = b2_div_up((long long)nseg * c, 256);
+  if (dtype == 0) {
+    k_colsum_partial<float, 1><<<grid, 256, 0, st>>>((const float*)x, seg_off, c, nullptr, partial);
+    k_colsum_final<<<GF, 256, 0, st>>>(partial, seg_off, c, nseg, mean);
+    k_colsum_partial<float, 2><<<grid, 256, 0, st>>>((const float*)x, seg_off, c, mean, partial);
+    k_colsum_final<<<GF, 256, 0, st>>>(partial, seg_off, c, nseg, var);
+  } else {
+    k_colsum_partial<__nv_bfloat16, 1><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, seg_off, c, nullptr, partial);
+    k_colsum_final<<<GF, 256, 0, st>>>(partial, seg_off, c, nseg, mean);
+    k_colsum_partial<__nv_bfloat16, 2><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, seg_off, c, mean, partial);
+    k_colsum_final<<<GF, 256, 0, st>>>(partial, seg_off, c, nseg, var);
+  }
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+// coords == NULL -> one (scale, shift) row for all; else row batch index selects scale[s, :]
+int b2_affine_act(const void* x, int dtype, const int* coords, long long n, int c, const float* scale, const float* shift,
+                  const void* residual, int act, void* y, void* stream) {
+  if (n == 0) return B2_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int G = b2_div_up(n * c, 256);
+  if (dtype == 0)
+    k_affine_act<float><<<G, 256, 0, st>>>((const float*)x, coords, n, c, scale, shift, (const float*)residual, act,
+                                           (float*)y);
+  else
+    k_affine_act<__nv_bfloat16><<<G, 256, 0, st>>>((const __nv_bfloat16*)x, coords, n, c, scale, shift,
+                                                   (const __nv_bfloat16*)residual, act, (__nv_bfloat16*)y);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_cast(const void* x, int src_dtype, long long n, void* y, void* stream) {
+  if (n == 0) return B2_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int G = b2_div_up(n, 256);
+  if (src_dtype == 0)
+    k_f32_to_bf16<<<G, 256, 0, st>>>((const float*)x, n, (__nv_bfloat16*)y);
+  else
+    k_bf16_to_f32<<<G, 256, 0, st>>>((const __nv_bfloat16*)x, n, (float*)y);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_quantize_points(const float* pts, long long n, int dim, int batch, float voxel_size, float feat_div,
+                       long long row0, int* coords, float* feats, void* stream) {
+  B2_CHECK_ARG(dim >= 3, "points need at least xyz");
+  if (n == 0) return B2_OK;
+  k_quantize_points<<<b2_div_up(n, 256), 256, 0, (cudaStream_t)stream>>>(pts, (int)n, dim, batch, voxel_size, feat_div,
+                                                                       (int)row0, coords, feats);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+}  // extern "C"

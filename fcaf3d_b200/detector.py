@@ -1,0 +1,506 @@
+"""Host-side mirror of the reference's FCAF3D model code on the fcaf3d_b200 ME surface.
+
+Mirrors (same module tree, attribute names and state-dict keys, same hyper-parameters):
+  MEResNet3D                      mmdet3d/models/backbones/me_resnet.py:8-123
+  Fcaf3DNeckWithHead              mmdet3d/models/dense_heads/fcaf3d_neck_with_head.py:13-374
+  SingleStageSparse3DDetector     mmdet3d/models/detectors/single_stage_sparse.py:9-62
+
+Two execution modes over the same modules and weights:
+  * `forward(...)`        – op by op through the ME-surface modules, like the reference code does;
+  * `forward_fused(...)`  – the B200 path: conv + folded BN + activation + residual in one kernel,
+                            fused head, batched top-k / decode / NMS with one host sync at the end.
+"""
+import math
+
+import torch
+import torch.nn as nn
+
+from . import me as ME
+from . import ops
+from .me.modules.resnet_block import BasicBlock, Bottleneck
+from .pcdet_nms import pcdet_nms_gpu, pcdet_nms_normal_gpu
+
+
+class Scale(nn.Module):
+    """mmcv.cnn.Scale: a learnable scalar multiplier."""
+
+    def __init__(self, scale=1.0):
+        super().__init__()
+        self.scale = nn.Parameter(torch.tensor(scale, dtype=torch.float))
+
+    def forward(self, x):
+        return x * self.scale
+
+
+def bias_init_with_prob(prior_prob):
+    return float(-math.log((1 - prior_prob) / prior_prob))
+
+
+# =============================================================================================== backbone
+class MEResNet3D(nn.Module):
+    ARCH = {
+        14: (BasicBlock, (1, 1, 1, 1)),
+        18: (BasicBlock, (2, 2, 2, 2)),
+        34: (BasicBlock, (3, 4, 6, 3)),
+        50: (Bottleneck, (4, 3, 6, 3)),
+        101: (Bottleneck, (3, 4, 23, 3)),
+    }
+    INIT_DIM = 64
+    PLANES = (64, 128, 256, 512)
+
+    def __init__(self, in_channels, depth, n_outs=4):
+        super().__init__()
+        if depth not in self.ARCH:
+            raise ValueError(f"invalid depth={depth}")
+        block, layers = self.ARCH[depth]
+        self.n_outs = n_outs
+        self.inplanes = self.INIT_DIM
+        self.conv1 = nn.Sequential(
+            ME.MinkowskiConvolution(in_channels, self.inplanes, kernel_size=3, stride=2, dimension=3),
+            ME.MinkowskiInstanceNorm(self.inplanes),
+            ME.MinkowskiReLU(inplace=True),
+            ME.MinkowskiMaxPooling(kernel_size=2, stride=2, dimension=3),
+        )
+        for i in range(n_outs):
+            setattr(self, f"layer{i + 1}", self._make_layer(block, self.PLANES[i], layers[i], stride=2))
+
+    def _make_layer(self, block, planes, blocks, stride=1, dilation=1):
+        downsample = None
+        if stride != 1 or self.inplanes != planes * block.expansion:
+            downsample = nn.Sequential(
+                ME.MinkowskiConvolution(self.inplanes, planes * block.expansion, kernel_size=1, stride=stride,
+                                        dimension=3),
+                ME.MinkowskiBatchNorm(planes * block.expansion),
+            )
+        mods = [block(self.inplanes, planes, stride=stride, dilation=dilation, downsample=downsample, dimension=3)]
+        self.inplanes = planes * block.expansion
+        mods += [block(self.inplanes, planes, stride=1, dilation=dilation, dimension=3) for _ in range(1, blocks)]
+        return nn.Sequential(*mods)
+
+    def init_weights(self):
+        for m in self.modules():
+            if isinstance(m, ME.MinkowskiConvolution):
+                ME.utils.kaiming_normal_(m.kernel, mode="fan_out", nonlinearity="relu")
+            if isinstance(m, ME.MinkowskiBatchNorm):
+                nn.init.constant_(m.bn.weight, 1)
+                nn.init.constant_(m.bn.bias, 0)
+
+    def forward(self, x):
+        outs = []
+        x = self.conv1(x)
+        for i in range(self.n_outs):
+            x = getattr(self, f"layer{i + 1}")(x)
+            outs.append(x)
+        return outs
+
+    # ---- fused execution ---------------------------------------------------------------------
+    def forward_fused(self, x):
+        cm = x.coordinate_manager
+        conv, inorm, _, pool = self.conv1
+        dt = ME.get_compute_dtype()
+        key, km = conv.maps(x)
+        f = ops.sparse_conv(x.F.contiguous(), conv._w3(), km, cm.size(key), out_dtype=dt)
+        m = cm.get_map(key)
+        scale, shift = inorm.scale_shift(f, m)
+        f = ops.affine_act(f, scale, shift, coords=m.coords, act=ops.ACT_RELU, out=f)
+        pkey = cm.stride(key, pool.stride)
+        f = ops.maxpool(f, cm.kernel_map(key, pkey, pool.kernel_size, pool.dilation))
+        key = pkey
+        outs = []
+        for i in range(self.n_outs):
+            for block in getattr(self, f"layer{i + 1}"):
+                f, key = _fused_block(block, f, key, cm)
+            outs.append(ME.SparseTensor(f, coordinate_map_key=key, coordinate_manager=cm))
+        return outs
+
+
+def conv_bn_act(conv, bn, f, km, n_out, act, residual=None):
+    """conv -> BatchNorm -> (+residual) -> activation.  Eval: one kernel (BN folded into the epilogue).
+    Train: conv, batch statistics, then one fused normalise/residual/activation pass."""
+    if bn.bn.training:
+        y = ops.sparse_conv(f, conv._w3(), km, n_out, wt_bf16=conv._wt_bf16())
+        scale, shift = bn.scale_shift(y)
+        return ops.affine_act(y, scale, shift, residual=residual, act=act, out=y)
+    scale, shift = bn.scale_shift(None)
+    return ops.sparse_conv(f, conv._w3(), km, n_out, wt_bf16=conv._wt_bf16(), scale=scale.reshape(-1),
+                           shift=shift.reshape(-1), residual=residual, act=act)
+
+
+def _fused_block(block, f, key, cm):
+    if not isinstance(block, BasicBlock):  # Bottleneck: no fused schedule, run op by op
+        out = block(ME.SparseTensor(f, coordinate_map_key=key, coordinate_manager=cm))
+        return out.F, out.coordinate_map_key
+    x = ME.SparseTensor(f, coordinate_map_key=key, coordinate_manager=cm)
+    out_key, km1 = block.conv1.maps(x)
+    n_out = cm.size(out_key)
+    h = conv_bn_act(block.conv1, block.norm1, f, km1, n_out, ops.ACT_RELU)
+    if block.downsample is not None:
+        dconv, dbn = block.downsample
+        kmd = cm.kernel_map(key, out_key, dconv.kernel_size, dconv.dilation) if dconv.stride != 1 else None
+        res = conv_bn_act(dconv, dbn, f, kmd, n_out, ops.ACT_NONE)
+    else:
+        res = f
+    km2 = cm.kernel_map(out_key, out_key, block.conv2.kernel_size, block.conv2.dilation)
+    out = conv_bn_act(block.conv2, block.norm2, h, km2, n_out, ops.ACT_RELU, residual=res)
+    return out, out_key
+
+
+# =============================================================================================== neck + head
+class Fcaf3DNeckWithHead(nn.Module):
+    def __init__(self, n_classes, in_channels, out_channels, n_reg_outs, voxel_size, pts_threshold, assigner=None,
+                 yaw_parametrization="fcaf3d", loss_centerness=None, loss_bbox=None, loss_cls=None, train_cfg=None,
+                 test_cfg=None):
+        super().__init__()
+        self.voxel_size = voxel_size
+        self.yaw_parametrization = yaw_parametrization
+        self.pts_threshold = pts_threshold
+        self.train_cfg = train_cfg
+        self.test_cfg = test_cfg or dict(nms_pre=1000, iou_thr=.5, score_thr=.01)
+        self.n_classes, self.n_reg_outs = n_classes, n_reg_outs
+        self.assigner_cfg = assigner
+        self.loss_cfg = dict(centerness=loss_centerness, bbox=loss_bbox, cls=loss_cls)
+        self._init_layers(in_channels, out_channels, n_reg_outs, n_classes)
+
+    @staticmethod
+    def _make_block(cin, cout):
+        return nn.Sequential(ME.MinkowskiConvolution(cin, cout, kernel_size=3, dimension=3),
+                             ME.MinkowskiBatchNorm(cout), ME.MinkowskiELU())
+
+    @staticmethod
+    def _make_up_block(cin, cout):
+        return nn.Sequential(
+            ME.MinkowskiGenerativeConvolutionTranspose(cin, cout, kernel_size=2, stride=2, dimension=3),
+            ME.MinkowskiBatchNorm(cout), ME.MinkowskiELU(),
+            ME.MinkowskiConvolution(cout, cout, kernel_size=3, dimension=3),
+            ME.MinkowskiBatchNorm(cout), ME.MinkowskiELU())
+
+    def _init_layers(self, in_channels, out_channels, n_reg_outs, n_classes):
+        self.pruning = ME.MinkowskiPruning()
+        for i in range(len(in_channels)):
+            if i > 0:
+                setattr(self, f"up_block_{i}", self._make_up_block(in_channels[i], in_channels[i - 1]))
+            setattr(self, f"out_block_{i}", self._make_block(in_channels[i], out_channels))
+        self.centerness_conv = ME.MinkowskiConvolution(out_channels, 1, kernel_size=1, dimension=3)
+        self.reg_conv = ME.MinkowskiConvolution(out_channels, n_reg_outs, kernel_size=1, dimension=3)
+        self.cls_conv = ME.MinkowskiConvolution(out_channels, n_classes, kernel_size=1, bias=True, dimension=3)
+        self.scales = nn.ModuleList([Scale(1.) for _ in range(len(in_channels))])
+
+    def init_weights(self):
+        nn.init.normal_(self.centerness_conv.kernel, std=.01)
+        nn.init.normal_(self.reg_conv.kernel, std=.01)
+        nn.init.normal_(self.cls_conv.kernel, std=.01)
+        nn.init.constant_(self.cls_conv.bias, bias_init_with_prob(.01))
+
+    def _cfg(self, name):
+        c = self.test_cfg
+        return c[name] if isinstance(c, dict) else getattr(c, name)
+
+    # ---- reference-style execution -------------------------------------------------------------
+    def forward(self, x):
+        outs = []
+        inputs = x
+        x = inputs[-1]
+        scores = None
+        for i in range(len(inputs) - 1, -1, -1):
+            if i < len(inputs) - 1:
+                x = getattr(self, f"up_block_{i + 1}")(x)
+                x = inputs[i] + x
+                x = self._prune(x, scores)
+            out = getattr(self, f"out_block_{i}")(x)
+            out = self.forward_single(out, self.scales[i])
+            scores = out[-1]
+            outs.append(out[:-1])
+        return zip(*outs[::-1])
+
+    def _prune(self, x, scores):
+        if self.pts_threshold < 0:
+            return x
+        with torch.no_grad():
+            interpolated = scores.features_at_coordinates(x.C.float())
+            m = x._map()
+            mask = ops.topk_mask(interpolated.reshape(-1).contiguous(), m.off_dev, m.num_batches, self.pts_threshold)
+        return self.pruning(x, mask.bool())
+
+    def forward_single(self, x, scale):
+        centerness = self.centerness_conv(x).features
+        scores = self.cls_conv(x)
+        cls_score = scores.features
+        prune_scores = ME.SparseTensor(cls_score.max(dim=1, keepdim=True).values,
+                                       coordinate_map_key=scores.coordinate_map_key,
+                                       coordinate_manager=scores.coordinate_manager)
+        reg_final = self.reg_conv(x).features
+        reg_distance = torch.exp(scale(reg_final[:, :6]))
+        bbox_pred = torch.cat((reg_distance, reg_final[:, 6:]), dim=1)
+        centernesses, bbox_preds, cls_scores = [], [], []
+        for perm in x.decomposition_permutations:
+            centernesses.append(centerness[perm])
+            bbox_preds.append(bbox_pred[perm])
+            cls_scores.append(cls_score[perm])
+        points = [p * self.voxel_size for p in x.decomposed_coordinates]
+        return centernesses, bbox_preds, cls_scores, points, prune_scores
+
+    def get_bboxes(self, centernesses, bbox_preds, cls_scores, points, img_metas, rescale=False):
+        results = []
+        for i in range(len(img_metas)):
+            results.append(self._get_bboxes_single([x[i] for x in centernesses], [x[i] for x in bbox_preds],
+                                                   [x[i] for x in cls_scores], [x[i] for x in points], img_metas[i]))
+        return results
+
+    def _get_bboxes_single(self, centernesses, bbox_preds, cls_scores, points, img_meta):
+        nms_pre = self._cfg("nms_pre")
+        mlvl_bboxes, mlvl_scores = [], []
+        for centerness, bbox_pred, cls_score, point in zip(centernesses, bbox_preds, cls_scores, points):
+            scores = cls_score.sigmoid() * centerness.sigmoid()
+            max_scores, _ = scores.max(dim=1)
+            if len(scores) > nms_pre > 0:
+                _, ids = max_scores.topk(nms_pre)
+                bbox_pred, scores, point = bbox_pred[ids], scores[ids], point[ids]
+            mlvl_bboxes.append(self._bbox_pred_to_bbox(point, bbox_pred))
+            mlvl_scores.append(scores)
+        return self._nms(torch.cat(mlvl_bboxes), torch.cat(mlvl_scores), img_meta)
+
+    def _yaw_mode(self, n_reg):
+        if n_reg == 6:
+            return ops.YAW_MODES["none"]
+        return ops.YAW_MODES[self.yaw_parametrization]
+
+    def _bbox_pred_to_bbox(self, points, bbox_pred):
+        if bbox_pred.shape[0] == 0:
+            return bbox_pred
+        n_reg = bbox_pred.shape[1]
+        out = ops.decode_boxes(points.float(), bbox_pred.float(), self._yaw_mode(n_reg))
+        return out[:, :6] if n_reg == 6 else out
+
+    def _nms(self, bboxes, scores, img_meta):
+        n_classes = scores.shape[1]
+        yaw_flag = bboxes.shape[1] == 7
+        score_thr, iou_thr = self._cfg("score_thr"), self._cfg("iou_thr")
+        nms_bboxes, nms_scores, nms_labels = [], [], []
+        for i in range(n_classes):
+            ids = scores[:, i] > score_thr
+            if not ids.any():
+                continue
+            class_scores = scores[ids, i]
+            class_bboxes = bboxes[ids]
+            if yaw_flag:
+                nms_function = pcdet_nms_gpu
+            else:
+                class_bboxes = torch.cat((class_bboxes, torch.zeros_like(class_bboxes[:, :1])), dim=1)
+                nms_function = pcdet_nms_normal_gpu
+            nms_ids, _ = nms_function(class_bboxes, class_scores, iou_thr)
+            nms_bboxes.append(class_bboxes[nms_ids])
+            nms_scores.append(class_scores[nms_ids])
+            nms_labels.append(bboxes.new_full(class_scores[nms_ids].shape, i, dtype=torch.long))
+        if len(nms_bboxes):
+            nms_bboxes, nms_scores, nms_labels = torch.cat(nms_bboxes), torch.cat(nms_scores), torch.cat(nms_labels)
+        else:
+            nms_bboxes = bboxes.new_zeros((0, bboxes.shape[1]))
+            nms_scores = bboxes.new_zeros((0,))
+            nms_labels = bboxes.new_zeros((0,), dtype=torch.long)
+        if not yaw_flag:
+            nms_bboxes = nms_bboxes[:, :6]
+        box_type = img_meta.get("box_type_3d") if isinstance(img_meta, dict) else None
+        if box_type is not None:
+            nms_bboxes = box_type(nms_bboxes, box_dim=nms_bboxes.shape[1], with_yaw=yaw_flag, origin=(.5, .5, .5))
+        return nms_bboxes, nms_scores, nms_labels
+
+    # ---- fused execution -----------------------------------------------------------------------
+    def _head_weights(self):
+        """One [1, C, 1 + n_reg + n_cls] kernel + bias for the three 1x1 head convolutions."""
+        ks = (self.centerness_conv.kernel, self.reg_conv.kernel, self.cls_conv.kernel, self.cls_conv.bias)
+        ver = tuple((k._version, k.data_ptr()) for k in ks)
+        if getattr(self, "_hw_ver", None) != ver:
+            w = torch.cat([k.detach() for k in ks[:3]], dim=1).unsqueeze(0).contiguous()
+            b = torch.cat([w.new_zeros(1 + self.n_reg_outs), self.cls_conv.bias.detach().reshape(-1)]).contiguous()
+            self._hw, self._hw_ver = (w, b), ver
+        return self._hw
+
+    def forward_fused(self, inputs, want_max_score=False):
+        """Returns per level (fine -> coarse) dicts with centerness / bbox_pred / cls / prune score (+max score)
+        tensors over the level's coordinate map."""
+        cm = inputs[0].coordinate_manager
+        levels = [None] * len(inputs)
+        f, key = inputs[-1].F, inputs[-1].coordinate_map_key
+        prev = None
+        for i in range(len(inputs) - 1, -1, -1):
+            if i < len(inputs) - 1:
+                gen, bn1, _, conv, bn2, _ = getattr(self, f"up_block_{i + 1}")
+                gkey = cm.generate_children(key)
+                if bn1.bn.training:
+                    g = gen.generate(f)
+                    s, b = bn1.scale_shift(g)
+                    g = ops.affine_act(g, s, b, act=ops.ACT_ELU, out=g)
+                else:
+                    s, b = bn1.scale_shift(None)
+                    g = gen.generate(f, scale=s.reshape(-1), shift=b.reshape(-1), act=ops.ACT_ELU)
+                km = cm.kernel_map(gkey, gkey, conv.kernel_size, conv.dilation)
+                g = conv_bn_act(conv, bn2, g, km, cm.size(gkey), ops.ACT_ELU)
+                # inputs[i] + x  (union of the backbone map and the generated map)
+                ukey, dst_a, dst_b = cm.union(inputs[i].coordinate_map_key, gkey)
+                nu = cm.size(ukey)
+                f = torch.zeros((nu, g.shape[1]), dtype=g.dtype, device=g.device)
+                ops.scatter_rows(inputs[i].F.contiguous(), dst_a, f, accumulate=False)
+                ops.scatter_rows(g, dst_b, f, accumulate=True)
+                key = ukey
+                # prune by the coarser level's interpolated max-class score
+                um = cm.get_map(key)
+                if self.pts_threshold >= 0 and max(um.off_host[b + 1] - um.off_host[b]
+                                                   for b in range(um.num_batches)) > self.pts_threshold:
+                    pm = cm.get_map(prev["key"])
+                    table, cap = pm.ensure_table()
+                    sc = ops.interp(table, cap, prev["prune"], pm.ts, um.coords.float())
+                    mask = ops.topk_mask(sc.reshape(-1), um.off_dev, um.num_batches, self.pts_threshold)
+                    key, m8, pos, n_keep = cm.prune(key, mask)
+                    f = ops.gather_rows(f, m8, pos, n_keep)
+            conv, bn, _ = getattr(self, f"out_block_{i}")
+            km = cm.kernel_map(key, key, conv.kernel_size, conv.dilation)
+            o = conv_bn_act(conv, bn, f, km, cm.size(key), ops.ACT_ELU)
+            w, b = self._head_weights()
+            h = ops.sparse_conv(o, w, None, o.shape[0], bias=b, out_dtype=torch.float32)
+            ctr, bbox, cls, prune, mx = ops.head_post(h, self.n_reg_outs, self.n_classes,
+                                                      self.scales[i].scale.detach().reshape(1), want_max_score)
+            prev = dict(key=key, centerness=ctr, bbox_pred=bbox, cls=cls, prune=prune, max_score=mx)
+            levels[i] = prev
+        return levels
+
+    def get_bboxes_fused(self, levels, cm):
+        """Batched tail: per (scene, level) top-k -> decode -> per (scene, class) BEV NMS, all scenes at once.
+        Returns a list over scenes of (boxes [n, 6|7], scores [n], labels [n]) on the device."""
+        nms_pre, score_thr, iou_thr = self._cfg("nms_pre"), self._cfg("score_thr"), self._cfg("iou_thr")
+        dev = levels[0]["cls"].device
+        nb = cm.num_batches
+        n_cls, n_reg = self.n_classes, self.n_reg_outs
+        yaw_mode = self._yaw_mode(n_reg)
+        rotated = n_reg != 6
+        # candidate counts per (scene, level) are known on the host from the batch offsets
+        maps = [cm.get_map(l["key"]) for l in levels]
+        cnt = [[min(m.off_host[b + 1] - m.off_host[b], nms_pre) if nms_pre > 0 else m.off_host[b + 1] - m.off_host[b]
+                for m in maps] for b in range(nb)]
+        cand_off = [0]
+        for b in range(nb):
+            cand_off.append(cand_off[-1] + sum(cnt[b]))
+        total = cand_off[-1]
+        cand_boxes = torch.empty((total, 7), dtype=torch.float32, device=dev)
+        cand_scores = torch.empty((total, n_cls), dtype=torch.float32, device=dev)
+        bases = []
+        for li in range(len(levels)):
+            bases += [cand_off[b] + sum(cnt[b][:li]) for b in range(nb)]
+        meta = torch.tensor(cand_off + bases, dtype=torch.int32, device=dev)
+        cand_off_dev = meta[: nb + 1]
+        for li, (l, m) in enumerate(zip(levels, maps)):
+            k = nms_pre if nms_pre > 0 else m.n
+            mask = ops.topk_mask(l["max_score"], m.off_dev, nb, k)
+            pos, _ = ops.scan_mask(mask)
+            base = meta[nb + 1 + li * nb: nb + 1 + (li + 1) * nb]
+            ops.call("b2_emit_candidates", ops.ptr(m.coords), ops.ptr(l["centerness"]), ops.ptr(l["bbox_pred"]),
+                     ops.ptr(l["cls"]), ops.ptr(mask), ops.ptr(pos), ops.ptr(m.off_dev), ops.ptr(base), m.n, n_reg,
+                     n_cls, yaw_mode, float(self.voxel_size), ops.ptr(cand_boxes), ops.ptr(cand_scores))
+        # (scene, class) segments of candidates above the score threshold
+        nf = total * n_cls
+        nseg = nb * n_cls
+        flags = torch.empty((max(nf, 1),), dtype=torch.uint8, device=dev)
+        pos = torch.empty((max(nf, 1),), dtype=torch.int32, device=dev)
+        seg_boxes = torch.empty((max(nf, 1), 7), dtype=torch.float32, device=dev)
+        seg_scores = torch.empty((max(nf, 1),), dtype=torch.float32, device=dev)
+        seg_src = torch.empty((max(nf, 1),), dtype=torch.int32, device=dev)
+        seg_off = torch.zeros((nseg + 2,), dtype=torch.int32, device=dev)
+        ws = ops.workspace(ops._lib.lib().b2_scan_ws_bytes(nf), dev)
+        ops.call("b2_class_segments", ops.ptr(cand_boxes), ops.ptr(cand_scores), ops.ptr(cand_off_dev), nb, n_cls, total,
+                 float(score_thr), ops.ptr(flags), ops.ptr(pos), ops.ptr(seg_off) + 4 * (nseg + 1), ops.ptr(seg_boxes),
+                 ops.ptr(seg_scores), ops.ptr(seg_src), ops.ptr(seg_off), ops.ptr(ws), ws.numel())
+        seg_off_host = ops.read_ints(seg_off)[: nseg + 1]  # the one host sync of the tail
+        n_in = seg_off_host[-1]
+        keep, order, sorted_boxes, _ = ops.nms_batched(seg_boxes[:n_in], seg_scores[:n_in], seg_off_host, iou_thr,
+                                                       rotated, sort=True)
+        kpos, ktotal = ops.scan_mask(keep)
+        out_boxes = torch.empty((n_in, 7), dtype=torch.float32, device=dev)
+        out_scores = torch.empty((n_in,), dtype=torch.float32, device=dev)
+        out_labels = torch.empty((n_in,), dtype=torch.int32, device=dev)
+        out_scene = torch.empty((n_in,), dtype=torch.int32, device=dev)
+        ops.call("b2_collect_dets", ops.ptr(sorted_boxes), ops.ptr(seg_scores), ops.ptr(order), ops.ptr(seg_off), nseg,
+                 n_cls, ops.ptr(keep), ops.ptr(kpos), n_in, ops.ptr(out_boxes), ops.ptr(out_scores), ops.ptr(out_labels),
+                 ops.ptr(out_scene))
+        return dict(boxes=out_boxes, scores=out_scores, labels=out_labels, scene=out_scene, count=ktotal,
+                    box_dim=7 if rotated else 6)
+
+
+def split_detections(dets, num_scenes):
+    """Device-side result dict -> host list of (boxes, scores, labels) per scene (one D2H copy each)."""
+    n = int(dets["count"].item())
+    boxes = dets["boxes"][:n, :dets["box_dim"]].cpu()
+    scores, labels, scene = dets["scores"][:n].cpu(), dets["labels"][:n].cpu().long(), dets["scene"][:n].cpu()
+    out = []
+    for b in range(num_scenes):
+        sel = scene == b
+        out.append((boxes[sel], scores[sel], labels[sel]))
+    return out
+
+
+# =============================================================================================== detector
+class SingleStageSparse3DDetector(nn.Module):
+    def __init__(self, backbone, neck_with_head, voxel_size, pretrained=False, train_cfg=None, test_cfg=None):
+        super().__init__()
+        backbone = dict(backbone)
+        backbone.pop("type", None)
+        neck_with_head = dict(neck_with_head)
+        neck_with_head.pop("type", None)
+        neck_with_head.update(train_cfg=train_cfg, test_cfg=test_cfg)
+        self.backbone = MEResNet3D(**backbone)
+        self.neck_with_head = Fcaf3DNeckWithHead(**neck_with_head)
+        self.voxel_size = voxel_size
+        self.train_cfg, self.test_cfg = train_cfg, test_cfg
+        self.init_weights()
+
+    def init_weights(self, pretrained=None):
+        self.backbone.init_weights()
+        self.neck_with_head.init_weights()
+
+    def _input_tensor(self, points):
+        coords, feats = ops.quantize_points([p.contiguous() for p in points], self.voxel_size, 255.0)
+        return ME.SparseTensor(coordinates=coords, features=feats)
+
+    def extract_feat(self, points, img_metas=None):
+        x = self._input_tensor(points)
+        x = self.backbone(x)
+        return self.neck_with_head(x)
+
+    @torch.no_grad()
+    def simple_test(self, points, img_metas, imgs=None, rescale=False):
+        """Reference-style inference (op by op, python loops over scenes / levels / classes)."""
+        x = self.extract_feat(points, img_metas)
+        return self.neck_with_head.get_bboxes(*x, img_metas, rescale=rescale)
+
+    @torch.no_grad()
+    def simple_test_fused(self, points, to_host=True):
+        """B200 inference path: fused backbone / neck / head and the batched tail."""
+        x = self._input_tensor(points)
+        feats = self.backbone.forward_fused(x)
+        levels = self.neck_with_head.forward_fused(feats, want_max_score=True)
+        dets = self.neck_with_head.get_bboxes_fused(levels, x.coordinate_manager)
+        return split_detections(dets, len(points)) if to_host else dets
+
+    @torch.no_grad()
+    def forward_features_fused(self, points):
+        x = self._input_tensor(points)
+        feats = self.backbone.forward_fused(x)
+        return self.neck_with_head.forward_fused(feats, want_max_score=True), x.coordinate_manager
+
+
+def build_fcaf3d(dataset="scannet", **overrides):
+    """FCAF3D detector with the hyper-parameters of configs/fcaf3d/fcaf3d.py:3-28 and the per-dataset overrides
+    (fcaf3d_scannet-3d-18class.py:4-8, fcaf3d_sunrgbd-3d-10class.py:4-7, fcaf3d_s3dis-3d-5class.py:4-8)."""
+    heads = {"scannet": (18, 6), "sunrgbd": (10, 8), "s3dis": (5, 6)}
+    n_classes, n_reg = heads[dataset]
+    voxel_size = overrides.pop("voxel_size", 0.01)
+    cfg = dict(
+        backbone=dict(in_channels=3, depth=overrides.pop("depth", 34), n_outs=overrides.pop("n_outs", 4)),
+        neck_with_head=dict(n_classes=n_classes, in_channels=(64, 128, 256, 512), out_channels=128, n_reg_outs=n_reg,
+                            voxel_size=voxel_size, pts_threshold=overrides.pop("pts_threshold", 100000),
+                            assigner=dict(type="Fcaf3DAssigner", limit=27, topk=18, n_scales=4),
+                            loss_bbox=dict(type="IoU3DLoss", loss_weight=1.0, with_yaw=(dataset == "sunrgbd"))),
+        voxel_size=voxel_size, train_cfg=dict(), test_cfg=dict(nms_pre=1000, iou_thr=.5, score_thr=.01))
+    n_outs = cfg["backbone"]["n_outs"]
+    cfg["neck_with_head"]["in_channels"] = cfg["neck_with_head"]["in_channels"][:n_outs]
+    cfg["neck_with_head"]["assigner"]["n_scales"] = n_outs
+    assert not overrides, f"unknown overrides {overrides}"
+    return SingleStageSparse3DDetector(**cfg)

@@ -1,0 +1,330 @@
+"""Functional host wrappers over the C ABI (include/fcaf3d_b200.h).
+
+Tensors are torch CUDA tensors used purely as device memory; every op enqueues on the current torch
+stream.  No op has a CPU path.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import DT, call, ptr, require_cuda, workspace
+
+ACT_NONE, ACT_RELU, ACT_ELU = 0, 1, 2
+I32 = torch.int32
+
+
+def next_pow2(v):
+    p = 1
+    while p < v:
+        p <<= 1
+    return p
+
+
+def table_capacity(n):
+    return max(1024, next_pow2(2 * int(n)))
+
+
+def alloc_table(n, device):
+    cap = table_capacity(n)
+    return torch.empty(cap * 16, dtype=torch.uint8, device=device), cap
+
+
+def read_ints(t):
+    """One device->host read (synchronises the current stream)."""
+    return t.cpu().tolist()
+
+
+# ----------------------------------------------------------------------------- coordinate maps
+def quantize_points(points_list, voxel_size, feat_div=255.0):
+    """[(N_i, 3+F) fp32 cuda] -> coords int32 [sum N, 4], feats fp32 [sum N, F]."""
+    dev = points_list[0].device
+    dim = points_list[0].shape[1]
+    total = sum(int(p.shape[0]) for p in points_list)
+    coords = torch.empty((total, 4), dtype=I32, device=dev)
+    feats = torch.empty((total, dim - 3), dtype=torch.float32, device=dev)
+    row0 = 0
+    for b, p in enumerate(points_list):
+        require_cuda(p, "points")
+        call("b2_quantize_points", ptr(p), p.shape[0], dim, b, float(voxel_size), float(feat_div), row0, ptr(coords),
+             ptr(feats))
+        row0 += int(p.shape[0])
+    return coords, feats
+
+
+def map_build(coords, quant=0):
+    """Dedup (first occurrence wins, first-occurrence order).  Returns
+    (out_coords[n_out,4], unique_index[n_out], inverse_map[n], table, cap, n_out)."""
+    require_cuda(coords, "coords")
+    n = int(coords.shape[0])
+    dev = coords.device
+    table, cap = alloc_table(n, dev)
+    out_coords = torch.empty((n, 4), dtype=I32, device=dev)
+    unique_index = torch.empty((n,), dtype=I32, device=dev)
+    inverse = torch.empty((n,), dtype=I32, device=dev)
+    status = torch.zeros((2,), dtype=I32, device=dev)  # [n_out, err]
+    ws_bytes = _lib.lib().b2_map_build_ws_bytes(n)
+    ws = workspace(ws_bytes, dev)
+    call("b2_map_build", ptr(coords), n, int(quant), ptr(table), cap, ptr(out_coords), ptr(unique_index), ptr(inverse),
+         ptr(status), ptr(status) + 4, ptr(ws), ws.numel())
+    n_out, err = read_ints(status)
+    if err:
+        raise _lib.B2Error("coordinate outside the packed key range (batch < 1023, |xyz| < 131072)")
+    return out_coords[:n_out], unique_index[:n_out], inverse, table, cap, n_out
+
+
+def map_table(coords):
+    n = int(coords.shape[0])
+    table, cap = alloc_table(n, coords.device)
+    err = torch.zeros((1,), dtype=I32, device=coords.device)
+    call("b2_map_table", ptr(coords), n, ptr(table), cap, ptr(err))
+    return table, cap
+
+
+def map_lookup(table, cap, query):
+    rows = torch.empty((query.shape[0],), dtype=I32, device=query.device)
+    call("b2_map_lookup", ptr(table), cap, ptr(query), query.shape[0], ptr(rows))
+    return rows
+
+
+def map_children(coords, half):
+    out = torch.empty((coords.shape[0] * 8, 4), dtype=I32, device=coords.device)
+    call("b2_map_children", ptr(coords), coords.shape[0], int(half), ptr(out))
+    return out
+
+
+def batch_offsets(coords, num_batches):
+    """Device int32 [B+1] + host list.  Raises if rows are not grouped by ascending batch index."""
+    dev = coords.device
+    buf = torch.zeros((num_batches + 2,), dtype=I32, device=dev)
+    call("b2_batch_offsets", ptr(coords), coords.shape[0], num_batches, ptr(buf), ptr(buf) + 4 * (num_batches + 1))
+    host = read_ints(buf)
+    if host[-1]:
+        raise _lib.B2Error("coordinate rows must be grouped by ascending batch index")
+    return buf[: num_batches + 1], host[: num_batches + 1]
+
+
+def map_union(a_table, a_cap, a_coords, a_off, b_coords, b_off):
+    dev = a_coords.device
+    na, nb = int(a_coords.shape[0]), int(b_coords.shape[0])
+    out_coords = torch.empty((na + nb, 4), dtype=I32, device=dev)
+    dst_a = torch.empty((na,), dtype=I32, device=dev)
+    dst_b = torch.empty((nb,), dtype=I32, device=dev)
+    n_out = torch.zeros((1,), dtype=I32, device=dev)
+    ws_bytes = _lib.lib().b2_map_union_ws_bytes(nb)
+    ws = workspace(ws_bytes, dev)
+    call("b2_map_union", ptr(a_table), a_cap, ptr(a_coords), na, ptr(a_off), ptr(b_coords), nb, ptr(b_off),
+         ptr(out_coords), ptr(dst_a), ptr(dst_b), ptr(n_out), ptr(ws), ws.numel())
+    n = read_ints(n_out)[0]
+    return out_coords[:n], dst_a, dst_b, n
+
+
+def scan_mask(mask):
+    """mask uint8/bool [n] -> (pos int32 [n], total int)."""
+    if mask.dtype == torch.bool:
+        mask = mask.view(torch.uint8)
+    n = int(mask.shape[0])
+    dev = mask.device
+    pos = torch.empty((n,), dtype=I32, device=dev)
+    total = torch.zeros((1,), dtype=I32, device=dev)
+    ws = workspace(_lib.lib().b2_scan_ws_bytes(n), dev)
+    call("b2_scan_mask", ptr(mask), n, ptr(pos), ptr(total), ptr(ws), ws.numel())
+    return pos, total
+
+
+def gather_coords(coords, mask, pos, n_out):
+    out = torch.empty((n_out, 4), dtype=I32, device=coords.device)
+    call("b2_gather_coords", ptr(coords), ptr(mask), ptr(pos), coords.shape[0], ptr(out))
+    return out
+
+
+def gather_rows(x, mask, pos, n_out):
+    x = x.contiguous()
+    out = torch.empty((n_out,) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
+    row_bytes = x.element_size() * (x.numel() // max(int(x.shape[0]), 1)) if x.shape[0] else x.element_size()
+    call("b2_gather_rows", ptr(x), ptr(mask), ptr(pos), x.shape[0], int(row_bytes), ptr(out))
+    return out
+
+
+def index_rows(x, idx):
+    """out[i] = x[idx[i]] (idx int32; negative -> zero row)."""
+    x = x.contiguous()
+    n = int(idx.shape[0])
+    out = torch.empty((n,) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
+    row_bytes = x.element_size() * int(torch.Size(x.shape[1:]).numel())
+    call("b2_index_rows", ptr(x), ptr(idx), n, int(row_bytes), ptr(out))
+    return out
+
+
+def scatter_rows(x, dst, out, accumulate):
+    call("b2_scatter_rows", ptr(x), ptr(dst), x.shape[0], x.shape[1], DT[x.dtype], int(accumulate), ptr(out))
+    return out
+
+
+# ----------------------------------------------------------------------------- kernel maps / conv
+class KernelMap:
+    """Neighbour table of one (in_map, out_map, kernel) triple."""
+    __slots__ = ("nbr", "ld", "tile_mask", "n_out", "kvol")
+
+    def __init__(self, nbr, ld, tile_mask, n_out, kvol):
+        self.nbr, self.ld, self.tile_mask, self.n_out, self.kvol = nbr, ld, tile_mask, n_out, kvol
+
+
+def kernel_map(in_table, in_cap, out_coords, ksize, step):
+    n_out = int(out_coords.shape[0])
+    dev = out_coords.device
+    ld = (n_out + 127) // 128 * 128
+    kvol = ksize ** 3
+    nbr = torch.empty((kvol, ld), dtype=I32, device=dev)
+    tile_mask = torch.empty((max(ld // 128, 1),), dtype=I32, device=dev)
+    call("b2_kernel_map", ptr(in_table), in_cap, ptr(out_coords), n_out, int(ksize), int(step), ptr(nbr), ld,
+         ptr(tile_mask))
+    return KernelMap(nbr, ld, tile_mask, n_out, kvol)
+
+
+_TC_ENABLED = True
+
+
+def set_tensor_cores(flag):
+    global _TC_ENABLED
+    _TC_ENABLED = bool(flag)
+
+
+def tc_eligible(x, cin, cout):
+    return _TC_ENABLED and x.dtype == torch.bfloat16 and cin % 64 == 0 and cout % 64 == 0
+
+
+def sparse_conv(x, w, kmap, n_out, wt_bf16=None, bias=None, scale=None, shift=None, residual=None, act=ACT_NONE,
+                ch_mod=0, out_dtype=None):
+    """out[o] = act((sum_k x[nbr[k][o]] @ w[k] + bias) * scale + shift + residual[o]).
+
+    w: fp32 [K, Cin, Cout]; wt_bf16: optional bf16 [K, Cout, Cin] for the tcgen05 path; kmap None = identity (K = 1).
+    """
+    require_cuda(x, "features")
+    kvol, cin, cout = int(w.shape[0]), int(w.shape[1]), int(w.shape[2])
+    out_dtype = out_dtype or x.dtype
+    out = torch.empty((n_out, cout), dtype=out_dtype, device=x.device)
+    nbr = kmap.nbr if kmap is not None else None
+    ld = kmap.ld if kmap is not None else 0
+    tmask = kmap.tile_mask if kmap is not None else None
+    if residual is not None:
+        assert residual.dtype == out_dtype and residual.shape == out.shape
+    if wt_bf16 is not None and tc_eligible(x, cin, cout):
+        call("b2_conv_tc", ptr(x), ptr(wt_bf16), ptr(nbr), ld, ptr(tmask), n_out, cin, cout, kvol, ptr(bias), ptr(scale),
+             ptr(shift), ptr(residual), act, ch_mod, ptr(out), DT[out_dtype])
+    else:
+        call("b2_conv_cc", ptr(x), DT[x.dtype], ptr(w), ptr(nbr), ld, ptr(tmask), n_out, cin, cout, kvol, ptr(bias),
+             ptr(scale), ptr(shift), ptr(residual), act, ch_mod, ptr(out), DT[out_dtype])
+    return out
+
+
+def maxpool(x, kmap, want_argmax=False):
+    out = torch.empty((kmap.n_out, x.shape[1]), dtype=x.dtype, device=x.device)
+    arg = torch.empty((kmap.n_out, x.shape[1]), dtype=I32, device=x.device) if want_argmax else None
+    call("b2_maxpool", ptr(x), DT[x.dtype], ptr(kmap.nbr), kmap.ld, kmap.kvol, kmap.n_out, x.shape[1], ptr(out),
+         ptr(arg))
+    return (out, arg) if want_argmax else out
+
+
+def segment_stats(x, seg_off, nseg):
+    c = int(x.shape[1])
+    mean = torch.empty((nseg, c), dtype=torch.float32, device=x.device)
+    var = torch.empty((nseg, c), dtype=torch.float32, device=x.device)
+    ws = workspace(_lib.lib().b2_segment_stats_ws_bytes(nseg, c), x.device, slot=1)
+    call("b2_segment_stats", ptr(x), DT[x.dtype], ptr(seg_off), nseg, c, ptr(mean), ptr(var), ptr(ws), ws.numel())
+    return mean, var
+
+
+def affine_act(x, scale=None, shift=None, coords=None, residual=None, act=ACT_NONE, out=None):
+    out = torch.empty_like(x) if out is None else out
+    call("b2_affine_act", ptr(x), DT[x.dtype], ptr(coords), x.shape[0], x.shape[1], ptr(scale), ptr(shift),
+         ptr(residual), act, ptr(out))
+    return out
+
+
+def cast(x, dtype):
+    if x.dtype == dtype:
+        return x
+    out = torch.empty(x.shape, dtype=dtype, device=x.device)
+    call("b2_cast", ptr(x), DT[x.dtype], x.numel(), ptr(out))
+    return out
+
+
+# ----------------------------------------------------------------------------- head tail
+def interp(table, cap, feats, tensor_stride, query):
+    feats = feats.contiguous()
+    query = query.contiguous()
+    out = torch.empty((query.shape[0], feats.shape[1]), dtype=torch.float32, device=feats.device)
+    call("b2_interp", ptr(table), cap, ptr(feats), feats.shape[1], int(tensor_stride), ptr(query), query.shape[0],
+         ptr(out))
+    return out
+
+
+def topk_mask(scores, seg_off, nseg, k):
+    mask = torch.empty((scores.shape[0],), dtype=torch.uint8, device=scores.device)
+    call("b2_topk_mask", ptr(scores), ptr(seg_off), nseg, int(k), ptr(mask))
+    return mask
+
+
+def head_post(feat, n_reg, n_cls, scale, want_max_score=False):
+    n = int(feat.shape[0])
+    dev = feat.device
+    f32 = torch.float32
+    centerness = torch.empty((n, 1), dtype=f32, device=dev)
+    bbox_pred = torch.empty((n, n_reg), dtype=f32, device=dev)
+    cls = torch.empty((n, n_cls), dtype=f32, device=dev)
+    prune = torch.empty((n, 1), dtype=f32, device=dev)
+    mx = torch.empty((n,), dtype=f32, device=dev) if want_max_score else None
+    call("b2_head_post", ptr(feat), n, n_reg, n_cls, ptr(scale), ptr(centerness), ptr(bbox_pred), ptr(cls), ptr(prune),
+         ptr(mx))
+    return centerness, bbox_pred, cls, prune, mx
+
+
+YAW_MODES = {"none": 0, "naive": 1, "sin-cos": 2, "fcaf3d": 3}
+
+
+def decode_boxes(points, bbox_pred, yaw_mode):
+    n = int(points.shape[0])
+    out = torch.empty((n, 7), dtype=torch.float32, device=points.device)
+    call("b2_decode_boxes", ptr(points.contiguous()), ptr(bbox_pred.contiguous()), n, bbox_pred.shape[1], yaw_mode,
+         ptr(out))
+    return out
+
+
+# ----------------------------------------------------------------------------- NMS
+def nms_plan(seg_off_host):
+    nseg = len(seg_off_host) - 1
+    so = (ctypes.c_int * (nseg + 1))(*seg_off_host)
+    to = (ctypes.c_int * (nseg + 1))()
+    mo = (ctypes.c_longlong * (nseg + 1))()
+    words = ctypes.c_longlong()
+    mx = ctypes.c_int()
+    rc = _lib.lib().b2_nms_plan(so, nseg, to, mo, ctypes.byref(words), ctypes.byref(mx))
+    _lib.check(rc, "b2_nms_plan")
+    return list(to), list(mo), words.value, mx.value
+
+
+def nms_batched(boxes, scores, seg_off_host, thresh, rotated, sort=True):
+    """boxes [n,7], scores [n] grouped into segments.  Returns (keep uint8 [n] in sorted order, order int32 [n]
+    (segment-local source index of every sorted slot), sorted_boxes, counts int32 [nseg])."""
+    dev = boxes.device
+    n = int(boxes.shape[0])
+    nseg = len(seg_off_host) - 1
+    tile_off, mask_off, words, max_seg = nms_plan(seg_off_host)
+    plan = torch.tensor(list(seg_off_host) + tile_off, dtype=I32, device=dev)
+    moff = torch.tensor(mask_off, dtype=torch.int64, device=dev)
+    mask = workspace(max(words, 1) * 8, dev, slot=2)
+    keep = torch.empty((n,), dtype=torch.uint8, device=dev)
+    counts = torch.zeros((max(nseg, 1),), dtype=I32, device=dev)
+    sorted_boxes = torch.empty_like(boxes) if sort else boxes
+    order = torch.empty((n,), dtype=I32, device=dev) if sort else None
+    call("b2_nms_batched", ptr(boxes), ptr(scores), ptr(plan), ptr(plan) + 4 * (nseg + 1), ptr(moff), nseg,
+         tile_off[-1], max_seg, float(thresh), int(bool(rotated)), int(bool(sort)), ptr(sorted_boxes), ptr(order),
+         ptr(mask), ptr(keep), ptr(counts))
+    return keep, order, sorted_boxes, counts
+
+
+def boxes_pair_matrix(a, b, mode):
+    out = torch.zeros((a.shape[0], b.shape[0]), dtype=torch.float32, device=a.device)
+    call("b2_boxes_pair_matrix", ptr(a.contiguous()), a.shape[0], ptr(b.contiguous()), b.shape[0], mode, ptr(out))
+    return out

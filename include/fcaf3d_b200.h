@@ -1,0 +1,154 @@
+/*
+ * fcaf3d_b200 — C ABI of the B200-native FCAF3D hot path (libfcaf3d_b200.so).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in _host;
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*) and allocates nothing:
+ *     outputs and scratch (`ws`, sized by the matching *_ws_bytes function) come from the caller;
+ *   - return value: 0 = ok, <0 = error (-1 bad argument, -2 CUDA error, -3 workspace too small);
+ *     b2_last_error() returns the message for the calling thread.  (The reference's ops instead
+ *     terminate the process: mmdet3d/ops/pcdet_nms/src/iou3d_nms.cpp:14-38.)
+ *   - coordinates are int32 rows (batch, x, y, z); rows of one map are grouped by ascending batch index;
+ *     valid range: 0 <= batch < 1023, -131072 <= x,y,z < 131072 (packed 64-bit hash keys);
+ *   - dtype codes: 0 = float32, 1 = bfloat16;  activation codes: 0 none, 1 ReLU, 2 ELU.
+ *
+ * "ME" below is MinkowskiEngine v0.5.4 (pinned at /root/reference docker/Dockerfile:24-32), whose C++/CUDA
+ * backend these entry points replace for the calls the reference makes; ME is not vendored in the
+ * reference tree, so the citations give the reference call sites.
+ */
+#ifndef FCAF3D_B200_H
+#define FCAF3D_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- library ------------------------------------------------------------------------------- */
+const char* b2_last_error(void);
+int b2_version(void);
+int b2_device_sm_count(void);
+
+/* ---- coordinate manager (ME CoordinateMapManager; call sites single_stage_sparse.py:34-37,
+ *      me_resnet.py:19-24,55-78, fcaf3d_neck_with_head.py:60-66,101,110-126) -------------------- */
+
+/* points [n, dim] fp32 (xyz + features) -> coords[row0.., 4] = (batch, floor(xyz / voxel_size)),
+ * feats[row0.., dim-3] = rest / feat_div.  single_stage_sparse.py:34-36 + ME.utils.batch_sparse_collate */
+int b2_quantize_points(const float* pts, long long n, int dim, int batch, float voxel_size, float feat_div,
+                       long long row0, int* coords, float* feats, void* stream);
+
+size_t b2_scan_ws_bytes(long long n);
+/* exclusive scan of a 0/1 byte mask: pos[i] = #set before i, *total = #set (order-preserving compaction) */
+int b2_scan_mask(const uint8_t* mask, long long n, int* pos, int* total, void* ws, size_t ws_bytes, void* stream);
+
+int b2_table_clear(void* table, long long cap, void* stream);
+size_t b2_map_build_ws_bytes(long long n);
+/* ME insert_and_map / stride: hash-insert n rows (optionally floored to multiples of `quant`), dedup with the
+ * LOWEST input row as representative, rows in first-occurrence order (ME CPU rule).  table: cap slots of 16 B,
+ * cap = power of two >= 2n.  Outputs: out_coords[*n_out,4], unique_index[*n_out], inverse_map[n],
+ * *err != 0 if a coordinate is out of the packed range. */
+int b2_map_build(const int* coords, long long n, int quant, void* table, long long cap, int* out_coords,
+                 int* unique_index, int* inverse_map, int* n_out, int* err, void* ws, size_t ws_bytes, void* stream);
+/* hash table over already-unique rows (value = row) */
+int b2_map_table(const int* coords, long long n, void* table, long long cap, int* err, void* stream);
+int b2_map_lookup(const void* table, long long cap, const int* query, long long m, int* rows, void* stream);
+/* ME stride_region for MinkowskiGenerativeConvolutionTranspose(k=2,s=2): row 8*i+k = coords[i] + {0,half}^3,
+ * k = ix + 2*iy + 4*iz.  fcaf3d_neck_with_head.py:60-66 */
+int b2_map_children(const int* coords, long long n, int half, int* out_coords, void* stream);
+/* offsets[b] = first row of batch b (offsets[num_batches] = n); *err = 2 if rows are not batch-grouped */
+int b2_batch_offsets(const int* coords, long long n, int num_batches, int* offsets, int* err, void* stream);
+size_t b2_map_union_ws_bytes(long long nb);
+/* ME union_map (SparseTensor.__add__ with different keys, fcaf3d_neck_with_head.py:101): out = a U b, rows of
+ * scene s = [a rows of s][b-only rows of s]; dst_a[na], dst_b[nb] give the output row of every input row. */
+int b2_map_union(const void* a_table, long long a_cap, const int* a_coords, long long na, const int* a_off,
+                 const int* b_coords, long long nb_rows, const int* b_off, int* out_coords, int* dst_a, int* dst_b,
+                 int* n_out, void* ws, size_t ws_bytes, void* stream);
+/* row compaction helpers (ME MinkowskiPruning, fcaf3d_neck_with_head.py:125) */
+int b2_gather_coords(const int* coords, const uint8_t* mask, const int* pos, long long n, int* out, void* stream);
+int b2_gather_rows(const void* in, const uint8_t* mask, const int* pos, long long n, int row_bytes, void* out,
+                   void* stream);
+int b2_index_rows(const void* in, const int* idx, long long n, int row_bytes, void* out, void* stream);
+int b2_scatter_rows(const void* in, const int* dst, long long n, int c, int dtype, int accumulate, void* out,
+                    void* stream);
+
+/* ---- kernel maps + sparse convolution (ME kernel_map / ConvolutionForwardKernelGPU; call sites
+ *      me_resnet.py:19-21,55-78, fcaf3d_neck_with_head.py:52,60-69,83-85) ------------------------ */
+
+/* nbr[k*ld + o] = input row at coord_o + offset_k (or -1); offsets x-fastest (ME order), odd kernels centred;
+ * tile_mask[o/128] bit k = some row of the 128-row tile has neighbour k.  ld = n_out rounded up to 128. */
+int b2_kernel_map(const void* in_table, long long cap, const int* out_coords, long long n_out, int ksize, int step,
+                  int* nbr, long long ld, unsigned int* tile_mask, void* stream);
+/* CUDA-core implicit GEMM (fp32 accumulate):
+ *   out[o,:] = act((sum_k in[nbr[k][o],:] @ w[k] + bias) * scale + shift + residual[o,:]);  w: [kvol, cin, cout] fp32.
+ * nbr == NULL: identity map (kvol == 1).  ch_mod > 0: epilogue channel = column % ch_mod. */
+int b2_conv_cc(const void* in, int in_dtype, const float* w, const int* nbr, long long ld,
+               const unsigned int* tile_mask, long long n_out, int cin, int cout, int kvol, const float* bias,
+               const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
+               int out_dtype, void* stream);
+/* tcgen05 implicit GEMM, bf16 operands / fp32 TMEM accumulators; wt: [kvol, cout, cin] bf16 (K-major).
+ * cin % 64 == 0, cout % 64 == 0.  Same epilogue as b2_conv_cc; out_dtype 0 or 1. */
+int b2_conv_tc(const void* in_bf16, const void* wt_bf16, const int* nbr, long long ld, const unsigned int* tile_mask,
+               long long n_out, int cin, int cout, int kvol, const float* bias, const float* scale, const float* shift,
+               const void* residual, int act, int ch_mod, void* out, int out_dtype, void* stream);
+
+/* ---- pooling / normalisation / activation (ME MinkowskiMaxPooling, InstanceNorm, BatchNorm, ReLU, ELU;
+ *      me_resnet.py:22-24,63; fcaf3d_neck_with_head.py:53-54,67-71) ------------------------------ */
+int b2_maxpool(const void* in, int dtype, const int* nbr, long long ld, int kvol, long long n_out, int c, void* out,
+               int* argmax, void* stream);
+size_t b2_segment_stats_ws_bytes(int nseg, int c);
+/* per-segment (contiguous row ranges) channel mean and biased variance, two-pass, deterministic */
+int b2_segment_stats(const void* x, int dtype, const int* seg_off, int nseg, int c, float* mean, float* var, void* ws,
+                     size_t ws_bytes, void* stream);
+/* y = act(x * scale[s,:] + shift[s,:] + residual), s = batch index of the row (coords) or 0 when coords == NULL */
+int b2_affine_act(const void* x, int dtype, const int* coords, long long n, int c, const float* scale,
+                  const float* shift, const void* residual, int act, void* y, void* stream);
+int b2_cast(const void* x, int src_dtype, long long n, void* y, void* stream);
+
+/* ---- head tail (fcaf3d_neck_with_head.py:110-126 _prune, :227-253 _get_bboxes_single, :256-279
+ *      forward_single, :281-330 _bbox_pred_to_bbox, :332-374 _nms) ------------------------------- */
+/* ME SparseTensor.features_at_coordinates: trilinear, absent corners contribute 0; query [m,4] fp32 (b,x,y,z) */
+int b2_interp(const void* table, long long cap, const float* feats, int c, int tensor_stride, const float* query,
+              long long m, float* out, void* stream);
+/* mask[i] = 1 for the k largest scores of each segment (ties at the k-th value: lowest rows first) */
+int b2_topk_mask(const float* scores, const int* seg_off, int nseg, int k, uint8_t* mask, void* stream);
+/* feat [n, 1+n_reg+n_cls] -> centerness[n], bbox_pred[n,n_reg] (first 6: exp(*scale * x), scale = the level's
+ * learnable Scale on the device), cls[n,n_cls], prune_score[n] = max class logit,
+ * max_score[n] = max_c sigmoid(cls_c)*sigmoid(centerness) (optional) */
+int b2_head_post(const float* feat, long long n, int n_reg, int n_cls, const float* scale, float* centerness,
+                 float* bbox_pred, float* cls, float* prune_score, float* max_score, void* stream);
+/* yaw_mode: 0 axis-aligned, 1 naive, 2 sin-cos, 3 fcaf3d (Mobius); out [n,7] */
+int b2_decode_boxes(const float* points, const float* bbox_pred, long long n, int n_reg, int yaw_mode, float* out,
+                    void* stream);
+int b2_emit_candidates(const int* coords, const float* centerness, const float* bbox_pred, const float* cls,
+                       const uint8_t* mask, const int* pos, const int* seg_off, const int* dst_base, long long n,
+                       int n_reg, int n_cls, int yaw_mode, float voxel_size, float* cand_boxes, float* cand_scores,
+                       void* stream);
+int b2_class_segments(const float* cand_boxes, const float* cand_scores, const int* cand_off, int nscene, int n_cls,
+                      long long total, float score_thr, uint8_t* flags, int* pos, int* n_flagged, float* seg_boxes,
+                      float* seg_scores, int* seg_src, int* seg_off, void* ws, size_t ws_bytes, void* stream);
+int b2_collect_dets(const float* sorted_boxes, const float* seg_scores, const int* order, const int* seg_off, int nseg,
+                    int n_cls, const uint8_t* keep, const int* pos, long long n, float* out_boxes, float* out_scores,
+                    int* out_labels, int* out_scene, void* stream);
+
+/* ---- BEV NMS (mmdet3d/ops/pcdet_nms: iou3d_nms.h:9-12 nms_gpu / nms_normal_gpu / boxes_iou_bev_gpu /
+ *      boxes_overlap_bev_gpu, kernels iou3d_nms_kernel.cu:104-372, host reduce iou3d_nms.cpp:116-132) ---- */
+/* HOST helper: tile_off_host[nseg+1], mask_off_host[nseg+1] (8-byte words), *mask_words, *max_seg */
+int b2_nms_plan(const int* seg_off_host, int nseg, int* tile_off_host, long long* mask_off_host, long long* mask_words,
+                int* max_seg);
+/* all segments in one launch per stage; keep[n] in (per-segment) sorted order, counts[nseg].
+ * sort == 0 reproduces nms_gpu / nms_normal_gpu on pre-sorted boxes (sorted_boxes/order unused). */
+int b2_nms_batched(const float* boxes, const float* scores, const int* seg_off, const int* tile_off,
+                   const long long* mask_off, int nseg, int total_tiles, int max_seg, float thresh, int rotated,
+                   int sort, float* sorted_boxes, int* order, unsigned long long* mask, uint8_t* keep, int* counts,
+                   void* stream);
+/* mode 0 = boxes_overlap_bev_gpu, 1 = boxes_iou_bev_gpu, 2 = axis-aligned BEV IoU (iou_normal) */
+int b2_boxes_pair_matrix(const float* a, long long na, const float* b, long long nb, int mode, float* out,
+                         void* stream);
+int b2_keep_list(const uint8_t* keep, const int* pos, long long n, long long* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FCAF3D_B200_H */
