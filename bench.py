@@ -1,0 +1,258 @@
+#!/usr/bin/env python
+"""bench.py — ScanNet-shape FCAF3D inference throughput (scenes/s) of the fcaf3d_b200 hot path.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--dtype bf16|fp32]
+
+One "step" = one full inference pass (quantise -> hash -> ME-ResNet34 backbone -> FCAF3D neck/head -> top-k ->
+decode -> per-class BEV NMS) over one batch of 8 synthetic ScanNet-shaped scenes (S0 family, 100 000 points each).
+N > 1 (torchrun): every rank runs its own batch of 8 scenes (scene sharding, no collective) -> "weak" scaling.
+Prints ONE JSON line (rank 0).  See DESIGN.md §Measurement for every field.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BATCH = 8
+PRESET = "S0"
+METRIC = "ScanNet-shape scenes/sec, FCAF3D full inference incl. axis-aligned BEV NMS, batch 8"
+WORKLOAD = "FCAF3D ScanNet-18class full inference incl. axis-aligned 3D(BEV) NMS, batch 8 synthetic S0 scenes x 100k pts"
+
+
+def peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], 0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = max(mx, float(r[1]))
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def cpu_forward_baseline(n_scenes=1, threads=None):
+    """CPU restatement of the ME path (oracle/model_cpu.py): backbone + neck + head forward of `n_scenes` S0 scenes
+    processed one by one (configs[0]; the reference has no CPU NMS: pcdet_nms aborts on CPU tensors)."""
+    import torch
+    from fcaf3d_b200.scenes import make_scene
+    from fcaf3d_b200.testing import deterministic_init
+    from oracle import model_cpu
+    threads = threads or os.cpu_count()
+    torch.set_num_threads(threads)
+    det = deterministic_init(model_cpu.Detector("scannet"), 0, cls_bias=0.0).eval()
+    scenes = [torch.from_numpy(make_scene(PRESET, 100 * i)[0]) for i in range(n_scenes)]
+    t0 = time.perf_counter()
+    for p in scenes:
+        det([p])
+    dt = time.perf_counter() - t0
+    return n_scenes / dt, dt, threads
+
+
+def run_reference(args):
+    """--impl reference: the reference's ME CPU backend cannot be installed (no MinkowskiEngine source, no network),
+    so the CPU port in oracle/ is timed on this box's host cores (kind = "port")."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch  # noqa: F401
+    per_step = []
+    for i in range(args.warmup + args.steps):
+        v, dt, threads = cpu_forward_baseline(1)
+        if i >= args.warmup:
+            per_step.append(dt)
+    ms = 1000.0 * sum(per_step) / len(per_step)
+    value = 1000.0 / ms
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "scenes/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "sample": "1 S0 scene per step, forward only (no CPU NMS in the reference)"},
+            "cpu_baseline": {"value": value, "unit": "scenes/s", "cores": threads, "kind": "port",
+                             "sample": "1 S0 scene (100k points) backbone+neck+head forward per step"},
+            "e2e": {"value": value, "unit": "scenes/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    from fcaf3d_b200 import me as ME
+    from fcaf3d_b200 import ops
+    from fcaf3d_b200.detector import build_fcaf3d, split_detections
+    from fcaf3d_b200.scenes import make_scene
+    from fcaf3d_b200.testing import deterministic_init
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    dtype = torch.bfloat16 if args.dtype == "bf16" else torch.float32
+    ME.set_compute_dtype(dtype)
+
+    # ---- model: FCAF3D ScanNet config, deterministic random weights; cls bias 0 so that candidates pass score_thr (F8);
+    #      BatchNorm running statistics calibrated by one train-mode pass (what a trained checkpoint would carry)
+    det = deterministic_init(build_fcaf3d("scannet"), 0, cls_bias=0.0).to(dev)
+    host_pts = [torch.from_numpy(make_scene(PRESET, 100 * (rank * BATCH + i))[0]).pin_memory() for i in range(BATCH)]
+    dev_pts = [p.to(dev) for p in host_pts]
+    with torch.no_grad():
+        det.train()
+        for m in det.modules():
+            if isinstance(m, torch.nn.BatchNorm1d):
+                m.momentum = 1.0
+        det.forward_features_fused(dev_pts)
+        det.eval()
+
+    def step_device():
+        return det.simple_test_fused(dev_pts, to_host=False)
+
+    def step_e2e():
+        pts = [p.to(dev, non_blocking=True) for p in host_pts]
+        dets = det.simple_test_fused(pts, to_host=False)
+        return split_detections(dets, BATCH)
+
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        times = []
+        for _ in range(steps):
+            flush.fill_(1)  # L2 flush between timed iterations (256 MB > 126 MB L2)
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            out = fn()
+            e.record()
+            torch.cuda.synchronize()
+            times.append(s.elapsed_time(e))
+        t = torch.tensor([sum(times)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item() / steps, out
+
+    with ClockSampler(local) as clk:
+        ms, dets = timed(step_device, args.steps, args.warmup)
+    clocks = clk.summary()
+    ms_e2e, res = timed(step_e2e, max(3, args.steps // 2), 1)
+    n_det = int(dets["count"].item())
+    d2h = sum(b.numel() * 4 + s.numel() * 4 + l.numel() * 8 for b, s, l in res) + 4
+    h2d = sum(p.numel() * 4 for p in host_pts)
+
+    # ---- per-kernel roofline pass (one extra step with CUDA events around the profiled launches)
+    ops.PROFILE = []
+    step_device()
+    torch.cuda.synchronize()
+    prof, ops.PROFILE = ops.PROFILE, None
+    agg = {}
+    for name, s, e, fl, by in prof:
+        a = agg.setdefault(name, [0, 0.0, 0.0, 0.0])
+        a[0] += 1
+        a[1] += s.elapsed_time(e)
+        a[2] += fl
+        a[3] += by
+    pk, pk_kind = peaks()
+    kernels = {}
+    for name, (cnt, t_ms, fl, by) in agg.items():
+        kernels[name] = {"launches": cnt, "ms": round(t_ms, 4), "tflops": fl / t_ms / 1e9 if fl else None,
+                         "gbs": by / t_ms / 1e6}
+    main_k = "conv_tc" if "conv_tc" in agg else "conv_cc"
+    cnt, t_ms, fl, by = agg[main_k]
+    peak = pk["bf16_tflops_sustained"] if main_k == "conv_tc" else 75.0
+    roofline = {"kernel": main_k, "bound": "tensor", "achieved": fl / t_ms / 1e9, "peak": peak, "unit": "TFLOP/s",
+                "frac": fl / t_ms / 1e9 / peak, "traffic": None, "peak_source": pk_kind,
+                "launches_per_step": cnt, "avg_launch_ms": t_ms / cnt, "share_of_step": t_ms / ms,
+                "algorithmic_flops_per_step": fl, "other_kernels": kernels}
+
+    launches = len(prof)  # profiled launches only; the full count comes from the ncu launch list under profiles/
+    line = {"metric": METRIC, "value": world * BATCH * 1000.0 / ms, "unit": "scenes/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+            "config": {"workload": WORKLOAD, "scenes_per_gpu": BATCH, "points_per_scene": 100000, "voxel_size": 0.01,
+                       "weights": "deterministic random init, cls bias 0 (all candidates pass score_thr), BN stats "
+                                  "calibrated on the batch", "l2": "256 MB flush write between timed iterations",
+                       "detections_per_step": n_det, "sharding": "whole scenes per GPU, no collective"},
+            "clocks": clocks,
+            "e2e": {"value": world * BATCH * 1000.0 / ms_e2e, "unit": "scenes/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e},
+            "gpu_launches": launches, "roofline": roofline}
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        v, dt, threads = cpu_forward_baseline(1)
+        line["cpu_baseline"] = {"value": v, "unit": "scenes/s", "cores": threads, "kind": "port",
+                                "sample": "1 S0 scene (100k points), backbone+neck+head forward on the CPU restatement "
+                                          "of the ME path (MinkowskiEngine itself unavailable); %.1f s" % dt}
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -65,9 +65,11 @@ def map_build(coords, quant=0):
     status = torch.zeros((2,), dtype=I32, device=dev)  # [n_out, err]
     ws_bytes = _lib.lib().b2_map_build_ws_bytes(n)
     ws = workspace(ws_bytes, dev)
+    t0 = _prof_start()
     call("b2_map_build", ptr(coords), n, int(quant), ptr(table), cap, ptr(out_coords), ptr(unique_index), ptr(inverse),
          ptr(status), ptr(status) + 4, ptr(ws), ws.numel())
     n_out, err = read_ints(status)
+    _prof_stop(t0, "hash_build", 0.0, 20.0 * n + 20.0 * n_out)
     if err:
         raise _lib.B2Error("coordinate outside the packed key range (batch < 1023, |xyz| < 131072)")
     return out_coords[:n_out], unique_index[:n_out], inverse, table, cap, n_out
@@ -164,10 +166,11 @@ def scatter_rows(x, dst, out, accumulate):
 # ----------------------------------------------------------------------------- kernel maps / conv
 class KernelMap:
     """Neighbour table of one (in_map, out_map, kernel) triple."""
-    __slots__ = ("nbr", "ld", "tile_mask", "n_out", "kvol")
+    __slots__ = ("nbr", "ld", "tile_mask", "n_out", "kvol", "pairs")
 
     def __init__(self, nbr, ld, tile_mask, n_out, kvol):
         self.nbr, self.ld, self.tile_mask, self.n_out, self.kvol = nbr, ld, tile_mask, n_out, kvol
+        self.pairs = None
 
 
 def kernel_map(in_table, in_cap, out_coords, ksize, step):
@@ -177,12 +180,42 @@ def kernel_map(in_table, in_cap, out_coords, ksize, step):
     kvol = ksize ** 3
     nbr = torch.empty((kvol, ld), dtype=I32, device=dev)
     tile_mask = torch.empty((max(ld // 128, 1),), dtype=I32, device=dev)
+    t0 = _prof_start()
     call("b2_kernel_map", ptr(in_table), in_cap, ptr(out_coords), n_out, int(ksize), int(step), ptr(nbr), ld,
          ptr(tile_mask))
+    _prof_stop(t0, "kernel_map", 0.0, 16.0 * n_out + 24.0 * kvol * n_out)
     return KernelMap(nbr, ld, tile_mask, n_out, kvol)
 
 
 _TC_ENABLED = True
+
+# Optional per-launch profiling (bench.py): list of [name, start_event, end_event, algorithmic_flops, algorithmic_bytes]
+PROFILE = None
+
+
+def _prof_start():
+    if PROFILE is None:
+        return None
+    e = torch.cuda.Event(enable_timing=True)
+    e.record()
+    return e
+
+
+def _prof_stop(start, name, flops=0.0, nbytes=0.0):
+    if start is None:
+        return
+    e = torch.cuda.Event(enable_timing=True)
+    e.record()
+    PROFILE.append([name, start, e, float(flops), float(nbytes)])
+
+
+def kmap_pairs(kmap, n_out):
+    """number of (in, out) pairs of a kernel map (one host sync, cached; profiling only)."""
+    if kmap is None:
+        return n_out
+    if getattr(kmap, "pairs", None) is None:
+        kmap.pairs = int((kmap.nbr >= 0).sum().item())
+    return kmap.pairs
 
 
 def set_tensor_cores(flag):
@@ -209,12 +242,21 @@ def sparse_conv(x, w, kmap, n_out, wt_bf16=None, bias=None, scale=None, shift=No
     tmask = kmap.tile_mask if kmap is not None else None
     if residual is not None:
         assert residual.dtype == out_dtype and residual.shape == out.shape
-    if wt_bf16 is not None and tc_eligible(x, cin, cout):
+    use_tc = wt_bf16 is not None and tc_eligible(x, cin, cout)
+    if PROFILE is not None:
+        pairs = kmap_pairs(kmap, n_out)
+        esz = x.element_size()
+        flops = 2.0 * pairs * cin * cout
+        nbytes = esz * (x.shape[0] * cin + kvol * cin * cout) + out.element_size() * n_out * cout + 4.0 * kvol * ld
+    t0 = _prof_start()
+    if use_tc:
         call("b2_conv_tc", ptr(x), ptr(wt_bf16), ptr(nbr), ld, ptr(tmask), n_out, cin, cout, kvol, ptr(bias), ptr(scale),
              ptr(shift), ptr(residual), act, ch_mod, ptr(out), DT[out_dtype])
     else:
         call("b2_conv_cc", ptr(x), DT[x.dtype], ptr(w), ptr(nbr), ld, ptr(tmask), n_out, cin, cout, kvol, ptr(bias),
              ptr(scale), ptr(shift), ptr(residual), act, ch_mod, ptr(out), DT[out_dtype])
+    if t0 is not None:
+        _prof_stop(t0, "conv_tc" if use_tc else "conv_cc", flops, nbytes)
     return out
 
 

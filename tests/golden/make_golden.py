@@ -1,0 +1,126 @@
+"""Generates the committed golden fixtures by running the REFERENCE's own python files
+(/root/reference/mmdet3d/models/{backbones/me_resnet.py,dense_heads/fcaf3d_neck_with_head.py,
+detectors/single_stage_sparse.py}, models/losses/iou3d_loss.py, ops/rotated_iou/*.py, loaded unmodified by
+oracle/ref_loader.py) on the CPU oracle.  Run in the build container only:
+
+    python tests/golden/make_golden.py
+
+MinkowskiEngine itself is absent, so these vectors pin OUR restatement of ME + the reference's real model code; the
+pcdet_nms arithmetic is pinned separately against the reference's compiled sources (oracle/_ref).
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from fcaf3d_b200.scenes import make_scene  # noqa: E402
+from fcaf3d_b200.testing import canonical_order, deterministic_init  # noqa: E402
+from oracle import ref_loader  # noqa: E402
+
+OUT = os.path.dirname(os.path.abspath(__file__))
+SAMPLE = 256
+
+
+def detector_fixture(config, seeds, name, n_points=3000):
+    det = ref_loader.build_reference_detector(config)
+    deterministic_init(det, seed=0, cls_bias=0.0)
+    det.eval()
+    pts = [make_scene("tiny", s, n_points)[0] for s in seeds]
+    with torch.no_grad():
+        x = det.extract_feat([torch.from_numpy(p) for p in pts], None)
+        x = [list(a) for a in x]
+        metas = [dict(box_type_3d=ref_loader.DepthBoxes)] * len(seeds)
+        res = det.neck_with_head.get_bboxes(*x, metas)
+    centernesses, bbox_preds, cls_scores, points = x
+    out = {"seeds": np.array(seeds), "n_points": np.array(n_points), "voxel_size": np.array(det.voxel_size)}
+    for i, p in enumerate(pts):
+        out["points_%d" % i] = p
+    for lvl in range(len(points)):
+        for b in range(len(seeds)):
+            vox = torch.round(points[lvl][b] / det.voxel_size).int()
+            order = canonical_order(vox)
+            feat = torch.cat([centernesses[lvl][b], bbox_preds[lvl][b], cls_scores[lvl][b]], 1)[order]
+            vox = vox[order]
+            step = max(1, len(vox) // SAMPLE)
+            out["l%d_b%d_n" % (lvl, b)] = np.array(len(vox))
+            out["l%d_b%d_vox" % (lvl, b)] = vox[::step].numpy()
+            out["l%d_b%d_feat" % (lvl, b)] = feat[::step].numpy()
+            out["l%d_b%d_colsum" % (lvl, b)] = feat.double().sum(0).numpy()
+            out["l%d_b%d_abssum" % (lvl, b)] = feat.double().abs().sum(0).numpy()
+    for b, (boxes, scores, labels) in enumerate(res):
+        bt = boxes.tensor.clone()
+        bt[:, 2] += bt[:, 5] * 0.5  # back to gravity centre, as the head produced them
+        out["det%d_boxes" % b] = bt.numpy()
+        out["det%d_scores" % b] = scores.numpy()
+        out["det%d_labels" % b] = labels.numpy()
+    np.savez_compressed(os.path.join(OUT, name), **out)
+    print(name, {k: v.shape for k, v in out.items() if k.startswith("det")})
+
+
+def ops_fixture():
+    ns = ref_loader.load()
+    g = torch.Generator().manual_seed(7)
+    out = {}
+    # docstring known-answer of axis_aligned_bbox_overlaps_3d (iou3d_calculator.py:228-248)
+    b1 = torch.tensor([[0, 0, 0, 10, 10, 10], [10, 10, 10, 20, 20, 20], [32, 32, 32, 38, 40, 42.]])
+    b2 = torch.tensor([[0, 0, 0, 10, 20, 20], [0, 10, 10, 10, 19, 20], [10, 10, 10, 20, 20, 20.]])
+    out["aa_b1"], out["aa_b2"] = b1.numpy(), b2.numpy()
+    out["aa_iou"] = ns.axis_aligned_bbox_overlaps_3d(b1, b2).numpy()
+    # _bbox_pred_to_bbox for the three parametrisations the head supports
+    head = ref_loader.build_reference_detector("fcaf3d_sunrgbd-3d-10class.py").neck_with_head
+    pts = torch.rand(64, 3, generator=g) * 4
+    bp8 = torch.cat([torch.rand(64, 6, generator=g) + .1, torch.randn(64, 2, generator=g)], 1)
+    out["dec_points"], out["dec_pred8"] = pts.numpy(), bp8.numpy()
+    out["dec_fcaf3d"] = head._bbox_pred_to_bbox(pts, bp8).numpy()
+    head.yaw_parametrization = "sin-cos"
+    out["dec_sincos"] = head._bbox_pred_to_bbox(pts, bp8).numpy()
+    head.yaw_parametrization = "naive"
+    out["dec_naive"] = head._bbox_pred_to_bbox(pts, bp8[:, :7]).numpy()
+    out["dec_aligned"] = head._bbox_pred_to_bbox(pts, bp8[:, :6]).numpy()
+    # IoU losses (value + gradient wrt prediction)
+    n = 96
+    tgt = torch.cat([torch.rand(n, 3, generator=g) * 3, torch.rand(n, 3, generator=g) + .3,
+                     (torch.rand(n, 1, generator=g) - .5) * 3], 1)
+    pred = (tgt + torch.randn(n, 7, generator=g) * torch.tensor([.2, .2, .2, .15, .15, .15, .3])).requires_grad_(True)
+    w = torch.rand(n, generator=g)
+    for with_yaw, tag in ((True, "rot"), (False, "aa")):
+        loss_fn = ns.IoU3DLoss(with_yaw=with_yaw, loss_weight=1.0)
+        p = pred if with_yaw else pred[:, :6]
+        t = tgt if with_yaw else tgt[:, :6]
+        loss = loss_fn(p, t, weight=w, avg_factor=w.sum())
+        grad, = torch.autograd.grad(loss, pred, allow_unused=True)
+        out["iou_%s_loss" % tag], out["iou_%s_grad" % tag] = loss.detach().numpy(), grad.numpy()
+    out["iou_pred"], out["iou_tgt"], out["iou_w"] = pred.detach().numpy(), tgt.numpy(), w.numpy()
+    out["iou_rot_values"] = ns.cal_iou_3d(pred.detach()[None], tgt[None])[0].numpy()
+    # focal / centerness-BCE
+    logits = torch.randn(200, 18, generator=g).requires_grad_(True)
+    labels = torch.randint(-1, 18, (200,), generator=g)
+    fl = ns.FocalLoss(use_sigmoid=True, gamma=2.0, alpha=0.25)(logits, labels, avg_factor=37.0)
+    out["focal_logits"], out["focal_labels"] = logits.detach().numpy(), labels.numpy()
+    out["focal_loss"] = fl.detach().numpy()
+    out["focal_grad"] = torch.autograd.grad(fl, logits)[0].numpy()
+    # assigner on a tiny scene (labels / centerness targets / box targets)
+    pts_np, gt, gl = make_scene("tiny", 3, 3000)
+    gtb = ns.DepthBoxes(torch.from_numpy(gt), origin=(.5, .5, .5))
+    lv_pts = []
+    for lvl, ts in enumerate((8, 16, 32, 64)):
+        v = np.unique(np.floor(pts_np[:, :3] / 0.01 / ts).astype(np.int64), axis=0) * ts
+        lv_pts.append(torch.from_numpy(v.astype(np.float32)) * 0.01)
+    asg = ns.Fcaf3DAssigner(limit=27, topk=18, n_scales=4)
+    ct, bt, lb = asg.assign(lv_pts, gtb, torch.from_numpy(gl))
+    for i, p in enumerate(lv_pts):
+        out["asg_points_%d" % i] = p.numpy()
+    out["asg_gt"], out["asg_gt_labels"] = gt, gl
+    out["asg_centerness"], out["asg_bbox_targets"], out["asg_labels"] = ct.numpy(), bt.numpy(), lb.numpy()
+    np.savez_compressed(os.path.join(OUT, "ops_ref.npz"), **out)
+    print("ops_ref", int((lb >= 0).sum()), "positives of", len(lb))
+
+
+if __name__ == "__main__":
+    torch.set_num_threads(8)
+    ops_fixture()
+    detector_fixture("fcaf3d_scannet-3d-18class.py", (0, 100), "fcaf3d_tiny_scannet.npz")
+    detector_fixture("fcaf3d_sunrgbd-3d-10class.py", (5,), "fcaf3d_tiny_sunrgbd.npz")

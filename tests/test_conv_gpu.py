@@ -1,0 +1,145 @@
+"""GPU parity (floating point): sparse convolution (CUDA-core fp32 path and tcgen05 bf16 path), generative
+transpose, pooling, normalisation and activations vs the CPU oracle.
+
+Tolerances (relative to the max |reference| of the tensor):
+  fp32 path  : 2e-5  (fp32 FMA accumulation in a different order than the oracle's index_add)
+  bf16 path  : 1.5e-2 (operands rounded to bf16 = 2^-8 relative, fp32 accumulate, bf16 output rounding)
+"""
+import pytest
+import torch
+
+import oracle.me_cpu as OME
+from fcaf3d_b200 import me as ME
+from fcaf3d_b200 import ops
+from util import rel_err, surface_coords
+
+pytestmark = pytest.mark.gpu
+FP32_TOL, BF16_TOL = 2e-5, 1.5e-2
+
+
+def _tensors(dev, c_in, batch=2, n_points=3000, seed=0, ts=1):
+    c = torch.from_numpy(surface_coords(n_points, batch, seed))
+    o = OME.SparseTensor(torch.zeros(len(c), 1), coordinates=c)
+    n = len(o)
+    torch.manual_seed(seed)
+    f = torch.randn(n, c_in)
+    o = OME.SparseTensor(f, coordinate_map_key=o.coordinate_map_key, coordinate_manager=o.coordinate_manager)
+    x0 = ME.SparseTensor(torch.zeros(len(c), 1, device=dev), coordinates=c.to(dev))
+    assert torch.equal(x0.C.cpu(), o.C)
+    x = ME.SparseTensor(f.to(dev), coordinate_map_key=x0.coordinate_map_key, coordinate_manager=x0.coordinate_manager)
+    return x, o
+
+
+def _copy_params(dst, src):
+    dst.load_state_dict(src.state_dict())
+    return dst
+
+
+@pytest.mark.parametrize("cin,cout,k,stride,bias", [(3, 64, 3, 2, False), (16, 24, 3, 1, True), (64, 64, 3, 1, False),
+                                                     (32, 18, 1, 1, True), (64, 128, 1, 2, False), (5, 7, 2, 2, False)])
+def test_conv_fp32_path(dev, cin, cout, k, stride, bias):
+    x, o = _tensors(dev, cin)
+    oc = OME.MinkowskiConvolution(cin, cout, kernel_size=k, stride=stride, bias=bias, dimension=3)
+    gc = _copy_params(ME.MinkowskiConvolution(cin, cout, kernel_size=k, stride=stride, bias=bias, dimension=3), oc).to(dev)
+    with torch.no_grad():
+        y, ry = gc(x), oc(o)
+    assert torch.equal(y.C.cpu(), ry.C)
+    assert y.F.dtype == torch.float32 and rel_err(y.F, ry.F) < FP32_TOL
+
+
+@pytest.mark.parametrize("cin,cout,k,stride", [(64, 64, 3, 1), (64, 128, 3, 2), (128, 128, 3, 1), (256, 64, 1, 2),
+                                               (128, 256, 3, 1)])
+def test_conv_tcgen05_path(dev, cin, cout, k, stride):
+    x, o = _tensors(dev, cin, seed=1)
+    oc = OME.MinkowskiConvolution(cin, cout, kernel_size=k, stride=stride, dimension=3)
+    gc = _copy_params(ME.MinkowskiConvolution(cin, cout, kernel_size=k, stride=stride, dimension=3), oc).to(dev)
+    xb = ME.SparseTensor(x.F.to(torch.bfloat16), coordinate_map_key=x.coordinate_map_key,
+                         coordinate_manager=x.coordinate_manager)
+    assert ops.tc_eligible(xb.F, cin, cout)
+    with torch.no_grad():
+        y, ry = gc(xb), oc(o)
+    torch.cuda.synchronize()
+    assert y.F.dtype == torch.bfloat16
+    assert rel_err(y.F, ry.F) < BF16_TOL
+    # same kernel, fp32 output and the fused epilogue (bias-free conv -> scale/shift -> residual -> ReLU)
+    out_key, km = gc.maps(xb)
+    n_out = x.coordinate_manager.size(out_key)
+    torch.manual_seed(2)
+    scale, shift = torch.rand(cout, device=dev) + .5, torch.randn(cout, device=dev)
+    res = torch.randn(n_out, cout, device=dev)
+    z = ops.sparse_conv(xb.F, gc._w3(), km, n_out, wt_bf16=gc._wt_bf16(), scale=scale, shift=shift, residual=res,
+                        act=ops.ACT_RELU, out_dtype=torch.float32)
+    ref = torch.relu(ry.F * scale.cpu() + shift.cpu() + res.cpu())
+    assert rel_err(z, ref) < BF16_TOL
+    # and against the CUDA-core kernel fed the same bf16-rounded operands: only accumulation order differs
+    ops.set_tensor_cores(False)
+    try:
+        z_cc = ops.sparse_conv(xb.F, gc._w3().to(torch.bfloat16).float(), km, n_out, scale=scale, shift=shift,
+                               residual=res, act=ops.ACT_RELU, out_dtype=torch.float32)
+    finally:
+        ops.set_tensor_cores(True)
+    assert rel_err(z, z_cc) < 5e-4
+
+
+def test_generative_transpose_both_paths(dev):
+    x, o = _tensors(dev, 128, n_points=1500)
+    cm, ocm = x.coordinate_manager, o.coordinate_manager
+    k8, ok8 = cm.stride(cm.stride(cm.stride(x.coordinate_map_key, 2), 2), 2), None
+    ok8 = ocm.stride(ocm.stride(ocm.stride(o.coordinate_map_key, 2), 2), 2)
+    n = cm.size(k8)
+    torch.manual_seed(3)
+    f = torch.randn(n, 128)
+    xs = ME.SparseTensor(f.to(dev), coordinate_map_key=k8, coordinate_manager=cm)
+    os_ = OME.SparseTensor(f, coordinate_map_key=ok8, coordinate_manager=ocm)
+    ou = OME.MinkowskiGenerativeConvolutionTranspose(128, 64, kernel_size=2, stride=2, dimension=3)
+    gu = _copy_params(ME.MinkowskiGenerativeConvolutionTranspose(128, 64, kernel_size=2, stride=2, dimension=3), ou).to(dev)
+    with torch.no_grad():
+        y, ry = gu(xs), ou(os_)
+        yb = gu(ME.SparseTensor(xs.F.to(torch.bfloat16), coordinate_map_key=k8, coordinate_manager=cm))
+    assert torch.equal(y.C.cpu(), ry.C) and y.tensor_stride == [4, 4, 4]
+    assert rel_err(y.F, ry.F) < FP32_TOL
+    assert rel_err(yb.F, ry.F) < BF16_TOL
+
+
+def test_pool_norms_activations(dev):
+    x, o = _tensors(dev, 64, batch=3)
+    with torch.no_grad():
+        y, ry = ME.MinkowskiMaxPooling(2, 2, dimension=3)(x), OME.MinkowskiMaxPooling(2, 2, dimension=3)(o)
+        assert torch.equal(y.C.cpu(), ry.C) and torch.equal(y.F.cpu(), ry.F)
+        oin = OME.MinkowskiInstanceNorm(64)
+        torch.nn.init.normal_(oin.weight), torch.nn.init.normal_(oin.bias)
+        gin = _copy_params(ME.MinkowskiInstanceNorm(64), oin).to(dev)
+        assert rel_err(gin(x).F, oin(o).F) < 1e-4
+        obn = OME.MinkowskiBatchNorm(64)
+        torch.nn.init.normal_(obn.bn.weight), torch.nn.init.normal_(obn.bn.bias)
+        gbn = _copy_params(ME.MinkowskiBatchNorm(64), obn).to(dev)
+        gbn.train(), obn.train()
+        assert rel_err(gbn(x).F, obn(o).F) < 1e-4
+        assert rel_err(gbn.bn.running_var, obn.bn.running_var) < 1e-5
+        assert rel_err(gbn.bn.running_mean, obn.bn.running_mean) < 1e-4
+        gbn.eval(), obn.eval()
+        assert rel_err(gbn(x).F, obn(o).F) < 1e-5
+        assert rel_err(ME.MinkowskiELU()(x).F, OME.MinkowskiELU()(o).F) < 1e-6
+        xa = x + x
+        assert rel_err(xa.F, o.F * 2) < 1e-7
+        assert torch.equal(ME.MinkowskiReLU()(x).F.cpu(), torch.relu(o.F))
+
+
+def test_basic_block_and_union_add(dev):
+    from fcaf3d_b200.me.modules.resnet_block import BasicBlock
+    x, o = _tensors(dev, 16)
+    ods = torch.nn.Sequential(OME.MinkowskiConvolution(16, 32, kernel_size=1, stride=2, dimension=3),
+                              OME.MinkowskiBatchNorm(32))
+    gds = torch.nn.Sequential(ME.MinkowskiConvolution(16, 32, kernel_size=1, stride=2, dimension=3),
+                              ME.MinkowskiBatchNorm(32))
+    ob = OME.BasicBlock(16, 32, stride=2, downsample=ods, dimension=3).eval()
+    gb = _copy_params(BasicBlock(16, 32, stride=2, downsample=gds, dimension=3), ob).to(dev).eval()
+    with torch.no_grad():
+        y, ry = gb(x), ob(o)
+        assert torch.equal(y.C.cpu(), ry.C) and rel_err(y.F, ry.F) < 1e-4
+        # generated children + backbone level: union add (different keys)
+        up_o = OME.MinkowskiGenerativeConvolutionTranspose(32, 16, kernel_size=2, stride=2, dimension=3)
+        up_g = _copy_params(ME.MinkowskiGenerativeConvolutionTranspose(32, 16, kernel_size=2, stride=2, dimension=3),
+                            up_o).to(dev)
+        s, rs = x + up_g(y), o + up_o(ry)
+        assert torch.equal(s.C.cpu(), rs.C) and rel_err(s.F, rs.F) < 1e-4

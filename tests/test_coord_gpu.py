@@ -1,0 +1,115 @@
+"""GPU parity (bit-exact, integer work): coordinate hash, dedup, stride / children / union / prune maps and kernel
+maps through the C ABI vs the CPU oracle on the same seeded inputs."""
+import numpy as np
+import pytest
+import torch
+
+import oracle.me_cpu as OME
+from fcaf3d_b200 import me as ME
+from fcaf3d_b200 import ops
+from util import random_coords, sort_rows, surface_coords
+
+pytestmark = pytest.mark.gpu
+
+
+def _pair(coords_np, dev, ts=1):
+    ct = torch.from_numpy(coords_np)
+    f = torch.arange(len(ct), dtype=torch.float32)[:, None].repeat(1, 2)
+    return (ME.SparseTensor(f.to(dev), coordinates=ct.to(dev), tensor_stride=ts),
+            OME.SparseTensor(f, coordinates=ct, tensor_stride=ts))
+
+
+@pytest.mark.parametrize("n,batch,seed", [(1, 1, 0), (50, 1, 1), (5000, 3, 2), (40000, 8, 3)])
+def test_insert_and_map_bit_exact(dev, n, batch, seed):
+    c = random_coords(n, batch, extent=12 if n > 100 else 3, seed=seed, dup_frac=0.3)
+    x, o = _pair(c, dev)
+    assert torch.equal(x.C.cpu(), o.C)                      # same rows, same (first-occurrence) order
+    assert torch.equal(x.unique_index.cpu(), o.unique_index)
+    assert torch.equal(x.inverse_mapping.cpu(), o.inverse_mapping)
+    assert torch.equal(x.F.cpu(), o.F)
+    # the hash table finds every row and rejects absent coordinates
+    m = x._map()
+    rows = ops.map_lookup(m.table, m.cap, x.C)
+    assert torch.equal(rows.cpu(), torch.arange(len(x), dtype=torch.int32))
+    far = x.C.clone()
+    far[:, 1] += 100000
+    assert bool((ops.map_lookup(m.table, m.cap, far) == -1).all())
+
+
+def test_ungrouped_batches_and_range_errors(dev):
+    c = random_coords(300, 3, extent=5, seed=4)
+    perm = np.random.default_rng(0).permutation(len(c))
+    x, o = _pair(c[perm], dev)
+    xs, = sort_rows(x.C)
+    os_, = sort_rows(o.C)
+    assert torch.equal(xs, os_)
+    assert torch.equal(x.C.cpu()[x.inverse_mapping.cpu()], torch.from_numpy(c[perm]))
+    bad = torch.tensor([[0, 0, 0, 0], [0, 1 << 20, 0, 0]], dtype=torch.int32, device=dev)
+    with pytest.raises(Exception, match="packed key range"):
+        ME.SparseTensor(torch.zeros(2, 1, device=dev), coordinates=bad)
+
+
+def test_empty_and_single(dev):
+    x = ME.SparseTensor(torch.zeros(1, 3, device=dev), coordinates=torch.tensor([[0, -7, 3, 2]], dtype=torch.int32,
+                                                                                 device=dev))
+    assert len(x) == 1 and x.C.tolist() == [[0, -7, 3, 2]]
+    pos, total = ops.scan_mask(torch.zeros(0, dtype=torch.uint8, device=dev))
+    assert total.item() == 0
+
+
+@pytest.mark.parametrize("n", [1, 4095, 4096, 4097, 300001])
+def test_scan_matches_cumsum(dev, n):
+    g = torch.Generator().manual_seed(n)
+    mask = (torch.rand(n, generator=g) < 0.37).to(torch.uint8).to(dev)
+    pos, total = ops.scan_mask(mask)
+    ref = torch.cumsum(mask.long(), 0) - mask.long()
+    assert torch.equal(pos.long(), ref) and total.item() == int(mask.sum())
+
+
+def test_stride_children_union_prune_bit_exact(dev):
+    c = surface_coords(3000, batch=3, seed=1)
+    x, o = _pair(c, dev)
+    cm, ocm = x.coordinate_manager, o.coordinate_manager
+    k2, ok2 = cm.stride(x.coordinate_map_key, 2), ocm.stride(o.coordinate_map_key, 2)
+    k4, ok4 = cm.stride(k2, 2), ocm.stride(ok2, 2)
+    k8, ok8 = cm.stride(k4, 2), ocm.stride(ok4, 2)
+    for k, ok in ((k2, ok2), (k4, ok4), (k8, ok8)):
+        assert torch.equal(cm.get_coordinates(k).cpu(), torch.from_numpy(ocm.get_map(ok).coords))
+        assert cm.get_map(k).off_host == ocm.get_map(ok).batch_offsets(3).tolist()
+    assert cm.stride(x.coordinate_map_key, 2) is k2                      # cached (ME A.3)
+    g, og = cm.generate_children(k8), ocm.generate_children(ok8)
+    assert torch.equal(cm.get_coordinates(g).cpu(), torch.from_numpy(ocm.get_map(og).coords))
+    assert cm.get_map(g).ts == 4
+    # union of the backbone map (stride 4) with the generated one
+    u, dst_a, dst_b = cm.union(k4, g)
+    ou, odst_a, odst_b = ocm.union(ok4, og)
+    assert torch.equal(cm.get_coordinates(u).cpu(), torch.from_numpy(ocm.get_map(ou).coords))
+    assert torch.equal(dst_a.cpu().long(), odst_a) and torch.equal(dst_b.cpu().long(), odst_b)
+    # prune with a random mask keeps order
+    mask = torch.rand(cm.size(u), generator=torch.Generator().manual_seed(3)) < 0.4
+    pk, _, _, n_keep = cm.prune(u, mask.to(dev))
+    opk = ocm.prune(ou, mask)
+    assert n_keep == int(mask.sum())
+    assert torch.equal(cm.get_coordinates(pk).cpu(), torch.from_numpy(ocm.get_map(opk).coords))
+
+
+@pytest.mark.parametrize("ksize,stride", [(3, 1), (3, 2), (2, 2), (1, 2)])
+def test_kernel_map_bit_exact(dev, ksize, stride):
+    c = surface_coords(3000, batch=2, seed=5)
+    x, o = _pair(c, dev)
+    cm, ocm = x.coordinate_manager, o.coordinate_manager
+    ik, oik = x.coordinate_map_key, o.coordinate_map_key
+    ok_, ook = (ik, oik) if stride == 1 else (cm.stride(ik, stride), ocm.stride(oik, stride))
+    km = cm.kernel_map(ik, ok_, ksize)
+    ref = ocm.neighbour_table(oik, ook, ksize)
+    n_out = cm.size(ok_)
+    assert km.nbr.shape == (ksize ** 3, (n_out + 127) // 128 * 128)
+    assert torch.equal(km.nbr[:, :n_out].cpu().long(), torch.from_numpy(ref))
+    assert bool((km.nbr[:, n_out:] == -1).all())
+    tiles = (n_out + 127) // 128
+    pad = np.full((ksize ** 3, tiles * 128), -1)
+    pad[:, :n_out] = ref
+    want = ((pad.reshape(ksize ** 3, tiles, 128) >= 0).any(2) * (1 << np.arange(ksize ** 3))[:, None]).sum(0)
+    assert km.tile_mask.cpu().numpy().astype(np.int64).tolist() == want.tolist()
+    if ksize == 3 and stride == 1:
+        assert torch.equal(km.nbr[13, :n_out].cpu(), torch.arange(n_out, dtype=torch.int32))  # centre = identity

@@ -1,0 +1,97 @@
+"""CPU: host-side logic that needs no GPU — scene generator, name-keyed weights, state-dict compatibility of the
+detector mirror with the reference's own model file loaded on our ME surface, config values, scene sharding."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ref_loader
+
+
+def test_scene_generator_is_deterministic_and_scannet_shaped():
+    from fcaf3d_b200.scenes import make_batch, make_scene
+    p, gt, lab = make_scene("S0", 0)
+    q, _, _ = make_scene("S0", 0)
+    assert p.shape == (100000, 6) and p.dtype == np.float32 and np.array_equal(p, q)
+    assert gt.shape == (15, 7) and lab.max() < 18
+    vox = np.unique(np.floor(p[:, :3] / 0.01).astype(np.int64), axis=0)
+    assert 95000 < len(vox) < 100000                       # ~1.7 % duplicate voxels at 1 cm
+    assert p[:, 3:].min() >= 0 and p[:, 3:].max() <= 255
+    batch = make_batch("tiny", 3, seed=1)
+    assert len(batch) == 3 and not np.array_equal(batch[0][0], batch[1][0])
+    s3, gt3, _ = make_scene("S3", 2)
+    assert s3.shape[0] == 100000 and np.abs(gt3[:, 6]).max() > 0
+
+
+def test_deterministic_init_is_order_independent():
+    from fcaf3d_b200.detector import build_fcaf3d
+    from fcaf3d_b200.testing import deterministic_init
+    a = deterministic_init(build_fcaf3d("s3dis", depth=14), 3)
+    torch.manual_seed(123)
+    b = deterministic_init(build_fcaf3d("s3dis", depth=14), 3)
+    for (ka, va), (kb, vb) in zip(a.state_dict().items(), b.state_dict().items()):
+        assert ka == kb and torch.equal(va, vb)
+
+
+def test_mirror_has_reference_hyperparameters():
+    from fcaf3d_b200.detector import build_fcaf3d
+    d = build_fcaf3d("scannet")
+    h = d.neck_with_head
+    assert (h.n_classes, h.n_reg_outs, h.pts_threshold, d.voxel_size) == (18, 6, 100000, 0.01)
+    assert h.test_cfg == dict(nms_pre=1000, iou_thr=.5, score_thr=.01)
+    assert abs(float(h.cls_conv.bias[0, 0]) + 4.59512) < 1e-4          # bias_init_with_prob(.01)
+    assert sum(p.numel() for p in d.parameters()) == 70479574
+    s = build_fcaf3d("sunrgbd").neck_with_head
+    assert (s.n_classes, s.n_reg_outs, s.yaw_parametrization) == (10, 8, "fcaf3d")
+
+
+@pytest.mark.skipif(not ref_loader.available(), reason="reference tree absent (GPU box)")
+def test_state_dict_and_config_match_the_reference_files():
+    """Keys / shapes of the mirror == keys / shapes of the reference's own detector (built from its own files and
+    its own config), so released checkpoints and the golden weights map one to one."""
+    from fcaf3d_b200.detector import build_fcaf3d
+    for cfg, ds in (("fcaf3d_scannet-3d-18class.py", "scannet"), ("fcaf3d_sunrgbd-3d-10class.py", "sunrgbd"),
+                    ("fcaf3d_s3dis-3d-5class.py", "s3dis")):
+        ref = ref_loader.build_reference_detector(cfg)
+        ours = build_fcaf3d(ds)
+        rs, os_ = ref.state_dict(), ours.state_dict()
+        assert list(rs.keys()) == list(os_.keys())
+        assert all(rs[k].shape == os_[k].shape for k in rs)
+        c = ref_loader.load_config(cfg)["model"]
+        assert c["neck_with_head"]["n_classes"] == ours.neck_with_head.n_classes
+        assert c["test_cfg"] == ours.neck_with_head.test_cfg and c["voxel_size"] == ours.voxel_size
+
+
+@pytest.mark.skipif(not ref_loader.available(), reason="reference tree absent (GPU box)")
+def test_reference_backbone_file_builds_on_our_me_surface(lib_built):
+    """Drop-in check that needs no GPU: the reference's me_resnet.py, imported unmodified with fcaf3d_b200.me
+    registered as `MinkowskiEngine`, constructs the same module tree (forward needs a GPU)."""
+    import importlib.util
+    import sys
+    import types
+    import fcaf3d_b200
+    saved = {k: sys.modules.get(k) for k in ("MinkowskiEngine", "MinkowskiEngine.modules",
+                                              "MinkowskiEngine.modules.resnet_block", "mmdet", "mmdet.models")}
+    try:
+        me = fcaf3d_b200.install_as_minkowski_engine()
+        reg = types.SimpleNamespace(register_module=lambda *a, **k: (lambda cls: cls))
+        sys.modules["mmdet"] = types.ModuleType("mmdet")
+        sys.modules["mmdet.models"] = types.SimpleNamespace(BACKBONES=reg, DETECTORS=reg)
+        path = os.path.join(ref_loader.REF, "mmdet3d/models/backbones/me_resnet.py")
+        spec = importlib.util.spec_from_file_location("ref_me_resnet_on_b200", path)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        net = mod.MEResNet3D(3, 34)
+        net.init_weights()
+        from fcaf3d_b200.detector import MEResNet3D
+        ours = MEResNet3D(3, 34)
+        assert list(net.state_dict().keys()) == list(ours.state_dict().keys())
+        assert isinstance(net.conv1[0], me.MinkowskiConvolution) and net.conv1[0].kernel.shape == (27, 3, 64)
+        assert net.layer1[0].downsample[0].kernel.shape == (1, 64, 64)      # K == 1 but stride 2 -> [1, in, out]
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
