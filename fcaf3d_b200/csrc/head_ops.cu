@@ -46,7 +46,8 @@ __global__ void k_interp(const B2Slot* __restrict__ table, unsigned int cap_mask
 // resolved towards the lowest row (torch.topk leaves this unspecified).
 // ---------------------------------------------------------------------------
 __device__ __forceinline__ unsigned int f32_ordered(float v) {
-  const unsigned int u = __float_as_uint(v);
+  unsigned int u = __float_as_uint(v);
+  if (u == 0x80000000u) u = 0u;  // -0.0 == +0.0 (torch.topk compares values, not bit patterns)
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
