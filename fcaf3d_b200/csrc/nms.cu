@@ -450,3 +450,102 @@ int b2_keep_list(const uint8_t* keep, const int* pos, long long n, long long* ou
 }
 
 }  // extern "C"
+
+// ===========================================================================
+// Allocation-free single-segment NMS.
+//
+// For callers that are not allowed to allocate device memory when they call us: a perception loop that
+// reserved its whole GPU budget at start-up and bans cudaMalloc afterwards (cudaMalloc can stall the device
+// and can fail late, once memory is fragmented or taken by other tenants), or a host runtime that owns the
+// GPU heap and gives this library no allocator.  b2_nms_batched needs a caller-provided mask buffer of
+// n * ceil(n/64) words; this variant keeps that scratch (and the three tiny plan arrays the kernels read)
+// in a fixed array inside the library image instead, so the caller passes only boxes in and keep/count out.
+//
+// The price: B2_NOALLOC_MAX_BOXES boxes at most, and ~0.5 MB of device memory held by every GPU that loads
+// the library, until the process exits.
+// ===========================================================================
+#define B2_NOALLOC_MAX_BOXES 2048
+#define B2_NOALLOC_HDR_WORDS 32  // 256 bytes: seg_off[2] | tile_off[2] | mask_off[2]
+#define B2_NOALLOC_WORDS (B2_NOALLOC_HDR_WORDS + B2_NOALLOC_MAX_BOXES * (B2_NOALLOC_MAX_BOXES / NMS_TILE))
+
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[B2_NOALLOC_WORDS];
+
+// plan of a one-segment problem, written on the device so that no host->device copy is needed
+__global__ void k_noalloc_plan(unsigned long long* hdr, int n) {
+  int* seg_off = reinterpret_cast<int*>(hdr);           // words 0
+  int* tile_off = reinterpret_cast<int*>(hdr + 1);      // word 1
+  long long* mask_off = reinterpret_cast<long long*>(hdr + 2);  // words 2..3
+  const int T = (n + NMS_TILE - 1) / NMS_TILE;
+  seg_off[0] = 0;
+  seg_off[1] = n;
+  tile_off[0] = 0;
+  tile_off[1] = T * (T + 1) / 2;
+  mask_off[0] = 0;
+  mask_off[1] = (long long)n * T;
+}
+
+#include <mutex>
+#define B2_MAX_DEVICES 64
+static std::mutex g_noalloc_mu;
+static unsigned long long* g_noalloc_ptr[B2_MAX_DEVICES] = {nullptr};
+
+// Device address of the scratch array on the CURRENT device.  In host code `g_noalloc_scratch` is only a
+// host-side handle of the symbol, never a device address, so it is resolved once per device through
+// cudaGetSymbolAddress (with that device current) and the resolved pointer is what the kernels receive.
+static int noalloc_scratch(unsigned long long** out) {
+  int dev = -1;
+  B2_CUDA(cudaGetDevice(&dev));
+  B2_CHECK_ARG(dev >= 0 && dev < B2_MAX_DEVICES, "device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    B2_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    g_noalloc_ptr[dev] = static_cast<unsigned long long*>(p);
+  }
+  *out = g_noalloc_ptr[dev];
+  return B2_OK;
+}
+
+extern "C" int b2_nms_single_noalloc_max_boxes(void) { return B2_NOALLOC_MAX_BOXES; }
+
+// Greedy BEV NMS of ONE list of boxes that is already sorted by descending score (the contract of the
+// reference's nms_gpu / nms_normal_gpu), with no allocation of any kind inside the call.
+//   boxes_sorted [n,7] device, keep [n] device (1 = kept), count [1] device (number kept); n <= 2048.
+// Notes for the caller:
+//  * the first call on each device resolves the scratch address (cudaGetSymbolAddress); make that first
+//    call during start-up, before any stream capture is begun on that device;
+//  * all calls on one device share the one scratch array: two calls whose kernels may overlap on the GPU
+//    (different streams, no dependency) race on it — serialise them;
+//  * the array keeps the previous call's contents; every mask word that a call reads is written earlier in
+//    that same call (upper-triangular tiles) and the plan words are rewritten each time, so nothing has to
+//    be cleared and stale data is never observed.
+extern "C" int b2_nms_single_noalloc(const float* boxes_sorted, long long n, float thresh, int rotated, uint8_t* keep,
+                                     int* count, void* stream) {
+  B2_CHECK_ARG(n >= 0, "negative box count");
+  B2_CHECK_ARG(n <= B2_NOALLOC_MAX_BOXES,
+               "b2_nms_single_noalloc handles at most %d boxes (got %lld): use b2_nms_batched with caller scratch",
+               B2_NOALLOC_MAX_BOXES, n);
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned long long* scratch = nullptr;
+  int rc = noalloc_scratch(&scratch);
+  if (rc) return rc;
+  const int* seg_off = reinterpret_cast<const int*>(scratch);
+  const int* tile_off = reinterpret_cast<const int*>(scratch + 1);
+  const long long* mask_off = reinterpret_cast<const long long*>(scratch + 2);
+  unsigned long long* mask = scratch + B2_NOALLOC_HDR_WORDS;
+  k_noalloc_plan<<<1, 1, 0, st>>>(scratch, (int)n);
+  B2_LAUNCH_CHECK();
+  const int T = (int)((n + NMS_TILE - 1) / NMS_TILE);
+  const int total_tiles = T * (T + 1) / 2;
+  if (total_tiles > 0) {
+    const int grid = total_tiles < 148 * 8 ? total_tiles : 148 * 8;
+    if (rotated)
+      k_nms_mask<true><<<grid, 256, 0, st>>>(boxes_sorted, seg_off, tile_off, mask_off, 1, total_tiles, thresh, mask);
+    else
+      k_nms_mask<false><<<grid, 256, 0, st>>>(boxes_sorted, seg_off, tile_off, mask_off, 1, total_tiles, thresh, mask);
+    B2_LAUNCH_CHECK();
+  }
+  k_nms_reduce<<<1, 128, 0, st>>>(mask, seg_off, mask_off, keep, count);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}

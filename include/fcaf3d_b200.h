@@ -147,6 +147,16 @@ int b2_nms_batched(const float* boxes, const float* scores, const int* seg_off, 
 int b2_boxes_pair_matrix(const float* a, long long na, const float* b, long long nb, int mode, float* out,
                          void* stream);
 int b2_keep_list(const uint8_t* keep, const int* pos, long long n, long long* out, void* stream);
+/* (No counterpart in the reference.)  Greedy BEV NMS of one pre-sorted box list that allocates nothing at all:
+ * for callers that may not allocate device memory at call time (a frame loop that fixed its GPU budget at start-up,
+ * a host runtime that owns the GPU heap).  The mask scratch that b2_nms_batched takes from the caller lives in a
+ * ~0.5 MB array inside the library image (held on every GPU that loads the library until exit), hence the limit
+ * n <= b2_nms_single_noalloc_max_boxes() (2048); larger n returns -1.  boxes_sorted [n,7], keep [n] (1 = kept),
+ * count [1]: device memory from the caller.  The first call on a device resolves the array's device address — make
+ * it at start-up, before any stream capture.  Calls on one device share the array: overlapping calls race. */
+int b2_nms_single_noalloc_max_boxes(void);
+int b2_nms_single_noalloc(const float* boxes_sorted, long long n, float thresh, int rotated, uint8_t* keep, int* count,
+                          void* stream);
 
 #ifdef __cplusplus
 }
