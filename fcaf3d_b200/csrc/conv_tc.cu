@@ -13,7 +13,6 @@
 
 #define TC_BM 128
 #define TC_BK 64
-#define TC_LAG 2
 #define TC_PRODUCERS 128
 #define TC_THREADS 160
 
@@ -89,11 +88,13 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
 
 template <int BN>
 struct TcCfg {
-  static constexpr int STAGES = (BN == 64) ? 4 : 3;
+  static constexpr int STAGES = (BN <= 64) ? 4 : 3;
+  static constexpr int LAG = STAGES - 1;  // cp.async groups kept in flight per producer thread
+  static constexpr int NBR_BYTES = 27 * TC_BM * 4;  // the tile's neighbour table (<= 27 offsets x 128 rows)
   static constexpr int A_BYTES = TC_BM * TC_BK * 2;
   static constexpr int B_BYTES = BN * TC_BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + NBR_BYTES;
 };
 
 template <int BN, typename TOut>
@@ -110,6 +111,8 @@ k_conv_tc(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict_
   uint64_t* empty_bar = full_bar + S;
   uint64_t* accum_bar = empty_bar + S;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
+  int* s_nbr = reinterpret_cast<int*>(smem + S * Cfg::STAGE_BYTES + 256);
+  constexpr int LAG = Cfg::LAG;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int row0 = blockIdx.x * TC_BM, col0 = blockIdx.y * BN;
@@ -131,6 +134,16 @@ k_conv_tc(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict_
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
+  // stage the tile's neighbour rows in shared memory once (coalesced, all loads independent), so that the
+  // producers' gather addresses never wait on a global load inside the pipeline
+  if (nbr != nullptr) {
+    for (int i = tid; i < kvol * TC_BM; i += TC_THREADS) {
+      const int k = i >> 7, r = i & (TC_BM - 1);
+      s_nbr[i] = ((kmask >> k) & 1u) ? __ldg(nbr + (long long)k * ld + row0 + r) : -1;
+    }
+  } else {
+    for (int r = tid; r < TC_BM; r += TC_THREADS) s_nbr[r] = (row0 + r < n_out) ? row0 + r : -1;
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -144,14 +157,7 @@ k_conv_tc(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict_
       if (!((kmask >> k) & 1u)) continue;
       int idx[TC_BM / 16];
 #pragma unroll
-      for (int p = 0; p < TC_BM / 16; ++p) {
-        const int r = p * 16 + rsub;
-        if (nbr != nullptr) {
-          idx[p] = __ldg(nbr + (long long)k * ld + row0 + r);
-        } else {
-          idx[p] = (row0 + r < n_out) ? row0 + r : -1;
-        }
-      }
+      for (int p = 0; p < TC_BM / 16; ++p) idx[p] = s_nbr[k * TC_BM + p * 16 + rsub];
       for (int c = 0; c < chunks; ++c, ++it) {
         const int s = it % S;
         const uint32_t ph = (uint32_t)(it / S) & 1u;
@@ -173,20 +179,20 @@ k_conv_tc(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict_
           cp_async16(b_base + r * 128 + ((chunk16 ^ (r & 7)) << 4), wk + (long long)r * cin, 16u);
         }
         cp_async_commit();
-        if (it >= TC_LAG) {
-          cp_async_wait<TC_LAG>();
+        if (it >= LAG) {
+          cp_async_wait<LAG>();
           fence_async_smem();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&full_bar[(it - TC_LAG) % S]);
+          if (lane == 0) mbar_arrive(&full_bar[(it - LAG) % S]);
         }
       }
     }
-    // drain the last TC_LAG groups
+    // drain the last LAG groups
     cp_async_wait<0>();
     fence_async_smem();
     __syncwarp();
     if (lane == 0) {
-      for (int j = (it > TC_LAG ? it - TC_LAG : 0); j < it; ++j) mbar_arrive(&full_bar[j % S]);
+      for (int j = (it > LAG ? it - LAG : 0); j < it; ++j) mbar_arrive(&full_bar[j % S]);
     }
 
     // ===================== epilogue: TMEM -> registers -> global ===========================
@@ -319,22 +325,25 @@ extern "C" int b2_conv_tc(const void* in_bf16, const void* wt_bf16, const int* n
                           const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
                           int out_dtype, void* stream) {
   B2_CHECK_ARG(cin % TC_BK == 0 && cin > 0, "b2_conv_tc needs cin %% 64 == 0 (got %d)", cin);
-  B2_CHECK_ARG(cout % 64 == 0 && cout > 0, "b2_conv_tc needs cout %% 64 == 0 (got %d)", cout);
+  B2_CHECK_ARG(cout % 32 == 0 && cout > 0, "b2_conv_tc needs cout %% 32 == 0 (got %d)", cout);
   B2_CHECK_ARG(nbr != nullptr || kvol == 1, "identity map requires kernel volume 1");
-  B2_CHECK_ARG(nbr == nullptr || (tile_mask != nullptr && kvol <= 32 && ld % TC_BM == 0),
-               "neighbour table needs a tile mask, kvol <= 32 and ld %% 128 == 0");
+  B2_CHECK_ARG(nbr == nullptr || (tile_mask != nullptr && kvol <= 27 && ld % TC_BM == 0),
+               "neighbour table needs a tile mask, kvol <= 27 and ld %% 128 == 0");
   B2_CHECK_ARG((scale == nullptr) == (shift == nullptr), "scale and shift come together");
   if (n_out == 0) return B2_OK;
   cudaStream_t st = (cudaStream_t)stream;
   const bool wide = (cout % 128 == 0);
+  const bool mid = (cout % 64 == 0);
 #define TC_GO(BN, T) \
   return launch_tc<BN, T>(in_bf16, wt_bf16, nbr, ld, tile_mask, n_out, cin, cout, kvol, bias, scale, shift, residual, act, ch_mod, out, st)
   if (out_dtype == 1) {
     if (wide) TC_GO(128, __nv_bfloat16);
-    TC_GO(64, __nv_bfloat16);
+    if (mid) TC_GO(64, __nv_bfloat16);
+    TC_GO(32, __nv_bfloat16);
   } else {
     if (wide) TC_GO(128, float);
-    TC_GO(64, float);
+    if (mid) TC_GO(64, float);
+    TC_GO(32, float);
   }
 #undef TC_GO
 }

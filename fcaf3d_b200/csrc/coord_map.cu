@@ -382,6 +382,31 @@ __global__ void k_scatter_rows_bf16(const __nv_bfloat16* __restrict__ in, const 
   out[o] = accumulate ? __float2bfloat16(__bfloat162float(out[o]) + __bfloat162float(in[t])) : in[t];
 }
 
+// 16-byte vectorised variant (8 bf16 per thread): one row = c/8 vectors
+__global__ void k_scatter_rows_bf16x8(const uint4* __restrict__ in, const int* __restrict__ dst, long long n, int vpr,
+                                      uint4* __restrict__ out, int accumulate) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n * vpr) return;
+  const long long i = t / vpr;
+  const int v = (int)(t - i * vpr);
+  const long long o = (long long)dst[i] * vpr + v;
+  uint4 a = __ldg(in + t);
+  if (accumulate) {
+    const uint4 b = out[o];
+    const unsigned aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
+    unsigned r[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float lo = __uint_as_float(aw[e] << 16) + __uint_as_float(bw[e] << 16);
+      const float hi = __uint_as_float(aw[e] & 0xFFFF0000u) + __uint_as_float(bw[e] & 0xFFFF0000u);
+      const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+      r[e] = *reinterpret_cast<const unsigned*>(&h);
+    }
+    a = make_uint4(r[0], r[1], r[2], r[3]);
+  }
+  out[o] = a;
+}
+
 // ---------------------------------------------------------------------------
 // extern "C" entry points
 // ---------------------------------------------------------------------------
@@ -573,6 +598,9 @@ int b2_scatter_rows(const void* in, const int* dst, long long n, int c, int dtyp
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == 0)
     k_scatter_rows_f32<<<b2_div_up(n * c, 256), 256, 0, st>>>((const float*)in, dst, n, c, (float*)out, accumulate);
+  else if (c % 8 == 0)
+    k_scatter_rows_bf16x8<<<b2_div_up(n * (c / 8), 256), 256, 0, st>>>((const uint4*)in, dst, n, c / 8, (uint4*)out,
+                                                                       accumulate);
   else
     k_scatter_rows_bf16<<<b2_div_up(n * c, 256), 256, 0, st>>>((const __nv_bfloat16*)in, dst, n, c, (__nv_bfloat16*)out,
                                                               accumulate);

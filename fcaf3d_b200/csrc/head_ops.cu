@@ -126,14 +126,13 @@ __global__ void __launch_bounds__(1024) k_topk_mask(const float* __restrict__ sc
 // Head post-processing on the fused head output feat[n, 1 + n_reg + n_cls]
 // (centerness | regression | class logits).  forward_single :257-269.
 // ---------------------------------------------------------------------------
-__global__ void k_head_post(const float* __restrict__ feat, int n, int n_reg, int n_cls,
+__global__ void k_head_post(const float* __restrict__ feat, int n, int feat_ld, int n_reg, int n_cls,
                             const float* __restrict__ scale_ptr,
                             float* __restrict__ centerness, float* __restrict__ bbox_pred, float* __restrict__ cls,
                             float* __restrict__ prune_score, float* __restrict__ max_score) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  const int c = 1 + n_reg + n_cls;
-  const float* f = feat + (long long)i * c;
+  const float* f = feat + (long long)i * feat_ld;
   const float ctr = f[0];
   const float scale = scale_ptr ? __ldg(scale_ptr) : 1.f;
   centerness[i] = ctr;
@@ -319,10 +318,12 @@ int b2_topk_mask(const float* scores, const int* seg_off, int nseg, int k, uint8
   return B2_OK;
 }
 
-int b2_head_post(const float* feat, long long n, int n_reg, int n_cls, const float* scale, float* centerness,
+int b2_head_post(const float* feat, long long n, int feat_ld, int n_reg, int n_cls, const float* scale,
+                 float* centerness,
                  float* bbox_pred, float* cls, float* prune_score, float* max_score, void* stream) {
   if (n == 0) return B2_OK;
-  k_head_post<<<b2_div_up(n, 256), 256, 0, (cudaStream_t)stream>>>(feat, (int)n, n_reg, n_cls, scale, centerness,
+  B2_CHECK_ARG(feat_ld >= 1 + n_reg + n_cls, "feat_ld smaller than 1 + n_reg + n_cls");
+  k_head_post<<<b2_div_up(n, 256), 256, 0, (cudaStream_t)stream>>>(feat, (int)n, feat_ld, n_reg, n_cls, scale, centerness,
                                                                  bbox_pred, cls, prune_score, max_score);
   B2_LAUNCH_CHECK();
   return B2_OK;

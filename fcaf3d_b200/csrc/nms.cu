@@ -230,8 +230,12 @@ __global__ void __launch_bounds__(256) k_nms_mask(const float* __restrict__ boxe
                                                   unsigned long long* __restrict__ mask) {
   __shared__ BoxPrep s_col[NMS_TILE];
   __shared__ BoxPrep s_row[NMS_TILE];
-  __shared__ float s_colraw[NMS_TILE * 7];
-  __shared__ float s_rowraw[NMS_TILE * 7];
+  // axis-aligned flavour: per-box edges (x1, x2, y1, y2) are hoisted out of the pair loop; they are the very
+  // expressions of iou_aligned (a[0] -+ a[3] / 2 ...), so every pair sees bit-identical operands
+  __shared__ float4 s_coledge[NMS_TILE];
+  __shared__ float2 s_colsize[NMS_TILE];
+  __shared__ float4 s_rowedge[NMS_TILE];
+  __shared__ float2 s_rowsize[NMS_TILE];
   __shared__ unsigned long long s_bits[NMS_TILE];
   for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
     // locate the segment (binary search) and the (row, col) tile inside its upper triangle
@@ -258,17 +262,23 @@ __global__ void __launch_bounds__(256) k_nms_mask(const float* __restrict__ boxe
       s_bits[t] = 0ull;
       if (t < col_n) {
         const float* b = boxes + (long long)(beg + tc * NMS_TILE + t) * 7;
-#pragma unroll
-        for (int u = 0; u < 7; ++u) s_colraw[t * 7 + u] = b[u];
-        if (ROTATED) prep_box(b, s_col[t]);
+        if (ROTATED) {
+          prep_box(b, s_col[t]);
+        } else {
+          s_coledge[t] = make_float4(b[0] - b[3] / 2, b[0] + b[3] / 2, b[1] - b[4] / 2, b[1] + b[4] / 2);
+          s_colsize[t] = make_float2(b[3], b[4]);
+        }
       }
     } else if (t < 2 * NMS_TILE) {
       const int r = t - NMS_TILE;
       if (r < row_n) {
         const float* b = boxes + (long long)(beg + tr * NMS_TILE + r) * 7;
-#pragma unroll
-        for (int u = 0; u < 7; ++u) s_rowraw[r * 7 + u] = b[u];
-        if (ROTATED) prep_box(b, s_row[r]);
+        if (ROTATED) {
+          prep_box(b, s_row[r]);
+        } else {
+          s_rowedge[r] = make_float4(b[0] - b[3] / 2, b[0] + b[3] / 2, b[1] - b[4] / 2, b[1] + b[4] / 2);
+          s_rowsize[r] = make_float2(b[3], b[4]);
+        }
       }
     }
     __syncthreads();
@@ -277,6 +287,12 @@ __global__ void __launch_bounds__(256) k_nms_mask(const float* __restrict__ boxe
       unsigned long long bits = 0ull;
       int c0 = quarter * 16, c1 = min(c0 + 16, col_n);
       if (tr == tc) c0 = max(c0, r + 1);
+      float4 ae = make_float4(0.f, 0.f, 0.f, 0.f);
+      float2 as = make_float2(0.f, 0.f);
+      if (!ROTATED) {
+        ae = s_rowedge[r];
+        as = s_rowsize[r];
+      }
       for (int c = c0; c < c1; ++c) {
         float iou;
         if (ROTATED) {
@@ -288,7 +304,17 @@ __global__ void __launch_bounds__(256) k_nms_mask(const float* __restrict__ boxe
           if (thresh >= 0.f && ddx * ddx + ddy * ddy > reach * reach) continue;
           iou = iou_rotated(A, B);
         } else {
-          iou = iou_aligned(s_rowraw + r * 7, s_colraw + c * 7);
+          const float4 be = s_coledge[c];
+          const float2 bs = s_colsize[c];
+          const float left = fmaxf(ae.x, be.x), right = fminf(ae.y, be.y);
+          const float top = fmaxf(ae.z, be.z), bottom = fminf(ae.w, be.w);
+          const float width = fmaxf(right - left, 0.f), height = fmaxf(bottom - top, 0.f);
+          // disjoint footprints: IoU is 0 (or NaN for degenerate boxes), never above a threshold >= 0
+          if (thresh >= 0.f && !(width > 0.f && height > 0.f)) continue;
+          const float inter = width * height;
+          const float Sa = as.x * as.y;
+          const float Sb = bs.x * bs.y;
+          iou = inter / fmaxf(Sa + Sb - inter, NMS_EPS);
         }
         if (iou > thresh) bits |= 1ull << c;
       }

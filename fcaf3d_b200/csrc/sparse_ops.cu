@@ -161,6 +161,89 @@ __global__ void __launch_bounds__(256) k_conv_cc(const TIn* __restrict__ in, con
   }
 }
 
+// Cin <= 8 (the stem: Cin = 3, K = 27): flatten (offset, channel) into one inner dimension of K*Cin so that the
+// 16-wide inner tiles are full (81 -> 6 tiles instead of 27 tiles with 3 of 16 lanes used).
+template <typename TIn, typename TOut>
+__global__ void __launch_bounds__(256) k_conv_flat(const TIn* __restrict__ in, const float* __restrict__ w,
+                                                   const int* __restrict__ nbr, int ld, int n_out, int cin, int cout,
+                                                   int kvol, const float* __restrict__ bias,
+                                                   const float* __restrict__ scale, const float* __restrict__ shift,
+                                                   const TOut* __restrict__ residual, int act, int ch_mod,
+                                                   TOut* __restrict__ out) {
+  __shared__ __align__(16) float As[CV_TK][CV_TM + 4];
+  __shared__ __align__(16) float Bs[CV_TK][CV_TN + 4];
+  __shared__ int s_nbr[27 * CV_TM];
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int row0 = blockIdx.x * CV_TM, col0 = blockIdx.y * CV_TN;
+  for (int i = tid; i < kvol * CV_TM; i += 256) {
+    const int k = i / CV_TM, r = i - k * CV_TM;
+    s_nbr[i] = (row0 + r < n_out) ? nbr[(long long)k * ld + row0 + r] : -1;
+  }
+  float acc[8][4];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  const int J = kvol * cin;
+  __syncthreads();
+  for (int j0 = 0; j0 < J; j0 += CV_TK) {
+    {
+      const int r = tid >> 1, cb = (tid & 1) * 8;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int j = j0 + cb + u;
+        float v = 0.f;
+        if (j < J) {
+          const int k = j / cin, c = j - k * cin;
+          const int src = s_nbr[k * CV_TM + r];
+          if (src >= 0) v = to_f32<TIn>(in[(long long)src * cin + c]);
+        }
+        As[cb + u][r] = v;
+      }
+    }
+    {
+      const int kk = tid >> 4, nb = (tid & 15) * 4;
+      const int j = j0 + kk;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int n = col0 + nb + u;
+        Bs[kk][nb + u] = (j < J && n < cout) ? __ldg(w + (long long)j * cout + n) : 0.f;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < CV_TK; ++kk) {
+      const float4 a0 = *reinterpret_cast<const float4*>(&As[kk][ty * 8]);
+      const float4 a1 = *reinterpret_cast<const float4*>(&As[kk][ty * 8 + 4]);
+      const float4 b = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
+      const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+      const float bb[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], bb[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int o = row0 + ty * 8 + i;
+    if (o >= n_out) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = col0 + tx * 4 + j;
+      if (n >= cout) continue;
+      const int ch = ch_mod > 0 ? (n % ch_mod) : n;
+      float v = acc[i][j];
+      if (bias) v += bias[ch];
+      if (scale) v = v * scale[ch] + shift[ch];
+      if (residual) v += to_f32<TOut>(residual[(long long)o * cout + n]);
+      out[(long long)o * cout + n] = from_f32<TOut>(b2_apply_act(v, act));
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------
 // Max pooling over a neighbour table (2^3, stride 2): out[o, c] = max_k in[nbr[k][o], c]
 // ---------------------------------------------------------------------------
@@ -184,6 +267,77 @@ __global__ void k_maxpool(const T* __restrict__ in, const int* __restrict__ nbr,
   }
   out[t] = from_f32<T>(besti >= 0 ? best : 0.f);
   if (arg) arg[t] = besti;
+}
+
+// 8 bf16 channels per thread (16-byte loads); same max / first-wins rule as k_maxpool
+__global__ void k_maxpool_bf16x8(const uint4* __restrict__ in, const int* __restrict__ nbr, int ld, int kvol, int n_out,
+                                 int vpr, uint4* __restrict__ out) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long long)n_out * vpr) return;
+  const int o = (int)(t / vpr), v = (int)(t - (long long)o * vpr);
+  float best[8];
+  bool any = false;
+  for (int k = 0; k < kvol; ++k) {
+    const int r = nbr[(long long)k * ld + o];
+    if (r < 0) continue;
+    const uint4 u = __ldg(in + (long long)r * vpr + v);
+    const unsigned w4[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float lo = __uint_as_float(w4[e] << 16), hi = __uint_as_float(w4[e] & 0xFFFF0000u);
+      best[2 * e] = (!any || lo > best[2 * e]) ? lo : best[2 * e];
+      best[2 * e + 1] = (!any || hi > best[2 * e + 1]) ? hi : best[2 * e + 1];
+    }
+    any = true;
+  }
+  unsigned r4[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(any ? best[2 * e] : 0.f, any ? best[2 * e + 1] : 0.f);
+    r4[e] = *reinterpret_cast<const unsigned*>(&h);
+  }
+  out[t] = make_uint4(r4[0], r4[1], r4[2], r4[3]);
+}
+
+__global__ void k_affine_act_bf16x8(const uint4* __restrict__ x, const int* __restrict__ coords, long long n, int c,
+                                    const float* __restrict__ scale, const float* __restrict__ shift,
+                                    const uint4* __restrict__ residual, int act, uint4* __restrict__ y) {
+  const int vpr = c / 8;
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n * vpr) return;
+  const long long r = t / vpr;
+  const int ch0 = (int)(t - r * vpr) * 8;
+  const int s = coords ? coords[4 * r] : 0;
+  const uint4 u = x[t];
+  const unsigned w4[4] = {u.x, u.y, u.z, u.w};
+  float f[8];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    f[2 * e] = __uint_as_float(w4[e] << 16);
+    f[2 * e + 1] = __uint_as_float(w4[e] & 0xFFFF0000u);
+  }
+  if (scale) {
+    const float* sc = scale + (long long)s * c + ch0;
+    const float* sh = shift + (long long)s * c + ch0;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) f[e] = f[e] * __ldg(sc + e) + __ldg(sh + e);
+  }
+  if (residual) {
+    const uint4 q = residual[t];
+    const unsigned q4[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      f[2 * e] += __uint_as_float(q4[e] << 16);
+      f[2 * e + 1] += __uint_as_float(q4[e] & 0xFFFF0000u);
+    }
+  }
+  unsigned r4[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(b2_apply_act(f[2 * e], act), b2_apply_act(f[2 * e + 1], act));
+    r4[e] = *reinterpret_cast<const unsigned*>(&h);
+  }
+  y[t] = make_uint4(r4[0], r4[1], r4[2], r4[3]);
 }
 
 // ---------------------------------------------------------------------------
@@ -309,9 +463,16 @@ int b2_conv_cc(const void* in, int in_dtype, const float* w, const int* nbr, lon
   if (n_out == 0) return B2_OK;
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid(b2_div_up(n_out, CV_TM), b2_div_up(cout, CV_TN));
-#define CC_LAUNCH(TI, TO)                                                                                        \
-  k_conv_cc<TI, TO><<<grid, 256, 0, st>>>((const TI*)in, w, nbr, (int)ld, tile_mask, (int)n_out, cin, cout, kvol, bias, \
-                                          scale, shift, (const TO*)residual, act, ch_mod, (TO*)out)
+  const bool flat = (nbr != nullptr && cin <= 8 && kvol <= 27);
+#define CC_LAUNCH(TI, TO)                                                                                          \
+  do {                                                                                                             \
+    if (flat)                                                                                                      \
+      k_conv_flat<TI, TO><<<grid, 256, 0, st>>>((const TI*)in, w, nbr, (int)ld, (int)n_out, cin, cout, kvol, bias,  \
+                                                scale, shift, (const TO*)residual, act, ch_mod, (TO*)out);         \
+    else                                                                                                           \
+      k_conv_cc<TI, TO><<<grid, 256, 0, st>>>((const TI*)in, w, nbr, (int)ld, tile_mask, (int)n_out, cin, cout,     \
+                                              kvol, bias, scale, shift, (const TO*)residual, act, ch_mod, (TO*)out); \
+  } while (0)
   if (in_dtype == 0 && out_dtype == 0) CC_LAUNCH(float, float);
   else if (in_dtype == 0 && out_dtype == 1) CC_LAUNCH(float, __nv_bfloat16);
   else if (in_dtype == 1 && out_dtype == 0) CC_LAUNCH(__nv_bfloat16, float);
@@ -328,6 +489,9 @@ int b2_maxpool(const void* in, int dtype, const int* nbr, long long ld, int kvol
   const int G = b2_div_up(n_out * c, 256);
   if (dtype == 0)
     k_maxpool<float><<<G, 256, 0, st>>>((const float*)in, nbr, (int)ld, kvol, (int)n_out, c, (float*)out, argmax);
+  else if (c % 8 == 0 && argmax == nullptr)
+    k_maxpool_bf16x8<<<b2_div_up(n_out * (c / 8), 256), 256, 0, st>>>((const uint4*)in, nbr, (int)ld, kvol, (int)n_out,
+                                                                    c / 8, (uint4*)out);
   else
     k_maxpool<__nv_bfloat16><<<G, 256, 0, st>>>((const __nv_bfloat16*)in, nbr, (int)ld, kvol, (int)n_out, c,
                                                 (__nv_bfloat16*)out, argmax);
@@ -373,6 +537,9 @@ int b2_affine_act(const void* x, int dtype, const int* coords, long long n, int 
   if (dtype == 0)
     k_affine_act<float><<<G, 256, 0, st>>>((const float*)x, coords, n, c, scale, shift, (const float*)residual, act,
                                            (float*)y);
+  else if (c % 8 == 0)
+    k_affine_act_bf16x8<<<b2_div_up(n * (c / 8), 256), 256, 0, st>>>((const uint4*)x, coords, n, c, scale, shift,
+                                                                   (const uint4*)residual, act, (uint4*)y);
   else
     k_affine_act<__nv_bfloat16><<<G, 256, 0, st>>>((const __nv_bfloat16*)x, coords, n, c, scale, shift,
                                                    (const __nv_bfloat16*)residual, act, (__nv_bfloat16*)y);

@@ -310,9 +310,12 @@ class Fcaf3DNeckWithHead(nn.Module):
         ks = (self.centerness_conv.kernel, self.reg_conv.kernel, self.cls_conv.kernel, self.cls_conv.bias)
         ver = tuple((k._version, k.data_ptr()) for k in ks)
         if getattr(self, "_hw_ver", None) != ver:
-            w = torch.cat([k.detach() for k in ks[:3]], dim=1).unsqueeze(0).contiguous()
-            b = torch.cat([w.new_zeros(1 + self.n_reg_outs), self.cls_conv.bias.detach().reshape(-1)]).contiguous()
-            self._hw, self._hw_ver = (w, b), ver
+            w = torch.cat([k.detach() for k in ks[:3]], dim=1)
+            b = torch.cat([w.new_zeros(1 + self.n_reg_outs), self.cls_conv.bias.detach().reshape(-1)])
+            pad = (-w.shape[1]) % 32                      # columns padded to a multiple of 32 for the tcgen05 path
+            w = torch.nn.functional.pad(w, (0, pad)).unsqueeze(0).contiguous()
+            b = torch.nn.functional.pad(b, (0, pad)).contiguous()
+            self._hw, self._hw_ver = (w, b, w.transpose(1, 2).contiguous().to(torch.bfloat16)), ver
         return self._hw
 
     def forward_fused(self, inputs, want_max_score=False):
@@ -355,8 +358,8 @@ class Fcaf3DNeckWithHead(nn.Module):
             conv, bn, _ = getattr(self, f"out_block_{i}")
             km = cm.kernel_map(key, key, conv.kernel_size, conv.dilation)
             o = conv_bn_act(conv, bn, f, km, cm.size(key), ops.ACT_ELU)
-            w, b = self._head_weights()
-            h = ops.sparse_conv(o, w, None, o.shape[0], bias=b, out_dtype=torch.float32)
+            w, b, wt = self._head_weights()
+            h = ops.sparse_conv(o, w, None, o.shape[0], wt_bf16=wt, bias=b, out_dtype=torch.float32)
             ctr, bbox, cls, prune, mx = ops.head_post(h, self.n_reg_outs, self.n_classes,
                                                       self.scales[i].scale.detach().reshape(1), want_max_score)
             prev = dict(key=key, centerness=ctr, bbox_pred=bbox, cls=cls, prune=prune, max_score=mx)

@@ -550,13 +550,21 @@ class MinkowskiBatchNorm(MinkowskiModuleBase):
                     bn.running_mean.mul_(1 - mom).add_(mean[0], alpha=mom)
                     bn.running_var.mul_(1 - mom).add_(unbiased, alpha=mom)
         else:
+            # eval: the folded (scale, shift) only changes when a parameter / buffer does -> cache it
+            ts = [t for t in (bn.weight, bn.bias, bn.running_mean, bn.running_var) if t is not None]
+            ver = tuple((t._version, t.data_ptr()) for t in ts)
+            if getattr(self, "_fold_ver", None) == ver:
+                return self._fold
             mean, var = bn.running_mean.unsqueeze(0), bn.running_var.unsqueeze(0)
         inv = torch.rsqrt(var + bn.eps)
         w = bn.weight.detach().unsqueeze(0) if bn.affine else torch.ones_like(inv)
         b = bn.bias.detach().unsqueeze(0) if bn.affine else torch.zeros_like(inv)
         scale = w * inv
         shift = b - mean * scale
-        return scale.float().contiguous(), shift.float().contiguous()
+        out = (scale.float().contiguous(), shift.float().contiguous())
+        if not (bn.training or not bn.track_running_stats):
+            self._fold, self._fold_ver = out, ver
+        return out
 
     def forward(self, x, act=ops.ACT_NONE, residual=None):
         f = x.F.contiguous()

@@ -224,7 +224,7 @@ def set_tensor_cores(flag):
 
 
 def tc_eligible(x, cin, cout):
-    return _TC_ENABLED and x.dtype == torch.bfloat16 and cin % 64 == 0 and cout % 64 == 0
+    return _TC_ENABLED and x.dtype == torch.bfloat16 and cin % 64 == 0 and cout % 32 == 0
 
 
 def sparse_conv(x, w, kmap, n_out, wt_bf16=None, bias=None, scale=None, shift=None, residual=None, act=ACT_NONE,
@@ -309,6 +309,7 @@ def topk_mask(scores, seg_off, nseg, k):
 
 
 def head_post(feat, n_reg, n_cls, scale, want_max_score=False):
+    """feat [n, >= 1+n_reg+n_cls] fp32 (extra padding columns are ignored)."""
     n = int(feat.shape[0])
     dev = feat.device
     f32 = torch.float32
@@ -317,7 +318,7 @@ def head_post(feat, n_reg, n_cls, scale, want_max_score=False):
     cls = torch.empty((n, n_cls), dtype=f32, device=dev)
     prune = torch.empty((n, 1), dtype=f32, device=dev)
     mx = torch.empty((n,), dtype=f32, device=dev) if want_max_score else None
-    call("b2_head_post", ptr(feat), n, n_reg, n_cls, ptr(scale), ptr(centerness), ptr(bbox_pred), ptr(cls), ptr(prune),
+    call("b2_head_post", ptr(feat), n, int(feat.shape[1]), n_reg, n_cls, ptr(scale), ptr(centerness), ptr(bbox_pred), ptr(cls), ptr(prune),
          ptr(mx))
     return centerness, bbox_pred, cls, prune, mx
 

@@ -88,7 +88,7 @@ int b2_conv_cc(const void* in, int in_dtype, const float* w, const int* nbr, lon
                const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
                int out_dtype, void* stream);
 /* tcgen05 implicit GEMM, bf16 operands / fp32 TMEM accumulators; wt: [kvol, cout, cin] bf16 (K-major).
- * cin % 64 == 0, cout % 64 == 0.  Same epilogue as b2_conv_cc; out_dtype 0 or 1. */
+ * cin % 64 == 0, cout % 32 == 0.  Same epilogue as b2_conv_cc; out_dtype 0 or 1. */
 int b2_conv_tc(const void* in_bf16, const void* wt_bf16, const int* nbr, long long ld, const unsigned int* tile_mask,
                long long n_out, int cin, int cout, int kvol, const float* bias, const float* scale, const float* shift,
                const void* residual, int act, int ch_mod, void* out, int out_dtype, void* stream);
@@ -113,11 +113,11 @@ int b2_interp(const void* table, long long cap, const float* feats, int c, int t
               long long m, float* out, void* stream);
 /* mask[i] = 1 for the k largest scores of each segment (ties at the k-th value: lowest rows first) */
 int b2_topk_mask(const float* scores, const int* seg_off, int nseg, int k, uint8_t* mask, void* stream);
-/* feat [n, 1+n_reg+n_cls] -> centerness[n], bbox_pred[n,n_reg] (first 6: exp(*scale * x), scale = the level's
+/* feat [n, feat_ld] (first 1+n_reg+n_cls columns used) -> centerness[n], bbox_pred[n,n_reg] (first 6: exp(*scale * x), scale = the level's
  * learnable Scale on the device), cls[n,n_cls], prune_score[n] = max class logit,
  * max_score[n] = max_c sigmoid(cls_c)*sigmoid(centerness) (optional) */
-int b2_head_post(const float* feat, long long n, int n_reg, int n_cls, const float* scale, float* centerness,
-                 float* bbox_pred, float* cls, float* prune_score, float* max_score, void* stream);
+int b2_head_post(const float* feat, long long n, int feat_ld, int n_reg, int n_cls, const float* scale,
+                 float* centerness, float* bbox_pred, float* cls, float* prune_score, float* max_score, void* stream);
 /* yaw_mode: 0 axis-aligned, 1 naive, 2 sin-cos, 3 fcaf3d (Mobius); out [n,7] */
 int b2_decode_boxes(const float* points, const float* bbox_pred, long long n, int n_reg, int yaw_mode, float* out,
                     void* stream);
