@@ -13,8 +13,8 @@
 
 #define TC_BM 128
 #define TC_BK 64
-#define TC_PRODUCERS 128
-#define TC_THREADS 160
+#define TC_PRODUCERS 256
+#define TC_THREADS 288
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -39,6 +39,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+// the mbarrier receives one arrival from this thread once all of its earlier cp.async copies have landed
+__device__ __forceinline__ void cp_async_arrive_noinc(uint64_t* bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
@@ -86,113 +90,120 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
-template <int BN>
+template <int BN, int ST>
 struct TcCfg {
-  static constexpr int STAGES = (BN <= 64) ? 4 : 3;
-  static constexpr int LAG = STAGES - 1;  // cp.async groups kept in flight per producer thread
-  static constexpr int NBR_BYTES = 27 * TC_BM * 4;  // the tile's neighbour table (<= 27 offsets x 128 rows)
+  static constexpr int STAGES = ST;
   static constexpr int A_BYTES = TC_BM * TC_BK * 2;
   static constexpr int B_BYTES = BN * TC_BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + NBR_BYTES;
+  static constexpr int NBR_BYTES = 27 * TC_BM * 4;  // the tile's neighbour table (<= 27 offsets x 128 rows)
+  static constexpr int EPI_BYTES = 3 * BN * 4;      // bias | scale | shift of the tile's columns
+  static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + NBR_BYTES + EPI_BYTES;
 };
 
-template <int BN, typename TOut>
+// Warp roles: warps 0..7 = producers (cp.async gathers), then epilogue; warp 8 = TMEM owner + MMA issuer.
+// Producer thread t: 16-byte chunk (t & 7) of rows (t >> 3) + 32 p; everything that does not depend on the stage is
+// hoisted (the producers are instruction-latency bound: a stage must cost them as few dependent instructions as possible).
+template <int BN, int ST, typename TOut>
 __global__ void __launch_bounds__(TC_THREADS)
 k_conv_tc(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict__ wt, const int* __restrict__ nbr, int ld,
           const unsigned int* __restrict__ tile_mask, int n_out, int cin, int cout, int kvol,
           const float* __restrict__ bias, const float* __restrict__ scale, const float* __restrict__ shift,
           const TOut* __restrict__ residual, int act, int ch_mod, TOut* __restrict__ out) {
-  using Cfg = TcCfg<BN>;
+  using Cfg = TcCfg<BN, ST>;
   constexpr int S = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // stays a shared-space pointer
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S * Cfg::STAGE_BYTES);
   uint64_t* empty_bar = full_bar + S;
   uint64_t* accum_bar = empty_bar + S;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
   int* s_nbr = reinterpret_cast<int*>(smem + S * Cfg::STAGE_BYTES + 256);
-  constexpr int LAG = Cfg::LAG;
+  float* s_epi = reinterpret_cast<float*>(smem + S * Cfg::STAGE_BYTES + 256 + Cfg::NBR_BYTES);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int row0 = blockIdx.x * TC_BM, col0 = blockIdx.y * BN;
   const unsigned int kmask = (nbr != nullptr) ? tile_mask[blockIdx.x] : 1u;
   const int chunks = cin / TC_BK;
-  const int nstage = __popc(kmask & (kvol >= 32 ? 0xFFFFFFFFu : ((1u << kvol) - 1u))) * chunks;
+  const int nstage = __popc(kmask & ((1u << kvol) - 1u)) * chunks;
 
   if (tid == 0) {
     for (int s = 0; s < S; ++s) {
-      mbar_init(&full_bar[s], TC_PRODUCERS / 32);
+      mbar_init(&full_bar[s], TC_PRODUCERS);
       mbar_init(&empty_bar[s], 1);
     }
     mbar_init(accum_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 4) {
+  if (warp == TC_PRODUCERS / 32) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                 "r"((uint32_t)(BN < 32 ? 32 : BN))
+                 "r"((uint32_t)BN)
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  // stage the tile's neighbour rows in shared memory once (coalesced, all loads independent), so that the
-  // producers' gather addresses never wait on a global load inside the pipeline
+  // stage the tile's neighbour rows in shared memory once (coalesced, independent loads in flight)
   if (nbr != nullptr) {
-    for (int i = tid; i < kvol * TC_BM; i += TC_THREADS) {
-      const int k = i >> 7, r = i & (TC_BM - 1);
-      s_nbr[i] = ((kmask >> k) & 1u) ? __ldg(nbr + (long long)k * ld + row0 + r) : -1;
+    const int total = kvol * TC_BM;
+    for (int i0 = tid; i0 < total; i0 += TC_THREADS * 4) {
+      int v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * TC_THREADS;
+        const int k = i >> 7, r = i & (TC_BM - 1);
+        v[u] = (i < total && ((kmask >> k) & 1u)) ? __ldg(nbr + (long long)k * ld + row0 + r) : -1;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (i0 + u * TC_THREADS < total) s_nbr[i0 + u * TC_THREADS] = v[u];
     }
   } else {
     for (int r = tid; r < TC_BM; r += TC_THREADS) s_nbr[r] = (row0 + r < n_out) ? row0 + r : -1;
+  }
+  for (int j = tid; j < BN; j += TC_THREADS) {
+    const int n = col0 + j;
+    const int ch = ch_mod > 0 ? (n % ch_mod) : n;
+    s_epi[j] = bias ? __ldg(bias + ch) : 0.f;
+    s_epi[BN + j] = scale ? __ldg(scale + ch) : 1.f;
+    s_epi[2 * BN + j] = shift ? __ldg(shift + ch) : 0.f;
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp < 4) {
-    // ===================== producers: gather A rows + W_k^T slice ==========================
-    const int chunk16 = tid & 7, rsub = tid >> 3;  // 16 B chunk of the 128 B row, row inside a 16-row pass
+  if (warp < TC_PRODUCERS / 32) {
+    // ===================== producers ======================================================
+    const int chunk16 = tid & 7, rsub = tid >> 3;  // rsub 0..31
+    const uint32_t dst_off = (uint32_t)(rsub * 128 + ((chunk16 ^ (rsub & 7)) << 4));  // + 4096 per pass (32 rows)
+    const __nv_bfloat16* in_thr = in + chunk16 * 8;
+    const __nv_bfloat16* w_thr = wt + (long long)(col0 + rsub) * cin + chunk16 * 8;
+    const long long w_pass = 32ll * cin;  // elements between two B passes
+    const uint32_t smem_base = smem_u32(smem);
     int it = 0;
     for (int k = 0; k < kvol; ++k) {
       if (!((kmask >> k) & 1u)) continue;
-      int idx[TC_BM / 16];
+      const int* nb = s_nbr + k * TC_BM + rsub;
+      const __nv_bfloat16* src[TC_BM / 32];
+      uint32_t nbytes[TC_BM / 32];
 #pragma unroll
-      for (int p = 0; p < TC_BM / 16; ++p) idx[p] = s_nbr[k * TC_BM + p * 16 + rsub];
+      for (int p = 0; p < TC_BM / 32; ++p) {
+        const int r = nb[p * 32];
+        src[p] = in_thr + (r >= 0 ? (long long)r * cin : 0ll);
+        nbytes[p] = r >= 0 ? 16u : 0u;
+      }
+      const __nv_bfloat16* wk = w_thr + (long long)k * cout * cin;
       for (int c = 0; c < chunks; ++c, ++it) {
         const int s = it % S;
-        const uint32_t ph = (uint32_t)(it / S) & 1u;
-        mbar_wait(&empty_bar[s], ph ^ 1u);
-        const uint32_t a_base = smem_u32(smem + s * Cfg::STAGE_BYTES);
-        const uint32_t b_base = a_base + Cfg::A_BYTES;
-        const int ch0 = c * TC_BK + chunk16 * 8;
+        mbar_wait(&empty_bar[s], ((uint32_t)(it / S) & 1u) ^ 1u);
+        const uint32_t a_dst = smem_base + s * Cfg::STAGE_BYTES + dst_off;
+        const uint32_t b_dst = a_dst + Cfg::A_BYTES;
 #pragma unroll
-        for (int p = 0; p < TC_BM / 16; ++p) {
-          const int r = p * 16 + rsub;
-          const int src = idx[p];
-          const __nv_bfloat16* g = in + (src >= 0 ? ((long long)src * cin + ch0) : 0);
-          cp_async16(a_base + r * 128 + ((chunk16 ^ (r & 7)) << 4), g, src >= 0 ? 16u : 0u);
-        }
-        const __nv_bfloat16* wk = wt + ((long long)k * cout + col0) * cin + ch0;
+        for (int p = 0; p < TC_BM / 32; ++p) cp_async16(a_dst + p * 4096, src[p] + c * TC_BK, nbytes[p]);
 #pragma unroll
-        for (int p = 0; p < BN / 16; ++p) {
-          const int r = p * 16 + rsub;
-          cp_async16(b_base + r * 128 + ((chunk16 ^ (r & 7)) << 4), wk + (long long)r * cin, 16u);
-        }
-        cp_async_commit();
-        if (it >= LAG) {
-          cp_async_wait<LAG>();
-          fence_async_smem();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&full_bar[(it - LAG) % S]);
-        }
+        for (int p = 0; p < BN / 32; ++p) cp_async16(b_dst + p * 4096, wk + p * w_pass + c * TC_BK, 16u);
+        // asynchronous completion: nobody waits here, so all S stages can be in flight
+        cp_async_arrive_noinc(&full_bar[s]);
       }
-    }
-    // drain the last LAG groups
-    cp_async_wait<0>();
-    fence_async_smem();
-    __syncwarp();
-    if (lane == 0) {
-      for (int j = (it > LAG ? it - LAG : 0); j < it; ++j) mbar_arrive(&full_bar[j % S]);
     }
 
     // ===================== epilogue: TMEM -> registers -> global ===========================
@@ -200,71 +211,68 @@ k_conv_tc(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict_
       mbar_wait(accum_bar, 0);
       tc_fence_after();
     }
-    const int r = warp * 32 + lane;
-    const int o = row0 + r;
-    for (int cc = 0; cc < BN; cc += 32) {
-      uint32_t v[32];
-      if (nstage > 0) {
-        tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)cc, v);
-      } else {
+    const int q = warp & 3, half = warp >> 2;          // TMEM lane quarter, column half
+    constexpr int CPW = (BN >= 64) ? BN / 2 : BN;       // columns per warp
+    const int o = row0 + q * 32 + lane;
+    if (BN >= 64 || half == 0) {
+      for (int cc = half * CPW; cc < half * CPW + CPW; cc += 32) {
+        uint32_t v[32];
+        if (nstage > 0) {
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)cc, v);
+        } else {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = 0u;
-      }
-      if (o < n_out) {
-        const long long base = (long long)o * cout + col0 + cc;
-        float f[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int n = col0 + cc + j;
-          const int ch = ch_mod > 0 ? (n % ch_mod) : n;
-          float x = __uint_as_float(v[j]);
-          if (bias) x += __ldg(bias + ch);
-          if (scale) x = x * __ldg(scale + ch) + __ldg(shift + ch);
-          f[j] = x;
+          for (int j = 0; j < 32; ++j) v[j] = 0u;
         }
-        if (residual) {
-          if (sizeof(TOut) == 2) {
-            const uint4* rp = reinterpret_cast<const uint4*>(residual + base);
+        if (o < n_out) {
+          const long long base = (long long)o * cout + col0 + cc;
+          float f[32];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              const uint4 u = __ldg(rp + q);
-              const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
+          for (int j = 0; j < 32; ++j)
+            f[j] = (__uint_as_float(v[j]) + s_epi[cc + j]) * s_epi[BN + cc + j] + s_epi[2 * BN + cc + j];
+          if (residual) {
+            if (sizeof(TOut) == 2) {
+              const uint4* rp = reinterpret_cast<const uint4*>(residual + base);
 #pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                f[q * 8 + e * 2] += __uint_as_float(w4[e] << 16);
-                f[q * 8 + e * 2 + 1] += __uint_as_float(w4[e] & 0xFFFF0000u);
+              for (int qq = 0; qq < 4; ++qq) {
+                const uint4 u = __ldg(rp + qq);
+                const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  f[qq * 8 + e * 2] += __uint_as_float(w4[e] << 16);
+                  f[qq * 8 + e * 2 + 1] += __uint_as_float(w4[e] & 0xFFFF0000u);
+                }
+              }
+            } else {
+              const float4* rp = reinterpret_cast<const float4*>(residual + base);
+#pragma unroll
+              for (int qq = 0; qq < 8; ++qq) {
+                const float4 u = __ldg(rp + qq);
+                f[qq * 4] += u.x;
+                f[qq * 4 + 1] += u.y;
+                f[qq * 4 + 2] += u.z;
+                f[qq * 4 + 3] += u.w;
               }
             }
+          }
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = b2_apply_act(f[j], act);
+          if (sizeof(TOut) == 2) {
+            uint4* op = reinterpret_cast<uint4*>(out + base);
+#pragma unroll
+            for (int qq = 0; qq < 4; ++qq) {
+              uint32_t w4[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const __nv_bfloat162 h = __floats2bfloat162_rn(f[qq * 8 + e * 2], f[qq * 8 + e * 2 + 1]);
+                w4[e] = *reinterpret_cast<const uint32_t*>(&h);
+              }
+              op[qq] = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+            }
           } else {
-            const float4* rp = reinterpret_cast<const float4*>(residual + base);
+            float4* op = reinterpret_cast<float4*>(out + base);
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-              const float4 u = __ldg(rp + q);
-              f[q * 4] += u.x;
-              f[q * 4 + 1] += u.y;
-              f[q * 4 + 2] += u.z;
-              f[q * 4 + 3] += u.w;
-            }
+            for (int qq = 0; qq < 8; ++qq) op[qq] = make_float4(f[qq * 4], f[qq * 4 + 1], f[qq * 4 + 2], f[qq * 4 + 3]);
           }
-        }
-#pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = b2_apply_act(f[j], act);
-        if (sizeof(TOut) == 2) {
-          uint4* op = reinterpret_cast<uint4*>(out + base);
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            uint32_t w4[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const __nv_bfloat162 h = __floats2bfloat162_rn(f[q * 8 + e * 2], f[q * 8 + e * 2 + 1]);
-              w4[e] = *reinterpret_cast<const uint32_t*>(&h);
-            }
-            op[q] = make_uint4(w4[0], w4[1], w4[2], w4[3]);
-          }
-        } else {
-          float4* op = reinterpret_cast<float4*>(out + base);
-#pragma unroll
-          for (int q = 0; q < 8; ++q) op[q] = make_float4(f[q * 4], f[q * 4 + 1], f[q * 4 + 2], f[q * 4 + 3]);
         }
       }
     }
@@ -273,12 +281,13 @@ k_conv_tc(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict_
     // ===================== MMA issuer (one thread) ==========================================
     if (lane == 0 && nstage > 0) {
       constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((128u >> 4) << 24);
+      const uint32_t smem_base = smem_u32(smem);
       for (int it = 0; it < nstage; ++it) {
         const int s = it % S;
-        const uint32_t ph = (uint32_t)(it / S) & 1u;
-        mbar_wait(&full_bar[s], ph);
+        mbar_wait(&full_bar[s], (uint32_t)(it / S) & 1u);
+        fence_async_smem();  // cp.async wrote through the generic proxy, tcgen05.mma reads through the async proxy
         tc_fence_after();
-        const uint32_t a_base = smem_u32(smem + s * Cfg::STAGE_BYTES);
+        const uint32_t a_base = smem_base + s * Cfg::STAGE_BYTES;
         const uint32_t b_base = a_base + Cfg::A_BYTES;
 #pragma unroll
         for (int kk = 0; kk < TC_BK / 16; ++kk) {
@@ -293,20 +302,18 @@ k_conv_tc(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict_
     __syncwarp();
   }
   __syncthreads();
-  if (warp == 4) {
+  if (warp == TC_PRODUCERS / 32) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
-                 "r"((uint32_t)(BN < 32 ? 32 : BN))
-                 : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)BN) : "memory");
   }
 }
 
-template <int BN, typename TOut>
+template <int BN, int ST, typename TOut>
 static int launch_tc(const void* in, const void* wt, const int* nbr, long long ld, const unsigned int* tile_mask,
                      long long n_out, int cin, int cout, int kvol, const float* bias, const float* scale,
                      const float* shift, const void* residual, int act, int ch_mod, void* out, cudaStream_t st) {
-  using Cfg = TcCfg<BN>;
-  auto kern = k_conv_tc<BN, TOut>;
+  using Cfg = TcCfg<BN, ST>;
+  auto kern = k_conv_tc<BN, ST, TOut>;
   static bool configured = false;  // per template instance; attribute is per device function
   if (!configured) {
     B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
@@ -334,8 +341,9 @@ extern "C" int b2_conv_tc(const void* in_bf16, const void* wt_bf16, const int* n
   cudaStream_t st = (cudaStream_t)stream;
   const bool wide = (cout % 128 == 0);
   const bool mid = (cout % 64 == 0);
-#define TC_GO(BN, T) \
-  return launch_tc<BN, T>(in_bf16, wt_bf16, nbr, ld, tile_mask, n_out, cin, cout, kvol, bias, scale, shift, residual, act, ch_mod, out, st)
+#define TC_GO(BN, T)                                                                                               \
+  return launch_tc<BN, (BN <= 64 ? 4 : 3), T>(in_bf16, wt_bf16, nbr, ld, tile_mask, n_out, cin, cout, kvol, bias, scale, \
+                                              shift, residual, act, ch_mod, out, st)
   if (out_dtype == 1) {
     if (wide) TC_GO(128, __nv_bfloat16);
     if (mid) TC_GO(64, __nv_bfloat16);

@@ -1,0 +1,52 @@
+"""Micro-benchmark of the sparse-conv kernels on real FCAF3D layer shapes (batch of 8 S0 scenes).
+    python tools/bench_conv.py [level ...]      level in {ts8, ts16, ts32, ts64, neck8}
+Prints per (shape) the CUDA-event time, algorithmic TFLOP/s (2*P*Cin*Cout) and effective gather GB/s."""
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from fcaf3d_b200 import me as ME  # noqa: E402
+from fcaf3d_b200 import ops  # noqa: E402
+from fcaf3d_b200.scenes import make_scene  # noqa: E402
+
+dev = torch.device("cuda", 0)
+pts = [torch.from_numpy(make_scene("S0", 100 * i)[0]).to(dev) for i in range(8)]
+coords, feats = ops.quantize_points(pts, 0.01)
+x = ME.SparseTensor(coordinates=coords, features=feats)
+cm = x.coordinate_manager
+keys = {1: x.coordinate_map_key}
+for ts in (2, 4, 8, 16, 32, 64):
+    keys[ts] = cm.stride(keys[ts // 2], 2)
+levels = sys.argv[1:] or ["ts8", "ts16", "ts32", "ts64", "neck8"]
+shapes = {"ts8": (8, 64, 64), "ts16": (16, 128, 128), "ts32": (32, 256, 256), "ts64": (64, 512, 512)}
+iters = int(os.environ.get("ITERS", "20"))
+for name in levels:
+    if name == "neck8":
+        key = cm.generate_children(keys[16])
+        cin = cout = 64
+    else:
+        ts, cin, cout = shapes[name]
+        key = keys[ts]
+    n = cm.size(key)
+    km = cm.kernel_map(key, key, 3)
+    pairs = ops.kmap_pairs(km, n)
+    torch.manual_seed(0)
+    f = torch.randn(n, cin, device=dev).to(torch.bfloat16)
+    w = torch.randn(27, cin, cout, device=dev) * 0.05
+    wt = w.transpose(1, 2).contiguous().to(torch.bfloat16)
+    for _ in range(3):
+        y = ops.sparse_conv(f, w, km, n, wt_bf16=wt)
+    torch.cuda.synchronize()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(iters):
+        y = ops.sparse_conv(f, w, km, n, wt_bf16=wt)
+    e.record()
+    torch.cuda.synchronize()
+    ms = s.elapsed_time(e) / iters
+    flops = 2.0 * pairs * cin * cout
+    gather = pairs * cin * 2 + (n + 127) // 128 * 27 * cin * cout * 2 * (1 if cout <= 128 else cout // 128)
+    print("%-6s rows=%7d pairs=%9d (%.1f/row) C=%d->%d : %8.1f us  %7.1f TFLOP/s  L2->SM %6.0f GB/s" %
+          (name, n, pairs, pairs / n, cin, cout, ms * 1000, flops / ms / 1e9, gather / ms / 1e6))
