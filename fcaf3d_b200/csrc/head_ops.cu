@@ -51,9 +51,11 @@ __device__ __forceinline__ unsigned int f32_ordered(float v) {
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
+#define TOPK_BINS 2048
+
 __global__ void __launch_bounds__(1024) k_topk_mask(const float* __restrict__ scores, const int* __restrict__ seg_off,
                                                     int k, uint8_t* __restrict__ mask) {
-  __shared__ unsigned int hist[256];
+  __shared__ unsigned int hist[TOPK_BINS];
   __shared__ unsigned int s_prefix, s_need;
   __shared__ int s_warp[32];
   __shared__ int s_run;
@@ -67,26 +69,57 @@ __global__ void __launch_bounds__(1024) k_topk_mask(const float* __restrict__ sc
     for (int i = threadIdx.x; i < n; i += blockDim.x) mask[beg + i] = 0;
     return;
   }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // radix select on the order-preserving key, 11 + 11 + 10 bits, most significant digit first
   unsigned int prefix = 0, need = (unsigned int)k;
-  for (int pass = 0; pass < 4; ++pass) {
-    const int shift = 24 - 8 * pass;
-    const unsigned int hi_mask = pass == 0 ? 0u : (0xFFFFFFFFu << (shift + 8));
-    if (threadIdx.x < 256) hist[threadIdx.x] = 0;
+  const int shifts[3] = {21, 10, 0}, widths[3] = {11, 11, 10};
+  for (int pass = 0; pass < 3; ++pass) {
+    const int shift = shifts[pass], bins = 1 << widths[pass];
+    const unsigned int hi_mask = pass == 0 ? 0u : (0xFFFFFFFFu << (shift + widths[pass]));
+    for (int i = threadIdx.x; i < TOPK_BINS; i += blockDim.x) hist[i] = 0;
     __syncthreads();
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-      const unsigned int u = f32_ordered(scores[beg + i]);
-      if ((u & hi_mask) == prefix) atomicAdd(&hist[(u >> shift) & 0xFF], 1u);
+    // 4 independent loads per thread per trip (the single CTA of a segment is latency bound otherwise)
+    for (int i0 = threadIdx.x; i0 - lane < n; i0 += blockDim.x * 4) {  // trip count is warp-uniform
+      unsigned int u4[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int i = i0 + e * (int)blockDim.x;
+        u4[e] = (i < n) ? f32_ordered(scores[beg + i]) : 0u;
+      }
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int i = i0 + e * (int)blockDim.x;
+        const bool valid = (i < n) && ((u4[e] & hi_mask) == prefix);
+        // warp-aggregated histogram update: scores cluster in a few bins, plain shared atomics would serialise
+        const unsigned int vm = __ballot_sync(0xffffffffu, valid);
+        if (valid) {
+          const unsigned int d = (u4[e] >> shift) & (unsigned int)(bins - 1);
+          const unsigned int peers = __match_any_sync(vm, d);
+          if (lane == __ffs(peers) - 1) atomicAdd(&hist[d], (unsigned int)__popc(peers));
+        }
+      }
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
-      unsigned int acc = 0;
-      int d = 255;
-      for (; d > 0; --d) {
-        if (acc + hist[d] >= need) break;
-        acc += hist[d];
+    if (warp == 0) {
+      // lane l owns bins [l*per, (l+1)*per); find the bin that holds the need-th largest element
+      const int per = bins / 32;
+      unsigned int mine = 0;
+      for (int j = 0; j < per; ++j) mine += hist[lane * per + j];
+      unsigned int above = 0;  // elements in lanes with higher bins
+      for (int l = 31; l >= 0; --l) {
+        const unsigned int v = __shfl_sync(0xffffffffu, mine, l);
+        if (l > lane) above += v;
       }
-      s_prefix = prefix | ((unsigned int)d << shift);
-      s_need = need - acc;
+      if (above < need && above + mine >= need) {
+        unsigned int acc = above;
+        int d = lane * per + per - 1;
+        for (; d > lane * per; --d) {
+          if (acc + hist[d] >= need) break;
+          acc += hist[d];
+        }
+        s_prefix = prefix | ((unsigned int)d << shift);
+        s_need = need - acc;
+      }
     }
     __syncthreads();
     prefix = s_prefix;
@@ -96,22 +129,34 @@ __global__ void __launch_bounds__(1024) k_topk_mask(const float* __restrict__ sc
   // prefix == ordered bits of the k-th largest score; `need` of the rows equal to it are taken, lowest rows first
   if (threadIdx.x == 0) s_run = 0;
   __syncthreads();
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int base = 0; base < n; base += blockDim.x) {
-    const int i = base + threadIdx.x;
-    unsigned int u = 0;
-    bool eq = false;
-    if (i < n) {
-      u = f32_ordered(scores[beg + i]);
-      eq = (u == prefix);
+  // ordered pass: every thread owns 4 consecutive rows, ties are ranked in row order
+  for (int base = 0; base < n; base += blockDim.x * 4) {
+    const int i = base + threadIdx.x * 4;
+    unsigned int u4[4];
+    int eqc = 0;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      u4[e] = (i + e < n) ? f32_ordered(scores[beg + i + e]) : 0u;
+      eqc += (i + e < n && u4[e] == prefix) ? 1 : 0;
     }
-    const unsigned int bal = __ballot_sync(0xffffffffu, eq);
-    if (lane == 0) s_warp[warp] = __popc(bal);
+    int incl = eqc;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
     __syncthreads();
-    int off = s_run;
-    for (int w = 0; w < warp; ++w) off += s_warp[w];
-    const int rank = off + __popc(bal & ((1u << lane) - 1u));
-    if (i < n) mask[beg + i] = (u > prefix || (eq && rank < (int)need)) ? 1 : 0;
+    int rank = s_run + incl - eqc;
+    for (int w = 0; w < warp; ++w) rank += s_warp[w];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      if (i + e < n) {
+        const bool eq = u4[e] == prefix;
+        mask[beg + i + e] = (u4[e] > prefix || (eq && rank < (int)need)) ? 1 : 0;
+        rank += eq ? 1 : 0;
+      }
+    }
     __syncthreads();
     if (threadIdx.x == 0) {
       int t = 0;

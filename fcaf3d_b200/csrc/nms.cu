@@ -325,6 +325,64 @@ __global__ void __launch_bounds__(256) k_nms_mask(const float* __restrict__ boxe
   }
 }
 
+// Axis-aligned flavour, wide work items: one CTA = 64 rows x up to 256 columns (4 column tiles) of one segment's
+// upper triangle; thread (row r, column tile j) evaluates 64 pairs and writes its whole 64-bit word, so there are no
+// shared atomics and one barrier per 16384 pairs.  grid = (items of the longest segment, segments).
+// Same per-pair arithmetic as above (hoisted edges, inline Sa/Sb products, IEEE division).
+#define NMS_WIDE 4
+__device__ __forceinline__ int nms_items_in_row(int T, int tr) { return (T - tr + NMS_WIDE - 1) / NMS_WIDE; }
+
+__global__ void __launch_bounds__(256) k_nms_mask_aligned(const float* __restrict__ boxes, const int* __restrict__ seg_off,
+                                                          const long long* __restrict__ mask_off, float thresh,
+                                                          unsigned long long* __restrict__ mask) {
+  __shared__ float4 s_coledge[NMS_WIDE * NMS_TILE];
+  __shared__ float2 s_colsize[NMS_WIDE * NMS_TILE];
+  const int q = blockIdx.y;
+  const int beg = seg_off[q], n = seg_off[q + 1] - beg;
+  const int T = (n + NMS_TILE - 1) / NMS_TILE;
+  int local = blockIdx.x, tr = 0;
+  while (tr < T && local >= nms_items_in_row(T, tr)) {
+    local -= nms_items_in_row(T, tr);
+    ++tr;
+  }
+  if (tr >= T) return;  // this segment has fewer work items than the longest one
+  const int tc0 = tr + local * NMS_WIDE;
+  const int t = threadIdx.x;
+  {
+    const int c = tc0 * NMS_TILE + t;  // one column box per thread
+    if (c < n) {
+      const float* b = boxes + (long long)(beg + c) * 7;
+      s_coledge[t] = make_float4(b[0] - b[3] / 2, b[0] + b[3] / 2, b[1] - b[4] / 2, b[1] + b[4] / 2);
+      s_colsize[t] = make_float2(b[3], b[4]);
+    }
+  }
+  __syncthreads();
+  const int r = t & 63, j = t >> 6;
+  const int tc = tc0 + j;
+  const int row = tr * NMS_TILE + r;
+  if (row >= n || tc >= T) return;
+  const float* a = boxes + (long long)(beg + row) * 7;
+  const float4 ae = make_float4(a[0] - a[3] / 2, a[0] + a[3] / 2, a[1] - a[4] / 2, a[1] + a[4] / 2);
+  const float2 as = make_float2(a[3], a[4]);
+  const int col_n = min(n - tc * NMS_TILE, NMS_TILE);
+  unsigned long long bits = 0ull;
+  for (int c = (tr == tc) ? r + 1 : 0; c < col_n; ++c) {
+    const float4 be = s_coledge[j * NMS_TILE + c];
+    const float2 bs = s_colsize[j * NMS_TILE + c];
+    const float left = fmaxf(ae.x, be.x), right = fminf(ae.y, be.y);
+    const float top = fmaxf(ae.z, be.z), bottom = fminf(ae.w, be.w);
+    const float width = fmaxf(right - left, 0.f), height = fmaxf(bottom - top, 0.f);
+    // disjoint footprints: IoU is 0 (or NaN for degenerate boxes), never above a threshold >= 0
+    if (thresh >= 0.f && !(width > 0.f && height > 0.f)) continue;
+    const float inter = width * height;
+    const float Sa = as.x * as.y;
+    const float Sb = bs.x * bs.y;
+    const float iou = inter / fmaxf(Sa + Sb - inter, NMS_EPS);
+    if (iou > thresh) bits |= 1ull << c;
+  }
+  mask[mask_off[q] + (long long)row * T + tc] = bits;
+}
+
 // ---------------------------------------------------------------------------
 // Stage 3: greedy reduce on the device, one CTA per segment (same visiting order
 // as the reference's host loop).  keep[i] in sorted order; counts[q] = kept boxes.
@@ -448,10 +506,16 @@ int b2_nms_batched(const float* boxes, const float* scores, const int* seg_off, 
   }
   if (total_tiles > 0) {
     const int grid = total_tiles < 148 * 8 ? total_tiles : 148 * 8;
-    if (rotated)
+    if (rotated) {
       k_nms_mask<true><<<grid, 256, 0, st>>>(sb, seg_off, tile_off, mask_off, nseg, total_tiles, thresh, mask);
-    else
+    } else if (nseg > 65535) {
       k_nms_mask<false><<<grid, 256, 0, st>>>(sb, seg_off, tile_off, mask_off, nseg, total_tiles, thresh, mask);
+    } else {
+      const int Tmax = (max_seg + NMS_TILE - 1) / NMS_TILE;
+      int items = 0;
+      for (int tr = 0; tr < Tmax; ++tr) items += (Tmax - tr + NMS_WIDE - 1) / NMS_WIDE;
+      k_nms_mask_aligned<<<dim3(items, nseg), 256, 0, st>>>(sb, seg_off, mask_off, thresh, mask);
+    }
     B2_LAUNCH_CHECK();
   }
   k_nms_reduce<<<nseg, 128, 0, st>>>(mask, seg_off, mask_off, keep, counts);
