@@ -1,0 +1,88 @@
+"""Autograd bindings of the training-path kernels.
+
+Forward / input-gradient run the same sparse-convolution kernels (the input gradient of a convolution is a convolution
+over the transposed neighbour table with flipped, transposed weights); the weight gradient is `b2_conv_wgrad`.
+Mirrors MinkowskiEngine's MinkowskiConvolutionFunction / MinkowskiLocalPoolingFunction semantics (SURVEY App. A.4,
+A.6); everything else of the training graph (BatchNorm1d, ReLU/ELU, indexing) is plain torch autograd, exactly as in
+ME, where those modules are torch modules applied to `.F`.
+"""
+import torch
+
+from . import ops
+from ._lib import DT, call, ptr
+
+
+def conv_wgrad(feats, grad_out, kmap, kvol, cin, cout):
+    dw = torch.zeros((kvol, cin, cout), dtype=torch.float32, device=feats.device)
+    n_out = int(grad_out.shape[0])
+    nbr = kmap.nbr if kmap is not None else None
+    ld = kmap.ld if kmap is not None else 0
+    call("b2_conv_wgrad", ptr(feats), DT[feats.dtype], ptr(grad_out), DT[grad_out.dtype], ptr(nbr), ld, n_out, cin, cout,
+         kvol, ptr(dw))
+    return dw
+
+
+class SparseConvFn(torch.autograd.Function):
+    """out[o] = sum_k feats[nbr[k][o]] @ w[k];  w: [K, Cin, Cout] fp32.
+
+    kmap: forward neighbour table (None = identity, K == 1); kmap_t: table of the transposed map (None = identity),
+    i.e. for every INPUT row the output rows at coord_in + offset_k' — the pair (i, o) of offset k is found at
+    k' = K - 1 - k (odd, centred kernels).
+    """
+
+    @staticmethod
+    def forward(ctx, feats, w, kmap, kmap_t, n_out, use_bf16):
+        feats = feats.contiguous()
+        wd = w.detach().contiguous()
+        kvol, cin, cout = wd.shape
+        x = feats
+        wt = None
+        if use_bf16 and cin % 64 == 0 and cout % 32 == 0:
+            x = ops.cast(feats, torch.bfloat16)
+            wt = wd.transpose(1, 2).contiguous().to(torch.bfloat16)
+        out = ops.sparse_conv(x, wd, kmap, n_out, wt_bf16=wt, out_dtype=torch.float32)
+        ctx.save_for_backward(x, wd)
+        ctx.kmap, ctx.kmap_t, ctx.n_in, ctx.use_bf16 = kmap, kmap_t, int(feats.shape[0]), use_bf16
+        ctx.in_dtype = feats.dtype
+        return out.to(feats.dtype) if feats.dtype != torch.float32 else out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        x, wd = ctx.saved_tensors
+        kvol, cin, cout = wd.shape
+        g = grad_out.contiguous().float()
+        d_feats = d_w = None
+        if ctx.needs_input_grad[0]:
+            w_back = wd.flip(0).transpose(1, 2).contiguous()          # [K, Cout, Cin]: W[K-1-k']^T
+            gb, wt = g, None
+            if ctx.use_bf16 and cout % 64 == 0 and cin % 32 == 0:
+                gb = ops.cast(g, torch.bfloat16)
+                wt = wd.flip(0).contiguous().to(torch.bfloat16)       # [K, Cin, Cout] is already "out x in" for dgrad
+            d_feats = ops.sparse_conv(gb, w_back, ctx.kmap_t, ctx.n_in, wt_bf16=wt, out_dtype=torch.float32)
+            d_feats = d_feats.to(ctx.in_dtype)
+        if ctx.needs_input_grad[1]:
+            gw = ops.cast(g, torch.bfloat16) if x.dtype == torch.bfloat16 else g
+            d_w = conv_wgrad(x, gw, ctx.kmap, kvol, cin, cout)
+        return d_feats, d_w, None, None, None, None
+
+
+class MaxPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, feats, kmap, n_in):
+        out, arg = ops.maxpool(feats.contiguous(), kmap, want_argmax=True)
+        ctx.save_for_backward(arg)
+        ctx.n_in, ctx.dtype = n_in, feats.dtype
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (arg,) = ctx.saved_tensors
+        g = grad_out.contiguous()
+        c = int(g.shape[1])
+        dx = torch.zeros((ctx.n_in, c), dtype=torch.float32, device=g.device)
+        call("b2_maxpool_bwd", ptr(g), DT[g.dtype], ptr(arg), g.shape[0], c, ptr(dx))
+        return dx.to(ctx.dtype), None, None
+
+
+def wants_grad(*tensors):
+    return torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors)

@@ -17,6 +17,7 @@ import torch.nn as nn
 
 from . import me as ME
 from . import ops
+from .losses import Fcaf3DAssigner, build_loss
 from .me.modules.resnet_block import BasicBlock, Bottleneck
 from .pcdet_nms import pcdet_nms_gpu, pcdet_nms_normal_gpu
 
@@ -30,6 +31,16 @@ class Scale(nn.Module):
 
     def forward(self, x):
         return x * self.scale
+
+
+def reduce_mean(t):
+    """mmdet.core.reduce_mean: identity on one process, all-reduce mean under torch.distributed"""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return t
+    t = t.clone()
+    dist.all_reduce(t.div_(dist.get_world_size()), op=dist.ReduceOp.SUM)
+    return t
 
 
 def bias_init_with_prob(prior_prob):
@@ -157,8 +168,14 @@ class Fcaf3DNeckWithHead(nn.Module):
         self.train_cfg = train_cfg
         self.test_cfg = test_cfg or dict(nms_pre=1000, iou_thr=.5, score_thr=.01)
         self.n_classes, self.n_reg_outs = n_classes, n_reg_outs
-        self.assigner_cfg = assigner
-        self.loss_cfg = dict(centerness=loss_centerness, bbox=loss_bbox, cls=loss_cls)
+        assigner = dict(assigner or dict(limit=27, topk=18, n_scales=len(in_channels)))
+        assigner.pop("type", None)
+        self.assigner = Fcaf3DAssigner(**assigner)
+        self.loss_centerness = build_loss(loss_centerness or dict(type="CrossEntropyLoss", use_sigmoid=True,
+                                                                  loss_weight=1.0))
+        self.loss_bbox = build_loss(loss_bbox or dict(type="IoU3DLoss", loss_weight=1.0))
+        self.loss_cls = build_loss(loss_cls or dict(type="FocalLoss", use_sigmoid=True, gamma=2.0, alpha=0.25,
+                                                    loss_weight=1.0))
         self._init_layers(in_channels, out_channels, n_reg_outs, n_classes)
 
     @staticmethod
@@ -238,6 +255,64 @@ class Fcaf3DNeckWithHead(nn.Module):
             cls_scores.append(cls_score[perm])
         points = [p * self.voxel_size for p in x.decomposed_coordinates]
         return centernesses, bbox_preds, cls_scores, points, prune_scores
+
+    # ---- training (fcaf3d_neck_with_head.py:128-203) ---------------------------------------------
+    def loss(self, centernesses, bbox_preds, cls_scores, points, gt_bboxes, gt_labels, img_metas=None):
+        """gt_bboxes: list over scenes of [B_i, 7] tensors (gravity centre, size, yaw); gt_labels: int64 [B_i]."""
+        n = len(gt_bboxes)
+        per_scene = [self._loss_single([x[i] for x in centernesses], [x[i] for x in bbox_preds],
+                                       [x[i] for x in cls_scores], [x[i] for x in points], gt_bboxes[i], gt_labels[i])
+                     for i in range(n)]
+        return dict(loss_centerness=torch.mean(torch.stack([p[0] for p in per_scene])),
+                    loss_bbox=torch.mean(torch.stack([p[1] for p in per_scene])),
+                    loss_cls=torch.mean(torch.stack([p[2] for p in per_scene])))
+
+    def _loss_single(self, centernesses, bbox_preds, cls_scores, points, gt_bboxes, gt_labels):
+        centerness_targets, bbox_targets, labels = self.assigner.assign(points, gt_bboxes, gt_labels)
+        centerness = torch.cat(centernesses)
+        bbox_preds = torch.cat(bbox_preds)
+        cls_scores = torch.cat(cls_scores)
+        points = torch.cat(points)
+        pos_inds = torch.nonzero(labels >= 0).squeeze(1)
+        n_pos = torch.tensor(len(pos_inds), dtype=torch.float, device=centerness.device)
+        n_pos = torch.clamp(reduce_mean(n_pos), min=1.)
+        loss_cls = self.loss_cls(cls_scores, labels, avg_factor=n_pos)
+        pos_centerness = centerness[pos_inds]
+        pos_bbox_preds = bbox_preds[pos_inds]
+        pos_centerness_targets = centerness_targets[pos_inds].unsqueeze(1)
+        pos_bbox_targets = bbox_targets[pos_inds]
+        centerness_denorm = torch.clamp(reduce_mean(pos_centerness_targets.sum().detach()), min=1e-6)
+        if len(pos_inds) > 0:
+            pos_points = points[pos_inds]
+            loss_centerness = self.loss_centerness(pos_centerness, pos_centerness_targets, avg_factor=n_pos)
+            pred = self._bbox_pred_to_bbox_train(pos_points, pos_bbox_preds)
+            target = pos_bbox_targets if pred.shape[1] == 7 else pos_bbox_targets[:, :6]
+            loss_bbox = self.loss_bbox(pred, target, weight=pos_centerness_targets.squeeze(1),
+                                       avg_factor=centerness_denorm)
+        else:
+            loss_centerness = pos_centerness.sum()
+            loss_bbox = pos_bbox_preds.sum()
+        return loss_centerness, loss_bbox, loss_cls
+
+    def _bbox_pred_to_bbox_train(self, points, bbox_pred):
+        """differentiable twin of _bbox_pred_to_bbox (:281-330); the inference path uses the fused kernel"""
+        xc = points[:, 0] + (bbox_pred[:, 1] - bbox_pred[:, 0]) / 2
+        yc = points[:, 1] + (bbox_pred[:, 3] - bbox_pred[:, 2]) / 2
+        zc = points[:, 2] + (bbox_pred[:, 5] - bbox_pred[:, 4]) / 2
+        base = torch.stack([xc, yc, zc, bbox_pred[:, 0] + bbox_pred[:, 1], bbox_pred[:, 2] + bbox_pred[:, 3],
+                            bbox_pred[:, 4] + bbox_pred[:, 5]], -1)
+        if bbox_pred.shape[1] == 6:
+            return base
+        if self.yaw_parametrization == "naive":
+            return torch.cat((base, bbox_pred[:, 6:7]), -1)
+        if self.yaw_parametrization == "sin-cos":
+            norm = torch.pow(torch.pow(bbox_pred[:, 6:7], 2) + torch.pow(bbox_pred[:, 7:8], 2), 0.5)
+            return torch.cat((base, torch.atan2(bbox_pred[:, 6:7] / norm, bbox_pred[:, 7:8] / norm)), -1)
+        scale = bbox_pred[:, 0] + bbox_pred[:, 1] + bbox_pred[:, 2] + bbox_pred[:, 3]
+        q = torch.exp(torch.sqrt(torch.pow(bbox_pred[:, 6], 2) + torch.pow(bbox_pred[:, 7], 2)))
+        alpha = 0.5 * torch.atan2(bbox_pred[:, 6], bbox_pred[:, 7])
+        return torch.stack((xc, yc, zc, scale / (1 + q), scale / (1 + q) * q, bbox_pred[:, 5] + bbox_pred[:, 4], alpha),
+                           dim=-1)
 
     def get_bboxes(self, centernesses, bbox_preds, cls_scores, points, img_metas, rescale=False):
         results = []
@@ -466,6 +541,11 @@ class SingleStageSparse3DDetector(nn.Module):
         x = self._input_tensor(points)
         x = self.backbone(x)
         return self.neck_with_head(x)
+
+    def forward_train(self, points, gt_bboxes_3d, gt_labels_3d, img_metas=None):
+        """single_stage_sparse.py:42-49.  gt_bboxes_3d: list of [B_i, 7] (gravity centre, size, yaw) tensors."""
+        x = self.extract_feat(points, img_metas)
+        return self.neck_with_head.loss(*x, gt_bboxes_3d, gt_labels_3d, img_metas)
 
     @torch.no_grad()
     def simple_test(self, points, img_metas, imgs=None, rescale=False):

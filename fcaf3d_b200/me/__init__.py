@@ -10,6 +10,7 @@ import math
 import torch
 import torch.nn as nn
 
+from .. import autograd as AG
 from .. import ops
 from .._lib import B2Error
 
@@ -197,6 +198,25 @@ class CoordinateManager:
         return km
 
 
+def _kernel_map_transposed(self, in_key, out_key, kernel_size, dilation=1):
+    """For every INPUT row the output rows at coord_in + offset_k (backward of a convolution in_key -> out_key)."""
+    if in_key == out_key:
+        return self.kernel_map(in_key, out_key, kernel_size, dilation)
+    if int(kernel_size) % 2 == 0:
+        raise B2Error("backward of even-sized convolution kernels is not implemented")
+    ck = (in_key, out_key, int(kernel_size), int(dilation), "T")
+    km = self._kmaps.get(ck)
+    if km is None:
+        src, dst = self._maps[in_key], self._maps[out_key]
+        table, cap = dst.ensure_table()
+        km = ops.kernel_map(table, cap, src.coords, int(kernel_size), src.ts * int(dilation))
+        self._kmaps[ck] = km
+    return km
+
+
+CoordinateManager.kernel_map_transposed = _kernel_map_transposed
+
+
 def _iso(v):
     if isinstance(v, (list, tuple)):
         assert all(x == v[0] for x in v), "only isotropic kernels/strides are supported"
@@ -328,20 +348,24 @@ class SparseTensor:
                                 coordinate_manager=self.coordinate_manager)
         if self.coordinate_manager is not other.coordinate_manager:
             raise B2Error("SparseTensor addition needs a shared coordinate manager")
+        grad = AG.wants_grad(self._F, other._F)
         if self._same_map(other):
-            f = ops.affine_act(self._F.contiguous(), residual=other._F.contiguous())
+            f = self._F + other._F if grad else ops.affine_act(self._F.contiguous(), residual=other._F.contiguous())
             return SparseTensor(f, coordinate_map_key=self.coordinate_map_key,
                                 coordinate_manager=self.coordinate_manager)
         # different maps: union (ME A.8)
         key, dst_a, dst_b = self.coordinate_manager.union(self.coordinate_map_key, other.coordinate_map_key)
         n = self.coordinate_manager.size(key)
         out = torch.zeros((n, self._F.shape[1]), dtype=self._F.dtype, device=self._F.device)
+        if grad:  # autograd flows through the indexing, as in ME
+            out = out.index_add(0, dst_a.long(), self._F).index_add(0, dst_b.long(), other._F.to(self._F.dtype))
+            return SparseTensor(out, coordinate_map_key=key, coordinate_manager=self.coordinate_manager)
         ops.scatter_rows(self._F.contiguous(), dst_a, out, accumulate=False)
         ops.scatter_rows(other._F.contiguous().to(self._F.dtype), dst_b, out, accumulate=True)
         return SparseTensor(out, coordinate_map_key=key, coordinate_manager=self.coordinate_manager)
 
     def __iadd__(self, other):
-        if isinstance(other, SparseTensor) and self._same_map(other):
+        if isinstance(other, SparseTensor) and self._same_map(other) and not AG.wants_grad(self._F, other._F):
             ops.affine_act(self._F, residual=other._F.contiguous(), out=self._F)
             return self
         return self.__add__(other)
@@ -425,6 +449,17 @@ class MinkowskiConvolution(_ConvBase):
     def forward(self, x, coordinates=None):
         out_key, km = self.maps(x)
         n_out = x.coordinate_manager.size(out_key)
+        if AG.wants_grad(x.F, self.kernel, self.bias):
+            cm = x.coordinate_manager
+            if self.use_mm:
+                f = x.F @ self.kernel.to(x.F.dtype)          # ME: F.mm(kernel) for 1x1 stride-1 convolutions
+            else:
+                km_t = None if km is None else cm.kernel_map_transposed(x.coordinate_map_key, out_key,
+                                                                         self.kernel_size, self.dilation)
+                f = AG.SparseConvFn.apply(x.F, self.kernel, km, km_t, n_out, get_compute_dtype() == torch.bfloat16)
+            if self.bias is not None:
+                f = f + self.bias.to(f.dtype)
+            return SparseTensor(f, coordinate_map_key=out_key, coordinate_manager=cm)
         bias = self.bias.detach().reshape(-1).contiguous() if self.bias is not None else None
         f = ops.sparse_conv(x.F.contiguous(), self._w3(), km, n_out, wt_bf16=self._wt_bf16(), bias=bias)
         return SparseTensor(f, coordinate_map_key=out_key, coordinate_manager=x.coordinate_manager)
@@ -470,7 +505,12 @@ class MinkowskiGenerativeConvolutionTranspose(_ConvBase):
     def forward(self, x):
         cm = x.coordinate_manager
         out_key = cm.generate_children(x.coordinate_map_key)
-        f = self.generate(x.F.contiguous())
+        if AG.wants_grad(x.F, self.kernel):
+            packed = self.kernel.permute(1, 0, 2).reshape(1, self.in_channels, 8 * self.out_channels)
+            f = AG.SparseConvFn.apply(x.F, packed, None, None, x.F.shape[0], get_compute_dtype() == torch.bfloat16)
+            f = f.reshape(x.F.shape[0] * 8, self.out_channels)
+        else:
+            f = self.generate(x.F.contiguous())
         return SparseTensor(f, coordinate_map_key=out_key, coordinate_manager=cm)
 
     def generate(self, feats, scale=None, shift=None, act=ops.ACT_NONE):
@@ -487,7 +527,7 @@ class MinkowskiPruning(MinkowskiModuleBase):
     def forward(self, x, mask):
         cm = x.coordinate_manager
         key, m8, pos, n_out = cm.prune(x.coordinate_map_key, mask.contiguous())
-        f = ops.gather_rows(x.F, m8, pos, n_out)
+        f = x.F[mask.bool()] if AG.wants_grad(x.F) else ops.gather_rows(x.F, m8, pos, n_out)
         return SparseTensor(f, coordinate_map_key=key, coordinate_manager=cm)
 
 
@@ -500,7 +540,11 @@ class MinkowskiMaxPooling(MinkowskiModuleBase):
         cm = x.coordinate_manager
         out_key = x.coordinate_map_key if self.stride == 1 else cm.stride(x.coordinate_map_key, self.stride)
         km = cm.kernel_map(x.coordinate_map_key, out_key, self.kernel_size, self.dilation)
-        return SparseTensor(ops.maxpool(x.F.contiguous(), km), coordinate_map_key=out_key, coordinate_manager=cm)
+        if AG.wants_grad(x.F):
+            f = AG.MaxPoolFn.apply(x.F, km, x.F.shape[0])
+        else:
+            f = ops.maxpool(x.F.contiguous(), km)
+        return SparseTensor(f, coordinate_map_key=out_key, coordinate_manager=cm)
 
 
 class MinkowskiInstanceNorm(MinkowskiModuleBase):
@@ -522,6 +566,17 @@ class MinkowskiInstanceNorm(MinkowskiModuleBase):
     def forward(self, x, act=ops.ACT_NONE):
         m = x._map()
         f = x.F.contiguous()
+        if AG.wants_grad(f, self.weight, self.bias):
+            # differentiable per-scene statistics (ME: global pooling + broadcast, both with autograd)
+            b = m.coords[:, 0].long()
+            cnt = torch.bincount(b, minlength=m.num_batches).clamp(min=1).to(f.dtype).unsqueeze(1)
+            mean = torch.zeros((m.num_batches, f.shape[1]), dtype=f.dtype, device=f.device).index_add(0, b, f) / cnt
+            xc = f - mean[b]
+            var = torch.zeros_like(mean).index_add(0, b, xc * xc) / cnt
+            out = xc / torch.sqrt(var[b] + self.eps) * self.weight + self.bias
+            if act == ops.ACT_RELU:
+                out = torch.relu(out)
+            return SparseTensor(out, coordinate_map_key=x.coordinate_map_key, coordinate_manager=x.coordinate_manager)
         scale, shift = self.scale_shift(f, m)
         out = ops.affine_act(f, scale, shift, coords=m.coords, act=act)
         return SparseTensor(out, coordinate_map_key=x.coordinate_map_key, coordinate_manager=x.coordinate_manager)
@@ -568,6 +623,12 @@ class MinkowskiBatchNorm(MinkowskiModuleBase):
 
     def forward(self, x, act=ops.ACT_NONE, residual=None):
         f = x.F.contiguous()
+        if AG.wants_grad(f, self.bn.weight, self.bn.bias):
+            out = self.bn(f.float()).to(f.dtype)             # exactly ME: nn.BatchNorm1d on the feature rows
+            if residual is not None:
+                out = out + residual
+            out = torch.relu(out) if act == ops.ACT_RELU else torch.nn.functional.elu(out) if act == ops.ACT_ELU else out
+            return SparseTensor(out, coordinate_map_key=x.coordinate_map_key, coordinate_manager=x.coordinate_manager)
         scale, shift = self.scale_shift(f)
         out = ops.affine_act(f, scale, shift, residual=residual, act=act)
         return SparseTensor(out, coordinate_map_key=x.coordinate_map_key, coordinate_manager=x.coordinate_manager)
@@ -580,6 +641,9 @@ class MinkowskiReLU(MinkowskiModuleBase):
 
     def forward(self, x):
         f = x.F
+        if AG.wants_grad(f):
+            return SparseTensor(torch.relu(f), coordinate_map_key=x.coordinate_map_key,
+                                coordinate_manager=x.coordinate_manager)
         out = ops.affine_act(f, act=ops.ACT_RELU, out=f if self.inplace else None)
         if self.inplace:
             return x
@@ -593,6 +657,9 @@ class MinkowskiELU(MinkowskiModuleBase):
         self.inplace = inplace
 
     def forward(self, x):
+        if AG.wants_grad(x.F):
+            return SparseTensor(torch.nn.functional.elu(x.F), coordinate_map_key=x.coordinate_map_key,
+                                coordinate_manager=x.coordinate_manager)
         out = ops.affine_act(x.F.contiguous(), act=ops.ACT_ELU)
         return SparseTensor(out, coordinate_map_key=x.coordinate_map_key, coordinate_manager=x.coordinate_manager)
 

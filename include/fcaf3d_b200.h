@@ -158,6 +158,29 @@ int b2_nms_single_noalloc_max_boxes(void);
 int b2_nms_single_noalloc(const float* boxes_sorted, long long n, float thresh, int rotated, uint8_t* keep, int* count,
                           void* stream);
 
+/* ---- training path ----------------------------------------------------------------------------- */
+/* ME ConvolutionBackwardKernelGPU, weight part: dw[k,ci,co] += sum_o in[nbr[k][o],ci] * dout[o,co] (fp32 atomics;
+ * dw zero-initialised by the caller).  The input gradient is b2_conv_cc / b2_conv_tc over the transposed map with
+ * transposed weights (host side: fcaf3d_b200/autograd.py). */
+int b2_conv_wgrad(const void* in, int a_dtype, const void* dout, int g_dtype, const int* nbr, long long ld,
+                  long long n_out, int cin, int cout, int kvol, float* dw, void* stream);
+/* ME max-pool backward: dx[argmax[o,c], c] += dy[o,c]; dx fp32, zero-initialised by the caller */
+int b2_maxpool_bwd(const void* dy, int dtype, const int* argmax, long long n_out, int c, float* dx, void* stream);
+/* Fcaf3DAssigner.assign for one scene (fcaf3d_neck_with_head.py:387-466): points [P,3] of all levels (level_off[L+1]),
+ * boxes [B,7] = (gravity centre, size, yaw), labels_in int64 [B] -> centerness_t [P], box_t [P,7], labels_out int64 [P]
+ * (-1 = background).  Scratch: counts int32 [L*B], best_level int32 [B], thr f32 [B]. */
+int b2_fcaf3d_assign(const float* points, long long P, const int* level_off, int L, const float* boxes, int B,
+                     const long long* labels_in, int limit, int topk, int* counts, int* best_level, float* thr,
+                     float* centerness_t, float* box_t, long long* labels_out, void* stream);
+/* mmcv.ops.sigmoid_focal_loss element-wise forward and d/dlogit (label outside [0,c) = all-negative row) */
+int b2_sigmoid_focal(const float* logits, const long long* labels, long long n, int c, float gamma, float alpha,
+                     float* loss, float* grad, void* stream);
+/* aligned-pair axis-aligned 3-D IoU (iou3d_calculator.py:279-312 through iou3d_loss.py:21-35) and d iou / d pred */
+int b2_aa_iou3d(const float* pred, const float* tgt, long long n, int stride, float* iou, float* dpred, void* stream);
+/* Rotated_IoU cuda_op.sort_v (box_intersection_2d.py:147): vertices [n,24,2], mask [n,24] u8, num_valid [n] -> idx [n,9] */
+int b2_sort_vertices(const float* vertices, const uint8_t* mask, const int* num_valid, long long n, int* idx,
+                     void* stream);
+
 #ifdef __cplusplus
 }
 #endif

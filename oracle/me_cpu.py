@@ -397,13 +397,13 @@ class MinkowskiMaxPooling(nn.Module):
     def forward(self, x):
         cm = x.coordinate_manager
         out_key = x.coordinate_map_key if self.stride == 1 else cm.stride(x.coordinate_map_key, self.stride)
-        pairs = cm.kernel_map(x.coordinate_map_key, out_key, self.kernel_size, self.dilation)
-        n_out = cm.size(out_key)
-        out = torch.full((n_out, x.F.shape[1]), -float("inf"), dtype=x.F.dtype)
-        for i, o in pairs:
-            if len(i):
-                idx = o[:, None].expand(-1, x.F.shape[1])
-                out = out.scatter_reduce(0, idx, x.F.index_select(0, i), reduce="amax", include_self=True)
+        # per output voxel the per-channel max over its present inputs; the gradient goes to the arg-max input only
+        # (ME keeps an arg-max index per output element; torch.max(dim) returns the first maximal index)
+        table = torch.from_numpy(cm.neighbour_table(x.coordinate_map_key, out_key, self.kernel_size, self.dilation))
+        n_in, c = x.F.shape
+        padded = torch.cat([x.F, torch.full((1, c), -float("inf"), dtype=x.F.dtype)], 0)
+        cand = padded[torch.where(table >= 0, table, torch.full_like(table, n_in)).t()]      # [n_out, K, C]
+        out = cand.max(dim=1).values
         out = torch.where(torch.isinf(out), torch.zeros_like(out), out)
         return SparseTensor(out, coordinate_map_key=out_key, coordinate_manager=cm)
 

@@ -119,8 +119,55 @@ def ops_fixture():
     print("ops_ref", int((lb >= 0).sum()), "positives of", len(lb))
 
 
+GRAD_KEYS = ["backbone.conv1.0.kernel", "backbone.conv1.1.weight", "backbone.layer1.0.conv1.kernel",
+             "backbone.layer1.0.downsample.0.kernel", "backbone.layer1.0.norm1.bn.weight", "backbone.layer2.1.conv2.kernel",
+             "backbone.layer4.2.conv2.kernel", "neck_with_head.up_block_1.0.kernel", "neck_with_head.up_block_3.3.kernel",
+             "neck_with_head.out_block_0.0.kernel", "neck_with_head.out_block_2.1.bn.bias",
+             "neck_with_head.centerness_conv.kernel", "neck_with_head.reg_conv.kernel", "neck_with_head.cls_conv.kernel",
+             "neck_with_head.cls_conv.bias", "neck_with_head.scales.0.scale", "neck_with_head.scales.3.scale"]
+
+
+def train_fixture(config, seeds, name, n_points=3000):
+    """losses + parameter gradients of one training step of the reference's own model / loss / assigner code"""
+    ns = ref_loader.load()
+    det = ref_loader.build_reference_detector(config)
+    deterministic_init(det, seed=1)
+    det.train()
+    scenes = [make_scene("tiny", s, n_points, n_classes=det.neck_with_head.cls_conv.out_channels) for s in seeds]
+    if "sunrgbd" in config:  # rotated ground truth for the rotated-IoU loss
+        rng = np.random.default_rng(11)
+        for _, gt, _ in scenes:
+            gt[:, 6] = rng.uniform(-0.6, 0.6, len(gt))
+    pts = [torch.from_numpy(p) for p, _, _ in scenes]
+    gtb = [ns.DepthBoxes(torch.from_numpy(g), origin=(.5, .5, .5)) for _, g, _ in scenes]
+    gtl = [torch.from_numpy(l) for _, _, l in scenes]
+    losses = det.forward_train(pts, gtb, gtl, [dict() for _ in seeds])
+    total = sum(losses.values())
+    total.backward()
+    out = {"seeds": np.array(seeds), "n_points": np.array(n_points)}
+    for i, (p, g, l) in enumerate(scenes):
+        out["points_%d" % i], out["gt_%d" % i], out["gt_labels_%d" % i] = p, g, l
+    for k, v in losses.items():
+        out[k] = v.detach().numpy()
+    params = dict(det.named_parameters())
+    for k in GRAD_KEYS:
+        g = params[k].grad
+        flat = g.reshape(-1)
+        step = max(1, flat.numel() // 4096)
+        out["grad/" + k] = flat[::step].numpy()
+        out["gradnorm/" + k] = np.array(float(g.double().norm()))
+    np.savez_compressed(os.path.join(OUT, name), **out)
+    print(name, {k: float(v) for k, v in losses.items()})
+
+
 if __name__ == "__main__":
     torch.set_num_threads(8)
+    if "--train-only" in sys.argv:
+        train_fixture("fcaf3d_scannet-3d-18class.py", (0, 100), "train_tiny_scannet.npz")
+        train_fixture("fcaf3d_sunrgbd-3d-10class.py", (5,), "train_tiny_sunrgbd.npz")
+        sys.exit(0)
     ops_fixture()
     detector_fixture("fcaf3d_scannet-3d-18class.py", (0, 100), "fcaf3d_tiny_scannet.npz")
     detector_fixture("fcaf3d_sunrgbd-3d-10class.py", (5,), "fcaf3d_tiny_sunrgbd.npz")
+    train_fixture("fcaf3d_scannet-3d-18class.py", (0, 100), "train_tiny_scannet.npz")
+    train_fixture("fcaf3d_sunrgbd-3d-10class.py", (5,), "train_tiny_sunrgbd.npz")
