@@ -124,6 +124,73 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def run_train(args, det, scenes, dev, world, rank, dtype):
+    """configs[4]: data-parallel training step (8 scenes per GPU), NCCL gradient all-reduce through DDP."""
+    import torch
+    import torch.distributed as dist
+    from fcaf3d_b200.train import TrainStepModule, make_optimizer, train_step, wrap_ddp
+    det.train()
+    module = wrap_ddp(TrainStepModule(det), dev)
+    opt = make_optimizer(module)
+    host = [(torch.from_numpy(p).pin_memory(), torch.from_numpy(g), torch.from_numpy(l)) for p, g, l in scenes]
+    gtb = [g.to(dev) for _, g, _ in host]
+    gtl = [l.to(dev) for _, _, l in host]
+    dev_pts = [p.to(dev) for p, _, _ in host]
+
+    def step(e2e):
+        pts = [p.to(dev, non_blocking=True) for p, _, _ in host] if e2e else dev_pts
+        total, _ = train_step(module, opt, pts, gtb, gtl)
+        return total.item() if e2e else total
+
+    def timed(e2e, steps, warmup):
+        for _ in range(warmup):
+            step(e2e)
+        times = []
+        for _ in range(steps):
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            out = step(e2e)
+            e.record()
+            torch.cuda.synchronize()
+            times.append(s.elapsed_time(e))
+        t = torch.tensor([sum(times)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item() / steps, out
+
+    if os.environ.get("BENCH_PROFILE"):
+        step(False), step(False)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        step(False)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+        print(json.dumps({"profile_step": "done"}))
+        return
+    with ClockSampler(dev.index) as clk:
+        ms, _ = timed(False, args.steps, args.warmup)
+    ms_e2e, loss = timed(True, max(2, args.steps // 2), 1)
+    n = len(scenes)
+    line = {"metric": METRIC, "value": world * n * 1000.0 / ms, "unit": "scenes/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": args.dtype, "data": "synthetic",
+            "config": {"workload": WORKLOAD, "scenes_per_gpu": n, "optimizer": "AdamW lr 1e-3 wd 1e-4, clip 10",
+                       "loss": "focal + centerness BCE + %s IoU" % ("rotated" if det.neck_with_head.loss_bbox.with_yaw
+                                                                   else "axis-aligned"),
+                       "l2": "activations of one step (GBs) exceed L2", "last_loss": loss},
+            "clocks": clk.summary(),
+            "e2e": {"value": world * n * 1000.0 / ms_e2e, "unit": "scenes/s",
+                    "h2d_bytes_per_step": sum(p.numel() * 4 for p, _, _ in host), "d2h_bytes_per_step": 4,
+                    "ms_per_step": ms_e2e}}
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -132,6 +199,11 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="scannet", choices=["scannet", "sunrgbd", "s3dis1m"],
+                    help="scannet = BASELINE configs[1] (default, the headline); sunrgbd = configs[2] rotated boxes + rotated "
+                         "NMS; s3dis1m = configs[3] ~1M-point rooms, one scene per step per GPU")
+    ap.add_argument("--mode", default="infer", choices=["infer", "train"],
+                    help="train = configs[4]: fwd + bwd + NCCL all-reduce + clip + AdamW on 8 scenes per GPU")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
@@ -157,8 +229,27 @@ def main():
 
     # ---- model: FCAF3D ScanNet config, deterministic random weights; cls bias 0 so that candidates pass score_thr (F8);
     #      BatchNorm running statistics calibrated by one train-mode pass (what a trained checkpoint would carry)
-    det = deterministic_init(build_fcaf3d("scannet"), 0, cls_bias=0.0).to(dev)
-    host_pts = [torch.from_numpy(make_scene(PRESET, 100 * (rank * BATCH + i))[0]).pin_memory() for i in range(BATCH)]
+    global BATCH, PRESET, METRIC, WORKLOAD
+    dataset = {"scannet": "scannet", "sunrgbd": "sunrgbd", "s3dis1m": "s3dis"}[args.workload]
+    if args.workload == "sunrgbd":
+        PRESET = "S3"
+        METRIC = "SUN RGB-D-shape scenes/sec, FCAF3D inference with rotated BEV NMS, batch 8"
+        WORKLOAD = "FCAF3D SUN RGB-D-10class rotated boxes (Mobius) inference incl. rotated BEV NMS, batch 8 synthetic S3 scenes x 100k pts"
+    elif args.workload == "s3dis1m":
+        PRESET, BATCH = "S2", 1
+        METRIC = "S3DIS-1M-shape scenes/sec, FCAF3D inference, 1 scene per GPU per step"
+        WORKLOAD = "FCAF3D S3DIS-5class large room (1M points) inference, scene-sharded, 1 synthetic S2 scene per GPU"
+    if args.mode == "train":
+        METRIC = METRIC.replace("full inference incl. axis-aligned BEV NMS", "training step").replace(
+            "inference with rotated BEV NMS", "training step").replace("inference", "training step")
+        WORKLOAD = WORKLOAD.replace(" incl. axis-aligned 3D(BEV) NMS", "").replace(" incl. rotated BEV NMS", "")
+        WORKLOAD = WORKLOAD.replace("inference", "training step (fwd+bwd+allreduce+clip+AdamW)")
+    n_cls = {"scannet": 18, "sunrgbd": 10, "s3dis": 5}[dataset]
+    det = deterministic_init(build_fcaf3d(dataset), 0, cls_bias=0.0).to(dev)
+    scenes = [make_scene(PRESET, 100 * (rank * BATCH + i), n_classes=n_cls) for i in range(BATCH)]
+    host_pts = [torch.from_numpy(sc[0]).pin_memory() for sc in scenes]
+    if args.mode == "train":
+        return run_train(args, det, scenes, dev, world, rank, dtype)
     dev_pts = [p.to(dev) for p in host_pts]
     with torch.no_grad():
         det.train()

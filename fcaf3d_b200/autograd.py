@@ -84,5 +84,20 @@ class MaxPoolFn(torch.autograd.Function):
         return dx.to(ctx.dtype), None, None
 
 
+class PruneFn(torch.autograd.Function):
+    """row compaction y = x[mask]; backward scatters the gradient rows back (rows that were dropped get zeros)"""
+
+    @staticmethod
+    def forward(ctx, feats, m8, pos, n_out):
+        ctx.save_for_backward(m8, pos)
+        return ops.gather_rows(feats.contiguous(), m8, pos, n_out)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        m8, pos = ctx.saved_tensors
+        idx = torch.where(m8.bool(), pos, torch.full_like(pos, -1))
+        return ops.index_rows(grad_out.contiguous(), idx), None, None, None
+
+
 def wants_grad(*tensors):
     return torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors)

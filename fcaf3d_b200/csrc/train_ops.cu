@@ -9,6 +9,7 @@
 //   axis-aligned IoU loss    mmdet3d/models/losses/iou3d_loss.py:21-35 + core/bbox/iou_calculators/iou3d_calculator.py:279-312
 //   sort_v                   lilanxiao/Rotated_IoU@3bdca6b cuda_op/sort_vert_kernel.cu (not vendored)
 #include "common.cuh"
+#include <mma.h>
 
 template <typename T>
 __device__ __forceinline__ float ldf(const T* p);
@@ -79,6 +80,83 @@ __global__ void __launch_bounds__(256) k_wgrad(const TA* __restrict__ in, const 
       if (co < cout && acc[i][j] != 0.f) atomicAdd(dw + ((long long)k * cin + ci) * cout + co, acc[i][j]);
     }
   }
+}
+
+// bf16 tensor-core variant (legacy mma.sync path through nvcuda::wmma; A is consumed transposed straight from the
+// row-major gathered tile: element (m = ci, k = row) of A^T lives at As[row][ci] = column-major with ld = WGT_LD).
+// CTA = 4 warps, 64 x 64 tile of dW[k]; each warp 32 x 32 (2 x 2 fragments); 64 gathered rows per iteration.
+#define WGT_ROWS 64
+#define WGT_LD 72  // 64 + 8 bf16 of padding: ldmatrix rows land in different banks
+
+__global__ void __launch_bounds__(128) k_wgrad_wmma(const __nv_bfloat16* __restrict__ in,
+                                                    const __nv_bfloat16* __restrict__ dout, const int* __restrict__ nbr,
+                                                    int ld, int n_out, int cin, int cout, int rows_per_cta,
+                                                    float* __restrict__ dw) {
+  using namespace nvcuda;
+  __shared__ __align__(32) __nv_bfloat16 As[WGT_ROWS * WGT_LD];
+  __shared__ __align__(32) __nv_bfloat16 Gs[WGT_ROWS * WGT_LD];
+  __shared__ __align__(32) float Cs[4][16 * 16];
+  __shared__ int s_idx[WGT_ROWS];
+  const int k = blockIdx.z;
+  const int tiles_co = cout / 64;
+  const int ci0 = (blockIdx.y / tiles_co) * 64, co0 = (blockIdx.y % tiles_co) * 64;
+  const int r_begin = blockIdx.x * rows_per_cta, r_end = min(r_begin + rows_per_cta, n_out);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int wm = (warp >> 1) * 32, wn = (warp & 1) * 32;
+  wmma::fragment<wmma::accumulator, 16, 16, 16, float> acc[2][2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 2; ++j) wmma::fill_fragment(acc[i][j], 0.f);
+  for (int r0 = r_begin; r0 < r_end; r0 += WGT_ROWS) {
+    __syncthreads();
+    if (tid < WGT_ROWS) {
+      const int o = r0 + tid;
+      s_idx[tid] = (o < r_end) ? (nbr ? nbr[(long long)k * ld + o] : o) : -1;
+    }
+    __syncthreads();
+    // 64 rows x 8 chunks of 16 B for each operand: 512 chunks, 4 per thread
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int e = tid + u * 128, rr = e >> 3, ch = e & 7;
+      const int src = s_idx[rr];
+      uint4 a = make_uint4(0u, 0u, 0u, 0u), g = make_uint4(0u, 0u, 0u, 0u);
+      if (src >= 0) {
+        a = __ldg(reinterpret_cast<const uint4*>(in + (long long)src * cin + ci0) + ch);
+        g = __ldg(reinterpret_cast<const uint4*>(dout + (long long)(r0 + rr) * cout + co0) + ch);
+      }
+      *reinterpret_cast<uint4*>(&As[rr * WGT_LD + ch * 8]) = a;
+      *reinterpret_cast<uint4*>(&Gs[rr * WGT_LD + ch * 8]) = g;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < WGT_ROWS; kk += 16) {
+      wmma::fragment<wmma::matrix_a, 16, 16, 16, __nv_bfloat16, wmma::col_major> fa[2];
+      wmma::fragment<wmma::matrix_b, 16, 16, 16, __nv_bfloat16, wmma::row_major> fb[2];
+#pragma unroll
+      for (int i = 0; i < 2; ++i) wmma::load_matrix_sync(fa[i], &As[kk * WGT_LD + wm + i * 16], WGT_LD);
+#pragma unroll
+      for (int j = 0; j < 2; ++j) wmma::load_matrix_sync(fb[j], &Gs[kk * WGT_LD + wn + j * 16], WGT_LD);
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) wmma::mma_sync(acc[i][j], fa[i], fb[j], acc[i][j]);
+    }
+  }
+  // fragments -> smem -> fp32 atomics into dW[k]
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      wmma::store_matrix_sync(Cs[warp], acc[i][j], 16, wmma::mem_row_major);
+      __syncwarp();
+      for (int e = lane; e < 256; e += 32) {
+        const int ci = ci0 + wm + i * 16 + (e >> 4), co = co0 + wn + j * 16 + (e & 15);
+        const float v = Cs[warp][e];
+        if (v != 0.f) atomicAdd(dw + ((long long)k * cin + ci) * cout + co, v);
+      }
+      __syncwarp();
+    }
 }
 
 // max-pool backward: dx[arg[o, c], c] += dy[o, c]
@@ -364,6 +442,17 @@ int b2_conv_wgrad(const void* in, int a_dtype, const void* dout, int g_dtype, co
   if (rows_per < 256) rows_per = 256;
   rows_per = (rows_per + WG_ROWS - 1) / WG_ROWS * WG_ROWS;
   dim3 grid((unsigned)((n_out + rows_per - 1) / rows_per), tiles, kvol);
+  if (a_dtype == 1 && g_dtype == 1 && cin % 64 == 0 && cout % 64 == 0) {
+    long long c2 = (148ll * 8 + (long long)tiles * kvol - 1) / ((long long)tiles * kvol);
+    long long rp = (n_out + (c2 < 1 ? 1 : c2) - 1) / (c2 < 1 ? 1 : c2);
+    if (rp < 1024) rp = 1024;
+    rp = (rp + WGT_ROWS - 1) / WGT_ROWS * WGT_ROWS;
+    dim3 g2((unsigned)((n_out + rp - 1) / rp), tiles, kvol);
+    k_wgrad_wmma<<<g2, 128, 0, st>>>((const __nv_bfloat16*)in, (const __nv_bfloat16*)dout, nbr, (int)ld, (int)n_out, cin,
+                                     cout, (int)rp, dw);
+    B2_LAUNCH_CHECK();
+    return B2_OK;
+  }
 #define WG_GO(TA, TG) \
   k_wgrad<TA, TG><<<grid, 256, 0, st>>>((const TA*)in, (const TG*)dout, nbr, (int)ld, (int)n_out, cin, cout, (int)rows_per, dw)
   if (a_dtype == 0 && g_dtype == 0) WG_GO(float, float);

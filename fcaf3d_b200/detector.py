@@ -249,10 +249,12 @@ class Fcaf3DNeckWithHead(nn.Module):
         reg_distance = torch.exp(scale(reg_final[:, :6]))
         bbox_pred = torch.cat((reg_distance, reg_final[:, 6:]), dim=1)
         centernesses, bbox_preds, cls_scores = [], [], []
-        for perm in x.decomposition_permutations:
-            centernesses.append(centerness[perm])
-            bbox_preds.append(bbox_pred[perm])
-            cls_scores.append(cls_score[perm])
+        m = x._map()
+        for b in range(m.num_batches):   # rows of a scene are contiguous: slices instead of index tensors
+            sl = slice(m.off_host[b], m.off_host[b + 1])
+            centernesses.append(centerness[sl])
+            bbox_preds.append(bbox_pred[sl])
+            cls_scores.append(cls_score[sl])
         points = [p * self.voxel_size for p in x.decomposed_coordinates]
         return centernesses, bbox_preds, cls_scores, points, prune_scores
 

@@ -527,7 +527,7 @@ class MinkowskiPruning(MinkowskiModuleBase):
     def forward(self, x, mask):
         cm = x.coordinate_manager
         key, m8, pos, n_out = cm.prune(x.coordinate_map_key, mask.contiguous())
-        f = x.F[mask.bool()] if AG.wants_grad(x.F) else ops.gather_rows(x.F, m8, pos, n_out)
+        f = AG.PruneFn.apply(x.F, m8, pos, n_out) if AG.wants_grad(x.F) else ops.gather_rows(x.F, m8, pos, n_out)
         return SparseTensor(f, coordinate_map_key=key, coordinate_manager=cm)
 
 
@@ -567,13 +567,20 @@ class MinkowskiInstanceNorm(MinkowskiModuleBase):
         m = x._map()
         f = x.F.contiguous()
         if AG.wants_grad(f, self.weight, self.bias):
-            # differentiable per-scene statistics (ME: global pooling + broadcast, both with autograd)
-            b = m.coords[:, 0].long()
-            cnt = torch.bincount(b, minlength=m.num_batches).clamp(min=1).to(f.dtype).unsqueeze(1)
-            mean = torch.zeros((m.num_batches, f.shape[1]), dtype=f.dtype, device=f.device).index_add(0, b, f) / cnt
-            xc = f - mean[b]
-            var = torch.zeros_like(mean).index_add(0, b, xc * xc) / cnt
-            out = xc / torch.sqrt(var[b] + self.eps) * self.weight + self.bias
+            # differentiable per-scene statistics (ME: global pooling + broadcast, both with autograd).  Rows of a
+            # scene are contiguous, so plain slices are used: indexing the [B, C] statistics with the per-row batch
+            # index would make autograd accumulate ~100k duplicate rows per scene in its backward
+            outs = []
+            for bi in range(m.num_batches):
+                fs = f[m.off_host[bi]:m.off_host[bi + 1]]
+                if fs.shape[0] == 0:
+                    outs.append(fs)
+                    continue
+                mean = fs.mean(0, keepdim=True)
+                xc = fs - mean
+                var = (xc * xc).mean(0, keepdim=True)
+                outs.append(xc / torch.sqrt(var + self.eps) * self.weight + self.bias)
+            out = torch.cat(outs, 0)
             if act == ops.ACT_RELU:
                 out = torch.relu(out)
             return SparseTensor(out, coordinate_map_key=x.coordinate_map_key, coordinate_manager=x.coordinate_manager)
