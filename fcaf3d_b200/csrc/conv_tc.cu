@@ -11,84 +11,8 @@
 // (reference call sites: me_resnet.py:66-78 BasicBlock convs, fcaf3d_neck_with_head.py:52,60-69).
 #include "common.cuh"
 
-#define TC_BM 128
-#define TC_BK 64
-#define TC_PRODUCERS 256
-#define TC_THREADS 288
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  const uint32_t addr = smem_u32(bar);
-  uint32_t ok;
-  do {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok)
-        : "r"(addr), "r"(parity)
-        : "memory");
-  } while (!ok);
-}
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
-}
-// the mbarrier receives one arrival from this thread once all of its earlier cp.async copies have landed
-__device__ __forceinline__ void cp_async_arrive_noinc(uint64_t* bar) {
-  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() {
-  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
-}
-__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
-               : "memory");
-}
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
-                                          uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-// K-major, 128-byte swizzle, 8-row atoms 1024 B apart (SBO); descriptor version 1 (sm_100)
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
-  uint64_t d = 0;
-  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
-  d |= (uint64_t)1 << 16;             // leading byte offset (unused for swizzled K-major)
-  d |= (uint64_t)(1024 >> 4) << 32;   // stride byte offset
-  d |= (uint64_t)1 << 46;             // version
-  d |= (uint64_t)2 << 61;             // SWIZZLE_128B
-  return d;
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
-      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr)
-      : "memory");
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
+#include "tc_common.cuh"
+#include <stdlib.h>
 
 template <int BN, int ST>
 struct TcCfg {
@@ -327,6 +251,11 @@ static int launch_tc(const void* in, const void* wt, const int* nbr, long long l
   return B2_OK;
 }
 
+int b2_conv_tc2_dispatch(const void* in, const void* wt, const int* nbr, long long ld, const unsigned int* tile_mask,
+                         long long n_out, int cin, int cout, int kvol, const float* bias, const float* scale,
+                         const float* shift, const void* residual, int act, int ch_mod, void* out, int out_dtype,
+                         cudaStream_t st);
+
 extern "C" int b2_conv_tc(const void* in_bf16, const void* wt_bf16, const int* nbr, long long ld,
                           const unsigned int* tile_mask, long long n_out, int cin, int cout, int kvol, const float* bias,
                           const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
@@ -339,6 +268,13 @@ extern "C" int b2_conv_tc(const void* in_bf16, const void* wt_bf16, const int* n
   B2_CHECK_ARG((scale == nullptr) == (shift == nullptr), "scale and shift come together");
   if (n_out == 0) return B2_OK;
   cudaStream_t st = (cudaStream_t)stream;
+  // two row tiles per CTA sharing each weight tile (conv_tc2.cu) halve the weight traffic but also halve the CTA count;
+  // measured on B200 it is 10-100 % SLOWER on every FCAF3D layer shape (profiles/r01_step2_summary.md), so it is
+  // opt-in (B2_TC2=1) and kept for the A/B record only
+  static const bool use_tc2 = (getenv("B2_TC2") && atoi(getenv("B2_TC2")) == 1);
+  if (use_tc2 && cout % 64 == 0 && n_out > TC_BM)
+    return b2_conv_tc2_dispatch(in_bf16, wt_bf16, nbr, ld, tile_mask, n_out, cin, cout, kvol, bias, scale, shift,
+                                residual, act, ch_mod, out, out_dtype, st);
   const bool wide = (cout % 128 == 0);
   const bool mid = (cout % 64 == 0);
 #define TC_GO(BN, T)                                                                                               \

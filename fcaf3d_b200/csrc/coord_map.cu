@@ -285,6 +285,21 @@ __global__ void k_batch_offsets(const int* __restrict__ coords, int n, int nb, i
   for (int b = prev + 1; b <= cur && b <= nb; ++b) offsets[b] = i;
 }
 
+// same, with the row count read from device memory (so the host needs no round trip before launching it)
+__global__ void k_batch_offsets_dev(const int* __restrict__ coords, const int* __restrict__ n_ptr, int nb,
+                                    int* __restrict__ offsets, int* err) {
+  const int n = *n_ptr;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i > n) return;
+  const int prev = (i == 0) ? -1 : coords[4 * (long long)(i - 1)];
+  const int cur = (i == n) ? nb : coords[4 * (long long)i];
+  if (i < n && (cur < prev || cur >= nb || cur < 0)) {
+    atomicExch(err, 2);
+    return;
+  }
+  for (int b = prev + 1; b <= cur && b <= nb; ++b) offsets[b] = i;
+}
+
 // union: flags of b-rows missing from a
 __global__ void k_union_probe(const B2Slot* __restrict__ a_table, unsigned int cap_mask, const int* __restrict__ b_coords,
                               int nb_rows, int* __restrict__ found, uint8_t* __restrict__ missing) {
@@ -498,6 +513,16 @@ int b2_map_children(const int* coords, long long n, int half, int* out_coords, v
 int b2_batch_offsets(const int* coords, long long n, int num_batches, int* offsets, int* err, void* stream) {
   B2_CHECK_ARG(num_batches > 0 && num_batches < 1023, "num_batches out of range");
   k_batch_offsets<<<b2_div_up(n + 1, 256), 256, 0, (cudaStream_t)stream>>>(coords, (int)n, num_batches, offsets, err);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+// row count taken from device memory (*n_dev <= max_n): lets the caller fetch count and offsets with ONE host read
+int b2_batch_offsets_dev(const int* coords, const int* n_dev, long long max_n, int num_batches, int* offsets, int* err,
+                         void* stream) {
+  B2_CHECK_ARG(num_batches > 0 && num_batches < 1023, "num_batches out of range");
+  k_batch_offsets_dev<<<b2_div_up(max_n + 1, 256), 256, 0, (cudaStream_t)stream>>>(coords, n_dev, num_batches, offsets,
+                                                                                 err);
   B2_LAUNCH_CHECK();
   return B2_OK;
 }

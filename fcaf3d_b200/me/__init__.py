@@ -109,11 +109,11 @@ class CoordinateManager:
         else:
             nb = 1
         self.num_batches = max(self.num_batches, nb)
-        out_coords, unique_index, inverse, table, cap, n_out = ops.map_build(coords, 0)
+        out_coords, unique_index, inverse, table, cap, n_out, off = ops.map_build(coords, 0, self.num_batches)
         key = CoordinateMapKey(ts, string_id)
         if key in self._maps:
             key = self._fresh_id(ts)
-        self._maps[key] = _Map(out_coords.contiguous(), ts, self.num_batches, table, cap)
+        self._maps[key] = _Map(out_coords.contiguous(), ts, self.num_batches, table, cap, off=off)
         unique_index = unique_index.long()
         inverse = inverse.long()
         if perm is not None:
@@ -131,11 +131,11 @@ class CoordinateManager:
             return self._stride_cache[ck]
         src = self._maps[in_key]
         ts_out = src.ts * s
-        out_coords, _, inverse, table, cap, _ = ops.map_build(src.coords, ts_out)
+        out_coords, _, inverse, table, cap, _, off = ops.map_build(src.coords, ts_out, self.num_batches)
         key = CoordinateMapKey(ts_out, "")
         if key in self._maps:
             key = self._fresh_id(ts_out)
-        m = _Map(out_coords.contiguous(), ts_out, self.num_batches, table, cap)
+        m = _Map(out_coords.contiguous(), ts_out, self.num_batches, table, cap, off=off)
         m.parent_of = {in_key: inverse}
         self._maps[key] = m
         self._stride_cache[ck] = key
@@ -158,19 +158,29 @@ class CoordinateManager:
         if a.ts != b.ts:
             raise B2Error("union of maps with different tensor strides")
         table, cap = a.ensure_table()
-        out_coords, dst_a, dst_b, n = ops.map_union(table, cap, a.coords, a.off_dev, b.coords, b.off_dev)
+        out_coords, dst_a, dst_b, n, off = ops.map_union(table, cap, a.coords, a.off_dev, b.coords, b.off_dev,
+                                                         self.num_batches)
         key = self._fresh_id(a.ts)
-        self._maps[key] = _Map(out_coords.contiguous(), a.ts, self.num_batches)
+        self._maps[key] = _Map(out_coords.contiguous(), a.ts, self.num_batches, off=off)
         return key, dst_a, dst_b
 
     def prune(self, in_key, mask):
         src = self._maps[in_key]
         m8 = mask.view(torch.uint8) if mask.dtype == torch.bool else mask
         pos, total = ops.scan_mask(m8)
-        n_out = ops.read_ints(total)[0]
+        # batch offsets of the pruned map = scan position of every scene's first row; fetched with the row count
+        nb = self.num_batches
+        if src.n > 0:
+            first = src.off_dev[:nb]
+            off = torch.where(first < src.n, pos[first.clamp(max=src.n - 1).long()], total.expand(nb))
+            off_dev = torch.cat((off, total)).to(torch.int32)
+        else:
+            off_dev = torch.zeros((nb + 1,), dtype=torch.int32, device=m8.device)
+        off_host = ops.read_ints(off_dev)
+        n_out = off_host[-1]
         coords = ops.gather_coords(src.coords, m8, pos, n_out)
         key = self._fresh_id(src.ts)
-        self._maps[key] = _Map(coords, src.ts, self.num_batches)
+        self._maps[key] = _Map(coords, src.ts, self.num_batches, off=(off_dev, off_host))
         return key, m8, pos, n_out
 
     # -- queries -----------------------------------------------------------------------------

@@ -52,9 +52,10 @@ def quantize_points(points_list, voxel_size, feat_div=255.0):
     return coords, feats
 
 
-def map_build(coords, quant=0):
+def map_build(coords, quant=0, num_batches=0):
     """Dedup (first occurrence wins, first-occurrence order).  Returns
-    (out_coords[n_out,4], unique_index[n_out], inverse_map[n], table, cap, n_out)."""
+    (out_coords[n_out,4], unique_index[n_out], inverse_map[n], table, cap, n_out[, (off_dev, off_host)]).
+    With num_batches > 0 the batch offsets of the new map come back from the same single host read."""
     require_cuda(coords, "coords")
     n = int(coords.shape[0])
     dev = coords.device
@@ -62,16 +63,24 @@ def map_build(coords, quant=0):
     out_coords = torch.empty((n, 4), dtype=I32, device=dev)
     unique_index = torch.empty((n,), dtype=I32, device=dev)
     inverse = torch.empty((n,), dtype=I32, device=dev)
-    status = torch.zeros((2,), dtype=I32, device=dev)  # [n_out, err]
+    status = torch.zeros((2 + num_batches + 1,), dtype=I32, device=dev)  # [n_out, err, offsets...]
     ws_bytes = _lib.lib().b2_map_build_ws_bytes(n)
     ws = workspace(ws_bytes, dev)
     t0 = _prof_start()
     call("b2_map_build", ptr(coords), n, int(quant), ptr(table), cap, ptr(out_coords), ptr(unique_index), ptr(inverse),
          ptr(status), ptr(status) + 4, ptr(ws), ws.numel())
-    n_out, err = read_ints(status)
+    if num_batches > 0:
+        call("b2_batch_offsets_dev", ptr(out_coords), ptr(status), n, num_batches, ptr(status) + 8, ptr(status) + 4)
+    host = read_ints(status)
+    n_out, err = host[0], host[1]
     _prof_stop(t0, "hash_build", 0.0, 20.0 * n + 20.0 * n_out)
-    if err:
+    if err == 1:
         raise _lib.B2Error("coordinate outside the packed key range (batch < 1023, |xyz| < 131072)")
+    if err == 2:
+        raise _lib.B2Error("coordinate rows must be grouped by ascending batch index")
+    if num_batches > 0:
+        return (out_coords[:n_out], unique_index[:n_out], inverse, table, cap, n_out,
+                (status[2:3 + num_batches], host[2:3 + num_batches]))
     return out_coords[:n_out], unique_index[:n_out], inverse, table, cap, n_out
 
 
@@ -106,18 +115,23 @@ def batch_offsets(coords, num_batches):
     return buf[: num_batches + 1], host[: num_batches + 1]
 
 
-def map_union(a_table, a_cap, a_coords, a_off, b_coords, b_off):
+def map_union(a_table, a_cap, a_coords, a_off, b_coords, b_off, num_batches=0):
     dev = a_coords.device
     na, nb = int(a_coords.shape[0]), int(b_coords.shape[0])
     out_coords = torch.empty((na + nb, 4), dtype=I32, device=dev)
     dst_a = torch.empty((na,), dtype=I32, device=dev)
     dst_b = torch.empty((nb,), dtype=I32, device=dev)
-    n_out = torch.zeros((1,), dtype=I32, device=dev)
+    n_out = torch.zeros((2 + num_batches + 1,), dtype=I32, device=dev)  # [n, err, offsets...]
     ws_bytes = _lib.lib().b2_map_union_ws_bytes(nb)
     ws = workspace(ws_bytes, dev)
     call("b2_map_union", ptr(a_table), a_cap, ptr(a_coords), na, ptr(a_off), ptr(b_coords), nb, ptr(b_off),
          ptr(out_coords), ptr(dst_a), ptr(dst_b), ptr(n_out), ptr(ws), ws.numel())
-    n = read_ints(n_out)[0]
+    if num_batches > 0:
+        call("b2_batch_offsets_dev", ptr(out_coords), ptr(n_out), na + nb, num_batches, ptr(n_out) + 8, ptr(n_out) + 4)
+    host = read_ints(n_out)
+    n = host[0]
+    if num_batches > 0:
+        return out_coords[:n], dst_a, dst_b, n, (n_out[2:3 + num_batches], host[2:3 + num_batches])
     return out_coords[:n], dst_a, dst_b, n
 
 

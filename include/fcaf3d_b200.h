@@ -59,6 +59,9 @@ int b2_map_lookup(const void* table, long long cap, const int* query, long long 
 int b2_map_children(const int* coords, long long n, int half, int* out_coords, void* stream);
 /* offsets[b] = first row of batch b (offsets[num_batches] = n); *err = 2 if rows are not batch-grouped */
 int b2_batch_offsets(const int* coords, long long n, int num_batches, int* offsets, int* err, void* stream);
+/* same with the row count in device memory (*n_dev <= max_n): count + offsets can be fetched with one host read */
+int b2_batch_offsets_dev(const int* coords, const int* n_dev, long long max_n, int num_batches, int* offsets, int* err,
+                         void* stream);
 size_t b2_map_union_ws_bytes(long long nb);
 /* ME union_map (SparseTensor.__add__ with different keys, fcaf3d_neck_with_head.py:101): out = a U b, rows of
  * scene s = [a rows of s][b-only rows of s]; dst_a[na], dst_b[nb] give the output row of every input row. */
