@@ -328,8 +328,15 @@ def main():
     main_k = "conv_tc" if "conv_tc" in agg else "conv_cc"
     cnt, t_ms, fl, by = agg[main_k]
     peak = pk["bf16_tflops_sustained"] if main_k == "conv_tc" else 75.0
+    traffic = None
+    try:  # DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/conv_tc_traffic.json)
+        if main_k == "conv_tc" and args.workload == "scannet":
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "conv_tc_traffic.json")))["dram_bytes_per_launch"]
+    except Exception:
+        pass
     roofline = {"kernel": main_k, "bound": "tensor", "achieved": fl / t_ms / 1e9, "peak": peak, "unit": "TFLOP/s",
-                "frac": fl / t_ms / 1e9 / peak, "traffic": None, "peak_source": pk_kind,
+                "frac": fl / t_ms / 1e9 / peak, "traffic": traffic, "algorithmic_bytes_per_launch": by / cnt,
+                "peak_source": pk_kind,
                 "launches_per_step": cnt, "avg_launch_ms": t_ms / cnt, "share_of_step": t_ms / ms,
                 "algorithmic_flops_per_step": fl, "other_kernels": kernels}
 
