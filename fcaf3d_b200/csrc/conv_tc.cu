@@ -30,7 +30,8 @@ struct TcCfg {
 // hoisted (the producers are instruction-latency bound: a stage must cost them as few dependent instructions as possible).
 template <int BN, int ST, typename TOut>
 __global__ void __launch_bounds__(TC_THREADS)
-k_conv_tc(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict__ wt, const int* __restrict__ nbr, int ld,
+k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __restrict__ in, const int* __restrict__ nbr,
+          int ld,
           const unsigned int* __restrict__ tile_mask, int n_out, int cin, int cout, int kvol,
           const float* __restrict__ bias, const float* __restrict__ scale, const float* __restrict__ shift,
           const TOut* __restrict__ residual, int act, int ch_mod, TOut* __restrict__ out) {
@@ -53,7 +54,7 @@ k_conv_tc(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict_
 
   if (tid == 0) {
     for (int s = 0; s < S; ++s) {
-      mbar_init(&full_bar[s], TC_PRODUCERS);
+      mbar_init(&full_bar[s], TC_PRODUCERS + 1);  // producers' cp.async arrivals + the weight tile's expect_tx
       mbar_init(&empty_bar[s], 1);
     }
     mbar_init(accum_bar, 1);
@@ -100,8 +101,6 @@ k_conv_tc(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict_
     const int chunk16 = tid & 7, rsub = tid >> 3;  // rsub 0..31
     const uint32_t dst_off = (uint32_t)(rsub * 128 + ((chunk16 ^ (rsub & 7)) << 4));  // + 4096 per pass (32 rows)
     const __nv_bfloat16* in_thr = in + chunk16 * 8;
-    const __nv_bfloat16* w_thr = wt + (long long)(col0 + rsub) * cin + chunk16 * 8;
-    const long long w_pass = 32ll * cin;  // elements between two B passes
     const uint32_t smem_base = smem_u32(smem);
     int it = 0;
     for (int k = 0; k < kvol; ++k) {
@@ -115,16 +114,18 @@ k_conv_tc(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict_
         src[p] = in_thr + (r >= 0 ? (long long)r * cin : 0ll);
         nbytes[p] = r >= 0 ? 16u : 0u;
       }
-      const __nv_bfloat16* wk = w_thr + (long long)k * cout * cin;
       for (int c = 0; c < chunks; ++c, ++it) {
         const int s = it % S;
         mbar_wait(&empty_bar[s], ((uint32_t)(it / S) & 1u) ^ 1u);
         const uint32_t a_dst = smem_base + s * Cfg::STAGE_BYTES + dst_off;
-        const uint32_t b_dst = a_dst + Cfg::A_BYTES;
+        const uint32_t b_dst = smem_base + s * Cfg::STAGE_BYTES + Cfg::A_BYTES;
 #pragma unroll
         for (int p = 0; p < TC_BM / 32; ++p) cp_async16(a_dst + p * 4096, src[p] + c * TC_BK, nbytes[p]);
-#pragma unroll
-        for (int p = 0; p < BN / 32; ++p) cp_async16(b_dst + p * 4096, wk + p * w_pass + c * TC_BK, 16u);
+        // the weight slice W_k^T[col0 : col0+BN, c*64 : c*64+64] is ONE TMA tile load (completion counted in bytes)
+        if (tid == 0) {
+          mbar_expect_tx(&full_bar[s], (uint32_t)Cfg::B_BYTES);
+          tma_tile_2d(b_dst, &map_b, &full_bar[s], c * TC_BK, k * cout + col0);
+        }
         // asynchronous completion: nobody waits here, so all S stages can be in flight
         cp_async_arrive_noinc(&full_bar[s]);
       }
@@ -243,8 +244,11 @@ static int launch_tc(const void* in, const void* wt, const int* nbr, long long l
     B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
     configured = true;
   }
+  CUtensorMap map_b;
+  const int rc = b2_make_bf16_map(&map_b, wt, (long long)kvol * cout, cin, BN);
+  if (rc) return rc;
   dim3 grid(b2_div_up(n_out, TC_BM), cout / BN);
-  kern<<<grid, TC_THREADS, Cfg::SMEM, st>>>((const __nv_bfloat16*)in, (const __nv_bfloat16*)wt, nbr, (int)ld, tile_mask,
+  kern<<<grid, TC_THREADS, Cfg::SMEM, st>>>(map_b, (const __nv_bfloat16*)in, nbr, (int)ld, tile_mask,
                                             (int)n_out, cin, cout, kvol, bias, scale, shift, (const TOut*)residual, act,
                                             ch_mod, (TOut*)out);
   B2_LAUNCH_CHECK();
@@ -256,7 +260,12 @@ int b2_conv_tc2_dispatch(const void* in, const void* wt, const int* nbr, long lo
                          const float* shift, const void* residual, int act, int ch_mod, void* out, int out_dtype,
                          cudaStream_t st);
 
-extern "C" int b2_conv_tc(const void* in_bf16, const void* wt_bf16, const int* nbr, long long ld,
+int b2_conv_tma_dispatch(const void* in, long long n_in, const void* wt, const int* nbr, long long ld,
+                         const unsigned int* tile_mask, long long n_out, int cin, int cout, int kvol, const float* bias,
+                         const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
+                         int out_dtype, cudaStream_t st);
+
+extern "C" int b2_conv_tc(const void* in_bf16, long long n_in, const void* wt_bf16, const int* nbr, long long ld,
                           const unsigned int* tile_mask, long long n_out, int cin, int cout, int kvol, const float* bias,
                           const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
                           int out_dtype, void* stream) {
@@ -274,6 +283,11 @@ extern "C" int b2_conv_tc(const void* in_bf16, const void* wt_bf16, const int* n
   static const bool use_tc2 = (getenv("B2_TC2") && atoi(getenv("B2_TC2")) == 1);
   if (use_tc2 && cout % 64 == 0 && n_out > TC_BM)
     return b2_conv_tc2_dispatch(in_bf16, wt_bf16, nbr, ld, tile_mask, n_out, cin, cout, kvol, bias, scale, shift,
+                                residual, act, ch_mod, out, out_dtype, st);
+  // operand staging by TMA (gather4 + tile loads, conv_tma.cu) instead of per-thread cp.async; B2_TC_TMA=0/1 for A/B runs
+  static const bool use_tma = (getenv("B2_TC_TMA") && atoi(getenv("B2_TC_TMA")) == 1);
+  if (use_tma)
+    return b2_conv_tma_dispatch(in_bf16, n_in, wt_bf16, nbr, ld, tile_mask, n_out, cin, cout, kvol, bias, scale, shift,
                                 residual, act, ch_mod, out, out_dtype, st);
   const bool wide = (cout % 128 == 0);
   const bool mid = (cout % 64 == 0);

@@ -264,7 +264,7 @@ def sparse_conv(x, w, kmap, n_out, wt_bf16=None, bias=None, scale=None, shift=No
         nbytes = esz * (x.shape[0] * cin + kvol * cin * cout) + out.element_size() * n_out * cout + 4.0 * kvol * ld
     t0 = _prof_start()
     if use_tc:
-        call("b2_conv_tc", ptr(x), ptr(wt_bf16), ptr(nbr), ld, ptr(tmask), n_out, cin, cout, kvol, ptr(bias), ptr(scale),
+        call("b2_conv_tc", ptr(x), x.shape[0], ptr(wt_bf16), ptr(nbr), ld, ptr(tmask), n_out, cin, cout, kvol, ptr(bias), ptr(scale),
              ptr(shift), ptr(residual), act, ch_mod, ptr(out), DT[out_dtype])
     else:
         call("b2_conv_cc", ptr(x), DT[x.dtype], ptr(w), ptr(nbr), ld, ptr(tmask), n_out, cin, cout, kvol, ptr(bias),

@@ -91,8 +91,9 @@ int b2_conv_cc(const void* in, int in_dtype, const float* w, const int* nbr, lon
                const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
                int out_dtype, void* stream);
 /* tcgen05 implicit GEMM, bf16 operands / fp32 TMEM accumulators; wt: [kvol, cout, cin] bf16 (K-major).
- * cin % 64 == 0, cout % 32 == 0.  Same epilogue as b2_conv_cc; out_dtype 0 or 1. */
-int b2_conv_tc(const void* in_bf16, const void* wt_bf16, const int* nbr, long long ld, const unsigned int* tile_mask,
+ * n_in = rows of the input feature matrix.  cin % 64 == 0, cout % 32 == 0.  Same epilogue as b2_conv_cc; out_dtype 0 or 1. */
+int b2_conv_tc(const void* in_bf16, long long n_in, const void* wt_bf16, const int* nbr, long long ld,
+               const unsigned int* tile_mask,
                long long n_out, int cin, int cout, int kvol, const float* bias, const float* scale, const float* shift,
                const void* residual, int act, int ch_mod, void* out, int out_dtype, void* stream);
 
