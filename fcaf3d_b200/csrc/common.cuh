@@ -29,7 +29,13 @@ void b2_set_error(const char* fmt, ...);
     }                                                                              \
   } while (0)
 
-#define B2_LAUNCH_CHECK() B2_CUDA(cudaGetLastError())
+// every kernel launch of the library is counted (bench.py reports the number launched inside its timed region)
+void b2_count_launches(int n);
+#define B2_LAUNCH_CHECK()          \
+  do {                             \
+    b2_count_launches(1);          \
+    B2_CUDA(cudaGetLastError());   \
+  } while (0)
 
 static inline int b2_div_up(long long a, long long b) { return (int)((a + b - 1) / b); }
 

@@ -30,6 +30,8 @@ extern "C" {
 const char* b2_last_error(void);
 int b2_version(void);
 int b2_device_sm_count(void);
+/* kernels launched by this library in this process so far (bench.py reports the count inside its timed region) */
+long long b2_launch_count(void);
 
 /* ---- coordinate manager (ME CoordinateMapManager; call sites single_stage_sparse.py:34-37,
  *      me_resnet.py:19-24,55-78, fcaf3d_neck_with_head.py:60-66,101,110-126) -------------------- */
