@@ -384,6 +384,62 @@ class SparseTensor:
         return "SparseTensor(F=%s, key=%r)" % (tuple(self._F.shape), self.coordinate_map_key)
 
 
+class TensorField:
+    """ME.TensorField: features on the ORIGINAL (unquantised) points plus the map to their voxels.
+
+    `sparse()` quantises (UNWEIGHTED_AVERAGE by default, as in ME), `SparseTensor.slice(field)` brings voxel features
+    back to the points.  Not used by the reference's FCAF3D files; provided for ME-surface completeness."""
+
+    def __init__(self, features, coordinates, tensor_stride=1,
+                 quantization_mode=SparseTensorQuantizationMode.UNWEIGHTED_AVERAGE, coordinate_manager=None, device=None):
+        if device is not None:
+            features, coordinates = features.to(device), coordinates.to(device)
+        if not coordinates.is_cuda:
+            raise B2Error("fcaf3d_b200 TensorField needs CUDA tensors (no CPU backend)")
+        self._F = features
+        self._C = coordinates
+        self.quantization_mode = quantization_mode
+        self.tensor_stride = _iso(tensor_stride)
+        self.coordinate_manager = coordinate_manager or CoordinateManager(D=coordinates.shape[1] - 1,
+                                                                          device=coordinates.device)
+        self.inverse_mapping = None
+        self.coordinate_map_key = None
+
+    @property
+    def F(self):
+        return self._F
+
+    features = F
+
+    @property
+    def C(self):
+        return self._C
+
+    coordinates = C
+
+    def sparse(self, quantization_mode=None):
+        mode = self.quantization_mode if quantization_mode is None else quantization_mode
+        c = torch.floor(self._C).to(torch.int32) if self._C.is_floating_point() else self._C.to(torch.int32)
+        st = SparseTensor(self._F, coordinates=c, tensor_stride=self.tensor_stride, quantization_mode=mode,
+                          coordinate_manager=self.coordinate_manager)
+        self.inverse_mapping, self.coordinate_map_key = st.inverse_mapping, st.coordinate_map_key
+        return st
+
+
+def _slice(self, field):
+    """SparseTensor.slice(TensorField): feature of every original point = feature of its voxel"""
+    if field.coordinate_map_key != self.coordinate_map_key or field.inverse_mapping is None:
+        raise B2Error("slice() needs the TensorField this tensor was created from (same coordinate map)")
+    out = TensorField(ops.index_rows(self._F.contiguous(), field.inverse_mapping.to(torch.int32)), field.C,
+                      tensor_stride=field.tensor_stride, quantization_mode=field.quantization_mode,
+                      coordinate_manager=self.coordinate_manager)
+    out.inverse_mapping, out.coordinate_map_key = field.inverse_mapping, field.coordinate_map_key
+    return out
+
+
+SparseTensor.slice = _slice
+
+
 # ------------------------------------------------------------------------------------------- modules
 _POLICY = {"dtype": torch.float32}
 

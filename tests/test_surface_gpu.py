@@ -1,0 +1,92 @@
+"""GPU: ME-surface completeness and edge cases beyond the default FCAF3D config — TensorField, 2-/3-scale variants,
+Bottleneck backbones, batches with an empty or tiny scene, negative / far coordinates."""
+import numpy as np
+import pytest
+import torch
+
+import oracle.me_cpu as OME
+from fcaf3d_b200 import me as ME
+from fcaf3d_b200.detector import MEResNet3D, build_fcaf3d
+from fcaf3d_b200.scenes import make_scene
+from fcaf3d_b200.testing import deterministic_init
+from util import rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+def test_tensor_field_quantise_and_slice(dev):
+    g = torch.Generator().manual_seed(0)
+    xyz = torch.rand(5000, 3, generator=g) * 20 - 10
+    coords = torch.cat([torch.zeros(5000, 1), xyz], 1).to(dev)
+    feats = torch.randn(5000, 4, generator=g).to(dev)
+    tf = ME.TensorField(feats, coords)
+    st = tf.sparse()
+    # UNWEIGHTED_AVERAGE: voxel feature = mean of its points
+    inv = tf.inverse_mapping
+    want = torch.zeros(len(st), 4, device=dev).index_add_(0, inv, feats)
+    want /= torch.bincount(inv, minlength=len(st)).unsqueeze(1)
+    assert torch.allclose(st.F, want, atol=1e-5)
+    assert torch.equal(st.C[inv], torch.floor(coords).int())
+    back = st.slice(tf)
+    assert back.F.shape == feats.shape and torch.equal(back.F, st.F[inv])
+
+
+@pytest.mark.parametrize("n_outs,voxel", [(2, 0.02), (3, 0.01)])
+def test_two_and_three_scale_variants(dev, n_outs, voxel):
+    """configs/fcaf3d/fcaf3d_{2,3}scales_scannet-3d-18class.py: fewer levels (and 2 cm voxels for the 2-scale one)"""
+    det = deterministic_init(build_fcaf3d("scannet", n_outs=n_outs, voxel_size=voxel), 0, cls_bias=0.0).to(dev).eval()
+    pts = [torch.from_numpy(make_scene("tiny", s, 3000)[0]).to(dev) for s in (1, 2)]
+    ME.set_compute_dtype(torch.float32)
+    with torch.no_grad():
+        fused = det.simple_test_fused(pts)
+        ref = det.simple_test(pts, [dict(), dict()])
+    assert len(fused) == 2
+    for (b, s, l), (rb, rs, rl) in zip(fused, ref):
+        assert b.shape[1] == 6 and abs(len(b) - len(rb)) <= 2 and len(b) > 0
+
+
+def test_bottleneck_backbone_runs_and_matches_unfused(dev):
+    net = MEResNet3D(3, 50, n_outs=2).to(dev).eval()
+    net.init_weights()
+    pts = make_scene("tiny", 3, 2000)[0]
+    c = torch.from_numpy(np.concatenate([np.zeros((len(pts), 1)), np.floor(pts[:, :3] / 0.02)], 1)).int().to(dev)
+    x = ME.SparseTensor(torch.from_numpy(pts[:, 3:] / 255).float().to(dev), coordinates=c)
+    with torch.no_grad():
+        a = net(x)
+        b = net.forward_fused(ME.SparseTensor(x.F, coordinate_map_key=x.coordinate_map_key,
+                                              coordinate_manager=x.coordinate_manager))
+    assert [t.F.shape[1] for t in a] == [256, 512]
+    for u, v in zip(a, b):
+        assert torch.equal(u.C, v.C) and rel_err(u.F, v.F) < 1e-4
+
+
+def test_batch_with_an_empty_and_a_tiny_scene(dev):
+    det = deterministic_init(build_fcaf3d("scannet", depth=14), 0, cls_bias=0.0).to(dev).eval()
+    full = torch.from_numpy(make_scene("tiny", 4, 3000)[0]).to(dev)
+    tiny = full[:40].contiguous()
+    empty = full[:0].contiguous()
+    ME.set_compute_dtype(torch.float32)
+    with torch.no_grad():
+        out = det.simple_test_fused([full, empty, tiny])
+        alone = det.simple_test_fused([full])
+    assert len(out) == 3 and len(out[1][0]) == 0
+    # scenes do not interact (InstanceNorm is per scene, BatchNorm uses running statistics in eval mode)
+    assert len(out[0][0]) == len(alone[0][0])
+    key = lambda t: sorted(zip(t[2].tolist(), [round(float(s), 5) for s in t[1].tolist()]))
+    assert key(out[0]) == key(alone[0])
+
+
+def test_negative_and_far_coordinates_match_oracle(dev):
+    g = torch.Generator().manual_seed(5)
+    c = torch.randint(-60000, 60000, (4000, 3), generator=g)
+    c[:2000] = c[:2000] // 4000 * 4  # a dense cluster with real neighbourhoods around the origin
+    coords = torch.cat([torch.zeros(4000, 1, dtype=torch.long), c], 1).int()
+    f = torch.randn(4000, 8, generator=g)
+    o = OME.SparseTensor(f, coordinates=coords)
+    x = ME.SparseTensor(f.to(dev), coordinates=coords.to(dev))
+    oc = OME.MinkowskiConvolution(8, 16, kernel_size=3, stride=2, dimension=3)
+    gc = ME.MinkowskiConvolution(8, 16, kernel_size=3, stride=2, dimension=3)
+    gc.load_state_dict(oc.state_dict())
+    with torch.no_grad():
+        y, ry = gc.to(dev)(x), oc(o)
+    assert torch.equal(y.C.cpu(), ry.C) and rel_err(y.F, ry.F) < 2e-5
