@@ -440,6 +440,143 @@ __global__ void __launch_bounds__(128) k_nms_reduce(const unsigned long long* __
   if (threadIdx.x == 0 && counts) counts[q] = kept;
 }
 
+// ---------------------------------------------------------------------------
+// Blocked greedy NMS: one CTA per segment walks its boxes in blocks of 64 (score order) and evaluates
+//   (1) the 64 x 64 diagonal tile of the block, (2) a serial resolve of the block against the boxes kept so far,
+//   (3) the rows of the boxes that were just KEPT against all later columns.
+// The reference's host loop only ever reads mask rows of kept boxes (iou3d_nms.cpp:121-131), so rows of suppressed
+// boxes are never needed: the keep-set is identical while the pair count drops from n^2/2 to ~n_kept * n / 2, and no
+// mask is materialised in global memory at all.  Per-pair arithmetic = the functions above.
+// ---------------------------------------------------------------------------
+__global__ void k_nms_prep(const float* __restrict__ boxes, int n, BoxPrep* __restrict__ prep) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) prep_box(boxes + (long long)i * 7, prep[i]);
+}
+
+template <bool ROTATED>
+__global__ void __launch_bounds__(256) k_nms_greedy(const float* __restrict__ boxes, const BoxPrep* __restrict__ prep,
+                                                    const int* __restrict__ seg_off, float thresh,
+                                                    uint8_t* __restrict__ keep, int* __restrict__ counts) {
+  __shared__ unsigned long long s_remv[RED_MAX_WORDS];
+  __shared__ unsigned long long s_diag[NMS_TILE];
+  __shared__ BoxPrep s_row[ROTATED ? NMS_TILE : 1];
+  __shared__ float4 s_rowedge[NMS_TILE];
+  __shared__ float2 s_rowsize[NMS_TILE];
+  __shared__ int s_klist[NMS_TILE];
+  __shared__ int s_nk;
+  const int q = blockIdx.x;
+  const int beg = seg_off[q], n = seg_off[q + 1] - beg;
+  const int T = (n + NMS_TILE - 1) / NMS_TILE;
+  const int t = threadIdx.x;
+  for (int j = t; j < T; j += blockDim.x) s_remv[j] = 0ull;
+  int kept = 0;
+  __syncthreads();
+  for (int blk = 0; blk < T; ++blk) {
+    const int rows = min(n - blk * NMS_TILE, NMS_TILE);
+    if (t < NMS_TILE) {
+      s_diag[t] = 0ull;
+      if (t < rows) {
+        const int gi = beg + blk * NMS_TILE + t;
+        if (ROTATED) {
+          s_row[t] = prep[gi];
+        } else {
+          const float* b = boxes + (long long)gi * 7;
+          s_rowedge[t] = make_float4(b[0] - b[3] / 2, b[0] + b[3] / 2, b[1] - b[4] / 2, b[1] + b[4] / 2);
+          s_rowsize[t] = make_float2(b[3], b[4]);
+        }
+      }
+    }
+    __syncthreads();
+    // (1) diagonal tile: thread (row r, quarter) -> 16 columns of the same block, only c > r
+    {
+      const int r = t & 63, quarter = t >> 6;
+      if (r < rows) {
+        unsigned long long bits = 0ull;
+        const int c1 = min(quarter * 16 + 16, rows);
+        for (int c = max(quarter * 16, r + 1); c < c1; ++c) {
+          float iou;
+          if (ROTATED) {
+            const BoxPrep& A = s_row[r];
+            const BoxPrep& B = s_row[c];
+            const float ddx = A.cx - B.cx, ddy = A.cy - B.cy;
+            const float reach = A.rad + B.rad + 0.05f;
+            if (thresh >= 0.f && ddx * ddx + ddy * ddy > reach * reach) continue;
+            iou = iou_rotated(A, B);
+          } else {
+            const float4 ae = s_rowedge[r], be = s_rowedge[c];
+            const float2 as = s_rowsize[r], bs = s_rowsize[c];
+            const float left = fmaxf(ae.x, be.x), right = fminf(ae.y, be.y);
+            const float top = fmaxf(ae.z, be.z), bottom = fminf(ae.w, be.w);
+            const float width = fmaxf(right - left, 0.f), height = fmaxf(bottom - top, 0.f);
+            if (thresh >= 0.f && !(width > 0.f && height > 0.f)) continue;
+            const float inter = width * height;
+            const float Sa = as.x * as.y;
+            const float Sb = bs.x * bs.y;
+            iou = inter / fmaxf(Sa + Sb - inter, NMS_EPS);
+          }
+          if (iou > thresh) bits |= 1ull << c;
+        }
+        if (bits) atomicOr(&s_diag[r], bits);
+      }
+    }
+    __syncthreads();
+    // (2) serial resolve of this block (same visiting order as the reference's host loop)
+    if (t == 0) {
+      unsigned long long cur = s_remv[blk], kw = 0ull;
+      int nk = 0;
+      for (int i = 0; i < rows; ++i) {
+        if (!((cur >> i) & 1ull)) {
+          kw |= 1ull << i;
+          cur |= s_diag[i];
+          s_klist[nk++] = i;
+        }
+      }
+      s_remv[blk] = ~kw;  // reused below as "not kept" bits of this block
+      s_nk = nk;
+    }
+    __syncthreads();
+    const int nk = s_nk;
+    kept += nk;
+    if (t < rows) keep[beg + blk * NMS_TILE + t] = (uint8_t)(((~s_remv[blk]) >> t) & 1ull);
+    // (3) rows of the boxes kept in this block against every later column
+    const int col0 = (blk + 1) * NMS_TILE;
+    const int rem = n - col0;
+    if (rem > 0 && nk > 0) {
+      const long long total = (long long)nk * rem;
+      for (long long e = t; e < total; e += blockDim.x) {
+        const int a = s_klist[(int)(e / rem)];
+        const int j = col0 + (int)(e % rem);
+        if ((s_remv[j >> 6] >> (j & 63)) & 1ull) continue;  // already suppressed: the bit cannot change the outcome
+        float iou;
+        if (ROTATED) {
+          const BoxPrep& A = s_row[a];
+          const BoxPrep B = prep[beg + j];
+          const float ddx = A.cx - B.cx, ddy = A.cy - B.cy;
+          const float reach = A.rad + B.rad + 0.05f;
+          if (thresh >= 0.f && ddx * ddx + ddy * ddy > reach * reach) continue;
+          iou = iou_rotated(A, B);
+        } else {
+          const float* b = boxes + (long long)(beg + j) * 7;
+          const float4 ae = s_rowedge[a];
+          const float2 as = s_rowsize[a];
+          const float4 be = make_float4(b[0] - b[3] / 2, b[0] + b[3] / 2, b[1] - b[4] / 2, b[1] + b[4] / 2);
+          const float left = fmaxf(ae.x, be.x), right = fminf(ae.y, be.y);
+          const float top = fmaxf(ae.z, be.z), bottom = fminf(ae.w, be.w);
+          const float width = fmaxf(right - left, 0.f), height = fmaxf(bottom - top, 0.f);
+          if (thresh >= 0.f && !(width > 0.f && height > 0.f)) continue;
+          const float inter = width * height;
+          const float Sa = as.x * as.y;
+          const float Sb = b[3] * b[4];
+          iou = inter / fmaxf(Sa + Sb - inter, NMS_EPS);
+        }
+        if (iou > thresh) atomicOr(&s_remv[j >> 6], 1ull << (j & 63));
+      }
+    }
+    __syncthreads();
+  }
+  if (t == 0 && counts) counts[q] = kept;
+}
+
 // pairwise BEV IoU / overlap matrices (reference: boxes_iou_bev_gpu / boxes_overlap_bev_gpu,
 // iou3d_nms_kernel.cu:236-265)
 __global__ void k_pair_matrix(const float* __restrict__ a, int na, const float* __restrict__ b, int nb, int mode,
@@ -523,6 +660,41 @@ int b2_nms_batched(const float* boxes, const float* scores, const int* seg_off, 
     B2_LAUNCH_CHECK();
   }
   k_nms_reduce<<<nseg, 128, 0, st>>>(mask, seg_off, mask_off, keep, counts);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+size_t b2_nms_greedy_ws_bytes(long long n, int rotated) { return rotated ? (size_t)n * sizeof(BoxPrep) + 256 : 256; }
+
+// Same contract as b2_nms_batched (keep[n] in per-segment sorted order, counts[nseg]) without a suppression mask:
+// ws (b2_nms_greedy_ws_bytes) holds the per-box corner / trig data of the rotated flavour.
+int b2_nms_greedy_batched(const float* boxes, const float* scores, const int* seg_off, int nseg, long long n,
+                          int max_seg, float thresh, int rotated, int sort, float* sorted_boxes, int* order, void* ws,
+                          size_t ws_bytes, uint8_t* keep, int* counts, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (nseg == 0) return B2_OK;
+  B2_CHECK_ARG(max_seg <= RED_MAX_WORDS * NMS_TILE, "segment too long for the device reduce (%d)", max_seg);
+  if (ws_bytes < b2_nms_greedy_ws_bytes(n, rotated)) {
+    b2_set_error("b2_nms_greedy_batched workspace too small");
+    return B2_ERR_WS;
+  }
+  const float* sb = boxes;
+  if (sort) {
+    B2_CHECK_ARG(max_seg <= SORT_MAX, "segment longer than %d cannot be sorted in-kernel (%d)", SORT_MAX, max_seg);
+    k_nms_sort<<<nseg, 1024, 0, st>>>(boxes, scores, seg_off, sorted_boxes, order);
+    B2_LAUNCH_CHECK();
+    sb = sorted_boxes;
+  }
+  BoxPrep* prep = reinterpret_cast<BoxPrep*>(ws);
+  if (rotated) {
+    if (n > 0) {
+      k_nms_prep<<<b2_div_up(n, 128), 128, 0, st>>>(sb, (int)n, prep);
+      B2_LAUNCH_CHECK();
+    }
+    k_nms_greedy<true><<<nseg, 256, 0, st>>>(sb, prep, seg_off, thresh, keep, counts);
+  } else {
+    k_nms_greedy<false><<<nseg, 256, 0, st>>>(sb, prep, seg_off, thresh, keep, counts);
+  }
   B2_LAUNCH_CHECK();
   return B2_OK;
 }

@@ -361,12 +361,27 @@ def nms_plan(seg_off_host):
     return list(to), list(mo), words.value, mx.value
 
 
-def nms_batched(boxes, scores, seg_off_host, thresh, rotated, sort=True):
+NMS_GREEDY = True  # blocked greedy kernel (rows of kept boxes only); False = full mask + device reduce
+
+
+def nms_batched(boxes, scores, seg_off_host, thresh, rotated, sort=True, greedy=None):
     """boxes [n,7], scores [n] grouped into segments.  Returns (keep uint8 [n] in sorted order, order int32 [n]
     (segment-local source index of every sorted slot), sorted_boxes, counts int32 [nseg])."""
     dev = boxes.device
     n = int(boxes.shape[0])
     nseg = len(seg_off_host) - 1
+    if (NMS_GREEDY if greedy is None else greedy) and nseg > 0:
+        max_seg = max(seg_off_host[i + 1] - seg_off_host[i] for i in range(nseg))
+        so = torch.tensor(list(seg_off_host), dtype=I32, device=dev)
+        keep = torch.empty((n,), dtype=torch.uint8, device=dev)
+        counts = torch.zeros((nseg,), dtype=I32, device=dev)
+        sorted_boxes = torch.empty_like(boxes) if sort else boxes
+        order = torch.empty((n,), dtype=I32, device=dev) if sort else None
+        ws = workspace(_lib.lib().b2_nms_greedy_ws_bytes(n, int(bool(rotated))), dev, slot=2)
+        call("b2_nms_greedy_batched", ptr(boxes), ptr(scores), ptr(so), nseg, n, max_seg, float(thresh),
+             int(bool(rotated)), int(bool(sort)), ptr(sorted_boxes), ptr(order), ptr(ws), ws.numel(), ptr(keep),
+             ptr(counts))
+        return keep, order, sorted_boxes, counts
     tile_off, mask_off, words, max_seg = nms_plan(seg_off_host)
     plan = torch.tensor(list(seg_off_host) + tile_off, dtype=I32, device=dev)
     moff = torch.tensor(mask_off, dtype=torch.int64, device=dev)

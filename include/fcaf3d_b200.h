@@ -149,6 +149,12 @@ int b2_nms_batched(const float* boxes, const float* scores, const int* seg_off, 
                    const long long* mask_off, int nseg, int total_tiles, int max_seg, float thresh, int rotated,
                    int sort, float* sorted_boxes, int* order, unsigned long long* mask, uint8_t* keep, int* counts,
                    void* stream);
+/* same result as b2_nms_batched, computed block by block so that only rows of KEPT boxes are ever evaluated (the
+ * reference's host loop reads no others, iou3d_nms.cpp:121-131) and no mask is written to global memory */
+size_t b2_nms_greedy_ws_bytes(long long n, int rotated);
+int b2_nms_greedy_batched(const float* boxes, const float* scores, const int* seg_off, int nseg, long long n,
+                          int max_seg, float thresh, int rotated, int sort, float* sorted_boxes, int* order, void* ws,
+                          size_t ws_bytes, uint8_t* keep, int* counts, void* stream);
 /* mode 0 = boxes_overlap_bev_gpu, 1 = boxes_iou_bev_gpu, 2 = axis-aligned BEV IoU (iou_normal) */
 int b2_boxes_pair_matrix(const float* a, long long na, const float* b, long long nb, int mode, float* out,
                          void* stream);

@@ -24,7 +24,7 @@ def _our_mask(boxes, thr, rotated):
     """suppression words of one segment, laid out [n, T] like the reference (upper triangle only)."""
     n = boxes.shape[0]
     tile_off, mask_off, words, mx = ops.nms_plan([0, n])
-    keep, _, _, _ = ops.nms_batched(boxes, None, [0, n], thr, rotated, sort=False)
+    keep, _, _, _ = ops.nms_batched(boxes, None, [0, n], thr, rotated, sort=False, greedy=False)
     raw = ops.workspace(1, boxes.device, slot=2)[: words * 8].view(torch.int64).clone()
     return raw.view(n, -1) if n else raw.view(0, 0), keep
 
@@ -96,6 +96,23 @@ def test_batched_segments_equal_per_segment_calls(dev):
         assert got.tolist() == want.tolist(), i
         assert counts[i].item() == len(want)
         assert torch.equal(sorted_boxes[off[i]:off[i + 1]].cpu(), torch.from_numpy(boxes[i])[order[off[i]:off[i + 1]].cpu().long()])
+
+
+@pytest.mark.parametrize("rotated", [True, False])
+def test_blocked_greedy_kernel_equals_mask_and_reduce(dev, rotated):
+    """the two device algorithms (full mask + reduce vs rows-of-kept-boxes-only) give the same keep flags"""
+    sizes = [0, 1, 64, 65, 700, 4000, 130]
+    boxes, scores = [], []
+    for i, n in enumerate(sizes):
+        b, s = random_boxes(max(n, 1), 60 + i, rotated, room=(8.0, 7.0, 2.7))
+        boxes.append(b[:n]), scores.append(s[:n])
+    off = np.concatenate([[0], np.cumsum(sizes)]).tolist()
+    B = torch.from_numpy(np.concatenate(boxes)).to(dev)
+    S = torch.from_numpy(np.concatenate(scores)).to(dev)
+    for thr in (0.5, 0.1):
+        k1, o1, _, c1 = ops.nms_batched(B, S, off, thr, rotated, sort=True, greedy=True)
+        k2, o2, _, c2 = ops.nms_batched(B, S, off, thr, rotated, sort=True, greedy=False)
+        assert torch.equal(o1, o2) and torch.equal(k1, k2) and torch.equal(c1, c2)
 
 
 def test_idempotence_and_threshold_extremes_at_full_size(dev):

@@ -37,7 +37,7 @@ def test_two_calls_in_a_row_match_the_regular_entry_point(dev):
     torch.cuda.synchronize()
     for (boxes, rot), (keep, count) in zip(inputs, outs):
         n = boxes.shape[0]
-        want, _, _, wcount = ops.nms_batched(boxes, None, [0, n], 0.5, rot, sort=False)
+        want, _, _, wcount = ops.nms_batched(boxes, None, [0, n], 0.5, rot, sort=False, greedy=False)
         assert torch.equal(keep[:n], want), (n, rot)
         assert count.item() == wcount[0].item() == int(want.sum())
 
