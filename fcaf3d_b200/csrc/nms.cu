@@ -453,8 +453,10 @@ __global__ void k_nms_prep(const float* __restrict__ boxes, int n, BoxPrep* __re
   if (i < n) prep_box(boxes + (long long)i * 7, prep[i]);
 }
 
-template <bool ROTATED>
-__global__ void __launch_bounds__(256) k_nms_greedy(const float* __restrict__ boxes, const BoxPrep* __restrict__ prep,
+// NT threads per segment: 256 for the cheap axis-aligned pairs, 512 for the rotated ones (their update phase is the
+// long pole: a few kept rows x thousands of columns of polygon clipping per round)
+template <bool ROTATED, int NT>
+__global__ void __launch_bounds__(NT) k_nms_greedy(const float* __restrict__ boxes, const BoxPrep* __restrict__ prep,
                                                     const int* __restrict__ seg_off, float thresh,
                                                     uint8_t* __restrict__ keep, int* __restrict__ counts) {
   __shared__ unsigned long long s_remv[RED_MAX_WORDS];
@@ -487,13 +489,14 @@ __global__ void __launch_bounds__(256) k_nms_greedy(const float* __restrict__ bo
       }
     }
     __syncthreads();
-    // (1) diagonal tile: thread (row r, quarter) -> 16 columns of the same block, only c > r
+    // (1) diagonal tile: thread (row r, part) -> 64 / (NT / 64) columns of the same block, only c > r
     {
-      const int r = t & 63, quarter = t >> 6;
+      constexpr int PARTS = NT / 64, CPP = 64 / PARTS;
+      const int r = t & 63, part = t >> 6;
       if (r < rows) {
         unsigned long long bits = 0ull;
-        const int c1 = min(quarter * 16 + 16, rows);
-        for (int c = max(quarter * 16, r + 1); c < c1; ++c) {
+        const int c1 = min(part * CPP + CPP, rows);
+        for (int c = max(part * CPP, r + 1); c < c1; ++c) {
           float iou;
           if (ROTATED) {
             const BoxPrep& A = s_row[r];
@@ -691,9 +694,9 @@ int b2_nms_greedy_batched(const float* boxes, const float* scores, const int* se
       k_nms_prep<<<b2_div_up(n, 128), 128, 0, st>>>(sb, (int)n, prep);
       B2_LAUNCH_CHECK();
     }
-    k_nms_greedy<true><<<nseg, 256, 0, st>>>(sb, prep, seg_off, thresh, keep, counts);
+    k_nms_greedy<true, 512><<<nseg, 512, 0, st>>>(sb, prep, seg_off, thresh, keep, counts);
   } else {
-    k_nms_greedy<false><<<nseg, 256, 0, st>>>(sb, prep, seg_off, thresh, keep, counts);
+    k_nms_greedy<false, 256><<<nseg, 256, 0, st>>>(sb, prep, seg_off, thresh, keep, counts);
   }
   B2_LAUNCH_CHECK();
   return B2_OK;
