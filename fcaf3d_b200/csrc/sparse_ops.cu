@@ -44,6 +44,35 @@ __global__ void __launch_bounds__(128) k_kernel_map(const B2Slot* __restrict__ t
   if (threadIdx.x == 0) tile_mask[blockIdx.x] = m;
 }
 
+// Neighbour table of a CHILDREN map (rows 8*i + c, c = cx + 2*cy + 4*cz, all eight children of every parent present)
+// derived from the parent's 3^3 table without touching the hash: the neighbour of child c at offset d lies in the parent
+// at offset e = floor((c + d) / 2) and is that parent's child c' = (c + d) - 2e.
+__global__ void k_kernel_map_children(const int* __restrict__ pnbr, int pld, int n_parent, int* __restrict__ nbr, int ld,
+                                      unsigned int* __restrict__ tile_mask) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int k = blockIdx.y;  // child offset index, x fastest
+  if (t >= ld) return;
+  int out = -1;
+  if (t < 8ll * n_parent) {
+    const int i = (int)(t >> 3), c = (int)(t & 7);
+    const int d[3] = {k % 3 - 1, (k / 3) % 3 - 1, k / 9 - 1};
+    const int cc[3] = {c & 1, (c >> 1) & 1, (c >> 2) & 1};
+    int ke = 0, cnew = 0;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      const int s = cc[a] + d[a];              // -1 .. 2
+      const int e = (s < 0) ? -1 : (s > 1 ? 1 : 0);
+      const int cn = s - 2 * e;
+      ke += (e + 1) * (a == 0 ? 1 : (a == 1 ? 3 : 9));
+      cnew += cn << a;
+    }
+    const int p = __ldg(pnbr + (long long)ke * pld + i);
+    out = (p >= 0) ? 8 * p + cnew : -1;
+  }
+  nbr[(long long)k * ld + t] = out;
+  if (k == 0 && (t & 127) == 0) tile_mask[t >> 7] = 0x7FFFFFFu;  // dense blocks: every offset is in use (conservative)
+}
+
 // ---------------------------------------------------------------------------
 // CUDA-core implicit-GEMM sparse convolution (the fp32-parity path and the path
 // for narrow layers: Cin = 3 stem, Cout <= 32 heads).  Output-stationary:
@@ -449,6 +478,18 @@ int b2_kernel_map(const void* in_table, long long cap, const int* out_coords, lo
   if (ksize == 1) k_kernel_map<1><<<G, 128, 0, st>>>(t, m, out_coords, (int)n_out, step, nbr, (int)ld, tile_mask);
   if (ksize == 2) k_kernel_map<2><<<G, 128, 0, st>>>(t, m, out_coords, (int)n_out, step, nbr, (int)ld, tile_mask);
   if (ksize == 3) k_kernel_map<3><<<G, 128, 0, st>>>(t, m, out_coords, (int)n_out, step, nbr, (int)ld, tile_mask);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+// 3^3 stride-1 table of a children map (b2_map_children order) from the parent map's 3^3 stride-1 table
+int b2_kernel_map_children(const int* parent_nbr, long long parent_ld, long long n_parent, int* nbr, long long ld,
+                           unsigned int* tile_mask, void* stream) {
+  B2_CHECK_ARG(ld % 128 == 0 && ld >= 8 * n_parent, "ld must be 8 * n_parent rounded up to 128");
+  if (ld == 0) return B2_OK;
+  dim3 grid(b2_div_up(ld, 256), 27);
+  k_kernel_map_children<<<grid, 256, 0, (cudaStream_t)stream>>>(parent_nbr, (int)parent_ld, (int)n_parent, nbr, (int)ld,
+                                                               tile_mask);
   B2_LAUNCH_CHECK();
   return B2_OK;
 }

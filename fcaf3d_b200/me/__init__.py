@@ -150,7 +150,9 @@ class CoordinateManager:
         coords = ops.map_children(src.coords, ts_out)
         off_host = [8 * o for o in src.off_host]
         key = self._fresh_id(ts_out)
-        self._maps[key] = _Map(coords, ts_out, self.num_batches, off=(src.off_dev * 8, off_host))
+        m = _Map(coords, ts_out, self.num_batches, off=(src.off_dev * 8, off_host))
+        m.children_of = in_key   # all 8 children of every parent, row 8 i + c: kernel maps can be derived, see kernel_map
+        self._maps[key] = m
         return key
 
     def union(self, key_a, key_b):
@@ -202,8 +204,14 @@ class CoordinateManager:
         km = self._kmaps.get(ck)
         if km is None:
             src, dst = self._maps[in_key], self._maps[out_key]
-            table, cap = src.ensure_table()
-            km = ops.kernel_map(table, cap, dst.coords, int(kernel_size), src.ts * int(dilation))
+            parent = getattr(src, "children_of", None)
+            if in_key == out_key and parent is not None and int(kernel_size) == 3 and int(dilation) == 1:
+                # map of ALL children of `parent` (generative transpose): derive the table from the parent's, no hash
+                pkm = self.kernel_map(parent, parent, 3, 1)
+                km = ops.kernel_map_children(pkm, self._maps[parent].n)
+            else:
+                table, cap = src.ensure_table()
+                km = ops.kernel_map(table, cap, dst.coords, int(kernel_size), src.ts * int(dilation))
             self._kmaps[ck] = km
         return km
 

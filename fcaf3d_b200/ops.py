@@ -201,6 +201,19 @@ def kernel_map(in_table, in_cap, out_coords, ksize, step):
     return KernelMap(nbr, ld, tile_mask, n_out, kvol)
 
 
+def kernel_map_children(parent_km, n_parent):
+    """3^3 table of the map of all children (rows 8 i + c) from the parent's 3^3 table, without hash probes."""
+    dev = parent_km.nbr.device
+    n_out = 8 * int(n_parent)
+    ld = (n_out + 127) // 128 * 128
+    nbr = torch.empty((27, ld), dtype=I32, device=dev)
+    tile_mask = torch.empty((max(ld // 128, 1),), dtype=I32, device=dev)
+    t0 = _prof_start()
+    call("b2_kernel_map_children", ptr(parent_km.nbr), parent_km.ld, int(n_parent), ptr(nbr), ld, ptr(tile_mask))
+    _prof_stop(t0, "kernel_map_children", 0.0, 4.0 * 27 * (n_parent + n_out))
+    return KernelMap(nbr, ld, tile_mask, n_out, 27)
+
+
 _TC_ENABLED = True
 
 # Optional per-launch profiling (bench.py): list of [name, start_event, end_event, algorithmic_flops, algorithmic_bytes]

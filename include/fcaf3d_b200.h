@@ -85,6 +85,10 @@ int b2_scatter_rows(const void* in, const int* dst, long long n, int c, int dtyp
  * tile_mask[o/128] bit k = some row of the 128-row tile has neighbour k.  ld = n_out rounded up to 128. */
 int b2_kernel_map(const void* in_table, long long cap, const int* out_coords, long long n_out, int ksize, int step,
                   int* nbr, long long ld, unsigned int* tile_mask, void* stream);
+/* 3^3 stride-1 table of a children map (rows 8*i + c as made by b2_map_children, all children present) derived from
+ * the parent map's 3^3 stride-1 table by index arithmetic, no hash probes; tile_mask is set to "all offsets" */
+int b2_kernel_map_children(const int* parent_nbr, long long parent_ld, long long n_parent, int* nbr, long long ld,
+                           unsigned int* tile_mask, void* stream);
 /* CUDA-core implicit GEMM (fp32 accumulate):
  *   out[o,:] = act((sum_k in[nbr[k][o],:] @ w[k] + bias) * scale + shift + residual[o,:]);  w: [kvol, cin, cout] fp32.
  * nbr == NULL: identity map (kvol == 1).  ch_mod > 0: epilogue channel = column % ch_mod. */

@@ -113,3 +113,26 @@ def test_kernel_map_bit_exact(dev, ksize, stride):
     assert km.tile_mask.cpu().numpy().astype(np.int64).tolist() == want.tolist()
     if ksize == 3 and stride == 1:
         assert torch.equal(km.nbr[13, :n_out].cpu(), torch.arange(n_out, dtype=torch.int32))  # centre = identity
+
+
+def test_children_kernel_map_derived_equals_hashed(dev):
+    """3^3 table of a generated (all-children) map: the table derived from the parent's table must equal the
+    hash-probed one and the oracle's; the derived tile mask is conservative (all 27 offsets)."""
+    c = surface_coords(4000, batch=3, seed=11)
+    x, o = _pair(c, dev)
+    cm, ocm = x.coordinate_manager, o.coordinate_manager
+    k4, ok4 = cm.stride(cm.stride(x.coordinate_map_key, 2), 2), ocm.stride(ocm.stride(o.coordinate_map_key, 2), 2)
+    g, og = cm.generate_children(k4), ocm.generate_children(ok4)
+    km = cm.kernel_map(g, g, 3)                                    # derived path (children_of is set)
+    n = cm.size(g)
+    assert n == 8 * cm.size(k4) and km.n_out == n
+    gm = cm.get_map(g)
+    table, cap = gm.ensure_table()
+    hashed = ops.kernel_map(table, cap, gm.coords, 3, gm.ts)
+    assert torch.equal(km.nbr[:, :n], hashed.nbr[:, :n])
+    assert bool((km.nbr[:, n:] == -1).all())
+    assert torch.equal(km.nbr[:, :n].cpu().long(), torch.from_numpy(ocm.neighbour_table(og, og, 3)))
+    assert bool(((km.tile_mask & hashed.tile_mask) == hashed.tile_mask).all())
+    # dilation 2 or another kernel size on the same map still takes the hash path
+    km2 = cm.kernel_map(g, g, 3, 2)
+    assert torch.equal(km2.nbr[:, :n].cpu().long(), torch.from_numpy(ocm.neighbour_table(og, og, 3, 2)))
