@@ -10,6 +10,7 @@
 //   sort_v                   lilanxiao/Rotated_IoU@3bdca6b cuda_op/sort_vert_kernel.cu (not vendored)
 #include "common.cuh"
 #include <mma.h>
+#include <stdlib.h>
 
 template <typename T>
 __device__ __forceinline__ float ldf(const T* p);
@@ -157,6 +158,64 @@ __global__ void __launch_bounds__(128) k_wgrad_wmma(const __nv_bfloat16* __restr
       }
       __syncwarp();
     }
+}
+
+// Narrow-input weight gradient (the stem: cin = 3, cout = 64, 27 offsets over ~92 k output rows per scene).
+// CTA = 256 threads = 64 output channels x 4 groups of kernel offsets (k = grp, grp + 4, ...: up to 7 per group);
+// a thread keeps its 7 x 4 partial sums in registers.  Per batch of 32 output rows the CTA stages the gathered
+// inputs as s_a[row][grp][7][4] (zero where the neighbour is absent) and dout as s_g[row][64]; the inner loop is
+// 7 broadcast LDS.128 + 1 LDS per 28 FMAs.  One fp32 atomic per (k, ci, co) and CTA at the end.
+#define WN_ROWS 32
+template <typename TA, typename TG>
+__global__ void __launch_bounds__(256) k_wgrad_narrow(const TA* __restrict__ in, const TG* __restrict__ dout,
+                                                      const int* __restrict__ nbr, int ld, int n_out, int cin, int cout,
+                                                      int kvol, int rows_per_cta, float* __restrict__ dw) {
+  __shared__ __align__(16) float s_a[WN_ROWS][4][7][4];
+  __shared__ float s_g[WN_ROWS][64];
+  const int tid = threadIdx.x, co = tid & 63, grp = tid >> 6;
+  const int r_begin = blockIdx.x * rows_per_cta, r_end = min(r_begin + rows_per_cta, n_out);
+  float acc[7][4];
+#pragma unroll
+  for (int i = 0; i < 7; ++i)
+#pragma unroll
+    for (int c = 0; c < 4; ++c) acc[i][c] = 0.f;
+  for (int e = tid; e < WN_ROWS * 4 * 7 * 4; e += 256) (&s_a[0][0][0][0])[e] = 0.f;  // slots of unused (k, ci) stay zero
+  for (int r0 = r_begin; r0 < r_end; r0 += WN_ROWS) {
+    __syncthreads();
+    for (int p = tid; p < kvol * WN_ROWS; p += 256) {
+      const int k = p / WN_ROWS, rr = p % WN_ROWS, o = r0 + rr;
+      const int src = (o < r_end) ? (nbr ? __ldg(nbr + (long long)k * ld + o) : o) : -1;
+      float* dst = &s_a[rr][k & 3][k >> 2][0];
+      for (int c = 0; c < cin; ++c) dst[c] = (src >= 0) ? ldf<TA>(in + (long long)src * cin + c) : 0.f;
+    }
+    for (int e = tid; e < WN_ROWS * 64; e += 256) {
+      const int rr = e >> 6, c = e & 63, o = r0 + rr;
+      s_g[rr][c] = (o < r_end && c < cout) ? ldf<TG>(dout + (long long)o * cout + c) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll 4
+    for (int rr = 0; rr < WN_ROWS; ++rr) {
+      const float g = s_g[rr][co];
+#pragma unroll
+      for (int i = 0; i < 7; ++i) {
+        const float4 a = *reinterpret_cast<const float4*>(&s_a[rr][grp][i][0]);
+        acc[i][0] = fmaf(a.x, g, acc[i][0]);
+        acc[i][1] = fmaf(a.y, g, acc[i][1]);
+        acc[i][2] = fmaf(a.z, g, acc[i][2]);
+        acc[i][3] = fmaf(a.w, g, acc[i][3]);
+      }
+    }
+  }
+  if (co < cout) {
+#pragma unroll
+    for (int i = 0; i < 7; ++i) {
+      const int k = grp + 4 * i;
+      if (k >= kvol) continue;
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        if (c < cin && acc[i][c] != 0.f) atomicAdd(dw + ((long long)k * cin + c) * cout + co, acc[i][c]);
+    }
+  }
 }
 
 // max-pool backward: dx[arg[o, c], c] += dy[o, c]
@@ -426,6 +485,9 @@ __global__ void k_sort_vertices(const float* __restrict__ vertices, const uint8_
   for (int j = cnt + 1; j < 9; ++j) out[j] = pad;
 }
 
+int b2_wgrad_tc_dispatch(const void* in, const void* dout, const int* nbr, long long ld, long long n_out, int cin,
+                         int cout, int kvol, float* dw, cudaStream_t st);
+
 extern "C" {
 
 // dw [kvol, cin, cout] fp32 must be zero-initialised by the caller; a_dtype / g_dtype: 0 = f32, 1 = bf16
@@ -442,6 +504,26 @@ int b2_conv_wgrad(const void* in, int a_dtype, const void* dout, int g_dtype, co
   if (rows_per < 256) rows_per = 256;
   rows_per = (rows_per + WG_ROWS - 1) / WG_ROWS * WG_ROWS;
   dim3 grid((unsigned)((n_out + rows_per - 1) / rows_per), tiles, kvol);
+  if (cin <= 4 && cout <= 64 && kvol <= 28) {
+    long long rp = b2_div_up(b2_div_up(n_out, 148ll * 4), (long long)WN_ROWS) * WN_ROWS;
+    if (rp < 8 * WN_ROWS) rp = 8 * WN_ROWS;
+    const unsigned gx = (unsigned)b2_div_up(n_out, rp);
+#define WN_GO(TA, TG) \
+  k_wgrad_narrow<TA, TG><<<gx, 256, 0, st>>>((const TA*)in, (const TG*)dout, nbr, (int)ld, (int)n_out, cin, cout, kvol, (int)rp, dw)
+    if (a_dtype == 0 && g_dtype == 0) WN_GO(float, float);
+    else if (a_dtype == 1 && g_dtype == 1) WN_GO(__nv_bfloat16, __nv_bfloat16);
+    else if (a_dtype == 0) WN_GO(float, __nv_bfloat16);
+    else WN_GO(__nv_bfloat16, float);
+#undef WN_GO
+    B2_LAUNCH_CHECK();
+    return B2_OK;
+  }
+  // tcgen05 path (wgrad_tc.cu); B2_WGRAD_WMMA=1 keeps the legacy mma.sync kernel below for A/B runs
+  static const bool legacy_wmma = (getenv("B2_WGRAD_WMMA") && atoi(getenv("B2_WGRAD_WMMA")) == 1);
+  const int c64n = cin / 64;
+  if (!legacy_wmma && a_dtype == 1 && g_dtype == 1 && cin % 64 == 0 && cout % 64 == 0 && (c64n & (c64n - 1)) == 0 &&
+      (nbr == nullptr || ld % 4 == 0))
+    return b2_wgrad_tc_dispatch(in, dout, nbr, ld, n_out, cin, cout, kvol, dw, st);
   if (a_dtype == 1 && g_dtype == 1 && cin % 64 == 0 && cout % 64 == 0) {
     long long c2 = (148ll * 8 + (long long)tiles * kvol - 1) / ((long long)tiles * kvol);
     long long rp = (n_out + (c2 < 1 ? 1 : c2) - 1) / (c2 < 1 ? 1 : c2);

@@ -35,7 +35,8 @@ def _pair(dev, c_in, seed=0, n_points=2000, batch=2):
     return x, o, fg, fo
 
 
-@pytest.mark.parametrize("cin,cout,k,stride", [(8, 16, 3, 1), (16, 8, 3, 2), (64, 64, 3, 1), (64, 128, 3, 2), (32, 64, 1, 2)])
+@pytest.mark.parametrize("cin,cout,k,stride", [(8, 16, 3, 1), (16, 8, 3, 2), (64, 64, 3, 1), (64, 128, 3, 2), (32, 64, 1, 2),
+                                                (3, 64, 3, 2), (4, 32, 3, 1)])
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 3e-2)])
 def test_conv_autograd(dev, cin, cout, k, stride, dtype, tol):
     x, o, fg, fo = _pair(dev, cin, seed=cin + k)
@@ -55,6 +56,27 @@ def test_conv_autograd(dev, cin, cout, k, stride, dtype, tol):
     assert rel_err(y.F.detach(), ry.F.detach()) < tol
     assert rel_err(fg.grad, fo.grad) < tol
     assert rel_err(gc.kernel.grad, oc.kernel.grad) < tol
+
+
+@pytest.mark.parametrize("cin,cout,k,stride,n_points", [(64, 64, 3, 1, 6000), (128, 128, 3, 1, 3000), (256, 64, 3, 2, 6000),
+                                                        (512, 128, 3, 1, 1500), (64, 128, 1, 1, 3000), (128, 192, 3, 1, 700)])
+def test_wgrad_tcgen05_matches_fp32_kernel(dev, cin, cout, k, stride, n_points):
+    """b2_conv_wgrad, bf16 operands: the tcgen05 kernel (MN-major operands, split over row chunks) against the fp32
+    CUDA-core kernel fed with the SAME bf16-rounded values; only the summation order differs: 2e-4 of max."""
+    from fcaf3d_b200 import autograd as AG
+    c = torch.from_numpy(surface_coords(n_points, 2, seed=cin + cout)).to(dev)
+    x0 = ME.SparseTensor(torch.zeros(len(c), 1, device=dev), coordinates=c)
+    cm, key = x0.coordinate_manager, x0.coordinate_map_key
+    okey = key if stride == 1 else cm.stride(key, stride)
+    km = cm.kernel_map(key, okey, k) if (k > 1 or stride > 1) else None
+    n_in, n_out = cm.size(key), cm.size(okey)
+    g = torch.Generator(device="cpu").manual_seed(3)
+    a = torch.randn(n_in, cin, generator=g).to(dev).to(torch.bfloat16)
+    d = torch.randn(n_out, cout, generator=g).to(dev).to(torch.bfloat16)
+    dw = AG.conv_wgrad(a, d, km, k ** 3, cin, cout)
+    ref = AG.conv_wgrad(a.float(), d.float(), km, k ** 3, cin, cout)
+    assert dw.shape == (k ** 3, cin, cout) and torch.isfinite(dw).all()
+    assert rel_err(dw, ref) < 2e-4
 
 
 def test_generative_pool_norm_union_autograd(dev):

@@ -50,3 +50,17 @@ for name in levels:
     gather = pairs * cin * 2 + (n + 127) // 128 * 27 * cin * cout * 2 * (1 if cout <= 128 else cout // 128)
     print("%-6s rows=%7d pairs=%9d (%.1f/row) C=%d->%d : %8.1f us  %7.1f TFLOP/s  L2->SM %6.0f GB/s" %
           (name, n, pairs, pairs / n, cin, cout, ms * 1000, flops / ms / 1e9, gather / ms / 1e6))
+    # weight gradient of the same layer (bf16 operands, fp32 dW)
+    from fcaf3d_b200.autograd import conv_wgrad  # noqa: E402
+    g = torch.randn(n, cout, device=dev).to(torch.bfloat16)
+    for _ in range(3):
+        dw = conv_wgrad(f, g, km, 27, cin, cout)
+    torch.cuda.synchronize()
+    s.record()
+    for _ in range(iters):
+        dw = conv_wgrad(f, g, km, 27, cin, cout)
+    e.record()
+    torch.cuda.synchronize()
+    ms = s.elapsed_time(e) / iters
+    print("%-6s   wgrad (incl. dW memset)                      : %8.1f us  %7.1f TFLOP/s  gathered %6.0f GB/s" %
+          (name, ms * 1000, flops / ms / 1e9, pairs * cin * 2 / ms / 1e6))
