@@ -35,34 +35,40 @@ class SparseConvFn(torch.autograd.Function):
         feats = feats.contiguous()
         wd = w.detach().contiguous()
         kvol, cin, cout = wd.shape
-        x = feats
-        wt = None
-        if use_bf16 and cin % 64 == 0 and cout % 32 == 0:
+        tc_on = bool(use_bf16) and ops._TC_ENABLED
+        tc_fwd = tc_on and cin % 64 == 0 and cout % 32 == 0
+        tc_bwd = tc_on and cout % 64 == 0 and cin % 32 == 0 and ctx.needs_input_grad[0]
+        x, wt, wt_b = feats, None, None
+        if tc_fwd or tc_bwd:
+            wt, wt_b = ops.pack_conv_weights(wd.float(), want_fwd=tc_fwd, want_bwd=tc_bwd)   # one launch, both layouts
+        if tc_fwd:
             x = ops.cast(feats, torch.bfloat16)
-            wt = wd.transpose(1, 2).contiguous().to(torch.bfloat16)
         out = ops.sparse_conv(x, wd, kmap, n_out, wt_bf16=wt, out_dtype=torch.float32)
-        ctx.save_for_backward(x, wd)
-        ctx.kmap, ctx.kmap_t, ctx.n_in, ctx.use_bf16 = kmap, kmap_t, int(feats.shape[0]), use_bf16
+        ctx.save_for_backward(x, wd, wt_b)
+        ctx.kmap, ctx.kmap_t, ctx.n_in = kmap, kmap_t, int(feats.shape[0])
         ctx.in_dtype = feats.dtype
         return out.to(feats.dtype) if feats.dtype != torch.float32 else out
 
     @staticmethod
     def backward(ctx, grad_out):
-        x, wd = ctx.saved_tensors
+        x, wd, wt_b = ctx.saved_tensors
         kvol, cin, cout = wd.shape
-        g = grad_out.contiguous().float()
+        g = grad_out.contiguous()
+        want_x, want_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        gb = None
+        if (want_x and wt_b is not None) or (want_w and x.dtype == torch.bfloat16):
+            gb = ops.cast(g, torch.bfloat16)                              # shared by the input and the weight gradient
         d_feats = d_w = None
-        if ctx.needs_input_grad[0]:
-            w_back = wd.flip(0).transpose(1, 2).contiguous()          # [K, Cout, Cin]: W[K-1-k']^T
-            gb, wt = g, None
-            if ctx.use_bf16 and cout % 64 == 0 and cin % 32 == 0:
-                gb = ops.cast(g, torch.bfloat16)
-                wt = wd.flip(0).contiguous().to(torch.bfloat16)       # [K, Cin, Cout] is already "out x in" for dgrad
-            d_feats = ops.sparse_conv(gb, w_back, ctx.kmap_t, ctx.n_in, wt_bf16=wt, out_dtype=torch.float32)
+        if want_x:
+            if wt_b is not None:                                          # [K, Cin, Cout] is already "out x in" for dgrad
+                d_feats = ops.sparse_conv(gb, (kvol, cout, cin), ctx.kmap_t, ctx.n_in, wt_bf16=wt_b,
+                                          out_dtype=torch.float32)
+            else:
+                w_back = wd.flip(0).transpose(1, 2).contiguous()          # [K, Cout, Cin]: W[K-1-k']^T
+                d_feats = ops.sparse_conv(g.float(), w_back, ctx.kmap_t, ctx.n_in, out_dtype=torch.float32)
             d_feats = d_feats.to(ctx.in_dtype)
-        if ctx.needs_input_grad[1]:
-            gw = ops.cast(g, torch.bfloat16) if x.dtype == torch.bfloat16 else g
-            d_w = conv_wgrad(x, gw, ctx.kmap, kvol, cin, cout)
+        if want_w:
+            d_w = conv_wgrad(x, gb if x.dtype == torch.bfloat16 else g.float(), ctx.kmap, kvol, cin, cout)
         return d_feats, d_w, None, None, None, None
 
 

@@ -218,6 +218,36 @@ __global__ void __launch_bounds__(256) k_wgrad_narrow(const TA* __restrict__ in,
   }
 }
 
+// bf16 operand layouts of a convolution kernel w [K, Cin, Cout] fp32, both in one pass:
+//   wt_fwd [K, Cout, Cin] = w[k]^T          (forward: "W_k^T" rows of the tcgen05 B operand)
+//   wt_bwd [K, Cin, Cout] = w[K-1-k]        (input gradient: the transposed map pairs offset k with K-1-k)
+__global__ void __launch_bounds__(256) k_pack_conv_weights(const float* __restrict__ w, int kvol, int cin, int cout,
+                                                           __nv_bfloat16* __restrict__ wt_fwd,
+                                                           __nv_bfloat16* __restrict__ wt_bwd) {
+  __shared__ float tile[32][33];
+  const int k = blockIdx.z, ci0 = blockIdx.y * 32, co0 = blockIdx.x * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const float* wk = w + (long long)k * cin * cout;
+  __nv_bfloat16* bk = wt_bwd ? wt_bwd + (long long)(kvol - 1 - k) * cin * cout : nullptr;
+  for (int r = ty; r < 32; r += 8) {
+    const int ci = ci0 + r, co = co0 + tx;
+    float v = 0.f;
+    if (ci < cin && co < cout) {
+      v = wk[(long long)ci * cout + co];
+      if (bk) bk[(long long)ci * cout + co] = __float2bfloat16(v);
+    }
+    tile[r][tx] = v;
+  }
+  __syncthreads();
+  if (wt_fwd) {
+    __nv_bfloat16* fk = wt_fwd + (long long)k * cin * cout;
+    for (int r = ty; r < 32; r += 8) {
+      const int co = co0 + r, ci = ci0 + tx;
+      if (ci < cin && co < cout) fk[(long long)co * cin + ci] = __float2bfloat16(tile[tx][r]);
+    }
+  }
+}
+
 // max-pool backward: dx[arg[o, c], c] += dy[o, c]
 template <typename T>
 __global__ void k_maxpool_bwd(const T* __restrict__ dy, const int* __restrict__ arg, long long n_out, int c,
@@ -371,6 +401,147 @@ __global__ void k_assign_final(const float* __restrict__ points, int P, const in
 #pragma unroll
   for (int u = 0; u < 7; ++u) box_t[7ll * p + u] = bx[u];
   labels_out[p] = (best_vol == float_max) ? -1 : labels_in[best];
+}
+
+// ---------------------------------------------------------------------------
+// Batched Fcaf3DAssigner: all scenes of the batch in three launches.  Points are LEVEL-major (the rows of each level's
+// coordinate map, scenes grouped inside a level): segment j = level * S + scene covers rows [seg[2j], seg[2j+1]).
+// Boxes of all scenes are concatenated, box_off[S+1].  Same arithmetic per (point, box) as the per-scene kernels.
+// ---------------------------------------------------------------------------
+#define AB_MAX_SEG 256
+__device__ __forceinline__ int find_segment(const int* s_seg, int nseg, int p) {
+  for (int j = 0; j < nseg; ++j)
+    if (p >= s_seg[2 * j] && p < s_seg[2 * j + 1]) return j;
+  return -1;
+}
+
+__global__ void k_assignb_count(const float* __restrict__ points, int P, const int* __restrict__ seg, int S, int L,
+                                const float* __restrict__ boxes, const int* __restrict__ box_off, int Btot,
+                                int* __restrict__ counts, int* __restrict__ scene_of) {
+  __shared__ int s_seg[2 * AB_MAX_SEG];
+  for (int i = threadIdx.x; i < 2 * S * L; i += blockDim.x) s_seg[i] = seg[i];
+  __syncthreads();
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= P) return;
+  const int j = find_segment(s_seg, S * L, p);
+  if (j < 0) {
+    scene_of[p] = -1;
+    return;
+  }
+  const int lvl = j / S, sc = j - lvl * S;
+  scene_of[p] = sc;
+  for (int b = box_off[sc]; b < box_off[sc + 1]; ++b) {
+    const FaceDist f = face_distances(points + 3ll * p, boxes + 7ll * b);
+    if (inside_box(f)) atomicAdd(&counts[lvl * Btot + b], 1);
+  }
+}
+
+__global__ void __launch_bounds__(256) k_assignb_select(const float* __restrict__ points, const int* __restrict__ seg,
+                                                        int S, int L, const float* __restrict__ boxes,
+                                                        const int* __restrict__ box_off, int Btot,
+                                                        const int* __restrict__ counts, int limit, int topk,
+                                                        int* __restrict__ best_level, float* __restrict__ thr) {
+  __shared__ unsigned int hist[2048];
+  __shared__ unsigned int s_prefix, s_need;
+  __shared__ int s_best, s_scene, s_np;
+  const int b = blockIdx.x;
+  if (threadIdx.x == 0) {
+    int sc = 0;
+    while (sc + 1 < S && b >= box_off[sc + 1]) ++sc;
+    int first_low = -1;
+    for (int l = 0; l < L; ++l)
+      if (counts[l * Btot + b] < limit) { first_low = l; break; }
+    const int best = (first_low < 0) ? L - 1 : max(first_low - 1, 0);
+    int np = 0;
+    for (int l = 0; l < L; ++l) np += seg[2 * (l * S + sc) + 1] - seg[2 * (l * S + sc)];
+    s_best = best;
+    s_scene = sc;
+    s_np = np;
+    best_level[b] = best;
+  }
+  __syncthreads();
+  const int lvl = s_best, sc = s_scene;
+  const int beg = seg[2 * (lvl * S + sc)], end = seg[2 * (lvl * S + sc) + 1];
+  const int kk = min(topk + 1, s_np);  // torch.topk(..., min(topk + 1, len(points))) over the scene's points
+  const int n_valid = counts[lvl * Btot + b];
+  if (n_valid < kk) {
+    if (threadIdx.x == 0) thr[b] = -1.f;
+    return;
+  }
+  unsigned int prefix = 0, need = (unsigned int)kk;
+  const int shifts[3] = {21, 10, 0}, widths[3] = {11, 11, 10};
+  for (int pass = 0; pass < 3; ++pass) {
+    const int shift = shifts[pass], bins = 1 << widths[pass];
+    const unsigned int hi_mask = pass == 0 ? 0u : (0xFFFFFFFFu << (shift + widths[pass]));
+    for (int i = threadIdx.x; i < 2048; i += blockDim.x) hist[i] = 0;
+    __syncthreads();
+    for (int p = beg + threadIdx.x; p < end; p += blockDim.x) {
+      const FaceDist f = face_distances(points + 3ll * p, boxes + 7ll * b);
+      if (!inside_box(f)) continue;
+      const unsigned int u = __float_as_uint(centerness_of(f));
+      if ((u & hi_mask) == prefix) atomicAdd(&hist[(u >> shift) & (bins - 1)], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      unsigned int acc = 0;
+      int d = bins - 1;
+      for (; d > 0; --d) {
+        if (acc + hist[d] >= need) break;
+        acc += hist[d];
+      }
+      s_prefix = prefix | ((unsigned int)d << shift);
+      s_need = need - acc;
+    }
+    __syncthreads();
+    prefix = s_prefix;
+    need = s_need;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) thr[b] = __uint_as_float(prefix);
+}
+
+__global__ void k_assignb_final(const float* __restrict__ points, int P, const int* __restrict__ seg, int S, int L,
+                                const float* __restrict__ boxes, const int* __restrict__ box_off,
+                                const long long* __restrict__ labels_in, const int* __restrict__ best_level,
+                                const float* __restrict__ thr, float* __restrict__ centerness_t,
+                                float* __restrict__ box_t, long long* __restrict__ labels_out,
+                                int* __restrict__ n_pos) {
+  __shared__ int s_seg[2 * AB_MAX_SEG];
+  for (int i = threadIdx.x; i < 2 * S * L; i += blockDim.x) s_seg[i] = seg[i];
+  __syncthreads();
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= P) return;
+  const int j = find_segment(s_seg, S * L, p);
+  const int lvl = j < 0 ? 0 : j / S, sc = j < 0 ? 0 : j - lvl * S;
+  const int b0 = j < 0 ? 0 : box_off[sc], b1 = j < 0 ? 0 : box_off[sc + 1];
+  const float float_max = 1e8f;
+  float best_vol = float_max;
+  int best = b0;
+  for (int b = b0; b < b1; ++b) {
+    const float* bx = boxes + 7ll * b;
+    const FaceDist f = face_distances(points + 3ll * p, bx);
+    float vol = float_max;
+    if (inside_box(f) && best_level[b] == lvl && centerness_of(f) > thr[b]) vol = bx[3] * bx[4] * bx[5];
+    if (vol < best_vol) {
+      best_vol = vol;
+      best = b;
+    }
+  }
+  if (b1 == b0) {  // scene without boxes: everything is background
+    centerness_t[p] = 0.f;
+#pragma unroll
+    for (int u = 0; u < 7; ++u) box_t[7ll * p + u] = 0.f;
+    labels_out[p] = -1;
+    return;
+  }
+  const float* bx = boxes + 7ll * best;
+  const FaceDist f = face_distances(points + 3ll * p, bx);
+  centerness_t[p] = centerness_of(f);
+#pragma unroll
+  for (int u = 0; u < 7; ++u) box_t[7ll * p + u] = bx[u];
+  const bool pos = best_vol != float_max;
+  labels_out[p] = pos ? labels_in[best] : -1;
+  if (pos) atomicAdd(&n_pos[sc], 1);
 }
 
 // ---------------------------------------------------------------------------
@@ -546,6 +717,17 @@ int b2_conv_wgrad(const void* in, int a_dtype, const void* dout, int g_dtype, co
   return B2_OK;
 }
 
+// bf16 tcgen05 operand layouts of w [kvol, cin, cout] fp32: wt_fwd [kvol, cout, cin] (= w[k]^T) and
+// wt_bwd [kvol, cin, cout] (= w[kvol-1-k]); either output may be NULL
+int b2_pack_conv_weights(const float* w, int kvol, int cin, int cout, void* wt_fwd, void* wt_bwd, void* stream) {
+  B2_CHECK_ARG(kvol > 0 && cin > 0 && cout > 0, "empty kernel");
+  dim3 grid(b2_div_up(cout, 32), b2_div_up(cin, 32), kvol);
+  k_pack_conv_weights<<<grid, 256, 0, (cudaStream_t)stream>>>(w, kvol, cin, cout, (__nv_bfloat16*)wt_fwd,
+                                                              (__nv_bfloat16*)wt_bwd);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
 // dx [n_in, c] fp32, zero-initialised by the caller
 int b2_maxpool_bwd(const void* dy, int dtype, const int* argmax, long long n_out, int c, float* dx, void* stream) {
   if (n_out == 0) return B2_OK;
@@ -577,6 +759,30 @@ int b2_fcaf3d_assign(const float* points, long long P, const int* level_off, int
   B2_LAUNCH_CHECK();
   k_assign_final<<<b2_div_up(P, 128), 128, 0, st>>>(points, (int)P, level_off, L, boxes, B, labels_in, best_level, thr,
                                                    centerness_t, box_t, labels_out);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+// batched assigner: points level-major, seg int32 [L*S][2] (row ranges, index level*S+scene), boxes of all scenes
+// concatenated with box_off int32 [S+1].  Scratch: counts int32 [L*Btot] (zeroed inside), best_level [Btot], thr [Btot].
+// Outputs as b2_fcaf3d_assign plus scene_of int32 [P] and n_pos int32 [S] (positives per scene, zeroed inside).
+int b2_fcaf3d_assign_batched(const float* points, long long P, const int* seg, int S, int L, const float* boxes,
+                             const int* box_off, int Btot, const long long* labels_in, int limit, int topk, int* counts,
+                             int* best_level, float* thr, float* centerness_t, float* box_t, long long* labels_out,
+                             int* scene_of, int* n_pos, void* stream) {
+  B2_CHECK_ARG(L >= 1 && S >= 1 && S * L <= AB_MAX_SEG && Btot >= 0, "bad batched assigner shape (scenes x levels <= 256)");
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_CUDA(cudaMemsetAsync(n_pos, 0, (size_t)S * 4, st));
+  if (P == 0) return B2_OK;
+  if (Btot > 0) B2_CUDA(cudaMemsetAsync(counts, 0, (size_t)L * Btot * 4, st));
+  k_assignb_count<<<b2_div_up(P, 128), 128, 0, st>>>(points, (int)P, seg, S, L, boxes, box_off, Btot, counts, scene_of);
+  B2_LAUNCH_CHECK();
+  if (Btot > 0) {
+    k_assignb_select<<<Btot, 256, 0, st>>>(points, seg, S, L, boxes, box_off, Btot, counts, limit, topk, best_level, thr);
+    B2_LAUNCH_CHECK();
+  }
+  k_assignb_final<<<b2_div_up(P, 128), 128, 0, st>>>(points, (int)P, seg, S, L, boxes, box_off, labels_in, best_level, thr,
+                                                    centerness_t, box_t, labels_out, n_pos);
   B2_LAUNCH_CHECK();
   return B2_OK;
 }

@@ -239,13 +239,22 @@ class Fcaf3DNeckWithHead(nn.Module):
         return self.pruning(x, mask.bool())
 
     def forward_single(self, x, scale):
-        centerness = self.centerness_conv(x).features
-        scores = self.cls_conv(x)
-        cls_score = scores.features
-        prune_scores = ME.SparseTensor(cls_score.max(dim=1, keepdim=True).values,
-                                       coordinate_map_key=scores.coordinate_map_key,
-                                       coordinate_manager=scores.coordinate_manager)
-        reg_final = self.reg_conv(x).features
+        if torch.is_grad_enabled() and x.F.requires_grad and x.F.dtype == self.cls_conv.kernel.dtype:
+            # training: the three 1x1 heads (ME: three F.mm calls) as ONE GEMM over the concatenated kernels, so the
+            # backward is two GEMMs over the level's rows instead of six
+            w = torch.cat((self.centerness_conv.kernel, self.reg_conv.kernel, self.cls_conv.kernel), dim=1)
+            h = x.F @ w
+            centerness, reg_final = h[:, :1], h[:, 1:1 + self.n_reg_outs]
+            cls_score = h[:, 1 + self.n_reg_outs:] + self.cls_conv.bias
+            ck, cmgr = x.coordinate_map_key, x.coordinate_manager
+        else:
+            centerness = self.centerness_conv(x).features
+            scores = self.cls_conv(x)
+            cls_score = scores.features
+            ck, cmgr = scores.coordinate_map_key, scores.coordinate_manager
+            reg_final = self.reg_conv(x).features
+        prune_scores = ME.SparseTensor(cls_score.max(dim=1, keepdim=True).values, coordinate_map_key=ck,
+                                       coordinate_manager=cmgr)
         reg_distance = torch.exp(scale(reg_final[:, :6]))
         bbox_pred = torch.cat((reg_distance, reg_final[:, 6:]), dim=1)
         centernesses, bbox_preds, cls_scores = [], [], []
@@ -295,6 +304,69 @@ class Fcaf3DNeckWithHead(nn.Module):
             loss_centerness = pos_centerness.sum()
             loss_bbox = pos_bbox_preds.sum()
         return loss_centerness, loss_bbox, loss_cls
+
+    # ---- batched training path: no python loop over scenes ------------------------------
+    def forward_train_batched(self, inputs, gt_bboxes, gt_labels):
+        """Same neck walk as forward(), but the heads keep every level as ONE tensor over all scenes and the losses are
+        computed for the whole batch at once (loss_batched)."""
+        levels = []
+        x = inputs[-1]
+        scores = None
+        for i in range(len(inputs) - 1, -1, -1):
+            if i < len(inputs) - 1:
+                x = getattr(self, f"up_block_{i + 1}")(x)
+                x = inputs[i] + x
+                x = self._prune(x, scores)
+            out = getattr(self, f"out_block_{i}")(x)
+            w = torch.cat((self.centerness_conv.kernel, self.reg_conv.kernel, self.cls_conv.kernel), dim=1)
+            h = out.F.float() @ w
+            reg = h[:, 1:1 + self.n_reg_outs]
+            bbox = torch.cat((torch.exp(self.scales[i](reg[:, :6])), reg[:, 6:]), dim=1)
+            cls = h[:, 1 + self.n_reg_outs:] + self.cls_conv.bias
+            scores = ME.SparseTensor(cls.max(dim=1, keepdim=True).values, coordinate_map_key=out.coordinate_map_key,
+                                     coordinate_manager=out.coordinate_manager)
+            levels.append((h[:, :1], bbox, cls, out))
+        return self.loss_batched(levels[::-1], gt_bboxes, gt_labels)
+
+    def loss_batched(self, levels, gt_bboxes, gt_labels):
+        """levels: fine -> coarse list of (centerness [N_l, 1], bbox_pred [N_l, R], cls [N_l, C], SparseTensor).
+        Per scene s the reference computes sum_p loss_p / normaliser_s and then averages over scenes
+        (fcaf3d_neck_with_head.py:128-203); here every row carries the weight 1 / (S * normaliser_scene(row))."""
+        S = len(gt_bboxes)
+        maps = [lv[3]._map() for lv in levels]
+        base, seg = 0, []
+        for m in maps:
+            seg.append([(base + m.off_host[b], base + m.off_host[b + 1]) for b in range(S)])
+            base += m.n
+        points = torch.cat([m.coords[:, 1:] * self.voxel_size for m in maps])
+        centerness = torch.cat([lv[0] for lv in levels])
+        bbox_preds = torch.cat([lv[1] for lv in levels])
+        cls_scores = torch.cat([lv[2] for lv in levels])
+        centerness_targets, bbox_targets, labels, scene_of, n_pos_i = self.assigner.assign_batched(
+            points, seg, gt_bboxes, gt_labels)
+        scene_of = scene_of.long()
+        n_pos = torch.clamp(reduce_mean(n_pos_i.float()), min=1.)                      # [S]
+        w_scene = 1.0 / (S * n_pos)
+        loss_cls = self.loss_cls(cls_scores, labels, weight=w_scene[scene_of], avg_factor=1.0)
+        pos_inds = torch.nonzero(labels >= 0).squeeze(1)                              # the one host sync of the loss
+        pos_centerness = centerness[pos_inds]
+        pos_bbox_preds = bbox_preds[pos_inds]
+        pos_scene = scene_of[pos_inds]
+        pos_ct = centerness_targets[pos_inds]
+        denorm = torch.clamp(reduce_mean(torch.zeros(S, device=pos_ct.device).index_add_(0, pos_scene, pos_ct)),
+                             min=1e-6)
+        if len(pos_inds) > 0:
+            loss_centerness = self.loss_centerness(pos_centerness, pos_ct.unsqueeze(1),
+                                                   weight=w_scene[pos_scene].unsqueeze(1), avg_factor=1.0)
+            pred = self._bbox_pred_to_bbox_train(points[pos_inds], pos_bbox_preds)
+            target = bbox_targets[pos_inds]
+            target = target if pred.shape[1] == 7 else target[:, :6]
+            loss_bbox = self.loss_bbox(pred, target, weight=pos_ct / (S * denorm[pos_scene]), avg_factor=1.0,
+                                       check_weight=False)
+        else:
+            loss_centerness = pos_centerness.sum()
+            loss_bbox = pos_bbox_preds.sum()
+        return dict(loss_centerness=loss_centerness, loss_bbox=loss_bbox, loss_cls=loss_cls)
 
     def _bbox_pred_to_bbox_train(self, points, bbox_pred):
         """differentiable twin of _bbox_pred_to_bbox (:281-330); the inference path uses the fused kernel"""
@@ -529,6 +601,7 @@ class SingleStageSparse3DDetector(nn.Module):
         self.neck_with_head = Fcaf3DNeckWithHead(**neck_with_head)
         self.voxel_size = voxel_size
         self.train_cfg, self.test_cfg = train_cfg, test_cfg
+        self.batched_loss = True   # forward_train: whole-batch assigner + losses (False: the reference's per-scene loop)
         self.init_weights()
 
     def init_weights(self, pretrained=None):
@@ -546,6 +619,9 @@ class SingleStageSparse3DDetector(nn.Module):
 
     def forward_train(self, points, gt_bboxes_3d, gt_labels_3d, img_metas=None):
         """single_stage_sparse.py:42-49.  gt_bboxes_3d: list of [B_i, 7] (gravity centre, size, yaw) tensors."""
+        if self.batched_loss:
+            feats = self.backbone(self._input_tensor(points))
+            return self.neck_with_head.forward_train_batched(feats, gt_bboxes_3d, gt_labels_3d)
         x = self.extract_feat(points, img_metas)
         return self.neck_with_head.loss(*x, gt_bboxes_3d, gt_labels_3d, img_metas)
 

@@ -59,6 +59,8 @@ class CrossEntropyLoss(nn.Module):
 
     def forward(self, cls_score, label, weight=None, avg_factor=None, reduction_override=None, **kw):
         loss = F.binary_cross_entropy_with_logits(cls_score, label.float(), reduction="none")
+        if weight is not None:
+            loss = loss * weight.reshape(loss.shape[0], -1)
         return self.loss_weight * (loss.sum() / avg_factor if avg_factor is not None else loss.mean())
 
 
@@ -169,7 +171,8 @@ class IoU3DLoss(nn.Module):
         self.with_yaw, self.reduction, self.loss_weight = with_yaw, reduction, loss_weight
 
     def forward(self, pred, target, weight=None, avg_factor=None, reduction_override=None, **kw):
-        if weight is not None and not torch.any(weight > 0):
+        # (the reference's check reads the device; callers that know their weights are positive pass check_weight=False)
+        if weight is not None and kw.get("check_weight", True) and not torch.any(weight > 0):
             return pred.sum() * weight.sum()
         if weight is not None and weight.dim() > 1:
             weight = weight.mean(-1)
@@ -210,6 +213,39 @@ class Fcaf3DAssigner:
         call("b2_fcaf3d_assign", ptr(pts), P, ptr(level_off), L, ptr(boxes), B, ptr(labels_in), self.limit, self.topk,
              ptr(counts), ptr(best), ptr(thr), ptr(ct), ptr(bt), ptr(lb))
         return ct, bt, lb
+
+
+    @torch.no_grad()
+    def assign_batched(self, points, seg, gt_boxes, gt_labels):
+        """All scenes at once (b2_fcaf3d_assign_batched).  points [P, 3] level-major; seg: host list over levels of lists
+        over scenes of (begin, end) row ranges; gt_boxes / gt_labels: lists over scenes.
+        Returns (centerness_targets [P], box_targets [P, 7], labels [P], scene_of int32 [P], n_pos int32 [S])."""
+        dev = points.device
+        L, S = len(seg), len(seg[0])
+        pts = points.contiguous().float()
+        P = int(pts.shape[0])
+        box_off = [0]
+        for g in gt_boxes:
+            box_off.append(box_off[-1] + int(g.shape[0]))
+        Btot = box_off[-1]
+        meta = torch.tensor([v for lvl in seg for be in lvl for v in be] + box_off, dtype=torch.int32).to(dev)
+        seg_dev, box_off_dev = meta[:2 * L * S], meta[2 * L * S:]
+        boxes = (torch.cat([g.to(dev).float().reshape(-1, 7) for g in gt_boxes]) if Btot else
+                 torch.zeros((1, 7), device=dev)).contiguous()
+        labels_in = (torch.cat([l.to(dev).long().reshape(-1) for l in gt_labels]) if Btot else
+                     torch.zeros((1,), dtype=torch.long, device=dev)).contiguous()
+        counts = torch.empty((max(L * Btot, 1),), dtype=torch.int32, device=dev)
+        best = torch.empty((max(Btot, 1),), dtype=torch.int32, device=dev)
+        thr = torch.empty((max(Btot, 1),), dtype=torch.float32, device=dev)
+        ct = torch.empty((P,), dtype=torch.float32, device=dev)
+        bt = torch.empty((P, 7), dtype=torch.float32, device=dev)
+        lb = torch.empty((P,), dtype=torch.int64, device=dev)
+        scene_of = torch.empty((P,), dtype=torch.int32, device=dev)
+        n_pos = torch.empty((S,), dtype=torch.int32, device=dev)
+        call("b2_fcaf3d_assign_batched", ptr(pts), P, ptr(seg_dev), S, L, ptr(boxes), ptr(box_off_dev), Btot,
+             ptr(labels_in), self.limit, self.topk, ptr(counts), ptr(best), ptr(thr), ptr(ct), ptr(bt), ptr(lb),
+             ptr(scene_of), ptr(n_pos))
+        return ct, bt, lb, scene_of, n_pos
 
 
 LOSSES = {"FocalLoss": FocalLoss, "CrossEntropyLoss": CrossEntropyLoss, "IoU3DLoss": IoU3DLoss}

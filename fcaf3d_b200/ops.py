@@ -261,7 +261,8 @@ def sparse_conv(x, w, kmap, n_out, wt_bf16=None, bias=None, scale=None, shift=No
     w: fp32 [K, Cin, Cout]; wt_bf16: optional bf16 [K, Cout, Cin] for the tcgen05 path; kmap None = identity (K = 1).
     """
     require_cuda(x, "features")
-    kvol, cin, cout = int(w.shape[0]), int(w.shape[1]), int(w.shape[2])
+    wshape = w.shape if torch.is_tensor(w) else w          # a bare (K, Cin, Cout) is enough for the tcgen05 path
+    kvol, cin, cout = int(wshape[0]), int(wshape[1]), int(wshape[2])
     out_dtype = out_dtype or x.dtype
     out = torch.empty((n_out, cout), dtype=out_dtype, device=x.device)
     nbr = kmap.nbr if kmap is not None else None
@@ -270,6 +271,8 @@ def sparse_conv(x, w, kmap, n_out, wt_bf16=None, bias=None, scale=None, shift=No
     if residual is not None:
         assert residual.dtype == out_dtype and residual.shape == out.shape
     use_tc = wt_bf16 is not None and tc_eligible(x, cin, cout)
+    if not use_tc and not torch.is_tensor(w):
+        raise B2Error("sparse_conv: fp32 weights are required off the tcgen05 path")
     if PROFILE is not None:
         pairs = kmap_pairs(kmap, n_out)
         esz = x.element_size()
@@ -309,6 +312,16 @@ def affine_act(x, scale=None, shift=None, coords=None, residual=None, act=ACT_NO
     call("b2_affine_act", ptr(x), DT[x.dtype], ptr(coords), x.shape[0], x.shape[1], ptr(scale), ptr(shift),
          ptr(residual), act, ptr(out))
     return out
+
+
+def pack_conv_weights(w, want_fwd=True, want_bwd=True):
+    """bf16 operand layouts of w [K, Cin, Cout] fp32 in one launch: (w[k]^T as [K, Cout, Cin], w[K-1-k] as [K, Cin, Cout])."""
+    kvol, cin, cout = (int(v) for v in w.shape)
+    fwd = torch.empty((kvol, cout, cin), dtype=torch.bfloat16, device=w.device) if want_fwd else None
+    bwd = torch.empty((kvol, cin, cout), dtype=torch.bfloat16, device=w.device) if want_bwd else None
+    if want_fwd or want_bwd:
+        call("b2_pack_conv_weights", ptr(w), kvol, cin, cout, ptr(fwd), ptr(bwd))
+    return fwd, bwd
 
 
 def cast(x, dtype):

@@ -181,6 +181,10 @@ int b2_nms_single_noalloc(const float* boxes_sorted, long long n, float thresh, 
 int b2_conv_wgrad(const void* in, int a_dtype, const void* dout, int g_dtype, const int* nbr, long long ld,
                   long long n_out, int cin, int cout, int kvol, float* dw, void* stream);
 /* ME max-pool backward: dx[argmax[o,c], c] += dy[o,c]; dx fp32, zero-initialised by the caller */
+/* bf16 operand layouts of a convolution kernel w [kvol, cin, cout] fp32 for b2_conv_tc, one pass: wt_fwd [kvol, cout, cin]
+ * (forward) and wt_bwd [kvol, cin, cout] with the offsets reversed (input gradient over the transposed map); either may
+ * be NULL.  Replaces the per-step torch transposes of ME's kernel tensor (MinkowskiConvolution.kernel, App. A.4). */
+int b2_pack_conv_weights(const float* w, int kvol, int cin, int cout, void* wt_fwd, void* wt_bwd, void* stream);
 int b2_maxpool_bwd(const void* dy, int dtype, const int* argmax, long long n_out, int c, float* dx, void* stream);
 /* Fcaf3DAssigner.assign for one scene (fcaf3d_neck_with_head.py:387-466): points [P,3] of all levels (level_off[L+1]),
  * boxes [B,7] = (gravity centre, size, yaw), labels_in int64 [B] -> centerness_t [P], box_t [P,7], labels_out int64 [P]
@@ -188,6 +192,14 @@ int b2_maxpool_bwd(const void* dy, int dtype, const int* argmax, long long n_out
 int b2_fcaf3d_assign(const float* points, long long P, const int* level_off, int L, const float* boxes, int B,
                      const long long* labels_in, int limit, int topk, int* counts, int* best_level, float* thr,
                      float* centerness_t, float* box_t, long long* labels_out, void* stream);
+/* The same assignment for ALL scenes of a batch in three launches (removes the reference's python loop over
+ * scenes, fcaf3d_neck_with_head.py:128-141).  points [P,3] level-major (rows of each level's coordinate map, scenes grouped
+ * inside a level); seg int32 [L*S][2] = row range of (level, scene) at index level*S+scene; boxes [Btot,7] of all scenes
+ * with box_off int32 [S+1]; extra outputs scene_of int32 [P] and n_pos int32 [S] (positives per scene). */
+int b2_fcaf3d_assign_batched(const float* points, long long P, const int* seg, int S, int L, const float* boxes,
+                             const int* box_off, int Btot, const long long* labels_in, int limit, int topk, int* counts,
+                             int* best_level, float* thr, float* centerness_t, float* box_t, long long* labels_out,
+                             int* scene_of, int* n_pos, void* stream);
 /* mmcv.ops.sigmoid_focal_loss element-wise forward and d/dlogit (label outside [0,c) = all-negative row) */
 int b2_sigmoid_focal(const float* logits, const long long* labels, long long n, int c, float gamma, float alpha,
                      float* loss, float* grad, void* stream);
