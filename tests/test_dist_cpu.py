@@ -25,13 +25,15 @@ def _worker(rank, world, port, out):
     shard = shard_scenes(11, rank, world)
     n_pos = torch.tensor(float(10 + 20 * rank))
     mean = reduce_mean(n_pos)
+    vec = reduce_mean(torch.tensor([1.0, 4.0 * rank, 7.0]))      # the batched loss reduces one [scenes] vector
     # DDP semantics on a tiny torch module: the averaged gradient equals the single-process gradient of the mean loss
     torch.manual_seed(0)
     lin = torch.nn.Linear(4, 1)
     ddp = torch.nn.parallel.DistributedDataParallel(lin)
     x = torch.arange(8, dtype=torch.float32).reshape(2, 4) + rank
     ddp(x).sum().backward()
-    out.put((rank, shard, mean.item(), n_pos.item(), lin.weight.grad.clone()))
+    # plain python objects only: a tensor in the queue is passed by file descriptor and races with the worker's exit
+    out.put((rank, shard, mean.item(), n_pos.item(), lin.weight.grad.reshape(-1).tolist(), vec.tolist()))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -50,7 +52,8 @@ def test_two_process_host_logic():
     assert res[0][2] == res[1][2] == pytest.approx(20.0)       # mean of 10 and 30
     assert res[0][3] == 10.0                                    # the caller's tensor is not modified in place
     want = (torch.arange(8, dtype=torch.float32).reshape(2, 4).sum(0) + (torch.arange(8.).reshape(2, 4) + 1).sum(0)) / 2
-    assert torch.allclose(res[0][4][0], want) and torch.allclose(res[1][4][0], want)
+    assert torch.allclose(torch.tensor(res[0][4]), want) and torch.allclose(torch.tensor(res[1][4]), want)
+    assert res[0][5] == res[1][5] == [1.0, 2.0, 7.0]
 
 
 def test_single_process_reduce_mean_is_identity():
