@@ -32,8 +32,8 @@ template <int BN, int ST, typename TOut>
 __global__ void __launch_bounds__(TC_THREADS)
 k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __restrict__ in, const int* __restrict__ nbr,
           int ld,
-          const unsigned int* __restrict__ tile_mask, int n_out, int cin, int cout, int kvol,
-          const float* __restrict__ bias, const float* __restrict__ scale, const float* __restrict__ shift,
+          const unsigned int* __restrict__ tile_mask, const int* __restrict__ out_rows, int n_out, int cin, int cout,
+          int kvol, const float* __restrict__ bias, const float* __restrict__ scale, const float* __restrict__ shift,
           const TOut* __restrict__ residual, int act, int ch_mod, TOut* __restrict__ out) {
   using Cfg = TcCfg<BN, ST>;
   constexpr int S = Cfg::STAGES;
@@ -47,8 +47,10 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __rest
   float* s_epi = reinterpret_cast<float*>(smem + S * Cfg::STAGE_BYTES + 256 + Cfg::NBR_BYTES);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int row0 = blockIdx.x * TC_BM, col0 = blockIdx.y * BN;
-  const unsigned int kmask = (nbr != nullptr) ? tile_mask[blockIdx.x] : 1u;
+  // sorted tables put the tiles with the most offsets last: walk them first so that the heavy tiles do not form the tail
+  const int tile = (out_rows != nullptr) ? (int)(gridDim.x - 1 - blockIdx.x) : (int)blockIdx.x;
+  const int row0 = tile * TC_BM, col0 = blockIdx.y * BN;
+  const unsigned int kmask = (nbr != nullptr) ? tile_mask[tile] : 1u;
   const int chunks = cin / TC_BK;
   const int nstage = __popc(kmask & ((1u << kvol) - 1u)) * chunks;
 
@@ -138,7 +140,12 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __rest
     }
     const int q = warp & 3, half = warp >> 2;          // TMEM lane quarter, column half
     constexpr int CPW = (BN >= 64) ? BN / 2 : BN;       // columns per warp
-    const int o = row0 + q * 32 + lane;
+    // tile position -> output row (identity, or the permutation of a sparsity-sorted neighbour table, kmap_sort.cu)
+    int o = row0 + q * 32 + lane;
+    if (out_rows != nullptr) {
+      o = __ldg(out_rows + o);
+      if (o < 0) o = n_out;
+    }
     if (BN >= 64 || half == 0) {
       for (int cc = half * CPW; cc < half * CPW + CPW; cc += 32) {
         uint32_t v[32];
@@ -235,7 +242,7 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __rest
 
 template <int BN, int ST, typename TOut>
 static int launch_tc(const void* in, const void* wt, const int* nbr, long long ld, const unsigned int* tile_mask,
-                     long long n_out, int cin, int cout, int kvol, const float* bias, const float* scale,
+                     const int* out_rows, long long n_out, int cin, int cout, int kvol, const float* bias, const float* scale,
                      const float* shift, const void* residual, int act, int ch_mod, void* out, cudaStream_t st) {
   using Cfg = TcCfg<BN, ST>;
   auto kern = k_conv_tc<BN, ST, TOut>;
@@ -248,7 +255,7 @@ static int launch_tc(const void* in, const void* wt, const int* nbr, long long l
   const int rc = b2_make_bf16_map(&map_b, wt, (long long)kvol * cout, cin, BN);
   if (rc) return rc;
   dim3 grid(b2_div_up(n_out, TC_BM), cout / BN);
-  kern<<<grid, TC_THREADS, Cfg::SMEM, st>>>(map_b, (const __nv_bfloat16*)in, nbr, (int)ld, tile_mask,
+  kern<<<grid, TC_THREADS, Cfg::SMEM, st>>>(map_b, (const __nv_bfloat16*)in, nbr, (int)ld, tile_mask, out_rows,
                                             (int)n_out, cin, cout, kvol, bias, scale, shift, (const TOut*)residual, act,
                                             ch_mod, (TOut*)out);
   B2_LAUNCH_CHECK();
@@ -266,7 +273,7 @@ int b2_conv_tma_dispatch(const void* in, long long n_in, const void* wt, const i
                          int out_dtype, cudaStream_t st);
 
 extern "C" int b2_conv_tc(const void* in_bf16, long long n_in, const void* wt_bf16, const int* nbr, long long ld,
-                          const unsigned int* tile_mask, long long n_out, int cin, int cout, int kvol, const float* bias,
+                          const unsigned int* tile_mask, const int* out_rows, long long n_out, int cin, int cout, int kvol, const float* bias,
                           const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
                           int out_dtype, void* stream) {
   B2_CHECK_ARG(cin % TC_BK == 0 && cin > 0, "b2_conv_tc needs cin %% 64 == 0 (got %d)", cin);
@@ -275,24 +282,25 @@ extern "C" int b2_conv_tc(const void* in_bf16, long long n_in, const void* wt_bf
   B2_CHECK_ARG(nbr == nullptr || (tile_mask != nullptr && kvol <= 27 && ld % TC_BM == 0),
                "neighbour table needs a tile mask, kvol <= 27 and ld %% 128 == 0");
   B2_CHECK_ARG((scale == nullptr) == (shift == nullptr), "scale and shift come together");
+  B2_CHECK_ARG(out_rows == nullptr || nbr != nullptr, "a row permutation needs a neighbour table");
   if (n_out == 0) return B2_OK;
   cudaStream_t st = (cudaStream_t)stream;
   // two row tiles per CTA sharing each weight tile (conv_tc2.cu) halve the weight traffic but also halve the CTA count;
   // measured on B200 it is 10-100 % SLOWER on every FCAF3D layer shape (profiles/r01_step2_summary.md), so it is
   // opt-in (B2_TC2=1) and kept for the A/B record only
   static const bool use_tc2 = (getenv("B2_TC2") && atoi(getenv("B2_TC2")) == 1);
-  if (use_tc2 && cout % 64 == 0 && n_out > TC_BM)
+  if (use_tc2 && out_rows == nullptr && cout % 64 == 0 && n_out > TC_BM)
     return b2_conv_tc2_dispatch(in_bf16, wt_bf16, nbr, ld, tile_mask, n_out, cin, cout, kvol, bias, scale, shift,
                                 residual, act, ch_mod, out, out_dtype, st);
   // operand staging by TMA (gather4 + tile loads, conv_tma.cu) instead of per-thread cp.async; B2_TC_TMA=0/1 for A/B runs
   static const bool use_tma = (getenv("B2_TC_TMA") && atoi(getenv("B2_TC_TMA")) == 1);
-  if (use_tma)
+  if (use_tma && out_rows == nullptr)
     return b2_conv_tma_dispatch(in_bf16, n_in, wt_bf16, nbr, ld, tile_mask, n_out, cin, cout, kvol, bias, scale, shift,
                                 residual, act, ch_mod, out, out_dtype, st);
   const bool wide = (cout % 128 == 0);
   const bool mid = (cout % 64 == 0);
 #define TC_GO(BN, T)                                                                                               \
-  return launch_tc<BN, (BN <= 64 ? 4 : 3), T>(in_bf16, wt_bf16, nbr, ld, tile_mask, n_out, cin, cout, kvol, bias, scale, \
+  return launch_tc<BN, (BN <= 64 ? 4 : 3), T>(in_bf16, wt_bf16, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, \
                                               shift, residual, act, ch_mod, out, st)
   if (out_dtype == 1) {
     if (wide) TC_GO(128, __nv_bfloat16);

@@ -5,6 +5,8 @@ stream.  No op has a CPU path.
 """
 import ctypes
 
+import os
+
 import torch
 
 from . import _lib
@@ -180,11 +182,37 @@ def scatter_rows(x, dst, out, accumulate):
 # ----------------------------------------------------------------------------- kernel maps / conv
 class KernelMap:
     """Neighbour table of one (in_map, out_map, kernel) triple."""
-    __slots__ = ("nbr", "ld", "tile_mask", "n_out", "kvol", "pairs")
+    __slots__ = ("nbr", "ld", "tile_mask", "n_out", "kvol", "pairs", "sorted", "tc_uses")
 
     def __init__(self, nbr, ld, tile_mask, n_out, kvol):
         self.nbr, self.ld, self.tile_mask, self.n_out, self.kvol = nbr, ld, tile_mask, n_out, kvol
         self.pairs = None
+        self.sorted = None      # (perm, nbr_sorted, tile_mask_sorted) once kmap_sorted() was asked for
+        self.tc_uses = 0        # tcgen05 convolutions that walked this table so far
+
+
+# Sparsity-sorted walk of the tcgen05 convolution (kmap_sort.cu), OPT-IN (B2_SORT_MIN_ROWS=65536).  Measured on B200:
+# in isolation (tools/bench_conv.py) the sorted walk saves 25 % of a 218 k-row 64->64 convolution (111 -> 83 us), 14 % at
+# 54 k rows, 8 % at 12 k rows, but building it costs ~90-115 us per table (row masks, 4 radix passes, table permutation);
+# in the full step (bench.py, inference and training) the two cancel (827 vs 819 scenes/s, 167 vs 166 scenes/s), so the
+# default is off.  When on, a table is sorted once its SECOND tcgen05 convolution arrives and it has >= SORT_MIN_ROWS rows.
+SORT_MIN_ROWS = int(os.environ.get("B2_SORT_MIN_ROWS", "0"))
+SORT_MIN_USES = int(os.environ.get("B2_SORT_MIN_USES", "2"))
+
+
+def kmap_sorted(km):
+    """(perm, nbr_sorted, tile_mask_sorted) of a neighbour table, built once per table."""
+    if km.sorted is None:
+        dev = km.nbr.device
+        perm = torch.empty((km.ld,), dtype=I32, device=dev)
+        nbr_s = torch.empty_like(km.nbr)
+        tm_s = torch.empty_like(km.tile_mask)
+        ws = workspace(_lib.lib().b2_kmap_sort_ws_bytes(km.n_out, km.kvol), dev, slot=2)
+        t0 = _prof_start()
+        call("b2_kmap_sort", ptr(km.nbr), km.ld, km.n_out, km.kvol, ptr(perm), ptr(nbr_s), ptr(tm_s), ptr(ws), ws.numel())
+        _prof_stop(t0, "kmap_sort", 0.0, 4.0 * km.kvol * km.n_out * 3)
+        km.sorted = (perm, nbr_s, tm_s)
+    return km.sorted
 
 
 def kernel_map(in_table, in_cap, out_coords, ksize, step):
@@ -280,8 +308,13 @@ def sparse_conv(x, w, kmap, n_out, wt_bf16=None, bias=None, scale=None, shift=No
         nbytes = esz * (x.shape[0] * cin + kvol * cin * cout) + out.element_size() * n_out * cout + 4.0 * kvol * ld
     t0 = _prof_start()
     if use_tc:
-        call("b2_conv_tc", ptr(x), x.shape[0], ptr(wt_bf16), ptr(nbr), ld, ptr(tmask), n_out, cin, cout, kvol, ptr(bias), ptr(scale),
-             ptr(shift), ptr(residual), act, ch_mod, ptr(out), DT[out_dtype])
+        perm = None
+        if kmap is not None and kvol == 27:
+            kmap.tc_uses += 1
+            if kmap.sorted is not None or (0 < SORT_MIN_ROWS <= n_out and kmap.tc_uses >= SORT_MIN_USES):
+                perm, nbr, tmask = kmap_sorted(kmap)
+        call("b2_conv_tc", ptr(x), x.shape[0], ptr(wt_bf16), ptr(nbr), ld, ptr(tmask), ptr(perm), n_out, cin, cout, kvol,
+             ptr(bias), ptr(scale), ptr(shift), ptr(residual), act, ch_mod, ptr(out), DT[out_dtype])
     else:
         call("b2_conv_cc", ptr(x), DT[x.dtype], ptr(w), ptr(nbr), ld, ptr(tmask), n_out, cin, cout, kvol, ptr(bias),
              ptr(scale), ptr(shift), ptr(residual), act, ch_mod, ptr(out), DT[out_dtype])

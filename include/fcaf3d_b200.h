@@ -97,11 +97,21 @@ int b2_conv_cc(const void* in, int in_dtype, const float* w, const int* nbr, lon
                const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
                int out_dtype, void* stream);
 /* tcgen05 implicit GEMM, bf16 operands / fp32 TMEM accumulators; wt: [kvol, cout, cin] bf16 (K-major).
- * n_in = rows of the input feature matrix.  cin % 64 == 0, cout % 32 == 0.  Same epilogue as b2_conv_cc; out_dtype 0 or 1. */
+ * n_in = rows of the input feature matrix.  cin % 64 == 0, cout % 32 == 0.  Same epilogue as b2_conv_cc; out_dtype 0 or 1.
+ * out_rows (may be NULL): position -> output row of a sparsity-sorted table from b2_kmap_sort (nbr / tile_mask are then the
+ * sorted ones); results are bit-identical to the unsorted walk. */
 int b2_conv_tc(const void* in_bf16, long long n_in, const void* wt_bf16, const int* nbr, long long ld,
-               const unsigned int* tile_mask,
+               const unsigned int* tile_mask, const int* out_rows,
                long long n_out, int cin, int cout, int kvol, const float* bias, const float* scale, const float* shift,
                const void* residual, int act, int ch_mod, void* out, int out_dtype, void* stream);
+
+/* Sparsity-aware grouping of the rows of a neighbour table (no counterpart in ME 0.5.4, which runs one GEMM per kernel
+ * offset; same idea as TorchSparse++'s sorted implicit GEMM): rows are ordered by their set of present offsets so that a
+ * 128-row tile of b2_conv_tc only walks the offsets its rows use.  perm int32 [ld] (-1 in the padding),
+ * nbr_sorted [kvol, ld], tile_mask_sorted [ld / 128]. */
+size_t b2_kmap_sort_ws_bytes(long long n_out, int kvol);
+int b2_kmap_sort(const int* nbr, long long ld, long long n_out, int kvol, int* perm, int* nbr_sorted,
+                 unsigned int* tile_mask_sorted, void* ws, size_t ws_bytes, void* stream);
 
 /* ---- pooling / normalisation / activation (ME MinkowskiMaxPooling, InstanceNorm, BatchNorm, ReLU, ELU;
  *      me_resnet.py:22-24,63; fcaf3d_neck_with_head.py:53-54,67-71) ------------------------------ */

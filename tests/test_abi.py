@@ -30,7 +30,7 @@ def test_host_helpers_and_argument_errors(lib_built):
     assert l.b2_table_clear(None, 1000, None) == -1
     assert "power of two" in _lib.last_error()
     assert l.b2_kernel_map(None, 1024, None, 10, 3, 1, None, 100, None, None) == -1
-    assert l.b2_conv_tc(None, 10, None, None, 0, None, 10, 48, 64, 1, None, None, None, None, 0, 0, None, 1, None) == -1
+    assert l.b2_conv_tc(None, 10, None, None, 0, None, None, 10, 48, 64, 1, None, None, None, None, 0, 0, None, 1, None) == -1
     assert "cin" in _lib.last_error()
 
 

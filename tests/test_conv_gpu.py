@@ -81,6 +81,44 @@ def test_conv_tcgen05_path(dev, cin, cout, k, stride):
     assert rel_err(z, z_cc) < 5e-4
 
 
+@pytest.mark.parametrize("cin,cout,stride,out_dtype", [(64, 64, 1, torch.bfloat16), (128, 128, 1, torch.float32),
+                                                        (64, 128, 2, torch.float32)])
+def test_sparsity_sorted_walk_is_bit_identical(dev, cin, cout, stride, out_dtype, monkeypatch):
+    """b2_kmap_sort: perm is a permutation of the output rows, the sorted table is the permuted table, its tile masks
+    are exact and have fewer offsets than the unsorted ones; the convolution over it equals the unsorted walk bit for
+    bit (same per-row accumulation order), with the fused epilogue and a residual."""
+    from util import surface_coords
+    c = torch.from_numpy(surface_coords(9000, 2, seed=3)).to(dev)
+    x0 = ME.SparseTensor(torch.zeros(len(c), 1, device=dev), coordinates=c)
+    cm, key = x0.coordinate_manager, x0.coordinate_map_key
+    okey = key if stride == 1 else cm.stride(key, stride)
+    km = cm.kernel_map(key, okey, 3)
+    n_in, n_out = cm.size(key), cm.size(okey)
+    perm, nbr_s, tm_s = ops.kmap_sorted(km)
+    p = perm[:n_out].long()
+    assert torch.equal(torch.sort(p).values, torch.arange(n_out, device=dev)) and bool((perm[n_out:] == -1).all())
+    assert torch.equal(nbr_s[:, :n_out], km.nbr[:, p]) and bool((nbr_s[:, n_out:] == -1).all())
+    present = (nbr_s >= 0).reshape(27, -1, 128).any(2).long()
+    want = (present << torch.arange(27, device=dev).reshape(27, 1)).sum(0)
+    assert torch.equal(tm_s.long() & 0x7FFFFFF, want)
+    popc = lambda t: sum(((t.long() >> b) & 1).sum().item() for b in range(27))   # noqa: E731
+    assert popc(tm_s) < popc(km.tile_mask)
+    torch.manual_seed(0)
+    f = torch.randn(n_in, cin, device=dev).to(torch.bfloat16)
+    w = torch.randn(27, cin, cout, device=dev) * 0.05
+    wt = w.transpose(1, 2).contiguous().to(torch.bfloat16)
+    scale, shift = torch.rand(cout, device=dev) + .5, torch.randn(cout, device=dev)
+    res = torch.randn(n_out, cout, device=dev).to(out_dtype)
+    kw = dict(wt_bf16=wt, scale=scale, shift=shift, residual=res, act=ops.ACT_RELU, out_dtype=out_dtype)
+    monkeypatch.setattr(ops, "SORT_MIN_ROWS", 1)
+    monkeypatch.setattr(ops, "SORT_MIN_USES", 1)
+    y_sorted = ops.sparse_conv(f, w, km, n_out, **kw)
+    km.sorted = None
+    monkeypatch.setattr(ops, "SORT_MIN_ROWS", 0)
+    y_plain = ops.sparse_conv(f, w, km, n_out, **kw)
+    assert km.sorted is None and torch.equal(y_sorted, y_plain)
+
+
 def test_generative_transpose_both_paths(dev):
     x, o = _tensors(dev, 128, n_points=1500)
     cm, ocm = x.coordinate_manager, o.coordinate_manager

@@ -36,6 +36,8 @@ for name in levels:
     f = torch.randn(n, cin, device=dev).to(torch.bfloat16)
     w = torch.randn(27, cin, cout, device=dev) * 0.05
     wt = w.transpose(1, 2).contiguous().to(torch.bfloat16)
+    if ops.SORT_MIN_ROWS and n >= ops.SORT_MIN_ROWS:
+        ops.kmap_sorted(km)          # time the steady state: the table is sorted from its second use on
     for _ in range(3):
         y = ops.sparse_conv(f, w, km, n, wt_bf16=wt)
     torch.cuda.synchronize()
@@ -50,6 +52,21 @@ for name in levels:
     gather = pairs * cin * 2 + (n + 127) // 128 * 27 * cin * cout * 2 * (1 if cout <= 128 else cout // 128)
     print("%-6s rows=%7d pairs=%9d (%.1f/row) C=%d->%d : %8.1f us  %7.1f TFLOP/s  L2->SM %6.0f GB/s" %
           (name, n, pairs, pairs / n, cin, cout, ms * 1000, flops / ms / 1e9, gather / ms / 1e6))
+    if ops.SORT_MIN_ROWS and km.sorted is not None:
+        import copy
+        ts_ = []
+        for _ in range(3):
+            km2 = copy.copy(km)
+            km2.sorted = None
+            torch.cuda.synchronize()
+            s.record()
+            ops.kmap_sorted(km2)
+            e.record()
+            torch.cuda.synchronize()
+            ts_.append(s.elapsed_time(e) * 1000)
+        tm_s = km.sorted[2].long()
+        popc = sum(((tm_s >> b) & 1).sum().item() for b in range(27)) / tm_s.numel()
+        print("%-6s   kmap_sort %.1f us; offsets per tile after sorting %.2f" % (name, min(ts_), popc))
     # weight gradient of the same layer (bf16 operands, fp32 dW)
     from fcaf3d_b200.autograd import conv_wgrad  # noqa: E402
     g = torch.randn(n, cout, device=dev).to(torch.bfloat16)
