@@ -124,6 +124,36 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def roofline_from_profile(prof, ms, use_traffic_file, main=None):
+    """Aggregates ops.PROFILE records [name, start, end, flops, bytes] of ONE step into the bench line's roofline object
+    (dominant kernel = the tcgen05 convolution; the other profiled kernels ride along in `other_kernels`)."""
+    agg = {}
+    for name, s, e, fl, by in prof:
+        a = agg.setdefault(name, [0, 0.0, 0.0, 0.0])
+        a[0] += 1
+        a[1] += s.elapsed_time(e)
+        a[2] += fl
+        a[3] += by
+    pk, pk_kind = peaks()
+    kernels = {}
+    for name, (cnt, t_ms, fl, by) in agg.items():
+        kernels[name] = {"launches": cnt, "ms": round(t_ms, 4), "tflops": fl / t_ms / 1e9 if fl else None,
+                         "gbs": by / t_ms / 1e6}
+    main_k = main or ("conv_tc" if "conv_tc" in agg else "conv_cc")
+    cnt, t_ms, fl, by = agg[main_k]
+    peak = pk["bf16_tflops_sustained"] if main_k in ("conv_tc", "wgrad_tc") else 75.0
+    traffic = None
+    try:  # DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/conv_tc_traffic.json)
+        if main_k == "conv_tc" and use_traffic_file:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "conv_tc_traffic.json")))["dram_bytes_per_launch"]
+    except Exception:
+        pass
+    return {"kernel": main_k, "bound": "tensor", "achieved": fl / t_ms / 1e9, "peak": peak, "unit": "TFLOP/s",
+            "frac": fl / t_ms / 1e9 / peak, "traffic": traffic, "algorithmic_bytes_per_launch": by / cnt,
+            "peak_source": pk_kind, "launches_per_step": cnt, "avg_launch_ms": t_ms / cnt, "share_of_step": t_ms / ms,
+            "algorithmic_flops_per_step": fl, "other_kernels": kernels}
+
+
 def run_train(args, det, scenes, dev, world, rank, dtype):
     """configs[4]: data-parallel training step (8 scenes per GPU), NCCL gradient all-reduce through DDP."""
     import torch
@@ -170,9 +200,23 @@ def run_train(args, det, scenes, dev, world, rank, dtype):
         torch.cuda.profiler.stop()
         print(json.dumps({"profile_step": "done"}))
         return
+    from fcaf3d_b200 import ops
+    lib = ops._lib.lib()
+    for _ in range(args.warmup):
+        step(False)
+    torch.cuda.synchronize()
+    launches0 = lib.b2_launch_count()
     with ClockSampler(dev.index) as clk:
-        ms, _ = timed(False, args.steps, args.warmup)
+        ms, _ = timed(False, args.steps, 0)
+    launches = lib.b2_launch_count() - launches0   # kernels of libfcaf3d_b200.so only (torch's own are not counted)
     ms_e2e, loss = timed(True, max(2, args.steps // 2), 1)
+    roofline = None
+    if args.dtype == "bf16":
+        ops.PROFILE = []
+        step(False)
+        torch.cuda.synchronize()
+        prof, ops.PROFILE = ops.PROFILE, None
+        roofline = roofline_from_profile(prof, ms, False)   # conv_tc = forward + input-gradient convolutions
     n = len(scenes)
     line = {"metric": METRIC, "value": world * n * 1000.0 / ms, "unit": "scenes/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -184,7 +228,8 @@ def run_train(args, det, scenes, dev, world, rank, dtype):
             "clocks": clk.summary(),
             "e2e": {"value": world * n * 1000.0 / ms_e2e, "unit": "scenes/s",
                     "h2d_bytes_per_step": sum(p.numel() * 4 for p, _, _ in host), "d2h_bytes_per_step": 4,
-                    "ms_per_step": ms_e2e}}
+                    "ms_per_step": ms_e2e},
+            "gpu_launches": launches, "roofline": roofline}
     if rank == 0:
         print(json.dumps(line))
     if world > 1:
@@ -319,32 +364,7 @@ def main():
     step_device()
     torch.cuda.synchronize()
     prof, ops.PROFILE = ops.PROFILE, None
-    agg = {}
-    for name, s, e, fl, by in prof:
-        a = agg.setdefault(name, [0, 0.0, 0.0, 0.0])
-        a[0] += 1
-        a[1] += s.elapsed_time(e)
-        a[2] += fl
-        a[3] += by
-    pk, pk_kind = peaks()
-    kernels = {}
-    for name, (cnt, t_ms, fl, by) in agg.items():
-        kernels[name] = {"launches": cnt, "ms": round(t_ms, 4), "tflops": fl / t_ms / 1e9 if fl else None,
-                         "gbs": by / t_ms / 1e6}
-    main_k = "conv_tc" if "conv_tc" in agg else "conv_cc"
-    cnt, t_ms, fl, by = agg[main_k]
-    peak = pk["bf16_tflops_sustained"] if main_k == "conv_tc" else 75.0
-    traffic = None
-    try:  # DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/conv_tc_traffic.json)
-        if main_k == "conv_tc" and args.workload == "scannet":
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "conv_tc_traffic.json")))["dram_bytes_per_launch"]
-    except Exception:
-        pass
-    roofline = {"kernel": main_k, "bound": "tensor", "achieved": fl / t_ms / 1e9, "peak": peak, "unit": "TFLOP/s",
-                "frac": fl / t_ms / 1e9 / peak, "traffic": traffic, "algorithmic_bytes_per_launch": by / cnt,
-                "peak_source": pk_kind,
-                "launches_per_step": cnt, "avg_launch_ms": t_ms / cnt, "share_of_step": t_ms / ms,
-                "algorithmic_flops_per_step": fl, "other_kernels": kernels}
+    roofline = roofline_from_profile(prof, ms, args.workload == "scannet")
 
     line = {"metric": METRIC, "value": world * BATCH * 1000.0 / ms, "unit": "scenes/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",

@@ -17,8 +17,14 @@ def conv_wgrad(feats, grad_out, kmap, kvol, cin, cout):
     n_out = int(grad_out.shape[0])
     nbr = kmap.nbr if kmap is not None else None
     ld = kmap.ld if kmap is not None else 0
+    t0 = ops._prof_start()
     call("b2_conv_wgrad", ptr(feats), DT[feats.dtype], ptr(grad_out), DT[grad_out.dtype], ptr(nbr), ld, n_out, cin, cout,
          kvol, ptr(dw))
+    if t0 is not None:
+        tc = feats.dtype == torch.bfloat16 and grad_out.dtype == torch.bfloat16 and cin % 64 == 0 and cout % 64 == 0
+        pairs = ops.kmap_pairs(kmap, n_out)
+        ops._prof_stop(t0, "wgrad_tc" if tc else "wgrad_cc", 2.0 * pairs * cin * cout,
+                       feats.element_size() * (feats.shape[0] * cin + n_out * cout) + 4.0 * kvol * (cin * cout + ld))
     return dw
 
 
