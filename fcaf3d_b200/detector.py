@@ -109,18 +109,28 @@ class MEResNet3D(nn.Module):
         cm = x.coordinate_manager
         conv, inorm, _, pool = self.conv1
         dt = ME.get_compute_dtype()
+        # Coordinate maps run one level ahead of the features: the build of the next strided map is enqueued before the
+        # convolutions of the current level, so that when the host reads its row count the GPU still has work queued
+        # (CoordinateManager.stride_prefetch) - the forward pass has no idle-GPU host round trips in the backbone.
         key, km = conv.maps(x)
+        cm.stride_prefetch(key, pool.stride)
         f = ops.sparse_conv(x.F.contiguous(), conv._w3(), km, cm.size(key), out_dtype=dt)
         m = cm.get_map(key)
         scale, shift = inorm.scale_shift(f, m)
         f = ops.affine_act(f, scale, shift, coords=m.coords, act=ops.ACT_RELU, out=f)
         pkey = cm.stride(key, pool.stride)
+        first = getattr(self, "layer1")[0]
+        if isinstance(first, BasicBlock):
+            cm.stride_prefetch(pkey, first.conv1.stride)
         f = ops.maxpool(f, cm.kernel_map(key, pkey, pool.kernel_size, pool.dilation))
         key = pkey
         outs = []
         for i in range(self.n_outs):
-            for block in getattr(self, f"layer{i + 1}"):
+            nxt = getattr(self, f"layer{i + 2}")[0] if i + 1 < self.n_outs else None
+            for j, block in enumerate(getattr(self, f"layer{i + 1}")):
                 f, key = _fused_block(block, f, key, cm)
+                if j == 0 and isinstance(nxt, BasicBlock):
+                    cm.stride_prefetch(key, nxt.conv1.stride)     # consumed by the first block of the next layer
             outs.append(ME.SparseTensor(f, coordinate_map_key=key, coordinate_manager=cm))
         return outs
 
@@ -473,11 +483,11 @@ class Fcaf3DNeckWithHead(nn.Module):
         cm = inputs[0].coordinate_manager
         levels = [None] * len(inputs)
         f, key = inputs[-1].F, inputs[-1].coordinate_map_key
-        prev = None
+        prev = pre_gen = None
         for i in range(len(inputs) - 1, -1, -1):
             if i < len(inputs) - 1:
                 gen, bn1, _, conv, bn2, _ = getattr(self, f"up_block_{i + 1}")
-                gkey = cm.generate_children(key)
+                gkey = pre_gen
                 if bn1.bn.training:
                     g = gen.generate(f)
                     s, b = bn1.scale_shift(g)
@@ -502,8 +512,15 @@ class Fcaf3DNeckWithHead(nn.Module):
                     table, cap = pm.ensure_table()
                     sc = ops.interp(table, cap, prev["prune"], pm.ts, um.coords.float())
                     mask = ops.topk_mask(sc.reshape(-1), um.off_dev, um.num_batches, self.pts_threshold)
-                    key, m8, pos, n_keep = cm.prune(key, mask)
+                    keep = [min(um.off_host[b + 1] - um.off_host[b], self.pts_threshold) for b in range(um.num_batches)]
+                    key, m8, pos, n_keep = cm.prune(key, mask, keep_counts=keep)   # top-k keeps exactly min(N_b, k) rows
                     f = ops.gather_rows(f, m8, pos, n_keep)
+            if i > 0:
+                # the next (finer) level's generated map and its union with the backbone map depend on coordinates only:
+                # enqueue them before this level's out_block / heads so that the union's row count is not waited for idle
+                nkey = cm.generate_children(key)
+                cm.union_prefetch(inputs[i - 1].coordinate_map_key, nkey)
+                pre_gen = nkey
             conv, bn, _ = getattr(self, f"out_block_{i}")
             km = cm.kernel_map(key, key, conv.kernel_size, conv.dilation)
             o = conv_bn_act(conv, bn, f, km, cm.size(key), ops.ACT_ELU)

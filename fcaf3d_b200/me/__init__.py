@@ -81,6 +81,7 @@ class CoordinateManager:
         self._maps = {}
         self._kmaps = {}
         self._stride_cache = {}
+        self._pending = {}      # deferred map builds (stride / union) whose row count has not been read yet
         self._auto = 0
         self.num_batches = 0
 
@@ -100,7 +101,10 @@ class CoordinateManager:
         coords = coordinates.to(torch.int32).contiguous()
         self.device = coords.device
         perm = None
-        if coords.shape[0]:
+        hint = getattr(coordinates, "_b2_num_batches", None)
+        if hint is not None:        # produced by ops.quantize_points: batch-grouped by construction, batch count known
+            nb = int(hint)
+        elif coords.shape[0]:
             b = coords[:, 0]
             nb = int(b.max().item()) + 1
             if bool((b[1:] < b[:-1]).any().item()):  # not batch-grouped: stable regroup (rare path)
@@ -123,6 +127,16 @@ class CoordinateManager:
             inverse = inv
         return key, (unique_index, inverse)
 
+    def stride_prefetch(self, in_key, stride):
+        """Enqueues the build of the strided map now and leaves its row count in flight; a later stride() call picks it
+        up.  Lets the caller put GPU work between the build and the host read (no idle GPU at the read)."""
+        s = stride if isinstance(stride, int) else int(stride[0])
+        ck = (in_key, s)
+        if ck in self._stride_cache or ("s", ck) in self._pending:
+            return
+        src = self._maps[in_key]
+        self._pending[("s", ck)] = ops.map_build_start(src.coords, src.ts * s, self.num_batches)
+
     def stride(self, in_key, stride):
         """Coordinates floored to multiples of ts*stride, deduplicated; cached per (key, stride) (ME A.3)."""
         s = stride if isinstance(stride, int) else int(stride[0])
@@ -131,7 +145,8 @@ class CoordinateManager:
             return self._stride_cache[ck]
         src = self._maps[in_key]
         ts_out = src.ts * s
-        out_coords, _, inverse, table, cap, _, off = ops.map_build(src.coords, ts_out, self.num_batches)
+        pending = self._pending.pop(("s", ck), None) or ops.map_build_start(src.coords, ts_out, self.num_batches)
+        out_coords, _, inverse, table, cap, _, off = ops.map_build_finish(pending)
         key = CoordinateMapKey(ts_out, "")
         if key in self._maps:
             key = self._fresh_id(ts_out)
@@ -155,18 +170,28 @@ class CoordinateManager:
         self._maps[key] = m
         return key
 
-    def union(self, key_a, key_b):
+    def _union_start(self, key_a, key_b):
         a, b = self._maps[key_a], self._maps[key_b]
         if a.ts != b.ts:
             raise B2Error("union of maps with different tensor strides")
         table, cap = a.ensure_table()
-        out_coords, dst_a, dst_b, n, off = ops.map_union(table, cap, a.coords, a.off_dev, b.coords, b.off_dev,
-                                                         self.num_batches)
+        return ops.map_union_start(table, cap, a.coords, a.off_dev, b.coords, b.off_dev, self.num_batches)
+
+    def union_prefetch(self, key_a, key_b):
+        """Enqueues the union now, row count left in flight (see stride_prefetch)."""
+        if ("u", key_a, key_b) not in self._pending:
+            self._pending[("u", key_a, key_b)] = self._union_start(key_a, key_b)
+
+    def union(self, key_a, key_b):
+        a = self._maps[key_a]
+        pending = self._pending.pop(("u", key_a, key_b), None) or self._union_start(key_a, key_b)
+        out_coords, dst_a, dst_b, n, off = ops.map_union_finish(pending)
         key = self._fresh_id(a.ts)
         self._maps[key] = _Map(out_coords.contiguous(), a.ts, self.num_batches, off=off)
         return key, dst_a, dst_b
 
-    def prune(self, in_key, mask):
+    def prune(self, in_key, mask, keep_counts=None):
+        """keep_counts: rows kept per scene when the caller knows them (a top-k mask) - saves the host read."""
         src = self._maps[in_key]
         m8 = mask.view(torch.uint8) if mask.dtype == torch.bool else mask
         pos, total = ops.scan_mask(m8)
@@ -178,7 +203,12 @@ class CoordinateManager:
             off_dev = torch.cat((off, total)).to(torch.int32)
         else:
             off_dev = torch.zeros((nb + 1,), dtype=torch.int32, device=m8.device)
-        off_host = ops.read_ints(off_dev)
+        if keep_counts is not None:
+            off_host = [0]
+            for c in keep_counts:
+                off_host.append(off_host[-1] + int(c))
+        else:
+            off_host = ops.read_ints(off_dev)
         n_out = off_host[-1]
         coords = ops.gather_coords(src.coords, m8, pos, n_out)
         key = self._fresh_id(src.ts)

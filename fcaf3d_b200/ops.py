@@ -32,9 +32,40 @@ def alloc_table(n, device):
     return torch.empty(cap * 16, dtype=torch.uint8, device=device), cap
 
 
+_PINNED = {"bufs": [], "next": 0}
+
+
+def _pinned_ints(n):
+    """Small pinned int32 staging buffers, reused round-robin (64 outstanding reads at most)."""
+    if not _PINNED["bufs"]:
+        _PINNED["bufs"] = [torch.empty((256,), dtype=I32).pin_memory() for _ in range(64)]
+    if n > 256:
+        return torch.empty((n,), dtype=I32).pin_memory()
+    i = _PINNED["next"]
+    _PINNED["next"] = (i + 1) % len(_PINNED["bufs"])
+    return _PINNED["bufs"][i][:n]
+
+
+class HostRead:
+    """Asynchronous device->host read of a small int32 tensor: the copy is enqueued now, `get()` waits for it only.
+    Work enqueued on the stream between the two keeps the GPU busy while the host looks at the numbers."""
+
+    def __init__(self, t):
+        self.host = _pinned_ints(t.numel())
+        self.host.copy_(t.reshape(-1), non_blocking=True)
+        self.event = torch.cuda.Event()
+        self.event.record()
+
+    def get(self):
+        self.event.synchronize()
+        return self.host.tolist()
+
+
 def read_ints(t):
-    """One device->host read (synchronises the current stream)."""
-    return t.cpu().tolist()
+    """One device->host read of an int32 tensor (waits for the current stream up to the copy)."""
+    if t.dtype != I32 or not t.is_cuda:
+        return t.cpu().tolist()
+    return HostRead(t).get()
 
 
 # ----------------------------------------------------------------------------- coordinate maps
@@ -51,13 +82,12 @@ def quantize_points(points_list, voxel_size, feat_div=255.0):
         call("b2_quantize_points", ptr(p), p.shape[0], dim, b, float(voxel_size), float(feat_div), row0, ptr(coords),
              ptr(feats))
         row0 += int(p.shape[0])
+    coords._b2_num_batches = len(points_list)   # rows are batch-grouped by construction: insert_and_map skips two host reads
     return coords, feats
 
 
-def map_build(coords, quant=0, num_batches=0):
-    """Dedup (first occurrence wins, first-occurrence order).  Returns
-    (out_coords[n_out,4], unique_index[n_out], inverse_map[n], table, cap, n_out[, (off_dev, off_host)]).
-    With num_batches > 0 the batch offsets of the new map come back from the same single host read."""
+def map_build_start(coords, quant=0, num_batches=0):
+    """Enqueues the dedup kernels and the asynchronous read of (n_out, err, batch offsets); see map_build_finish."""
     require_cuda(coords, "coords")
     n = int(coords.shape[0])
     dev = coords.device
@@ -73,17 +103,30 @@ def map_build(coords, quant=0, num_batches=0):
          ptr(status), ptr(status) + 4, ptr(ws), ws.numel())
     if num_batches > 0:
         call("b2_batch_offsets_dev", ptr(out_coords), ptr(status), n, num_batches, ptr(status) + 8, ptr(status) + 4)
-    host = read_ints(status)
+    _prof_stop(t0, "hash_build", 0.0, 40.0 * n)
+    return dict(read=HostRead(status), status=status, out_coords=out_coords, unique_index=unique_index, inverse=inverse,
+                table=table, cap=cap, num_batches=num_batches)
+
+
+def map_build_finish(p):
+    host = p["read"].get()
     n_out, err = host[0], host[1]
-    _prof_stop(t0, "hash_build", 0.0, 20.0 * n + 20.0 * n_out)
     if err == 1:
         raise _lib.B2Error("coordinate outside the packed key range (batch < 1023, |xyz| < 131072)")
     if err == 2:
         raise _lib.B2Error("coordinate rows must be grouped by ascending batch index")
-    if num_batches > 0:
-        return (out_coords[:n_out], unique_index[:n_out], inverse, table, cap, n_out,
-                (status[2:3 + num_batches], host[2:3 + num_batches]))
-    return out_coords[:n_out], unique_index[:n_out], inverse, table, cap, n_out
+    nb = p["num_batches"]
+    if nb > 0:
+        return (p["out_coords"][:n_out], p["unique_index"][:n_out], p["inverse"], p["table"], p["cap"], n_out,
+                (p["status"][2:3 + nb], host[2:3 + nb]))
+    return p["out_coords"][:n_out], p["unique_index"][:n_out], p["inverse"], p["table"], p["cap"], n_out
+
+
+def map_build(coords, quant=0, num_batches=0):
+    """Dedup (first occurrence wins, first-occurrence order).  Returns
+    (out_coords[n_out,4], unique_index[n_out], inverse_map[n], table, cap, n_out[, (off_dev, off_host)]).
+    With num_batches > 0 the batch offsets of the new map come back from the same single host read."""
+    return map_build_finish(map_build_start(coords, quant, num_batches))
 
 
 def map_table(coords):
@@ -117,7 +160,7 @@ def batch_offsets(coords, num_batches):
     return buf[: num_batches + 1], host[: num_batches + 1]
 
 
-def map_union(a_table, a_cap, a_coords, a_off, b_coords, b_off, num_batches=0):
+def map_union_start(a_table, a_cap, a_coords, a_off, b_coords, b_off, num_batches=0):
     dev = a_coords.device
     na, nb = int(a_coords.shape[0]), int(b_coords.shape[0])
     out_coords = torch.empty((na + nb, 4), dtype=I32, device=dev)
@@ -130,11 +173,19 @@ def map_union(a_table, a_cap, a_coords, a_off, b_coords, b_off, num_batches=0):
          ptr(out_coords), ptr(dst_a), ptr(dst_b), ptr(n_out), ptr(ws), ws.numel())
     if num_batches > 0:
         call("b2_batch_offsets_dev", ptr(out_coords), ptr(n_out), na + nb, num_batches, ptr(n_out) + 8, ptr(n_out) + 4)
-    host = read_ints(n_out)
-    n = host[0]
-    if num_batches > 0:
-        return out_coords[:n], dst_a, dst_b, n, (n_out[2:3 + num_batches], host[2:3 + num_batches])
-    return out_coords[:n], dst_a, dst_b, n
+    return dict(read=HostRead(n_out), n_out=n_out, out_coords=out_coords, dst_a=dst_a, dst_b=dst_b, num_batches=num_batches)
+
+
+def map_union_finish(p):
+    host = p["read"].get()
+    n, nb = host[0], p["num_batches"]
+    if nb > 0:
+        return p["out_coords"][:n], p["dst_a"], p["dst_b"], n, (p["n_out"][2:3 + nb], host[2:3 + nb])
+    return p["out_coords"][:n], p["dst_a"], p["dst_b"], n
+
+
+def map_union(a_table, a_cap, a_coords, a_off, b_coords, b_off, num_batches=0):
+    return map_union_finish(map_union_start(a_table, a_cap, a_coords, a_off, b_coords, b_off, num_batches))
 
 
 def scan_mask(mask):
