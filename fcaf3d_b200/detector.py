@@ -554,7 +554,7 @@ class Fcaf3DNeckWithHead(nn.Module):
         bases = []
         for li in range(len(levels)):
             bases += [cand_off[b] + sum(cnt[b][:li]) for b in range(nb)]
-        meta = torch.tensor(cand_off + bases, dtype=torch.int32, device=dev)
+        meta = ops.ints_to_device(cand_off + bases, dev)
         cand_off_dev = meta[: nb + 1]
         for li, (l, m) in enumerate(zip(levels, maps)):
             k = nms_pre if nms_pre > 0 else m.n
@@ -577,10 +577,17 @@ class Fcaf3DNeckWithHead(nn.Module):
         ops.call("b2_class_segments", ops.ptr(cand_boxes), ops.ptr(cand_scores), ops.ptr(cand_off_dev), nb, n_cls, total,
                  float(score_thr), ops.ptr(flags), ops.ptr(pos), ops.ptr(seg_off) + 4 * (nseg + 1), ops.ptr(seg_boxes),
                  ops.ptr(seg_scores), ops.ptr(seg_src), ops.ptr(seg_off), ops.ptr(ws), ws.numel())
-        seg_off_host = ops.read_ints(seg_off)[: nseg + 1]  # the one host sync of the tail
-        n_in = seg_off_host[-1]
-        keep, order, sorted_boxes, _ = ops.nms_batched(seg_boxes[:n_in], seg_scores[:n_in], seg_off_host, iou_thr,
-                                                       rotated, sort=True)
+        max_seg = max([sum(c) for c in cnt] + [0])       # a (scene, class) segment holds at most the scene's candidates
+        if ops.NMS_GREEDY and max_seg <= ops.NMS_GREEDY_MAX_SEG:
+            # no host read: the greedy kernels take the segment offsets from the device, buffers are sized by the bound
+            n_in = nf
+            keep, order, sorted_boxes, _ = ops.nms_batched(seg_boxes, seg_scores, None, iou_thr, rotated, sort=True,
+                                                           seg_off_dev=seg_off[: nseg + 1], max_seg=max_seg)
+        else:
+            seg_off_host = ops.read_ints(seg_off)[: nseg + 1]
+            n_in = seg_off_host[-1]
+            keep, order, sorted_boxes, _ = ops.nms_batched(seg_boxes[:n_in], seg_scores[:n_in], seg_off_host, iou_thr,
+                                                           rotated, sort=True)
         kpos, ktotal = ops.scan_mask(keep)
         out_boxes = torch.empty((n_in, 7), dtype=torch.float32, device=dev)
         out_scores = torch.empty((n_in,), dtype=torch.float32, device=dev)

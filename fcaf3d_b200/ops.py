@@ -61,6 +61,16 @@ class HostRead:
         return self.host.tolist()
 
 
+def ints_to_device(values, dev):
+    """Small host list -> int32 device tensor through a pinned staging buffer (asynchronous H2D, no pageable staging)."""
+    n = len(values)
+    if n == 0:
+        return torch.empty((0,), dtype=I32, device=dev)
+    host = _pinned_ints(n)
+    host.copy_(torch.tensor(values, dtype=I32))
+    return host.to(dev, non_blocking=True)
+
+
 def read_ints(t):
     """One device->host read of an int32 tensor (waits for the current stream up to the copy)."""
     if t.dtype != I32 or not t.is_cuda:
@@ -472,17 +482,33 @@ def nms_plan(seg_off_host):
 
 
 NMS_GREEDY = True  # blocked greedy kernel (rows of kept boxes only); False = full mask + device reduce
+NMS_GREEDY_MAX_SEG = 4096  # in-kernel sort capacity (SORT_MAX, nms.cu)
 
 
-def nms_batched(boxes, scores, seg_off_host, thresh, rotated, sort=True, greedy=None):
+def nms_batched(boxes, scores, seg_off_host, thresh, rotated, sort=True, greedy=None, seg_off_dev=None, max_seg=None):
     """boxes [n,7], scores [n] grouped into segments.  Returns (keep uint8 [n] in sorted order, order int32 [n]
-    (segment-local source index of every sorted slot), sorted_boxes, counts int32 [nseg])."""
+    (segment-local source index of every sorted slot), sorted_boxes, counts int32 [nseg]).
+    Without a host copy of the segment offsets (seg_off_host None) the greedy kernels run from the DEVICE offsets
+    seg_off_dev int32 [nseg+1] and an upper bound max_seg of the segment length; boxes / scores may then be longer than
+    seg_off[nseg] and keep is 0 past it - no host read anywhere."""
     dev = boxes.device
     n = int(boxes.shape[0])
+    if seg_off_host is None:
+        nseg = int(seg_off_dev.shape[0]) - 1
+        keep = torch.zeros((n,), dtype=torch.uint8, device=dev)
+        counts = torch.zeros((max(nseg, 1),), dtype=I32, device=dev)
+        sorted_boxes = torch.empty_like(boxes) if sort else boxes
+        order = torch.empty((n,), dtype=I32, device=dev) if sort else None
+        if nseg > 0 and n > 0:
+            ws = workspace(_lib.lib().b2_nms_greedy_ws_bytes(n, int(bool(rotated))), dev, slot=2)
+            call("b2_nms_greedy_batched", ptr(boxes), ptr(scores), ptr(seg_off_dev), nseg, n, int(max_seg), float(thresh),
+                 int(bool(rotated)), int(bool(sort)), ptr(sorted_boxes), ptr(order), ptr(ws), ws.numel(), ptr(keep),
+                 ptr(counts))
+        return keep, order, sorted_boxes, counts
     nseg = len(seg_off_host) - 1
     if (NMS_GREEDY if greedy is None else greedy) and nseg > 0:
         max_seg = max(seg_off_host[i + 1] - seg_off_host[i] for i in range(nseg))
-        so = torch.tensor(list(seg_off_host), dtype=I32, device=dev)
+        so = ints_to_device(list(seg_off_host), dev)
         keep = torch.empty((n,), dtype=torch.uint8, device=dev)
         counts = torch.zeros((nseg,), dtype=I32, device=dev)
         sorted_boxes = torch.empty_like(boxes) if sort else boxes
