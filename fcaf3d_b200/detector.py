@@ -634,6 +634,8 @@ class SingleStageSparse3DDetector(nn.Module):
 
     def _input_tensor(self, points):
         coords, feats = ops.quantize_points([p.contiguous() for p in points], self.voxel_size, 255.0)
+        stem = self.backbone.conv1[0]
+        coords._b2_prefetch_stride = int(stem.stride) if isinstance(stem.stride, int) else int(stem.stride[0])
         return ME.SparseTensor(coordinates=coords, features=feats)
 
     def extract_feat(self, points, img_metas=None):

@@ -113,11 +113,19 @@ class CoordinateManager:
         else:
             nb = 1
         self.num_batches = max(self.num_batches, nb)
-        out_coords, unique_index, inverse, table, cap, n_out, off = ops.map_build(coords, 0, self.num_batches)
+        p0 = ops.map_build_start(coords, 0, self.num_batches)
+        # The first strided map can be built from the raw rows as well (dedup keeps first-occurrence order, so flooring the
+        # raw rows gives the same map as flooring the deduplicated ones): callers that know the stride of their first
+        # convolution ask for it here and both row counts come back behind one wait.
+        pre = int(getattr(coordinates, "_b2_prefetch_stride", 0) or 0)
+        p1 = ops.map_build_start(coords, ts * pre, self.num_batches) if pre > 1 and perm is None else None
+        out_coords, unique_index, inverse, table, cap, n_out, off = ops.map_build_finish(p0)
         key = CoordinateMapKey(ts, string_id)
         if key in self._maps:
             key = self._fresh_id(ts)
         self._maps[key] = _Map(out_coords.contiguous(), ts, self.num_batches, table, cap, off=off)
+        if p1 is not None:
+            self._pending[("s", (key, pre))] = p1
         unique_index = unique_index.long()
         inverse = inverse.long()
         if perm is not None:

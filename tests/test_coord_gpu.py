@@ -136,3 +136,41 @@ def test_children_kernel_map_derived_equals_hashed(dev):
     # dilation 2 or another kernel size on the same map still takes the hash path
     km2 = cm.kernel_map(g, g, 3, 2)
     assert torch.equal(km2.nbr[:, :n].cpu().long(), torch.from_numpy(ocm.neighbour_table(og, og, 3, 2)))
+
+
+def test_prefetched_maps_equal_the_lazy_ones(dev):
+    """stride_prefetch / union_prefetch / the raw-row build of the first strided map (asynchronous row counts) give the
+    same maps, bit for bit, as the lazy calls; prune with host-known keep counts equals prune with a device read."""
+    c = surface_coords(6000, batch=3, seed=21)
+    c = torch.from_numpy(np.concatenate([c, c[::7]], 0))           # duplicates: the input map really deduplicates
+    c = c[torch.sort(c[:, 0], stable=True).indices].contiguous().to(dev)
+    lazy = ME.SparseTensor(torch.zeros(len(c), 1, device=dev), coordinates=c.clone())
+    hinted = c.clone()
+    hinted._b2_num_batches, hinted._b2_prefetch_stride = 3, 2
+    pre = ME.SparseTensor(torch.zeros(len(c), 1, device=dev), coordinates=hinted)
+    cl, cp = lazy.coordinate_manager, pre.coordinate_manager
+    assert torch.equal(lazy.C, pre.C) and len(cp._pending) == 1
+    kl, kp = lazy.coordinate_map_key, pre.coordinate_map_key
+    for _ in range(3):
+        nl = cl.stride(kl, 2)
+        cp.stride_prefetch(kp, 2)
+        np_ = cp.stride(kp, 2)
+        assert torch.equal(cl.get_coordinates(nl), cp.get_coordinates(np_))
+        assert cl.get_map(nl).off_host == cp.get_map(np_).off_host
+        kl, kp = nl, np_
+    assert not cp._pending
+    # union of the stride-4 map with the children of the stride-8 map, prefetched vs lazy
+    l4, p4 = cl.stride(cl.stride(lazy.coordinate_map_key, 2), 2), cp.stride(cp.stride(pre.coordinate_map_key, 2), 2)
+    gl, gp = cl.generate_children(kl), cp.generate_children(kp)
+    cp.union_prefetch(p4, gp)
+    ul, al, bl = cl.union(l4, gl)
+    up, ap, bp = cp.union(p4, gp)
+    assert torch.equal(cl.get_coordinates(ul), cp.get_coordinates(up)) and torch.equal(al, ap) and torch.equal(bl, bp)
+    # prune: counts known on the host
+    um = cl.get_map(ul)
+    mask = ops.topk_mask(torch.rand(um.n, device=dev), um.off_dev, 3, 500)
+    keep = [min(um.off_host[b + 1] - um.off_host[b], 500) for b in range(3)]
+    k1, _, _, n1 = cl.prune(ul, mask)
+    k2, _, _, n2 = cp.prune(up, mask, keep_counts=keep)
+    assert n1 == n2 and torch.equal(cl.get_coordinates(k1), cp.get_coordinates(k2))
+    assert cl.get_map(k1).off_host == cp.get_map(k2).off_host
