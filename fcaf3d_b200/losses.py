@@ -55,13 +55,20 @@ class CrossEntropyLoss(nn.Module):
     def __init__(self, use_sigmoid=False, use_mask=False, reduction="mean", class_weight=None, loss_weight=1.0):
         super().__init__()
         assert use_sigmoid, "FCAF3D uses the sigmoid (binary) flavour for centerness"
-        self.loss_weight = loss_weight
+        self.loss_weight, self.reduction = loss_weight, reduction
 
     def forward(self, cls_score, label, weight=None, avg_factor=None, reduction_override=None, **kw):
+        reduction = reduction_override if reduction_override else self.reduction     # mmdet weight_reduce_loss rules
         loss = F.binary_cross_entropy_with_logits(cls_score, label.float(), reduction="none")
         if weight is not None:
             loss = loss * weight.reshape(loss.shape[0], -1)
-        return self.loss_weight * (loss.sum() / avg_factor if avg_factor is not None else loss.mean())
+        if avg_factor is None:
+            loss = loss.mean() if reduction == "mean" else loss.sum() if reduction == "sum" else loss
+        elif reduction == "mean":
+            loss = loss.sum() / avg_factor
+        elif reduction != "none":
+            raise ValueError('avg_factor can not be used with reduction="sum"')
+        return self.loss_weight * loss
 
 
 # ------------------------------------------------------------------------------------------- IoU losses

@@ -46,7 +46,7 @@ class Registry:
 
 
 BACKBONES, HEADS, DETECTORS, LOSSES = Registry("backbone"), Registry("head"), Registry("detector"), Registry("loss")
-BBOX_ASSIGNERS, IOU_CALCULATORS = Registry("assigner"), Registry("iou")
+BBOX_ASSIGNERS, IOU_CALCULATORS, NECKS = Registry("assigner"), Registry("iou"), Registry("neck")
 
 
 class Scale(nn.Module):  # mmcv.cnn.Scale
@@ -109,15 +109,24 @@ class FocalLoss(nn.Module):  # mmdet.models.losses.FocalLoss(use_sigmoid=True)
 
 
 @LOSSES.register_module()
-class CrossEntropyLoss(nn.Module):  # mmdet CrossEntropyLoss(use_sigmoid=True) -> binary_cross_entropy
+class CrossEntropyLoss(nn.Module):  # mmdet 2.14 CrossEntropyLoss(use_sigmoid=True) -> binary_cross_entropy + weight_reduce_loss
     def __init__(self, use_sigmoid=False, use_mask=False, reduction="mean", class_weight=None, loss_weight=1.0):
         super().__init__()
         assert use_sigmoid
-        self.loss_weight = loss_weight
+        self.loss_weight, self.reduction = loss_weight, reduction
 
     def forward(self, cls_score, label, weight=None, avg_factor=None, reduction_override=None, **kw):
+        reduction = reduction_override if reduction_override else self.reduction
         loss = F.binary_cross_entropy_with_logits(cls_score, label.float(), reduction="none")
-        return self.loss_weight * (loss.sum() / avg_factor if avg_factor is not None else loss.mean())
+        if weight is not None:
+            loss = loss * weight.float()
+        if avg_factor is None:
+            loss = loss.mean() if reduction == "mean" else loss.sum() if reduction == "sum" else loss
+        elif reduction == "mean":
+            loss = loss.sum() / avg_factor
+        elif reduction != "none":
+            raise ValueError('avg_factor can not be used with reduction="sum"')
+        return self.loss_weight * loss
 
 
 def sort_v(vertices, mask, num_valid):
@@ -205,7 +214,7 @@ def load():
     _mod("mmcv")
     _mod("mmcv.cnn", Scale=Scale, bias_init_with_prob=bias_init_with_prob)
     _mod("mmdet")
-    _mod("mmdet.models", BACKBONES=BACKBONES, DETECTORS=DETECTORS)
+    _mod("mmdet.models", BACKBONES=BACKBONES, DETECTORS=DETECTORS, NECKS=NECKS, build_loss=build_loss)
     _mod("mmdet.models.builder", HEADS=HEADS, LOSSES=LOSSES, build_loss=build_loss)
     _mod("mmdet.models.losses")
     _mod("mmdet.models.losses.utils", weighted_loss=weighted_loss)
@@ -243,8 +252,9 @@ def load():
     _mod("mmdet3d.models.detectors")
     _mod("mmdet3d.models.detectors.base", Base3DDetector=nn.Module)
     det = _load("mmdet3d.models.detectors.single_stage_sparse", "mmdet3d/models/detectors/single_stage_sparse.py")
+    fpn = _load("mmdet3d.models.necks.me_fpn", "mmdet3d/models/necks/me_fpn.py")
     ns = types.SimpleNamespace(
-        MEResNet3D=backbone.MEResNet3D, Fcaf3DNeckWithHead=head.Fcaf3DNeckWithHead, Fcaf3DAssigner=head.Fcaf3DAssigner,
+        MEFPN3D=fpn.MEFPN3D, MEResNet3D=backbone.MEResNet3D, Fcaf3DNeckWithHead=head.Fcaf3DNeckWithHead, Fcaf3DAssigner=head.Fcaf3DAssigner,
         compute_centerness=head.compute_centerness, SingleStageSparse3DDetector=det.SingleStageSparse3DDetector,
         IoU3DLoss=losses.IoU3DLoss, cal_iou_3d=riou.cal_iou_3d,
         axis_aligned_bbox_overlaps_3d=iouc.axis_aligned_bbox_overlaps_3d,

@@ -160,8 +160,60 @@ def train_fixture(config, seeds, name, n_points=3000):
     print(name, {k: float(v) for k, v in losses.items()})
 
 
+def mefpn_fixture(seeds=(3, 103), n_points=3000, name="mefpn_tiny.npz"):
+    """The reference's own necks/me_fpn.py (MEFPN3D with score blocks and pruning) behind its own MEResNet3D, on the
+    oracle: evaluation outputs per level and one training forward/backward (pruning loss + sampled gradients)."""
+    ns = ref_loader.load()
+    torch.manual_seed(0)
+    model = torch.nn.Module()
+    model.backbone = ns.MEResNet3D(in_channels=3, depth=34)
+    model.neck = ns.MEFPN3D(in_channels=(64, 128, 256, 512), out_channels=128, voxel_size=.01, pts_threshold=400)
+    deterministic_init(model, seed=2)
+    import MinkowskiEngine as OME
+    scenes = [make_scene("tiny", s, n_points, n_classes=18) for s in seeds]
+    out = {"seeds": np.array(seeds), "n_points": np.array(n_points)}
+    for i, (p, g, l) in enumerate(scenes):
+        out["points_%d" % i], out["gt_%d" % i] = p, g
+
+    def feats():
+        coords, f = OME.utils.batch_sparse_collate(
+            [(torch.from_numpy(p[:, :3] / .01), torch.from_numpy(p[:, 3:] / 255.)) for p, _, _ in scenes])
+        return model.backbone(OME.SparseTensor(coordinates=coords, features=f))
+
+    model.eval()
+    with torch.no_grad():
+        outs = model.neck(feats(), img_metas=[dict() for _ in seeds])
+    for lvl, o in enumerate(outs):
+        order = canonical_order(o.C)
+        c, f = o.C[order], o.F[order]
+        step = max(1, len(c) // SAMPLE)
+        out["eval_l%d_n" % lvl] = np.array(len(c))
+        out["eval_l%d_coords" % lvl] = c[::step].numpy()
+        out["eval_l%d_feat" % lvl] = f[::step].numpy()
+        out["eval_l%d_colsum" % lvl] = f.double().sum(0).numpy()
+    model.train()
+    gtb = [ns.DepthBoxes(torch.from_numpy(g), origin=(.5, .5, .5)) for _, g, _ in scenes]
+    gtl = [torch.from_numpy(l) for _, _, l in scenes]
+    outs, losses = model.neck(feats(), gtb, gtl, [dict() for _ in seeds])
+    total = losses["loss_pruning"] + sum(o.F.square().mean() for o in outs)
+    total.backward()
+    out["loss_pruning"] = losses["loss_pruning"].detach().numpy()
+    out["train_rows"] = np.array([len(o.F) for o in outs])
+    params = dict(model.named_parameters())
+    for k in ("neck.score_block_1.kernel", "neck.score_block_3.bias", "neck.up_block_2.0.kernel", "neck.out_block_0.0.kernel",
+              "backbone.layer3.0.conv1.kernel"):
+        g = params[k].grad.reshape(-1)
+        step = max(1, g.numel() // 4096)
+        out["grad/" + k] = g[::step].numpy()
+    np.savez_compressed(os.path.join(OUT, name), **out)
+    print(name, float(out["loss_pruning"]), out["train_rows"], [int(out["eval_l%d_n" % l]) for l in range(4)])
+
+
 if __name__ == "__main__":
     torch.set_num_threads(8)
+    if "--mefpn-only" in sys.argv:
+        mefpn_fixture()
+        sys.exit(0)
     if "--train-only" in sys.argv:
         train_fixture("fcaf3d_scannet-3d-18class.py", (0, 100), "train_tiny_scannet.npz")
         train_fixture("fcaf3d_sunrgbd-3d-10class.py", (5,), "train_tiny_sunrgbd.npz")
@@ -171,3 +223,4 @@ if __name__ == "__main__":
     detector_fixture("fcaf3d_sunrgbd-3d-10class.py", (5,), "fcaf3d_tiny_sunrgbd.npz")
     train_fixture("fcaf3d_scannet-3d-18class.py", (0, 100), "train_tiny_scannet.npz")
     train_fixture("fcaf3d_sunrgbd-3d-10class.py", (5,), "train_tiny_sunrgbd.npz")
+    mefpn_fixture()

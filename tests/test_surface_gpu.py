@@ -90,3 +90,55 @@ def test_negative_and_far_coordinates_match_oracle(dev):
     with torch.no_grad():
         y, ry = gc.to(dev)(x), oc(o)
     assert torch.equal(y.C.cpu(), ry.C) and rel_err(y.F, ry.F) < 2e-5
+
+
+def test_mefpn3d_matches_reference_golden(dev):
+    """fcaf3d_b200.necks.MEFPN3D against the reference's own necks/me_fpn.py run on the oracle
+    (tests/golden/mefpn_tiny.npz): evaluation outputs of the four levels (row sets exact, features 2e-3 of the column
+    max) and one training forward/backward (pruning loss 2e-3, sampled gradients 1e-2 of max)."""
+    import os
+    import numpy as np
+    from conftest import GOLDEN
+    from fcaf3d_b200.detector import MEResNet3D
+    from fcaf3d_b200.necks import MEFPN3D
+    from fcaf3d_b200.testing import canonical_order, deterministic_init
+    g = np.load(os.path.join(GOLDEN, "mefpn_tiny.npz"))
+    model = torch.nn.Module()
+    model.backbone = MEResNet3D(in_channels=3, depth=34)
+    model.neck = MEFPN3D(in_channels=(64, 128, 256, 512), out_channels=128, voxel_size=.01, pts_threshold=400)
+    deterministic_init(model, seed=2)
+    model = model.to(dev)
+    nb = len(g["seeds"])
+    scenes = [torch.from_numpy(g["points_%d" % i]).to(dev) for i in range(nb)]
+
+    def feats():
+        coords, f = ME.utils.batch_sparse_collate([(p[:, :3] / .01, p[:, 3:] / 255.) for p in scenes], device=dev)
+        return model.backbone(ME.SparseTensor(coordinates=coords, features=f))
+
+    ME.set_compute_dtype(torch.float32)
+    model.eval()
+    with torch.no_grad():
+        outs = model.neck(feats(), img_metas=[dict()] * nb)
+    for lvl, o in enumerate(outs):
+        order = canonical_order(o.C.cpu())
+        c, f = o.C.cpu()[order], o.F.float().cpu()[order]
+        assert len(c) == int(g["eval_l%d_n" % lvl])
+        step = max(1, len(c) // 256)
+        assert np.array_equal(c[::step].numpy(), g["eval_l%d_coords" % lvl])
+        want = torch.from_numpy(g["eval_l%d_feat" % lvl])
+        scale = want.abs().max(0).values.clamp(min=1e-6)
+        assert ((f[::step] - want).abs() / scale).max().item() < 2e-3
+    model.train()
+    gtb = [torch.from_numpy(g["gt_%d" % i]).to(dev) for i in range(nb)]          # gravity centre, size, yaw
+    outs, losses = model.neck(feats(), gtb, None, [dict()] * nb)
+    assert [len(o.F) for o in outs] == g["train_rows"].tolist()
+    want_loss = float(g["loss_pruning"])
+    assert abs(losses["loss_pruning"].item() - want_loss) < 2e-3 * abs(want_loss)
+    (losses["loss_pruning"] + sum(o.F.square().mean() for o in outs)).backward()
+    params = dict(model.named_parameters())
+    for key in [k[5:] for k in g.files if k.startswith("grad/")]:
+        flat = params[key].grad.reshape(-1)
+        step = max(1, flat.numel() // 4096)
+        want = torch.from_numpy(g["grad/" + key])
+        err = ((flat[::step].cpu() - want).abs().max() / want.abs().max().clamp(min=1e-12)).item()
+        assert err < 1e-2, (key, err)
