@@ -184,6 +184,20 @@ int b2_nms_single_noalloc_max_boxes(void);
 int b2_nms_single_noalloc(const float* boxes_sorted, long long n, float thresh, int rotated, uint8_t* keep, int* count,
                           void* stream);
 
+/* ---- device-side data path (reference: numpy pipeline datasets/pipelines/transforms_3d.py) ----------- */
+/* IndoorPointSample (:838-880) + RandomFlip3D (:144-160) + GlobalRotScaleTrans (:541-648) in one pass per scene:
+ * out[i] = T(in[choices[i]]), T = flip signs, rotation about z by `angle` (xyz @ rot_mat_T as base_points.py:139-179),
+ * uniform scale, translation; attribute columns (colour) are copied.  choices int64 [n_out] device (NULL = identity).
+ * err int32 [1] device flag, zeroed by the caller: 1 = index out of range.  Random numbers are drawn by the caller. */
+int b2_augment_points(const float* in, long long n_in, int dim, const long long* choices, long long n_out, int flip_h,
+                      int flip_v, float angle, float scale, float tx, float ty, float tz, float* out, int* err,
+                      void* stream);
+/* the same maps on ground-truth boxes (cx, cy, cz, dx, dy, dz, yaw), gravity centre (depth_box3d.py:119-208,
+ * base_box3d.py:149-222): yaw -> pi - yaw / -yaw under flips, yaw -= angle; without yaw the x / y sizes become the extents
+ * of the rotated footprint */
+int b2_augment_boxes(const float* boxes, int n, int with_yaw, int flip_h, int flip_v, float angle, float scale, float tx,
+                     float ty, float tz, float* out, void* stream);
+
 /* ---- training path ----------------------------------------------------------------------------- */
 /* ME ConvolutionBackwardKernelGPU, weight part: dw[k,ci,co] += sum_o in[nbr[k][o],ci] * dout[o,co] (fp32 atomics;
  * dw zero-initialised by the caller).  The input gradient is b2_conv_cc / b2_conv_tc over the transposed map with

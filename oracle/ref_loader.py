@@ -290,3 +290,21 @@ def build_reference_detector(config="fcaf3d_scannet-3d-18class.py", **head_overr
     tc = types.SimpleNamespace(**cfg["test_cfg"])
     cfg["test_cfg"] = tc
     return ns.SingleStageSparse3DDetector(**cfg)
+
+
+def load_structures():
+    """The reference's own box / point containers, loaded by path (core/bbox/structures/{base_box3d,depth_box3d}.py,
+    core/points/{base_points,depth_points}.py): their flip / rotate / scale / translate methods are what the training
+    pipeline's RandomFlip3D and GlobalRotScaleTrans call (datasets/pipelines/transforms_3d.py:100-160,541-636).
+    The CUDA-extension imports those files make (iou3d_cuda, points_in_boxes_batch) are not touched by these methods."""
+    load()
+    if "mmdet3d.core.points.depth_points" not in sys.modules:
+        _mod("mmdet3d.ops.iou3d", iou3d_cuda=None)
+        sys.modules["mmdet3d.ops"].points_in_boxes_batch = None
+        bp = _load("mmdet3d.core.points.base_points", "mmdet3d/core/points/base_points.py")
+        _mod("mmdet3d.core.points", BasePoints=bp.BasePoints)
+        _load("mmdet3d.core.points.depth_points", "mmdet3d/core/points/depth_points.py")
+        _load("mmdet3d.core.bbox.structures.base_box3d", "mmdet3d/core/bbox/structures/base_box3d.py")
+        _load("mmdet3d.core.bbox.structures.depth_box3d", "mmdet3d/core/bbox/structures/depth_box3d.py")
+    return (sys.modules["mmdet3d.core.bbox.structures.depth_box3d"].DepthInstance3DBoxes,
+            sys.modules["mmdet3d.core.points.depth_points"].DepthPoints)

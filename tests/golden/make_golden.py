@@ -209,8 +209,51 @@ def mefpn_fixture(seeds=(3, 103), n_points=3000, name="mefpn_tiny.npz"):
     print(name, float(out["loss_pruning"]), out["train_rows"], [int(out["eval_l%d_n" % l]) for l in range(4)])
 
 
+def augment_fixture(name="augment_ref.npz"):
+    """RandomFlip3D / GlobalRotScaleTrans arithmetic through the reference's OWN containers (DepthInstance3DBoxes,
+    DepthPoints loaded by path, oracle/ref_loader.load_structures) for a few parameter sets; boxes are stored with
+    their gravity centre."""
+    Boxes, Points = ref_loader.load_structures()
+    rng = np.random.default_rng(7)
+    out = {}
+    cases = [dict(with_yaw=True, flip_h=True, flip_v=True, angle=0.05, scale=1.07, trans=(0.11, -0.07, 0.03)),
+             dict(with_yaw=True, flip_h=False, flip_v=True, angle=-0.08, scale=0.93, trans=(-0.2, 0.05, 0.0)),
+             dict(with_yaw=False, flip_h=True, flip_v=False, angle=0.0872, scale=1.1, trans=(0.0, 0.3, -0.1)),
+             dict(with_yaw=False, flip_h=False, flip_v=False, angle=-0.03, scale=0.9, trans=(0.05, 0.05, 0.05))]
+    for ci, c in enumerate(cases):
+        pts = (rng.uniform(-3, 3, (500, 6))).astype(np.float32)
+        pts[:, 3:] = rng.uniform(0, 255, (500, 3)).astype(np.float32)
+        gt = np.concatenate([rng.uniform(-2, 2, (9, 3)), rng.uniform(0.3, 2, (9, 3)), rng.uniform(-1.5, 1.5, (9, 1))],
+                            1).astype(np.float32)
+        if not c["with_yaw"]:
+            gt[:, 6] = 0
+        b = Boxes(torch.from_numpy(gt[:, :7 if c["with_yaw"] else 6].copy()), box_dim=7 if c["with_yaw"] else 6,
+                  with_yaw=c["with_yaw"], origin=(.5, .5, .5))
+        p = Points(torch.from_numpy(pts.copy()), points_dim=6)
+        if c["flip_h"]:
+            p = b.flip("horizontal", points=p)
+        if c["flip_v"]:
+            p = b.flip("vertical", points=p)
+        p, _ = b.rotate(c["angle"], p)
+        p.scale(c["scale"])
+        b.scale(c["scale"])
+        t = np.array(c["trans"], dtype=np.float32)
+        p.translate(t)
+        b.translate(t)
+        res = torch.cat([b.gravity_center, b.tensor[:, 3:]], 1).numpy()
+        out["c%d_points_in" % ci], out["c%d_boxes_in" % ci] = pts, gt
+        out["c%d_points_out" % ci], out["c%d_boxes_out" % ci] = p.tensor.numpy(), res
+        out["c%d_params" % ci] = np.array([c["with_yaw"], c["flip_h"], c["flip_v"], c["angle"], c["scale"], *c["trans"]],
+                                          dtype=np.float64)
+    np.savez_compressed(os.path.join(OUT, name), **out)
+    print(name, len(cases), "cases")
+
+
 if __name__ == "__main__":
     torch.set_num_threads(8)
+    if "--augment-only" in sys.argv:
+        augment_fixture()
+        sys.exit(0)
     if "--mefpn-only" in sys.argv:
         mefpn_fixture()
         sys.exit(0)
@@ -224,3 +267,4 @@ if __name__ == "__main__":
     train_fixture("fcaf3d_scannet-3d-18class.py", (0, 100), "train_tiny_scannet.npz")
     train_fixture("fcaf3d_sunrgbd-3d-10class.py", (5,), "train_tiny_sunrgbd.npz")
     mefpn_fixture()
+    augment_fixture()

@@ -144,3 +144,28 @@ def test_golden_fixtures_match_a_fresh_reference_run():
     # (pcdet counts corners within a 1 cm MARGIN as inside, the torch code does not: a few pairs differ by ~1e-2)
     diff = np.abs(iou3d - g["iou_rot_values"])
     assert np.quantile(diff, 0.8) < 1e-4 and diff.max() < 3e-2
+
+
+def test_augmentation_oracle_matches_reference_containers():
+    """oracle/data_cpu.py against vectors produced by the reference's own DepthInstance3DBoxes / DepthPoints methods
+    (tests/golden/augment_ref.npz, generated by make_golden.py --augment-only); fp32 rounding only: 1e-6."""
+    import os
+    import numpy as np
+    from conftest import GOLDEN
+    from oracle import data_cpu as D
+    g = np.load(os.path.join(GOLDEN, "augment_ref.npz"))
+    for ci in range(4):
+        wy, fh, fv, ang, sc, tx, ty, tz = g["c%d_params" % ci]
+        p, b = D.random_flip(g["c%d_points_in" % ci], g["c%d_boxes_in" % ci], bool(fh), bool(fv), bool(wy))
+        p, b = D.global_rot_scale_trans(p, b, ang, sc, (tx, ty, tz), bool(wy))
+        assert np.abs(p - g["c%d_points_out" % ci]).max() < 1e-6 * 4
+        assert np.abs(b - g["c%d_boxes_out" % ci]).max() < 1e-6 * 4
+    # sampling: without replacement when the scene is large enough, with replacement otherwise; reproducible draw order
+    rng = np.random.default_rng(0)
+    pts = np.arange(50, dtype=np.float32).reshape(50, 1).repeat(6, 1)
+    s, ch = D.indoor_point_sample(pts, 20, rng)
+    assert len(np.unique(ch)) == 20 and np.array_equal(s, pts[ch])
+    s, ch = D.indoor_point_sample(pts, 80, rng)
+    assert len(ch) == 80 and ch.max() < 50
+    a, b = D.draw_params(np.random.default_rng(3), 1000, 100), D.draw_params(np.random.default_rng(3), 1000, 100)
+    assert a["angle"] == b["angle"] and np.array_equal(a["choices"], b["choices"]) and abs(a["angle"]) <= 0.087266

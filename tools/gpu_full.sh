@@ -3,7 +3,7 @@
 # lists of one inference step and one training step (each after its plain run exited 0).  Logs land in gpurun_out/.
 mkdir -p gpurun_out
 rc=0
-for t in test_coord_gpu test_head_gpu test_nms_gpu test_conv_gpu test_detector_gpu test_train_gpu test_fullsize_gpu test_surface_gpu test_zz_no_alloc; do
+for t in test_coord_gpu test_head_gpu test_nms_gpu test_conv_gpu test_detector_gpu test_train_gpu test_fullsize_gpu test_surface_gpu test_data_gpu test_zz_no_alloc; do
   timeout 420 python -m pytest tests/$t.py -m gpu -q -x --no-header -p no:cacheprovider > gpurun_out/$t.log 2>&1
   r=$?; echo "$t exit $r: $(tail -n 1 gpurun_out/$t.log)"; [ $r -ne 0 ] && rc=1
 done
