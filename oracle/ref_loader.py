@@ -308,3 +308,43 @@ def load_structures():
         _load("mmdet3d.core.bbox.structures.depth_box3d", "mmdet3d/core/bbox/structures/depth_box3d.py")
     return (sys.modules["mmdet3d.core.bbox.structures.depth_box3d"].DepthInstance3DBoxes,
             sys.modules["mmdet3d.core.points.depth_points"].DepthPoints)
+
+
+def load_indoor_eval():
+    """The reference's own mmdet3d/core/evaluation/indoor_eval.py, loaded by path on top of its own box containers.
+    Stand-ins: mmcv.utils.print_log / terminaltables.AsciiTable (printing only) and iou3d_cuda.boxes_overlap_bev_gpu
+    (mmdet3d/ops/iou3d/src/iou3d_kernel.cu:111-119,127-245: XYXYR boxes, corners rotated by MINUS the angle) computed
+    with the C restatement of the BEV overlap (oracle/nms_oracle.c) on the mirrored angle.  `BaseInstance3DBoxes.overlaps`
+    calls `.cuda()` on its temporaries (base_box3d.py:422-426); call indoor_eval inside `cpu_tensors_as_cuda()` here."""
+    Boxes, _ = load_structures()
+
+    def boxes_overlap_bev_gpu(a, b, out):
+        def conv(x):
+            x = x.detach().cpu().float()
+            r = torch.zeros((x.shape[0], 7))
+            r[:, 0], r[:, 1] = (x[:, 0] + x[:, 2]) / 2, (x[:, 1] + x[:, 3]) / 2
+            r[:, 3], r[:, 4], r[:, 5], r[:, 6] = x[:, 2] - x[:, 0], x[:, 3] - x[:, 1], 1.0, -x[:, 4]
+            return r.numpy()
+        out.copy_(torch.from_numpy(nms_cpu.pair_matrix(conv(a), conv(b), 0)))
+
+    sys.modules["mmdet3d.ops.iou3d"].iou3d_cuda = types.SimpleNamespace(boxes_overlap_bev_gpu=boxes_overlap_bev_gpu)
+    sys.modules["mmdet3d.core.bbox.structures.base_box3d"].iou3d_cuda = sys.modules["mmdet3d.ops.iou3d"].iou3d_cuda
+    _mod("mmcv.utils", print_log=lambda *a, **k: None)
+    _mod("terminaltables", AsciiTable=lambda data: types.SimpleNamespace(table="", inner_footing_row_border=False))
+    _mod("mmdet3d.ops.roiaware_pool3d", points_in_boxes_gpu=None)
+    _load("mmdet3d.core.bbox.structures.cam_box3d", "mmdet3d/core/bbox/structures/cam_box3d.py")
+    _load("mmdet3d.core.bbox.structures.lidar_box3d", "mmdet3d/core/bbox/structures/lidar_box3d.py")
+    mode = _load("mmdet3d.core.bbox.structures.box_3d_mode", "mmdet3d/core/bbox/structures/box_3d_mode.py")
+    ev = _load("mmdet3d.core.evaluation.indoor_eval", "mmdet3d/core/evaluation/indoor_eval.py")
+    return ev.indoor_eval, Boxes, mode.Box3DMode
+
+
+class cpu_tensors_as_cuda:
+    """Context manager: Tensor.cuda() returns the tensor itself (golden generation on a GPU-less host only)."""
+
+    def __enter__(self):
+        self._orig = torch.Tensor.cuda
+        torch.Tensor.cuda = lambda self, *a, **k: self
+
+    def __exit__(self, *exc):
+        torch.Tensor.cuda = self._orig

@@ -249,8 +249,55 @@ def augment_fixture(name="augment_ref.npz"):
     print(name, len(cases), "cases")
 
 
+def eval_fixture(name="indoor_eval_ref.npz"):
+    """mAP / mAR of synthetic detections computed by the reference's own indoor_eval.py (see
+    oracle/ref_loader.load_indoor_eval for the two stand-ins) for an axis-aligned (ScanNet-like) and a rotated
+    (SUN RGB-D-like) case."""
+    indoor_eval, Boxes, Box3DMode = ref_loader.load_indoor_eval()
+    out = {}
+    for case, with_yaw in (("aa", False), ("rot", True)):
+        rng = np.random.default_rng(3 if with_yaw else 4)
+        n_img, n_cls = 8, 5
+        gt_annos, dt_annos = [], []
+        for i in range(n_img):
+            ng = int(rng.integers(4, 10)) if i else 0           # the first image has no ground truth
+            gt = np.concatenate([rng.uniform(-3, 3, (ng, 3)), rng.uniform(0.4, 1.8, (ng, 3)),
+                                 rng.uniform(-1.5, 1.5, (ng, 1)) * with_yaw], 1).astype(np.float32)
+            gl = rng.integers(0, n_cls - 1, ng)                  # class n_cls-1 never appears in the ground truth
+            gt_annos.append(dict(gt_num=ng, gt_boxes_upright_depth=gt if with_yaw else gt[:, :6], **{"class": gl}))
+            # detections: jittered copies of the ground truth (some duplicated, some mislabelled) + random boxes
+            k = int(rng.integers(3, 12))
+            rnd = np.concatenate([rng.uniform(-3, 3, (k, 3)), rng.uniform(0.4, 1.8, (k, 3)),
+                                  rng.uniform(-1.5, 1.5, (k, 1)) * with_yaw], 1).astype(np.float32)
+            rl = rng.integers(0, n_cls if with_yaw else n_cls - 1, k)   # rot: a class without ground truth (nan AP)
+            rep = np.repeat(gt, 2, 0) + rng.normal(0, 0.17, (2 * ng, 7)).astype(np.float32) * np.array([1, 1, 1, 1, 1, 1, with_yaw], np.float32)
+            repl = np.repeat(gl, 2)
+            if len(repl):
+                repl[rng.random(len(repl)) < 0.15] = rng.integers(0, n_cls - 1)
+            det = np.concatenate([rep, rnd], 0).astype(np.float32)
+            lab = np.concatenate([repl, rl]).astype(np.int64)
+            sc = rng.uniform(0.05, 1, len(det)).astype(np.float32)
+            bottom = det.copy()
+            bottom[:, 2] -= bottom[:, 5] / 2
+            dt_annos.append(dict(boxes_3d=Boxes(torch.from_numpy(bottom), box_dim=7, with_yaw=with_yaw),
+                                 scores_3d=torch.from_numpy(sc), labels_3d=torch.from_numpy(lab)))
+            out["%s_gt%d" % (case, i)], out["%s_gtl%d" % (case, i)] = gt, gl
+            out["%s_det%d" % (case, i)], out["%s_detl%d" % (case, i)], out["%s_dets%d" % (case, i)] = det, lab, sc
+        label2cat = {c: "c%d" % c for c in range(n_cls)}
+        with ref_loader.cpu_tensors_as_cuda(), np.errstate(all="ignore"):
+            ret = indoor_eval(gt_annos, dt_annos, (0.25, 0.5), label2cat, box_type_3d=Boxes, box_mode_3d=Box3DMode.DEPTH)
+        keys = sorted(ret)
+        out["%s_keys" % case] = np.array(keys)
+        out["%s_vals" % case] = np.array([ret[k] for k in keys], dtype=np.float64)
+        print(case, {k: round(v, 4) for k, v in ret.items() if k.startswith("mA")})
+    np.savez_compressed(os.path.join(OUT, name), **out)
+
+
 if __name__ == "__main__":
     torch.set_num_threads(8)
+    if "--eval-only" in sys.argv:
+        eval_fixture()
+        sys.exit(0)
     if "--augment-only" in sys.argv:
         augment_fixture()
         sys.exit(0)
@@ -268,3 +315,4 @@ if __name__ == "__main__":
     train_fixture("fcaf3d_sunrgbd-3d-10class.py", (5,), "train_tiny_sunrgbd.npz")
     mefpn_fixture()
     augment_fixture()
+    eval_fixture()

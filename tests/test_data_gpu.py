@@ -70,3 +70,27 @@ def test_scene_prefetcher_overlapped_staging(dev):
     for gb, hb in zip(got, batches):
         for t, h in zip(gb, hb):
             assert t.is_cuda and np.array_equal(t.cpu().numpy(), h)
+
+
+@pytest.mark.parametrize("case", ["aa", "rot"])
+def test_indoor_eval_matches_reference_golden(dev, case):
+    """fcaf3d_b200.evaluation.indoor_eval (GPU IoU) against the reference's own indoor_eval.py
+    (tests/golden/indoor_eval_ref.npz): every key of the result dict, 1e-5 absolute (nan where the reference has nan)."""
+    from fcaf3d_b200.evaluation import indoor_eval
+    g = np.load(os.path.join(GOLDEN, "indoor_eval_ref.npz"))
+    n_img = len([k for k in g.files if k.startswith(case + "_gt") and not k.startswith(case + "_gtl")])
+    gt_annos, dt_annos = [], []
+    for i in range(n_img):
+        gt, gl = g["%s_gt%d" % (case, i)], g["%s_gtl%d" % (case, i)]
+        gt_annos.append(dict(gt_num=len(gt), gt_boxes_upright_depth=gt if case == "rot" else gt[:, :6], **{"class": gl}))
+        dt_annos.append(dict(boxes_3d=torch.from_numpy(g["%s_det%d" % (case, i)]).to(dev),
+                             scores_3d=torch.from_numpy(g["%s_dets%d" % (case, i)]),
+                             labels_3d=torch.from_numpy(g["%s_detl%d" % (case, i)])))
+    ret = indoor_eval(gt_annos, dt_annos, (0.25, 0.5), {c: "c%d" % c for c in range(5)})
+    want = dict(zip([str(k) for k in g["%s_keys" % case]], g["%s_vals" % case]))
+    assert set(ret) == set(want)
+    for k, v in want.items():
+        if np.isnan(v):
+            assert np.isnan(ret[k]), k
+        else:
+            assert abs(ret[k] - v) < 1e-5, (k, ret[k], v)

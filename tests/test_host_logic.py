@@ -95,3 +95,37 @@ def test_reference_backbone_file_builds_on_our_me_surface(lib_built):
                 sys.modules.pop(k, None)
             else:
                 sys.modules[k] = v
+
+
+def test_checkpoint_round_trip_in_the_reference_format(tmp_path):
+    """mmcv-style checkpoint (meta + state_dict, `module.` prefix of a DataParallel wrapper) -> strict load into a fresh
+    mirror; a tensor of the wrong shape or a missing key is refused."""
+    import collections
+    import pytest
+    import torch
+    from fcaf3d_b200.checkpoint import load_checkpoint, save_checkpoint
+    from fcaf3d_b200.detector import build_fcaf3d
+    from fcaf3d_b200.testing import deterministic_init
+    src = deterministic_init(build_fcaf3d("s3dis", depth=14), 5)
+    path = str(tmp_path / "epoch_12.pth")
+    save_checkpoint(src, path, meta=dict(epoch=12, CLASSES=("table", "chair")))
+    dst = build_fcaf3d("s3dis", depth=14)
+    meta = load_checkpoint(dst, path)
+    assert meta["epoch"] == 12
+    for (ka, va), (kb, vb) in zip(src.state_dict().items(), dst.state_dict().items()):
+        assert ka == kb and torch.equal(va, vb)
+    wrapped = {"meta": {}, "state_dict": collections.OrderedDict(("module." + k, v) for k, v in src.state_dict().items())}
+    torch.save(wrapped, path)
+    dst2 = build_fcaf3d("s3dis", depth=14)
+    load_checkpoint(dst2, path)
+    assert torch.equal(dst2.state_dict()["backbone.conv1.0.kernel"], src.state_dict()["backbone.conv1.0.kernel"])
+    sd = dict(src.state_dict())
+    sd["backbone.conv1.0.kernel"] = sd["backbone.conv1.0.kernel"][:, :, :32]
+    torch.save({"state_dict": sd}, path)
+    with pytest.raises(RuntimeError, match="another shape"):
+        load_checkpoint(build_fcaf3d("s3dis", depth=14), path)
+    sd = dict(src.state_dict())
+    sd.pop("neck_with_head.cls_conv.bias")
+    torch.save({"state_dict": sd}, path)
+    with pytest.raises(RuntimeError, match="missing"):
+        load_checkpoint(build_fcaf3d("s3dis", depth=14), path)
