@@ -12,6 +12,13 @@ from . import ops
 from ._lib import DT, call, ptr
 
 
+# With bf16 compute (me.set_compute_dtype(torch.bfloat16)) a tcgen05 convolution hands its output on in bf16, so the
+# BatchNorm / activation / residual passes between convolutions move half the bytes and the next convolution needs no
+# cast (activation storage as in mixed-precision training; accumulation, BatchNorm statistics, losses and weights stay
+# fp32).  False = fp32 activations between the layers (bf16 only inside the convolutions).
+BF16_ACTIVATIONS = True
+
+
 def conv_wgrad(feats, grad_out, kmap, kvol, cin, cout):
     dw = torch.zeros((kvol, cin, cout), dtype=torch.float32, device=feats.device)
     n_out = int(grad_out.shape[0])
@@ -49,10 +56,13 @@ class SparseConvFn(torch.autograd.Function):
             wt, wt_b = ops.pack_conv_weights(wd.float(), want_fwd=tc_fwd, want_bwd=tc_bwd)   # one launch, both layouts
         if tc_fwd:
             x = ops.cast(feats, torch.bfloat16)
-        out = ops.sparse_conv(x, wd, kmap, n_out, wt_bf16=wt, out_dtype=torch.float32)
+        out_dt = torch.bfloat16 if (tc_fwd and BF16_ACTIVATIONS) else torch.float32
+        out = ops.sparse_conv(x, wd, kmap, n_out, wt_bf16=wt, out_dtype=out_dt)
         ctx.save_for_backward(x, wd, wt_b)
         ctx.kmap, ctx.kmap_t, ctx.n_in = kmap, kmap_t, int(feats.shape[0])
         ctx.in_dtype = feats.dtype
+        if out_dt == torch.bfloat16:
+            return out
         return out.to(feats.dtype) if feats.dtype != torch.float32 else out
 
     @staticmethod
@@ -68,7 +78,7 @@ class SparseConvFn(torch.autograd.Function):
         if want_x:
             if wt_b is not None:                                          # [K, Cin, Cout] is already "out x in" for dgrad
                 d_feats = ops.sparse_conv(gb, (kvol, cout, cin), ctx.kmap_t, ctx.n_in, wt_bf16=wt_b,
-                                          out_dtype=torch.float32)
+                                          out_dtype=ctx.in_dtype if ctx.in_dtype == torch.bfloat16 else torch.float32)
             else:
                 w_back = wd.flip(0).transpose(1, 2).contiguous()          # [K, Cout, Cin]: W[K-1-k']^T
                 d_feats = ops.sparse_conv(g.float(), w_back, ctx.kmap_t, ctx.n_in, out_dtype=torch.float32)

@@ -97,10 +97,20 @@ class MEResNet3D(nn.Module):
                 nn.init.constant_(m.bn.bias, 0)
 
     def forward(self, x):
+        """me_resnet.py:66-78, op by op.  The only additions are look-ahead hints to the coordinate manager: the next strided
+        map is enqueued one level early so that its row count is read while the GPU still has work (stride_prefetch)."""
         outs = []
-        x = self.conv1(x)
+        cm = x.coordinate_manager
+        for j, m in enumerate(self.conv1):
+            x = m(x)
+            if j == 0 and len(self.conv1) > 3:
+                cm.stride_prefetch(x.coordinate_map_key, self.conv1[3].stride)      # the pooling map
+        cm.stride_prefetch(x.coordinate_map_key, 2)
         for i in range(self.n_outs):
-            x = getattr(self, f"layer{i + 1}")(x)
+            for j, block in enumerate(getattr(self, f"layer{i + 1}")):
+                x = block(x)
+                if j == 0 and i + 1 < self.n_outs:
+                    cm.stride_prefetch(x.coordinate_map_key, 2)
             outs.append(x)
         return outs
 
@@ -327,6 +337,9 @@ class Fcaf3DNeckWithHead(nn.Module):
                 x = getattr(self, f"up_block_{i + 1}")(x)
                 x = inputs[i] + x
                 x = self._prune(x, scores)
+            if i > 0:   # look-ahead: the next level's generated map and its union depend on coordinates only
+                cm = x.coordinate_manager
+                cm.union_prefetch(inputs[i - 1].coordinate_map_key, cm.generate_children(x.coordinate_map_key))
             out = getattr(self, f"out_block_{i}")(x)
             w = torch.cat((self.centerness_conv.kernel, self.reg_conv.kernel, self.cls_conv.kernel), dim=1)
             h = out.F.float() @ w

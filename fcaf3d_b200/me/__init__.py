@@ -82,6 +82,7 @@ class CoordinateManager:
         self._kmaps = {}
         self._stride_cache = {}
         self._pending = {}      # deferred map builds (stride / union) whose row count has not been read yet
+        self._children_cache = {}
         self._auto = 0
         self.num_batches = 0
 
@@ -166,6 +167,9 @@ class CoordinateManager:
 
     def generate_children(self, in_key):
         """New map holding the 8 children of every voxel (generative transpose, ME A.5): row 8*i + k."""
+        cached = self._children_cache.get(in_key)
+        if cached is not None:      # one children map per parent map (lets callers create it ahead of the module call)
+            return cached
         src = self._maps[in_key]
         if src.ts % 2:
             raise B2Error("generative transpose needs an even tensor stride")
@@ -176,6 +180,7 @@ class CoordinateManager:
         m = _Map(coords, ts_out, self.num_batches, off=(src.off_dev * 8, off_host))
         m.children_of = in_key   # all 8 children of every parent, row 8 i + c: kernel maps can be derived, see kernel_map
         self._maps[key] = m
+        self._children_cache[in_key] = key
         return key
 
     def _union_start(self, key_a, key_b):
@@ -743,7 +748,8 @@ class MinkowskiBatchNorm(MinkowskiModuleBase):
     def forward(self, x, act=ops.ACT_NONE, residual=None):
         f = x.F.contiguous()
         if AG.wants_grad(f, self.bn.weight, self.bn.bias):
-            out = self.bn(f.float()).to(f.dtype)             # exactly ME: nn.BatchNorm1d on the feature rows
+            # exactly ME: nn.BatchNorm1d on the feature rows (bf16 rows: torch's mixed-dtype kernels, fp32 statistics)
+            out = self.bn(f) if f.dtype == torch.bfloat16 else self.bn(f.float()).to(f.dtype)
             if residual is not None:
                 out = out + residual
             out = torch.relu(out) if act == ops.ACT_RELU else torch.nn.functional.elu(out) if act == ops.ACT_ELU else out

@@ -38,3 +38,23 @@ with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
     torch.cuda.synchronize()
 print(prof.key_averages().table(sort_by="self_cpu_time_total", row_limit=40, max_name_column_width=60))
 print(prof.key_averages().table(sort_by="self_cuda_time_total", row_limit=30, max_name_column_width=60))
+# GPU idle gaps: sort kernel events by start, list the largest gaps and what ran before / after
+evs = sorted([e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA and e.time_range is not None],
+             key=lambda e: e.time_range.start)
+gaps = []
+for a, b in zip(evs[:-1], evs[1:]):
+    g = b.time_range.start - a.time_range.end
+    if g > 0:
+        gaps.append((g, a.name[:60], b.name[:60], a.time_range.end - evs[0].time_range.start))
+tot = sum(g[0] for g in gaps)
+span = evs[-1].time_range.end - evs[0].time_range.start
+busy = sum(e.time_range.end - e.time_range.start for e in evs)
+print("GPU span %.2f ms, busy %.2f ms, idle %.2f ms in %d gaps" % (span / 1e3, busy / 1e3, tot / 1e3, len(gaps)))
+for g, a, b, t in sorted(gaps, reverse=True)[:40]:
+    print("  gap %7.1f us at %6.2f ms  after %-60s before %s" % (g, t / 1e3, a, b))
+# idle time per 2 ms window of the step
+import collections
+win = collections.Counter()
+for g, a, b, t in gaps:
+    win[int(t // 2000)] += g
+print("idle us per 2 ms window:", [int(win[i]) for i in range(int(span // 2000) + 1)])
