@@ -302,6 +302,18 @@ extern "C" int b2_conv_tc(const void* in_bf16, long long n_in, const void* wt_bf
 #define TC_GO(BN, T)                                                                                               \
   return launch_tc<BN, (BN <= 64 ? 4 : 3), T>(in_bf16, wt_bf16, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, \
                                               shift, residual, act, ch_mod, out, st)
+  // 256 output columns per CTA (one CTA per SM, 48 KB stages): half as many MMA instructions and gathered bytes per flop.
+  // Measured: 256->256 on 12.5 k rows 63 -> 53 us; but 512->512 on 2.7 k rows (42 CTAs instead of 84) 78 -> 88 us, so it
+  // is used only when it still yields at least half an SM wave of CTAs.  B2_TC_BN256=0 / 1 forces it off / on.
+  static const int bn256_env = getenv("B2_TC_BN256") ? atoi(getenv("B2_TC_BN256")) : -1;
+  const long long cta256 = (long long)b2_div_up(n_out, TC_BM) * (cout / 256);
+  if (cout % 256 == 0 && bn256_env != 0 && (bn256_env == 1 || cta256 >= 74)) {
+    if (out_dtype == 1)
+      return launch_tc<256, 3, __nv_bfloat16>(in_bf16, wt_bf16, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias,
+                                              scale, shift, residual, act, ch_mod, out, st);
+    return launch_tc<256, 3, float>(in_bf16, wt_bf16, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale,
+                                    shift, residual, act, ch_mod, out, st);
+  }
   if (out_dtype == 1) {
     if (wide) TC_GO(128, __nv_bfloat16);
     if (mid) TC_GO(64, __nv_bfloat16);

@@ -114,6 +114,38 @@ class MEResNet3D(nn.Module):
             outs.append(x)
         return outs
 
+    def prebuild_maps(self, x, training=True):
+        """Builds every coordinate map and kernel map the backbone will ask for on input tensor `x` - they depend on the
+        coordinates only.  A trainer calls this for the NEXT batch between the forward and the backward of the current
+        one: the host reads of the row counts then wait for little queued GPU work, and the next forward is enqueued
+        without any host round trip while the GPU is still busy with this step's backward."""
+        cm, key = x.coordinate_manager, x.coordinate_map_key
+
+        def conv_maps(conv, in_key):
+            out_key = in_key if conv.stride == 1 else cm.stride(in_key, conv.stride)
+            if not (conv.kernel_size == 1 and conv.stride == 1):
+                cm.kernel_map(in_key, out_key, conv.kernel_size, conv.dilation)
+                if training:
+                    cm.kernel_map_transposed(in_key, out_key, conv.kernel_size, conv.dilation)
+            return out_key
+
+        for m in self.conv1:
+            if isinstance(m, ME.MinkowskiConvolution):
+                key = conv_maps(m, key)
+            elif isinstance(m, ME.MinkowskiMaxPooling):
+                pkey = cm.stride(key, m.stride)
+                cm.kernel_map(key, pkey, m.kernel_size, m.dilation)
+                key = pkey
+        for i in range(self.n_outs):
+            for block in getattr(self, f"layer{i + 1}"):
+                convs = [c for c in (getattr(block, n, None) for n in ("conv1", "conv2", "conv3")) if c is not None]
+                in_key = key
+                for c in convs:
+                    key = conv_maps(c, key)
+                if block.downsample is not None:
+                    conv_maps(block.downsample[0], in_key)
+        return x
+
     # ---- fused execution ---------------------------------------------------------------------
     def forward_fused(self, x):
         cm = x.coordinate_manager
@@ -656,12 +688,18 @@ class SingleStageSparse3DDetector(nn.Module):
         x = self.backbone(x)
         return self.neck_with_head(x)
 
+    def prepare(self, points, training=True):
+        """Input tensor of a batch with all backbone coordinate / kernel maps already built (MEResNet3D.prebuild_maps);
+        forward_train / extract_feat accept it in place of the point list."""
+        return self.backbone.prebuild_maps(self._input_tensor(points), training=training)
+
     def forward_train(self, points, gt_bboxes_3d, gt_labels_3d, img_metas=None):
-        """single_stage_sparse.py:42-49.  gt_bboxes_3d: list of [B_i, 7] (gravity centre, size, yaw) tensors."""
+        """single_stage_sparse.py:42-49.  gt_bboxes_3d: list of [B_i, 7] (gravity centre, size, yaw) tensors.
+        `points`: list of [N_i, 6] tensors, or the tensor returned by prepare()."""
+        x0 = points if isinstance(points, ME.SparseTensor) else self._input_tensor(points)
         if self.batched_loss:
-            feats = self.backbone(self._input_tensor(points))
-            return self.neck_with_head.forward_train_batched(feats, gt_bboxes_3d, gt_labels_3d)
-        x = self.extract_feat(points, img_metas)
+            return self.neck_with_head.forward_train_batched(self.backbone(x0), gt_bboxes_3d, gt_labels_3d)
+        x = self.neck_with_head(self.backbone(x0))
         return self.neck_with_head.loss(*x, gt_bboxes_3d, gt_labels_3d, img_metas)
 
     @torch.no_grad()

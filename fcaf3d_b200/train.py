@@ -36,11 +36,22 @@ class TrainStepModule(torch.nn.Module):
         return sum(losses.values()), losses
 
 
-def train_step(module, optimizer, points, gt_boxes, gt_labels, max_norm=10.0):
-    """one optimisation step; returns (total loss tensor, dict of detached losses)"""
+def train_step(module, optimizer, points, gt_boxes, gt_labels, max_norm=10.0, next_points=None):
+    """One optimisation step; returns (total loss tensor, dict of detached losses[, prepared next batch]).
+
+    `points` is a list of point tensors or a batch prepared by `detector.prepare`.  With `next_points` the coordinate and
+    kernel maps of the NEXT batch are built between this step's forward and backward (software pipelining: they depend
+    on the points only), and the prepared batch is returned as third value to be passed as `points` of the next call -
+    its forward then needs no host round trip and is enqueued while the GPU still runs this step's backward."""
     optimizer.zero_grad(set_to_none=True)
     total, losses = module(points, gt_boxes, gt_labels)
+    nxt = None
+    if next_points is not None:
+        det = (module.module if hasattr(module, "module") else module).detector
+        with torch.no_grad():
+            nxt = det.prepare(next_points)
     total.backward()
     torch.nn.utils.clip_grad_norm_(module.parameters(), max_norm)
     optimizer.step()
-    return total.detach(), {k: v.detach() for k, v in losses.items()}
+    out = (total.detach(), {k: v.detach() for k, v in losses.items()})
+    return out + (nxt,) if next_points is not None else out

@@ -119,6 +119,36 @@ def test_sparsity_sorted_walk_is_bit_identical(dev, cin, cout, stride, out_dtype
     assert km.sorted is None and torch.equal(y_sorted, y_plain)
 
 
+def test_conv_tcgen05_wide_tiles(dev):
+    """cout % 256 == 0 on a map with >= 74 row tiles takes the 256-column tile (one CTA per SM); same checks as above:
+    against the CUDA-core kernel on the same bf16-rounded operands (5e-4) with the fused epilogue."""
+    from util import surface_coords
+    c = torch.from_numpy(surface_coords(16000, 2, seed=8)).to(dev)
+    x0 = ME.SparseTensor(torch.zeros(len(c), 1, device=dev), coordinates=c)
+    cm, key = x0.coordinate_manager, x0.coordinate_map_key
+    n = cm.size(key)
+    assert (n + 127) // 128 >= 74
+    km = cm.kernel_map(key, key, 3)
+    torch.manual_seed(4)
+    for cin, cout in ((64, 256), (128, 512)):
+        f = torch.randn(n, cin, device=dev).to(torch.bfloat16)
+        w = (torch.randn(27, cin, cout, device=dev) * 0.05).to(torch.bfloat16).float()
+        wt = w.transpose(1, 2).contiguous().to(torch.bfloat16)
+        scale, shift = torch.rand(cout, device=dev) + .5, torch.randn(cout, device=dev)
+        res = torch.randn(n, cout, device=dev)
+        kw = dict(scale=scale, shift=shift, residual=res, act=ops.ACT_ELU, out_dtype=torch.float32)
+        z = ops.sparse_conv(f, w, km, n, wt_bf16=wt, **kw)
+        ops.set_tensor_cores(False)
+        try:
+            z_cc = ops.sparse_conv(f, w, km, n, **kw)
+        finally:
+            ops.set_tensor_cores(True)
+        assert rel_err(z, z_cc) < 5e-4
+        zb = ops.sparse_conv(f, w, km, n, wt_bf16=wt, scale=scale, shift=shift, act=ops.ACT_RELU, out_dtype=torch.bfloat16)
+        ref_b = torch.relu(ops.sparse_conv(f, w, km, n, wt_bf16=wt, scale=scale, shift=shift, out_dtype=torch.float32))
+        assert rel_err(zb, ref_b) < 1e-2
+
+
 def test_generative_transpose_both_paths(dev):
     x, o = _tensors(dev, 128, n_points=1500)
     cm, ocm = x.coordinate_manager, o.coordinate_manager

@@ -215,3 +215,43 @@ def test_training_step_matches_reference_golden(dev, name, dataset, batched):
         err = rel_err(flat[::step], want)
         assert err < 1e-2, (key, err)
         assert abs(float(grad.double().norm()) - float(g["gradnorm/" + key])) <= 1e-2 * float(g["gradnorm/" + key]) + 1e-12, key
+
+
+@pytest.mark.parametrize("bf16_act", [True, False], ids=["bf16_activations", "fp32_activations"])
+def test_bf16_training_step_tracks_the_fp32_golden(dev, bf16_act):
+    """bf16 mode (tcgen05 forward / input-gradient / weight-gradient convolutions, optionally bf16 activation storage
+    between them): the losses of one step stay within 2 % of the reference's fp32 golden values; sampled gradients
+    keep cosine similarity > 0.95 with the fp32 ones and deviate by < 35 % of the largest entry (measured on this tiny
+    scene: neck / head kernels 3e-3 and cosine 0.99999; the deep backbone kernel 0.21-0.25 and 0.97-0.98 in BOTH
+    flavours, i.e. the deviation comes from the bf16 operands of the convolutions, not from the activation storage)."""
+    from fcaf3d_b200 import autograd as AG
+    g = np.load(os.path.join(GOLDEN, "train_tiny_scannet.npz"))
+    det = deterministic_init(build_fcaf3d("scannet"), seed=1).to(dev).train()
+    nb = len(g["seeds"])
+    pts = [torch.from_numpy(g["points_%d" % i]).to(dev) for i in range(nb)]
+    gtb = [torch.from_numpy(g["gt_%d" % i]).to(dev) for i in range(nb)]
+    gtl = [torch.from_numpy(g["gt_labels_%d" % i]).to(dev) for i in range(nb)]
+    ME.set_compute_dtype(torch.bfloat16)
+    old = AG.BF16_ACTIVATIONS
+    AG.BF16_ACTIVATIONS = bf16_act
+    try:
+        prepared = det.prepare(pts)                      # the pipelined trainer's entry: maps prebuilt
+        losses = det.forward_train(prepared, gtb, gtl)
+        sum(losses.values()).backward()
+    finally:
+        ME.set_compute_dtype(torch.float32)
+        AG.BF16_ACTIVATIONS = old
+    for k, v in losses.items():
+        assert abs(v.item() - float(g[k])) < 2e-2 * abs(float(g[k])), (k, v.item(), float(g[k]))
+    params = dict(det.named_parameters())
+    errs = {}
+    for key in ("backbone.layer2.1.conv2.kernel", "neck_with_head.out_block_0.0.kernel", "neck_with_head.cls_conv.kernel"):
+        flat = params[key].grad.reshape(-1)
+        step = max(1, flat.numel() // 4096)
+        want = torch.from_numpy(g["grad/" + key])
+        got = flat[::step].float().cpu()
+        cos = torch.nn.functional.cosine_similarity(got, want, dim=0).item()
+        errs[key] = (rel_err(got, want), cos)
+    print("bf16_act=%s" % bf16_act, errs)
+    for key, (err, cos) in errs.items():
+        assert cos > 0.95 and err < 0.35, (key, err, cos)
