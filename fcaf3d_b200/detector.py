@@ -646,10 +646,13 @@ class Fcaf3DNeckWithHead(nn.Module):
 
 
 def split_detections(dets, num_scenes):
-    """Device-side result dict -> host list of (boxes, scores, labels) per scene (one D2H copy each)."""
+    """Device-side result dict -> host list of (boxes, scores, labels) per scene: one read of the count, then ONE packed
+    device->host copy of (box, score, label, scene) rows."""
     n = int(dets["count"].item())
-    boxes = dets["boxes"][:n, :dets["box_dim"]].cpu()
-    scores, labels, scene = dets["scores"][:n].cpu(), dets["labels"][:n].cpu().long(), dets["scene"][:n].cpu()
+    d = dets["box_dim"]
+    packed = torch.cat((dets["boxes"][:n, :d], dets["scores"][:n, None], dets["labels"][:n, None].float(),
+                        dets["scene"][:n, None].float()), dim=1).cpu()
+    boxes, scores, labels, scene = packed[:, :d], packed[:, d], packed[:, d + 1].long(), packed[:, d + 2].long()
     out = []
     for b in range(num_scenes):
         sel = scene == b

@@ -33,8 +33,16 @@ torch.cuda.synchronize()
 t2 = time.perf_counter()
 print("host enqueue %.1f ms, + drain %.1f ms" % ((t1 - t0) * 1e3, (t2 - t1) * 1e3))
 from torch.profiler import ProfilerActivity, profile  # noqa: E402
+PIPE = os.environ.get("PIPELINED", "0") == "1"
+if PIPE:   # steady state of the software-pipelined trainer: profile the 2nd and 3rd of four chained steps
+    prepared = det.prepare(pts)
+    _, _, prepared = train_step(module, opt, prepared, gtb, gtl, next_points=pts)
 with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
-    train_step(module, opt, pts, gtb, gtl)
+    if PIPE:
+        _, _, prepared = train_step(module, opt, prepared, gtb, gtl, next_points=pts)
+        _, _, prepared = train_step(module, opt, prepared, gtb, gtl, next_points=pts)
+    else:
+        train_step(module, opt, pts, gtb, gtl)
     torch.cuda.synchronize()
 print(prof.key_averages().table(sort_by="self_cpu_time_total", row_limit=40, max_name_column_width=60))
 print(prof.key_averages().table(sort_by="self_cuda_time_total", row_limit=30, max_name_column_width=60))
