@@ -121,5 +121,55 @@ class PruneFn(torch.autograd.Function):
         return ops.index_rows(grad_out.contiguous(), idx), None, None, None
 
 
+# Training-mode BatchNorm (+ residual + ReLU / ELU) on the library's kernels (bn_ops.cu) instead of torch's batch-norm,
+# add and activation kernels; False = plain torch modules (what ME itself does).
+FUSED_BN = True
+
+
+class BNActFn(torch.autograd.Function):
+    """y = act(batch_norm(x) [+ residual]) over the rows of x [N, C] with batch statistics; running statistics are
+    updated in place like nn.BatchNorm1d.  Backward: b2_bn_act_bwd (dx, d weight, d bias, d residual)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, residual, bn, act):
+        x = x.contiguous()
+        n, c = int(x.shape[0]), int(x.shape[1])
+        dev = x.device
+        stats = torch.empty((4, c), dtype=torch.float32, device=dev)       # mean | invstd | scale | shift
+        ws = ops.workspace(ops._lib.lib().b2_bn_ws_bytes(c), dev, slot=3)
+        track = bn.track_running_stats and bn.running_mean is not None
+        call("b2_bn_train_stats", ptr(x), DT[x.dtype], n, c, ptr(weight.detach().float()) if weight is not None else None,
+             ptr(bias.detach().float()) if bias is not None else None, ptr(bn.running_mean) if track else None,
+             ptr(bn.running_var) if track else None, ptr(bn.num_batches_tracked) if track else None,
+             float(bn.momentum), float(bn.eps), ptr(stats[0]), ptr(stats[1]), ptr(stats[2]), ptr(stats[3]), ptr(ws),
+             ws.numel())
+        res = residual.contiguous() if residual is not None else None
+        y = ops.affine_act(x, stats[2:3], stats[3:4], residual=res, act=act)
+        ctx.save_for_backward(x, y if act != ops.ACT_NONE else None, stats, weight)
+        ctx.act, ctx.has_res = act, residual is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, y, stats, weight = ctx.saved_tensors
+        n, c = int(x.shape[0]), int(x.shape[1])
+        dy = dy.contiguous().to(x.dtype)
+        dx = torch.empty_like(x)
+        dres = torch.empty_like(x) if (ctx.has_res and ctx.needs_input_grad[3]) else None
+        sums = torch.empty((2, c), dtype=torch.float32, device=x.device)
+        ws = ops.workspace(ops._lib.lib().b2_bn_ws_bytes(c), x.device, slot=3)
+        call("b2_bn_act_bwd", ptr(x), ptr(dy), ptr(y), DT[x.dtype], n, c, int(ctx.act), ptr(stats[0]), ptr(stats[1]),
+             ptr(weight.detach().float()) if weight is not None else None, ptr(sums), ptr(dx), ptr(dres), ptr(ws),
+             ws.numel())
+        dw = sums[1].to(weight.dtype) if weight is not None and ctx.needs_input_grad[1] else None
+        db = sums[0].to(weight.dtype) if weight is not None and ctx.needs_input_grad[2] else None
+        return dx, dw, db, dres, None, None
+
+
+def bn_act_supported(x, bn):
+    return (FUSED_BN and x.is_cuda and x.dim() == 2 and x.shape[0] > 1 and x.shape[1] % 8 == 0 and x.shape[1] <= 2048
+            and x.dtype in (torch.float32, torch.bfloat16) and bn.momentum is not None)
+
+
 def wants_grad(*tensors):
     return torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors)

@@ -177,6 +177,25 @@ class MEResNet3D(nn.Module):
         return outs
 
 
+class BlockSequential(nn.Sequential):
+    """nn.Sequential (same children, same state-dict keys) whose forward hands a MinkowskiBatchNorm and the ReLU / ELU
+    module that follows it to the normalisation as one call, so that the pair is one pass over the rows."""
+
+    def forward(self, x):
+        mods = list(self)
+        i = 0
+        while i < len(mods):
+            m = mods[i]
+            nxt = mods[i + 1] if i + 1 < len(mods) else None
+            if isinstance(m, ME.MinkowskiBatchNorm) and isinstance(nxt, (ME.MinkowskiReLU, ME.MinkowskiELU)):
+                x = m(x, act=ops.ACT_RELU if isinstance(nxt, ME.MinkowskiReLU) else ops.ACT_ELU)
+                i += 2
+            else:
+                x = m(x)
+                i += 1
+        return x
+
+
 def conv_bn_act(conv, bn, f, km, n_out, act, residual=None):
     """conv -> BatchNorm -> (+residual) -> activation.  Eval: one kernel (BN folded into the epilogue).
     Train: conv, batch statistics, then one fused normalise/residual/activation pass."""
@@ -232,12 +251,12 @@ class Fcaf3DNeckWithHead(nn.Module):
 
     @staticmethod
     def _make_block(cin, cout):
-        return nn.Sequential(ME.MinkowskiConvolution(cin, cout, kernel_size=3, dimension=3),
-                             ME.MinkowskiBatchNorm(cout), ME.MinkowskiELU())
+        return BlockSequential(ME.MinkowskiConvolution(cin, cout, kernel_size=3, dimension=3),
+                               ME.MinkowskiBatchNorm(cout), ME.MinkowskiELU())
 
     @staticmethod
     def _make_up_block(cin, cout):
-        return nn.Sequential(
+        return BlockSequential(
             ME.MinkowskiGenerativeConvolutionTranspose(cin, cout, kernel_size=2, stride=2, dimension=3),
             ME.MinkowskiBatchNorm(cout), ME.MinkowskiELU(),
             ME.MinkowskiConvolution(cout, cout, kernel_size=3, dimension=3),

@@ -748,6 +748,11 @@ class MinkowskiBatchNorm(MinkowskiModuleBase):
     def forward(self, x, act=ops.ACT_NONE, residual=None):
         f = x.F.contiguous()
         if AG.wants_grad(f, self.bn.weight, self.bn.bias):
+            if self.bn.training and AG.bn_act_supported(f, self.bn):
+                # batch statistics, normalisation, residual and activation on the library's kernels (bn_ops.cu)
+                res = None if residual is None else residual.to(f.dtype)
+                out = AG.BNActFn.apply(f, self.bn.weight, self.bn.bias, res, self.bn, act)
+                return SparseTensor(out, coordinate_map_key=x.coordinate_map_key, coordinate_manager=x.coordinate_manager)
             # exactly ME: nn.BatchNorm1d on the feature rows (bf16 rows: torch's mixed-dtype kernels, fp32 statistics)
             out = self.bn(f) if f.dtype == torch.bfloat16 else self.bn(f.float()).to(f.dtype)
             if residual is not None:

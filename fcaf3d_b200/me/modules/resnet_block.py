@@ -1,7 +1,12 @@
 """MinkowskiEngine.modules.resnet_block (A.7): BasicBlock / Bottleneck with ME's attribute names."""
 import torch.nn as nn
 
+from ... import ops
 from .. import MinkowskiBatchNorm, MinkowskiConvolution, MinkowskiReLU
+
+
+def _same_map(a, b):
+    return a.coordinate_manager is b.coordinate_manager and a.coordinate_map_key == b.coordinate_map_key
 
 
 class BasicBlock(nn.Module):
@@ -20,17 +25,19 @@ class BasicBlock(nn.Module):
         self.downsample = downsample
 
     def forward(self, x):
+        # same dataflow as ME's BasicBlock (conv-bn-relu-conv-bn, += residual, relu); the normalisation, the residual add
+        # and the ReLU go to MinkowskiBatchNorm as ONE call each, which runs them as one pass over the rows
         residual = x
         out = self.conv1(x)
-        out = self.norm1(out)
-        out = self.relu(out)
+        out = self.norm1(out, act=ops.ACT_RELU)
         out = self.conv2(out)
-        out = self.norm2(out)
         if self.downsample is not None:
             residual = self.downsample(x)
+        if _same_map(out, residual):
+            return self.norm2(out, act=ops.ACT_RELU, residual=residual.F)
+        out = self.norm2(out)
         out += residual
-        out = self.relu(out)
-        return out
+        return self.relu(out)
 
 
 class Bottleneck(nn.Module):
@@ -51,11 +58,13 @@ class Bottleneck(nn.Module):
 
     def forward(self, x):
         residual = x
-        out = self.relu(self.norm1(self.conv1(x)))
-        out = self.relu(self.norm2(self.conv2(out)))
-        out = self.norm3(self.conv3(out))
+        out = self.norm1(self.conv1(x), act=ops.ACT_RELU)
+        out = self.norm2(self.conv2(out), act=ops.ACT_RELU)
+        out = self.conv3(out)
         if self.downsample is not None:
             residual = self.downsample(x)
+        if _same_map(out, residual):
+            return self.norm3(out, act=ops.ACT_RELU, residual=residual.F)
+        out = self.norm3(out)
         out += residual
-        out = self.relu(out)
-        return out
+        return self.relu(out)

@@ -12,6 +12,7 @@ from torch import nn
 
 from . import me as ME
 from . import ops
+from .detector import BlockSequential
 from .losses import build_loss
 
 
@@ -38,12 +39,12 @@ class MEFPN3D(nn.Module):
 
     @staticmethod
     def _make_block(cin, cout):
-        return nn.Sequential(ME.MinkowskiConvolution(cin, cout, kernel_size=3, dimension=3), ME.MinkowskiBatchNorm(cout),
-                             ME.MinkowskiELU())
+        return BlockSequential(ME.MinkowskiConvolution(cin, cout, kernel_size=3, dimension=3),
+                               ME.MinkowskiBatchNorm(cout), ME.MinkowskiELU())
 
     @staticmethod
     def _make_up_block(cin, cout):
-        return nn.Sequential(
+        return BlockSequential(
             ME.MinkowskiGenerativeConvolutionTranspose(cin, cout, kernel_size=2, stride=2, dimension=3),
             ME.MinkowskiBatchNorm(cout), ME.MinkowskiELU(),
             ME.MinkowskiConvolution(cout, cout, kernel_size=3, dimension=3), ME.MinkowskiBatchNorm(cout),

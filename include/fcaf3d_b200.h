@@ -210,6 +210,18 @@ int b2_conv_wgrad(const void* in, int a_dtype, const void* dout, int g_dtype, co
  * be NULL.  Replaces the per-step torch transposes of ME's kernel tensor (MinkowskiConvolution.kernel, App. A.4). */
 int b2_pack_conv_weights(const float* w, int kvol, int cin, int cout, void* wt_fwd, void* wt_bwd, void* stream);
 int b2_maxpool_bwd(const void* dy, int dtype, const int* argmax, long long n_out, int c, float* dx, void* stream);
+/* Training-mode MinkowskiBatchNorm (= nn.BatchNorm1d on the feature rows, ME App. A.6) fused with activation / residual:
+ * statistics of x [n, c] (dtype 0 f32 / 1 bf16, c % 8 == 0) -> mean, invstd, folded scale / shift (apply with
+ * b2_affine_act); running statistics and num_batches_tracked updated like torch (momentum, unbiased variance). */
+size_t b2_bn_ws_bytes(int c);
+int b2_bn_train_stats(const void* x, int dtype, long long n, int c, const float* weight, const float* bias,
+                      float* running_mean, float* running_var, long long* num_batches_tracked, float momentum, float eps,
+                      float* mean, float* invstd, float* scale, float* shift, void* ws, size_t ws_bytes, void* stream);
+/* backward of y = act(bn(x) [+ residual]) (act: 0 none, 1 ReLU, 2 ELU; derivative taken from y): sums f32 [2, c] =
+ * (d bias, d weight), dx [n, c], dres [n, c] (gradient of the residual branch) or NULL */
+int b2_bn_act_bwd(const void* x, const void* dy, const void* y, int dtype, long long n, int c, int act, const float* mean,
+                  const float* invstd, const float* weight, float* sums, void* dx, void* dres, void* ws, size_t ws_bytes,
+                  void* stream);
 /* Fcaf3DAssigner.assign for one scene (fcaf3d_neck_with_head.py:387-466): points [P,3] of all levels (level_off[L+1]),
  * boxes [B,7] = (gravity centre, size, yaw), labels_in int64 [B] -> centerness_t [P], box_t [P,7], labels_out int64 [P]
  * (-1 = background).  Scratch: counts int32 [L*B], best_level int32 [B], thr f32 [B]. */

@@ -255,3 +255,44 @@ def test_bf16_training_step_tracks_the_fp32_golden(dev, bf16_act):
     print("bf16_act=%s" % bf16_act, errs)
     for key, (err, cos) in errs.items():
         assert cos > 0.95 and err < 0.35, (key, err, cos)
+
+
+@pytest.mark.parametrize("act", [0, 1, 2], ids=["none", "relu", "elu"])
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.bfloat16, 2e-2)])
+@pytest.mark.parametrize("n,c,with_res", [(50000, 64, True), (3001, 128, False), (700, 512, True)])
+def test_fused_batchnorm_act_matches_torch(dev, act, dtype, tol, n, c, with_res):
+    """BNActFn (bn_ops.cu) against nn.BatchNorm1d + residual add + ReLU / ELU in torch autograd: output, gradients of x,
+    weight, bias and residual, running statistics and num_batches_tracked.  fp32: 2e-5 of max; bf16 rows: 2e-2."""
+    from fcaf3d_b200 import autograd as AG
+    from fcaf3d_b200 import ops
+    g = torch.Generator().manual_seed(n + c + act)
+    x0 = (torch.randn(n, c, generator=g) * 1.7 + 0.8).to(dev).to(dtype)
+    r0 = torch.randn(n, c, generator=g).to(dev).to(dtype) if with_res else None
+    gy = torch.randn(n, c, generator=g).to(dev).to(dtype)
+    bn_a, bn_b = torch.nn.BatchNorm1d(c).to(dev), torch.nn.BatchNorm1d(c).to(dev)
+    with torch.no_grad():
+        bn_a.weight.copy_(torch.rand(c, generator=g) + 0.5)
+        bn_a.bias.copy_(torch.randn(c, generator=g) * 0.1)
+        bn_a.running_mean.copy_(torch.randn(c, generator=g) * 0.1)
+        bn_b.load_state_dict(bn_a.state_dict())
+    # ours
+    xa = x0.clone().requires_grad_(True)
+    ra = r0.clone().requires_grad_(True) if with_res else None
+    assert AG.bn_act_supported(xa, bn_a)
+    ya = AG.BNActFn.apply(xa, bn_a.weight, bn_a.bias, ra, bn_a, act)
+    (ya.float() * gy.float()).sum().backward()
+    # torch, fp32 maths on the same (rounded) inputs
+    xb = x0.float().clone().requires_grad_(True)
+    rb = r0.float().clone().requires_grad_(True) if with_res else None
+    yb = bn_b(xb)
+    if with_res:
+        yb = yb + rb
+    yb = torch.relu(yb) if act == 1 else torch.nn.functional.elu(yb) if act == 2 else yb
+    (yb * gy.float()).sum().backward()
+    assert ya.dtype == dtype and rel_err(ya, yb) < tol
+    assert rel_err(xa.grad, xb.grad) < tol
+    assert rel_err(bn_a.weight.grad, bn_b.weight.grad) < tol and rel_err(bn_a.bias.grad, bn_b.bias.grad) < tol
+    if with_res:
+        assert rel_err(ra.grad, rb.grad) < tol
+    assert rel_err(bn_a.running_mean, bn_b.running_mean) < 1e-5 and rel_err(bn_a.running_var, bn_b.running_var) < 1e-5
+    assert int(bn_a.num_batches_tracked) == int(bn_b.num_batches_tracked) == 1
