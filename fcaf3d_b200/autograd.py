@@ -171,5 +171,28 @@ def bn_act_supported(x, bn):
             and x.dtype in (torch.float32, torch.bfloat16) and bn.momentum is not None)
 
 
+class UnionAddFn(torch.autograd.Function):
+    """out[dst_a[i]] = a[i]; out[dst_b[j]] += b[j] over the union map (ME A.8: `inputs[i] + x` on different maps);
+    backward = two row gathers.  Replaces torch's index_add / gather kernels on bf16 rows (0.2 ms per call)."""
+
+    @staticmethod
+    def forward(ctx, a, b, dst_a, dst_b, n):
+        a = a.contiguous()
+        b = b.contiguous().to(a.dtype)
+        out = torch.zeros((n, a.shape[1]), dtype=a.dtype, device=a.device)
+        ops.scatter_rows(a, dst_a, out, accumulate=False)
+        ops.scatter_rows(b, dst_b, out, accumulate=True)
+        ctx.save_for_backward(dst_a, dst_b)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        dst_a, dst_b = ctx.saved_tensors
+        g = g.contiguous()
+        da = ops.index_rows(g, dst_a) if ctx.needs_input_grad[0] else None
+        db = ops.index_rows(g, dst_b) if ctx.needs_input_grad[1] else None
+        return da, db, None, None, None
+
+
 def wants_grad(*tensors):
     return torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors)

@@ -393,7 +393,10 @@ class Fcaf3DNeckWithHead(nn.Module):
                 cm.union_prefetch(inputs[i - 1].coordinate_map_key, cm.generate_children(x.coordinate_map_key))
             out = getattr(self, f"out_block_{i}")(x)
             w = torch.cat((self.centerness_conv.kernel, self.reg_conv.kernel, self.cls_conv.kernel), dim=1)
-            h = out.F.float() @ w
+            if out.F.dtype == torch.bfloat16:    # bf16 rows: tensor-core GEMM (fp32 accumulate), logits back to fp32
+                h = (out.F @ w.to(torch.bfloat16)).float()
+            else:
+                h = out.F @ w
             reg = h[:, 1:1 + self.n_reg_outs]
             bbox = torch.cat((torch.exp(self.scales[i](reg[:, :6])), reg[:, 6:]), dim=1)
             cls = h[:, 1 + self.n_reg_outs:] + self.cls_conv.bias

@@ -417,10 +417,15 @@ class SparseTensor:
         # different maps: union (ME A.8)
         key, dst_a, dst_b = self.coordinate_manager.union(self.coordinate_map_key, other.coordinate_map_key)
         n = self.coordinate_manager.size(key)
-        out = torch.zeros((n, self._F.shape[1]), dtype=self._F.dtype, device=self._F.device)
-        if grad:  # autograd flows through the indexing, as in ME
-            out = out.index_add(0, dst_a.long(), self._F).index_add(0, dst_b.long(), other._F.to(self._F.dtype))
+        if grad:  # autograd flows through the row scatter, as through ME's indexing
+            rows_ok = (self._F.shape[1] * self._F.element_size()) % 16 == 0 and self._F.dtype in ops.DT
+            if rows_ok:
+                out = AG.UnionAddFn.apply(self._F, other._F, dst_a, dst_b, n)
+            else:
+                out = torch.zeros((n, self._F.shape[1]), dtype=self._F.dtype, device=self._F.device)
+                out = out.index_add(0, dst_a.long(), self._F).index_add(0, dst_b.long(), other._F.to(self._F.dtype))
             return SparseTensor(out, coordinate_map_key=key, coordinate_manager=self.coordinate_manager)
+        out = torch.zeros((n, self._F.shape[1]), dtype=self._F.dtype, device=self._F.device)
         ops.scatter_rows(self._F.contiguous(), dst_a, out, accumulate=False)
         ops.scatter_rows(other._F.contiguous().to(self._F.dtype), dst_b, out, accumulate=True)
         return SparseTensor(out, coordinate_map_key=key, coordinate_manager=self.coordinate_manager)
