@@ -166,6 +166,56 @@ class BNActFn(torch.autograd.Function):
         return dx, dw, db, dres, None, None
 
 
+class InstanceNormActFn(torch.autograd.Function):
+    """MinkowskiInstanceNorm (+ ReLU) in training: per scene (contiguous row range) and channel statistics, biased
+    variance, eps inside the square root, shared affine weight / bias (ME App. A.6; me_resnet.py:22).  Runs the
+    BatchNorm kernels of bn_ops.cu once per scene on the row slice: no per-scene torch graph (sum / div / mul / cat and
+    their backward accumulations over the largest tensor of the network)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, off_host, eps, act):
+        x = x.contiguous()
+        c = int(x.shape[1])
+        nb = len(off_host) - 1
+        dev = x.device
+        y = torch.empty_like(x)
+        stats = torch.zeros((nb, 4, c), dtype=torch.float32, device=dev)   # per scene: mean | invstd | scale | shift
+        ws = ops.workspace(ops._lib.lib().b2_bn_ws_bytes(c), dev, slot=3)
+        w32, b32 = weight.detach().float().contiguous(), bias.detach().float().contiguous()
+        for b in range(nb):
+            lo, hi = off_host[b], off_host[b + 1]
+            if hi <= lo:
+                continue
+            xs = x[lo:hi]
+            call("b2_bn_train_stats", ptr(xs), DT[x.dtype], hi - lo, c, ptr(w32), ptr(b32), None, None, None, 0.0,
+                 float(eps), ptr(stats[b, 0]), ptr(stats[b, 1]), ptr(stats[b, 2]), ptr(stats[b, 3]), ptr(ws), ws.numel())
+            ops.affine_act(xs, stats[b, 2:3], stats[b, 3:4], act=act, out=y[lo:hi])
+        ctx.save_for_backward(x, y if act != ops.ACT_NONE else None, stats, w32)
+        ctx.off_host, ctx.act, ctx.wdtype, ctx.wshape = list(off_host), act, weight.dtype, weight.shape
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, y, stats, w32 = ctx.saved_tensors
+        c = int(x.shape[1])
+        nb = len(ctx.off_host) - 1
+        dy = dy.contiguous().to(x.dtype)
+        dx = torch.zeros_like(x) if any(ctx.off_host[b + 1] <= ctx.off_host[b] for b in range(nb)) else torch.empty_like(x)
+        sums = torch.zeros((nb, 2, c), dtype=torch.float32, device=x.device)
+        ws = ops.workspace(ops._lib.lib().b2_bn_ws_bytes(c), x.device, slot=3)
+        for b in range(nb):
+            lo, hi = ctx.off_host[b], ctx.off_host[b + 1]
+            if hi <= lo:
+                continue
+            call("b2_bn_act_bwd", ptr(x[lo:hi]), ptr(dy[lo:hi]), ptr(y[lo:hi]) if y is not None else None, DT[x.dtype],
+                 hi - lo, c, int(ctx.act), ptr(stats[b, 0]), ptr(stats[b, 1]), ptr(w32), ptr(sums[b]), ptr(dx[lo:hi]), None,
+                 ptr(ws), ws.numel())
+        tot = sums.sum(0)
+        dw = tot[1].reshape(ctx.wshape).to(ctx.wdtype) if ctx.needs_input_grad[1] else None
+        db = tot[0].reshape(ctx.wshape).to(ctx.wdtype) if ctx.needs_input_grad[2] else None
+        return dx, dw, db, None, None, None
+
+
 def bn_act_supported(x, bn):
     return (FUSED_BN and x.is_cuda and x.dim() == 2 and x.shape[0] > 1 and x.shape[1] % 8 == 0 and x.shape[1] <= 2048
             and x.dtype in (torch.float32, torch.bfloat16) and bn.momentum is not None)

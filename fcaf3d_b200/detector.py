@@ -101,10 +101,18 @@ class MEResNet3D(nn.Module):
         map is enqueued one level early so that its row count is read while the GPU still has work (stride_prefetch)."""
         outs = []
         cm = x.coordinate_manager
-        for j, m in enumerate(self.conv1):
-            x = m(x)
-            if j == 0 and len(self.conv1) > 3:
-                cm.stride_prefetch(x.coordinate_map_key, self.conv1[3].stride)      # the pooling map
+        stem, j = list(self.conv1), 0
+        while j < len(stem):
+            m = stem[j]
+            nxt = stem[j + 1] if j + 1 < len(stem) else None
+            if isinstance(m, ME.MinkowskiInstanceNorm) and isinstance(nxt, ME.MinkowskiReLU):
+                x = m(x, act=ops.ACT_RELU)       # normalisation + ReLU as one pass
+                j += 1
+            else:
+                x = m(x)
+            if j == 0 and len(stem) > 3:
+                cm.stride_prefetch(x.coordinate_map_key, stem[3].stride)            # the pooling map
+            j += 1
         cm.stride_prefetch(x.coordinate_map_key, 2)
         for i in range(self.n_outs):
             for j, block in enumerate(getattr(self, f"layer{i + 1}")):

@@ -688,6 +688,10 @@ class MinkowskiInstanceNorm(MinkowskiModuleBase):
     def forward(self, x, act=ops.ACT_NONE):
         m = x._map()
         f = x.F.contiguous()
+        if (AG.wants_grad(f, self.weight, self.bias) and AG.FUSED_BN and f.shape[1] % 8 == 0 and f.shape[1] <= 2048
+                and f.dtype in ops.DT):
+            out = AG.InstanceNormActFn.apply(f, self.weight, self.bias, m.off_host, self.eps, act)
+            return SparseTensor(out, coordinate_map_key=x.coordinate_map_key, coordinate_manager=x.coordinate_manager)
         if AG.wants_grad(f, self.weight, self.bias):
             # differentiable per-scene statistics (ME: global pooling + broadcast, both with autograd).  Rows of a
             # scene are contiguous, so plain slices are used: indexing the [B, C] statistics with the per-row batch

@@ -296,3 +296,35 @@ def test_fused_batchnorm_act_matches_torch(dev, act, dtype, tol, n, c, with_res)
         assert rel_err(ra.grad, rb.grad) < tol
     assert rel_err(bn_a.running_mean, bn_b.running_mean) < 1e-5 and rel_err(bn_a.running_var, bn_b.running_var) < 1e-5
     assert int(bn_a.num_batches_tracked) == int(bn_b.num_batches_tracked) == 1
+
+
+@pytest.mark.parametrize("act", [0, 1], ids=["none", "relu"])
+def test_fused_instance_norm_matches_torch_graph(dev, act):
+    """InstanceNormActFn (per-scene BatchNorm kernels on row slices) against the per-scene torch graph it replaces
+    (MinkowskiInstanceNorm with AG.FUSED_BN off): output and gradients of x, weight and bias, one scene empty."""
+    from fcaf3d_b200 import autograd as AG
+    from fcaf3d_b200 import ops
+    c = torch.from_numpy(surface_coords(3000, 3, seed=2))
+    c = c[c[:, 0] != 1].contiguous()                     # scene 1 has no rows
+    x0 = ME.SparseTensor(torch.zeros(len(c), 1, device=dev), coordinates=c.to(dev))
+    torch.manual_seed(3)
+    f = (torch.randn(len(x0), 64, device=dev) * 2 + 0.5)
+    gy = torch.randn(len(x0), 64, device=dev)
+    outs = []
+    for fused in (True, False):
+        old = AG.FUSED_BN
+        AG.FUSED_BN = fused
+        try:
+            inorm = ME.MinkowskiInstanceNorm(64).to(dev)
+            with torch.no_grad():
+                inorm.weight.copy_(torch.linspace(0.5, 1.5, 64).reshape(1, 64))
+                inorm.bias.copy_(torch.linspace(-0.2, 0.2, 64).reshape(1, 64))
+            fi = f.clone().requires_grad_(True)
+            x = ME.SparseTensor(fi, coordinate_map_key=x0.coordinate_map_key, coordinate_manager=x0.coordinate_manager)
+            y = inorm(x, act=act).F
+            (y * gy).sum().backward()
+            outs.append((y.detach(), fi.grad, inorm.weight.grad, inorm.bias.grad))
+        finally:
+            AG.FUSED_BN = old
+    for a, b in zip(*outs):
+        assert a.shape == b.shape and rel_err(a, b) < 5e-5
