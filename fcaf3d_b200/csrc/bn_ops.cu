@@ -116,50 +116,49 @@ __global__ void __launch_bounds__(256) k_bn_partial(const T* __restrict__ x, con
         t1 += red[(j * lanes + tl) * 16 + i];
         t2 += red[(j * lanes + tl) * 16 + 8 + i];
       }
-      partial[((long long)blockIdx.x * 2) * c + tl * 8 + i] = t1;
-      partial[((long long)blockIdx.x * 2 + 1) * c + tl * 8 + i] = t2;
+      // layout [stat][channel][part]: the final reduction reads a channel's partials contiguously
+      partial[((long long)(tl * 8 + i)) * gridDim.x + blockIdx.x] = t1;
+      partial[((long long)(c + tl * 8 + i)) * gridDim.x + blockIdx.x] = t2;
     }
   }
 }
 
-// Final reduction of the partial sums: a CTA of 1024 threads owns 32 channels; thread (channel lane, part lane) adds every
-// 32nd partial in double, the 32 part lanes are combined through shared memory (a single thread per channel walking all
-// BN_PARTS partials is latency bound: measured 90 us per call).
-__device__ __forceinline__ void bn_reduce_parts(const float* __restrict__ partial, int parts, int c, int ch, int pl,
-                                                double (*red)[32][2], double& s1, double& s2) {
+// Final reduction of the partial sums: one warp per channel adds its contiguous run of partials (both statistics) in
+// double and combines the lanes by shuffles (one thread per channel walking all partials was latency bound at 90 us per
+// call, a 1024-thread CTA per 32 channels still 18 us: too few CTAs for 64-channel layers).
+__device__ __forceinline__ void bn_reduce_parts(const float* __restrict__ partial, int parts, int c, int ch, double& s1,
+                                                double& s2) {
+  const int lane = threadIdx.x & 31;
   double a1 = 0.0, a2 = 0.0;
-  if (ch < c) {
-    for (int p = pl; p < parts; p += 32) {
-      a1 += (double)partial[((long long)p * 2) * c + ch];
-      a2 += (double)partial[((long long)p * 2 + 1) * c + ch];
-    }
+  const float* p1 = partial + (long long)ch * parts;
+  const float* p2 = partial + (long long)(c + ch) * parts;
+  for (int p = lane; p < parts; p += 32) {
+    a1 += (double)p1[p];
+    a2 += (double)p2[p];
   }
-  red[pl][threadIdx.x & 31][0] = a1;
-  red[pl][threadIdx.x & 31][1] = a2;
-  __syncthreads();
-  s1 = s2 = 0.0;
-  if (pl == 0) {
-    for (int j = 0; j < 32; ++j) {
-      s1 += red[j][threadIdx.x & 31][0];
-      s2 += red[j][threadIdx.x & 31][1];
-    }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    a1 += __shfl_xor_sync(0xFFFFFFFFu, a1, o);
+    a2 += __shfl_xor_sync(0xFFFFFFFFu, a2, o);
   }
+  s1 = a1;
+  s2 = a2;
 }
 
 // partial sums -> mean / invstd / folded scale, shift; running statistics like nn.BatchNorm1d
 template <typename T>
-__global__ void __launch_bounds__(1024) k_bn_finalize(const float* __restrict__ partial, int parts, long long n, int c,
-                                                      const T* __restrict__ x, const float* __restrict__ weight,
-                                                      const float* __restrict__ bias, float* running_mean,
-                                                      float* running_var, long long* num_batches_tracked, float momentum,
-                                                      float eps, float* __restrict__ mean, float* __restrict__ invstd,
-                                                      float* __restrict__ scale, float* __restrict__ shift) {
-  __shared__ double red[32][32][2];
-  const int ch = blockIdx.x * 32 + (threadIdx.x & 31), pl = threadIdx.x >> 5;
+__global__ void __launch_bounds__(256) k_bn_finalize(const float* __restrict__ partial, int parts, long long n, int c,
+                                                     const T* __restrict__ x, const float* __restrict__ weight,
+                                                     const float* __restrict__ bias, float* running_mean,
+                                                     float* running_var, long long* num_batches_tracked, float momentum,
+                                                     float eps, float* __restrict__ mean, float* __restrict__ invstd,
+                                                     float* __restrict__ scale, float* __restrict__ shift) {
+  const int ch = blockIdx.x * 8 + (threadIdx.x >> 5);
   if (blockIdx.x == 0 && threadIdx.x == 0 && num_batches_tracked) *num_batches_tracked += 1;
+  if (ch >= c) return;
   double s1, s2;
-  bn_reduce_parts(partial, parts, c, ch, pl, red, s1, s2);
-  if (pl != 0 || ch >= c) return;
+  bn_reduce_parts(partial, parts, c, ch, s1, s2);
+  if ((threadIdx.x & 31) != 0) return;
   float k;
   {
     float k8[8];
@@ -182,13 +181,13 @@ __global__ void __launch_bounds__(1024) k_bn_finalize(const float* __restrict__ 
   }
 }
 
-__global__ void __launch_bounds__(1024) k_bn_bwd_finalize(const float* __restrict__ partial, int parts, int c,
-                                                          float* __restrict__ sums) {
-  __shared__ double red[32][32][2];
-  const int ch = blockIdx.x * 32 + (threadIdx.x & 31), pl = threadIdx.x >> 5;
+__global__ void __launch_bounds__(256) k_bn_bwd_finalize(const float* __restrict__ partial, int parts, int c,
+                                                         float* __restrict__ sums) {
+  const int ch = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (ch >= c) return;
   double s1, s2;
-  bn_reduce_parts(partial, parts, c, ch, pl, red, s1, s2);
-  if (pl != 0 || ch >= c) return;
+  bn_reduce_parts(partial, parts, c, ch, s1, s2);
+  if ((threadIdx.x & 31) != 0) return;
   sums[ch] = (float)s1;      // d bias
   sums[c + ch] = (float)s2;  // d weight
 }
@@ -243,13 +242,13 @@ int b2_bn_train_stats(const void* x, int dtype, long long n, int c, const float*
   const int parts = (int)(n < BN_PARTS ? n : BN_PARTS);
   if (dtype == 0) {
     k_bn_partial<float, 0><<<parts, 256, 0, st>>>((const float*)x, nullptr, nullptr, n, c, 0, nullptr, nullptr, partial);
-    k_bn_finalize<float><<<b2_div_up(c, 32), 1024, 0, st>>>(partial, parts, n, c, (const float*)x, weight, bias,
+    k_bn_finalize<float><<<b2_div_up(c, 8), 256, 0, st>>>(partial, parts, n, c, (const float*)x, weight, bias,
                                                             running_mean, running_var, num_batches_tracked, momentum, eps,
                                                             mean, invstd, scale, shift);
   } else {
     k_bn_partial<__nv_bfloat16, 0><<<parts, 256, 0, st>>>((const __nv_bfloat16*)x, nullptr, nullptr, n, c, 0, nullptr,
                                                          nullptr, partial);
-    k_bn_finalize<__nv_bfloat16><<<b2_div_up(c, 32), 1024, 0, st>>>(partial, parts, n, c, (const __nv_bfloat16*)x, weight,
+    k_bn_finalize<__nv_bfloat16><<<b2_div_up(c, 8), 256, 0, st>>>(partial, parts, n, c, (const __nv_bfloat16*)x, weight,
                                                                     bias, running_mean, running_var, num_batches_tracked,
                                                                     momentum, eps, mean, invstd, scale, shift);
   }
@@ -276,13 +275,13 @@ int b2_bn_act_bwd(const void* x, const void* dy, const void* y, int dtype, long 
   if (dtype == 0) {
     k_bn_partial<float, 1><<<parts, 256, 0, st>>>((const float*)x, (const float*)dy, (const float*)y, n, c, act, mean,
                                                   invstd, partial);
-    k_bn_bwd_finalize<<<b2_div_up(c, 32), 1024, 0, st>>>(partial, parts, c, sums);
+    k_bn_bwd_finalize<<<b2_div_up(c, 8), 256, 0, st>>>(partial, parts, c, sums);
     k_bn_bwd_apply<float><<<G, 256, 0, st>>>((const float*)x, (const float*)dy, (const float*)y, n, c, act, mean, invstd,
                                              weight, sums, (float*)dx, (float*)dres);
   } else {
     k_bn_partial<__nv_bfloat16, 1><<<parts, 256, 0, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)dy,
                                                          (const __nv_bfloat16*)y, n, c, act, mean, invstd, partial);
-    k_bn_bwd_finalize<<<b2_div_up(c, 32), 1024, 0, st>>>(partial, parts, c, sums);
+    k_bn_bwd_finalize<<<b2_div_up(c, 8), 256, 0, st>>>(partial, parts, c, sums);
     k_bn_bwd_apply<__nv_bfloat16><<<G, 256, 0, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)dy,
                                                      (const __nv_bfloat16*)y, n, c, act, mean, invstd, weight, sums,
                                                      (__nv_bfloat16*)dx, (__nv_bfloat16*)dres);
