@@ -14,7 +14,9 @@ def shard_scenes(n_scenes, rank, world_size):
 
 
 def make_optimizer(model, lr=1e-3, weight_decay=1e-4):
-    return torch.optim.AdamW(model.parameters(), lr=lr, weight_decay=weight_decay)
+    params = list(model.parameters())
+    fused = bool(params) and all(p.is_cuda for p in params)      # one multi-tensor kernel chain instead of ~10 per step
+    return torch.optim.AdamW(params, lr=lr, weight_decay=weight_decay, fused=fused)
 
 
 def wrap_ddp(model, device):
