@@ -5,6 +5,9 @@
 //   _prune :110-126 (features_at_coordinates + per-scene topk mask), forward_single :256-279,
 //   _get_bboxes_single :227-253, _bbox_pred_to_bbox :281-330, _nms :332-374 (score threshold).
 #include "common.cuh"
+#include <cooperative_groups.h>
+#include <stdlib.h>
+namespace cg = cooperative_groups;
 
 // ---------------------------------------------------------------------------
 // features_at_coordinates: 8-corner trilinear interpolation on the source grid
@@ -165,6 +168,153 @@ __global__ void __launch_bounds__(1024) k_topk_mask(const float* __restrict__ sc
     }
     __syncthreads();
   }
+}
+
+// Same selection for LONG segments (the prune step: 8 scenes x 180 k scores): a thread-block cluster of CL CTAs shares one
+// segment.  Every CTA histograms its slice of the rows, the slices' histograms are added into CTA 0's shared memory
+// through distributed shared memory, CTA 0 picks the digit, everybody reads it back; for the ties at the threshold the
+// CTAs exchange their counts of equal rows so that the lowest rows win exactly as in the one-CTA kernel (bit-identical
+// masks).  Eight cluster barriers per call instead of one CTA walking the whole segment four times.
+template <int CL>
+__global__ void __launch_bounds__(1024) k_topk_mask_cl(const float* __restrict__ scores, const int* __restrict__ seg_off,
+                                                       int k, uint8_t* __restrict__ mask) {
+  cg::cluster_group cluster = cg::this_cluster();
+  __shared__ unsigned int hist[TOPK_BINS];
+  __shared__ unsigned int merged[3][TOPK_BINS];  // used in CTA 0 only: cluster-wide histogram of each pass
+  __shared__ unsigned int s_prefix, s_need;
+  __shared__ int s_warp[32];
+  __shared__ int s_run, s_eq;
+  const int crank = (int)cluster.block_rank();
+  const int seg = blockIdx.x / CL;
+  const int beg = seg_off[seg], n = seg_off[seg + 1] - beg;
+  const int per = ((n + CL - 1) / CL + 3) & ~3;
+  const int lo = min(crank * per, n), hi = min(lo + per, n);
+  if (n <= 0) return;
+  if (k >= n || k <= 0) {  // cluster-uniform
+    for (int i = lo + threadIdx.x; i < hi; i += blockDim.x) mask[beg + i] = (k >= n) ? 1 : 0;
+    return;
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (crank == 0)
+    for (int i = threadIdx.x; i < 3 * TOPK_BINS; i += blockDim.x) (&merged[0][0])[i] = 0;
+  cluster.sync();
+  unsigned int* merged0 = cluster.map_shared_rank(&merged[0][0], 0);
+  const unsigned int* prefix0 = cluster.map_shared_rank(&s_prefix, 0);
+  const unsigned int* need0 = cluster.map_shared_rank(&s_need, 0);
+  unsigned int prefix = 0, need = (unsigned int)k;
+  const int shifts[3] = {21, 10, 0}, widths[3] = {11, 11, 10};
+  const int m = hi - lo;
+  for (int pass = 0; pass < 3; ++pass) {
+    const int shift = shifts[pass], bins = 1 << widths[pass];
+    const unsigned int hi_mask = pass == 0 ? 0u : (0xFFFFFFFFu << (shift + widths[pass]));
+    for (int i = threadIdx.x; i < TOPK_BINS; i += blockDim.x) hist[i] = 0;
+    __syncthreads();
+    for (int i0 = threadIdx.x; i0 - lane < m; i0 += blockDim.x * 4) {
+      unsigned int u4[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int i = i0 + e * (int)blockDim.x;
+        u4[e] = (i < m) ? f32_ordered(scores[beg + lo + i]) : 0u;
+      }
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int i = i0 + e * (int)blockDim.x;
+        const bool valid = (i < m) && ((u4[e] & hi_mask) == prefix);
+        const unsigned int vm = __ballot_sync(0xffffffffu, valid);
+        if (valid) {
+          const unsigned int d = (u4[e] >> shift) & (unsigned int)(bins - 1);
+          const unsigned int peers = __match_any_sync(vm, d);
+          if (lane == __ffs(peers) - 1) atomicAdd(&hist[d], (unsigned int)__popc(peers));
+        }
+      }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < bins; i += blockDim.x) {
+      const unsigned int v = hist[i];
+      if (v) atomicAdd(merged0 + pass * TOPK_BINS + i, v);
+    }
+    cluster.sync();
+    if (crank == 0 && warp == 0) {
+      const unsigned int* h = &merged[pass][0];
+      const int per_l = bins / 32;
+      unsigned int mine = 0;
+      for (int j = 0; j < per_l; ++j) mine += h[lane * per_l + j];
+      unsigned int above = 0;
+      for (int l = 31; l >= 0; --l) {
+        const unsigned int v = __shfl_sync(0xffffffffu, mine, l);
+        if (l > lane) above += v;
+      }
+      if (above < need && above + mine >= need) {
+        unsigned int acc = above;
+        int d = lane * per_l + per_l - 1;
+        for (; d > lane * per_l; --d) {
+          if (acc + h[d] >= need) break;
+          acc += h[d];
+        }
+        s_prefix = prefix | ((unsigned int)d << shift);
+        s_need = need - acc;
+      }
+    }
+    cluster.sync();
+    prefix = *prefix0;
+    need = *need0;
+  }
+  // ties: rows equal to the threshold are taken in row order; the slices are in row order, so a CTA starts its count at
+  // the number of equal rows in the slices before it
+  int eq_local = 0;
+  for (int i = threadIdx.x; i < m; i += blockDim.x) eq_local += (f32_ordered(scores[beg + lo + i]) == prefix) ? 1 : 0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) eq_local += __shfl_xor_sync(0xffffffffu, eq_local, o);
+  if (lane == 0) s_warp[warp] = eq_local;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += s_warp[w];
+    s_eq = t;
+  }
+  cluster.sync();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int r = 0; r < crank; ++r) t += *cluster.map_shared_rank(&s_eq, r);
+    s_run = t;
+  }
+  __syncthreads();
+  for (int base = 0; base < m; base += blockDim.x * 4) {
+    const int i = base + threadIdx.x * 4;
+    unsigned int u4[4];
+    int eqc = 0;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      u4[e] = (i + e < m) ? f32_ordered(scores[beg + lo + i + e]) : 0u;
+      eqc += (i + e < m && u4[e] == prefix) ? 1 : 0;
+    }
+    int incl = eqc;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    int rank = s_run + incl - eqc;
+    for (int w = 0; w < warp; ++w) rank += s_warp[w];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      if (i + e < m) {
+        const bool eq = u4[e] == prefix;
+        mask[beg + lo + i + e] = (u4[e] > prefix || (eq && rank < (int)need)) ? 1 : 0;
+        rank += eq ? 1 : 0;
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int t = 0;
+      for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += s_warp[w];
+      s_run += t;
+    }
+    __syncthreads();
+  }
+  cluster.sync();  // nobody leaves while a peer may still read its shared memory
 }
 
 // ---------------------------------------------------------------------------
@@ -356,11 +506,34 @@ int b2_interp(const void* table, long long cap, const float* feats, int c, int t
   return B2_OK;
 }
 
-int b2_topk_mask(const float* scores, const int* seg_off, int nseg, int k, uint8_t* mask, void* stream) {
+// n_total: rows over all segments (host-known); long segments take the 8-CTA cluster kernel
+int b2_topk_mask_n(const float* scores, const int* seg_off, int nseg, int k, long long n_total, uint8_t* mask,
+                   void* stream) {
   if (nseg == 0) return B2_OK;
-  k_topk_mask<<<nseg, 1024, 0, (cudaStream_t)stream>>>(scores, seg_off, k, mask);
+  static const int cl_env = getenv("B2_TOPK_CLUSTER") ? atoi(getenv("B2_TOPK_CLUSTER")) : -1;
+  const bool use_cl = cl_env >= 0 ? cl_env > 0 : (n_total / nseg >= 32768);
+  if (use_cl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)nseg * 8);
+    cfg.blockDim = dim3(1024);
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 8;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    B2_CUDA(cudaLaunchKernelEx(&cfg, k_topk_mask_cl<8>, scores, seg_off, k, mask));
+  } else {
+    k_topk_mask<<<nseg, 1024, 0, (cudaStream_t)stream>>>(scores, seg_off, k, mask);
+  }
   B2_LAUNCH_CHECK();
   return B2_OK;
+}
+
+int b2_topk_mask(const float* scores, const int* seg_off, int nseg, int k, uint8_t* mask, void* stream) {
+  return b2_topk_mask_n(scores, seg_off, nseg, k, 0, mask, stream);
 }
 
 int b2_head_post(const float* feat, long long n, int feat_ld, int n_reg, int n_cls, const float* scale,

@@ -438,7 +438,7 @@ def interp(table, cap, feats, tensor_stride, query):
 
 def topk_mask(scores, seg_off, nseg, k):
     mask = torch.empty((scores.shape[0],), dtype=torch.uint8, device=scores.device)
-    call("b2_topk_mask", ptr(scores), ptr(seg_off), nseg, int(k), ptr(mask))
+    call("b2_topk_mask_n", ptr(scores), ptr(seg_off), nseg, int(k), int(scores.shape[0]), ptr(mask))
     return mask
 
 

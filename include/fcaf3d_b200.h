@@ -133,6 +133,10 @@ int b2_interp(const void* table, long long cap, const float* feats, int c, int t
               long long m, float* out, void* stream);
 /* mask[i] = 1 for the k largest scores of each segment (ties at the k-th value: lowest rows first) */
 int b2_topk_mask(const float* scores, const int* seg_off, int nseg, int k, uint8_t* mask, void* stream);
+/* same, with the total row count known to the host: segments of >= 32768 rows on average are selected by a cluster of 8
+ * CTAs per segment (histograms merged through distributed shared memory); masks are identical to b2_topk_mask */
+int b2_topk_mask_n(const float* scores, const int* seg_off, int nseg, int k, long long n_total, uint8_t* mask,
+                   void* stream);
 /* feat [n, feat_ld] (first 1+n_reg+n_cls columns used) -> centerness[n], bbox_pred[n,n_reg] (first 6: exp(*scale * x), scale = the level's
  * learnable Scale on the device), cls[n,n_cls], prune_score[n] = max class logit,
  * max_score[n] = max_c sigmoid(cls_c)*sigmoid(centerness) (optional) */
