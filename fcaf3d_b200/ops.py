@@ -10,7 +10,7 @@ import os
 import torch
 
 from . import _lib
-from ._lib import DT, call, ptr, require_cuda, workspace
+from ._lib import B2Error, DT, call, ptr, require_cuda, workspace
 
 ACT_NONE, ACT_RELU, ACT_ELU = 0, 1, 2
 I32 = torch.int32
@@ -377,6 +377,8 @@ def sparse_conv(x, w, kmap, n_out, wt_bf16=None, bias=None, scale=None, shift=No
         call("b2_conv_tc", ptr(x), x.shape[0], ptr(wt_bf16), ptr(nbr), ld, ptr(tmask), ptr(perm), n_out, cin, cout, kvol,
              ptr(bias), ptr(scale), ptr(shift), ptr(residual), act, ch_mod, ptr(out), DT[out_dtype])
     else:
+        if cin <= 4 and x.shape[0] >= (1 << 26):
+            raise B2Error("narrow-input convolution packs (offset, row) into 32 bits: at most 2^26 input rows")
         call("b2_conv_cc", ptr(x), DT[x.dtype], ptr(w), ptr(nbr), ld, ptr(tmask), n_out, cin, cout, kvol, ptr(bias),
              ptr(scale), ptr(shift), ptr(residual), act, ch_mod, ptr(out), DT[out_dtype])
     if t0 is not None:
