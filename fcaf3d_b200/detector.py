@@ -675,18 +675,31 @@ class Fcaf3DNeckWithHead(nn.Module):
                     box_dim=7 if rotated else 6)
 
 
+_PINNED_OUT = {}
+
+
 def split_detections(dets, num_scenes):
     """Device-side result dict -> host list of (boxes, scores, labels) per scene: one read of the count, then ONE packed
-    device->host copy of (box, score, label, scene) rows."""
+    device->host copy of (box, score, label, scene) rows into a reused pinned buffer; the rows come out of the NMS in
+    (scene, class) order, so the per-scene split is a slice."""
     n = int(dets["count"].item())
     d = dets["box_dim"]
-    packed = torch.cat((dets["boxes"][:n, :d], dets["scores"][:n, None], dets["labels"][:n, None].float(),
-                        dets["scene"][:n, None].float()), dim=1).cpu()
+    packed_dev = torch.cat((dets["boxes"][:n, :d], dets["scores"][:n, None], dets["labels"][:n, None].float(),
+                            dets["scene"][:n, None].float()), dim=1)
+    buf = _PINNED_OUT.get(d)
+    if buf is None or buf.shape[0] < n:
+        buf = torch.empty((max(n, 1) * 2, d + 3), dtype=torch.float32).pin_memory()
+        _PINNED_OUT[d] = buf
+    host = buf[:n]
+    host.copy_(packed_dev, non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    packed = host.clone()                      # the pinned buffer is reused by the next call
     boxes, scores, labels, scene = packed[:, :d], packed[:, d], packed[:, d + 1].long(), packed[:, d + 2].long()
-    out = []
+    cnt = torch.bincount(scene, minlength=num_scenes).tolist() if n else [0] * num_scenes
+    out, lo = [], 0
     for b in range(num_scenes):
-        sel = scene == b
-        out.append((boxes[sel], scores[sel], labels[sel]))
+        out.append((boxes[lo:lo + cnt[b]], scores[lo:lo + cnt[b]], labels[lo:lo + cnt[b]]))
+        lo += cnt[b]
     return out
 
 
