@@ -703,6 +703,58 @@ def split_detections(dets, num_scenes):
     return out
 
 
+class DetectionRead:
+    """Asynchronous read-back of one step's detections: the packed copy (count + the first `cap` rows) is enqueued on a side
+    stream behind the step's last kernel, so the caller can enqueue the NEXT step before it looks at the result
+    (`finish()`); the GPU never waits for the host between two steps."""
+    _stream = None
+    _ring = {}
+    _next = 0
+    CAP = 16384
+
+    def __init__(self, dets, num_scenes):
+        self.dets, self.num_scenes, self.d = dets, num_scenes, dets["box_dim"]
+        dev = dets["boxes"].device
+        if DetectionRead._stream is None:
+            DetectionRead._stream = torch.cuda.Stream(device=dev)
+        done = torch.cuda.Event()
+        done.record()
+        cap = min(self.CAP, int(dets["boxes"].shape[0]))
+        self.cap = cap
+        with torch.cuda.stream(DetectionRead._stream):
+            DetectionRead._stream.wait_event(done)
+            packed = torch.cat((dets["boxes"][:cap, :self.d], dets["scores"][:cap, None], dets["labels"][:cap, None].float(),
+                                dets["scene"][:cap, None].float()), dim=1)
+            ring = DetectionRead._ring.setdefault((self.d, str(dets["count"].dtype)), [])
+            if len(ring) < 4:                 # four pinned staging buffers, reused round-robin
+                ring.append((torch.empty((self.CAP, self.d + 3), dtype=torch.float32).pin_memory(),
+                             torch.empty((1,), dtype=dets["count"].dtype).pin_memory()))
+            DetectionRead._next = (DetectionRead._next + 1) % 4
+            full, self.count_host = ring[DetectionRead._next % len(ring)]
+            self.host = full[:cap]
+            if cap:
+                self.host.copy_(packed, non_blocking=True)
+            self.count_host.copy_(dets["count"].reshape(1), non_blocking=True)
+            self.event = torch.cuda.Event()
+            self.event.record()
+            self._keep = packed
+
+    def finish(self):
+        self.event.synchronize()
+        n = int(self.count_host[0])
+        if n > self.cap:                      # more detections than the staged rows: fall back to the blocking read
+            return split_detections(self.dets, self.num_scenes)
+        d = self.d
+        packed = self.host[:n]
+        boxes, scores, labels, scene = packed[:, :d], packed[:, d], packed[:, d + 1].long(), packed[:, d + 2].long()
+        cnt = torch.bincount(scene, minlength=self.num_scenes).tolist() if n else [0] * self.num_scenes
+        out, lo = [], 0
+        for b in range(self.num_scenes):
+            out.append((boxes[lo:lo + cnt[b]], scores[lo:lo + cnt[b]], labels[lo:lo + cnt[b]]))
+            lo += cnt[b]
+        return out
+
+
 # =============================================================================================== detector
 class SingleStageSparse3DDetector(nn.Module):
     def __init__(self, backbone, neck_with_head, voxel_size, pretrained=False, train_cfg=None, test_cfg=None):

@@ -129,6 +129,10 @@ def test_fused_tail_equals_reference_style_tail_on_same_head_outputs(dev):
         dets = head.get_bboxes_fused(levels, cm)
         from fcaf3d_b200.detector import split_detections
         fused = split_detections(dets, len(pts))
+        from fcaf3d_b200.detector import DetectionRead
+        later = DetectionRead(dets, len(pts)).finish()            # asynchronous packed read-back: same rows
+        for (b1, s1, l1), (b2, s2, l2) in zip(fused, later):
+            assert torch.equal(b1, b2) and torch.equal(s1, s2) and torch.equal(l1, l2)
         per = _levels_from_fused(levels, cm)
         for b in range(len(pts)):
             cs, bs, ss, ps = [], [], [], []
