@@ -388,8 +388,9 @@ def main():
         detections back, all inside one timed bracket; the copy of step i+1 is double-buffered on a side stream
         (fcaf3d_b200.data.ScenePrefetcher) and overlaps the compute of step i; L2 is flushed inside the loop."""
         from fcaf3d_b200.data import ScenePrefetcher
-        for pts in ScenePrefetcher((host_pts for _ in range(max(warmup, 3))), dev):   # warms the side stream's pool too
-            split_detections(det.simple_test_fused(pts, to_host=False), BATCH)
+        # warm-up through the SAME path (side streams, pinned staging rings and their first allocations stay out of the bracket)
+        for pts in ScenePrefetcher((host_pts for _ in range(max(warmup, 5))), dev):
+            DetectionRead(det.simple_test_fused(pts, to_host=False), BATCH).finish()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
