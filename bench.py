@@ -182,6 +182,7 @@ def run_train(args, det, scenes, dev, world, rank, dtype):
         copies its own inputs and (end to end) has its loss read back - one step late, through pinned memory."""
         prepared = det.prepare(fetch(e2e))
         pending, last = None, None
+        loss_ring = [torch.empty((1,), dtype=torch.float32).pin_memory() for _ in range(2)] if e2e else None
         for i in range(steps):
             nxt = fetch(e2e) if i + 1 < steps else None
             out = train_step(module, opt, prepared, gtb, gtl, next_points=nxt)
@@ -190,7 +191,7 @@ def run_train(args, det, scenes, dev, world, rank, dtype):
                 if pending is not None:
                     pending[1].synchronize()
                     last = float(pending[0][0])
-                hostbuf = torch.empty((1,), dtype=torch.float32).pin_memory()
+                hostbuf = loss_ring[i % 2]
                 hostbuf.copy_(out[0].reshape(1), non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record()
