@@ -175,6 +175,8 @@ def run_train(args, det, scenes, dev, world, rank, dtype):
     def fetch(e2e):
         return [p.to(dev, non_blocking=True) for p, _, _ in host] if e2e else dev_pts
 
+    loss_ring = [torch.empty((1,), dtype=torch.float32).pin_memory() for _ in range(2)]   # pinned loss read-back
+
     def run_steps(e2e, steps):
         """K training steps, software-pipelined: the coordinate / kernel maps of batch i+1 (and, end to end, its
         host->device copy) are issued between the forward and the backward of batch i (train_step(next_points=...)), so
@@ -182,7 +184,6 @@ def run_train(args, det, scenes, dev, world, rank, dtype):
         copies its own inputs and (end to end) has its loss read back - one step late, through pinned memory."""
         prepared = det.prepare(fetch(e2e))
         pending, last = None, None
-        loss_ring = [torch.empty((1,), dtype=torch.float32).pin_memory() for _ in range(2)] if e2e else None
         for i in range(steps):
             nxt = fetch(e2e) if i + 1 < steps else None
             out = train_step(module, opt, prepared, gtb, gtl, next_points=nxt)
