@@ -56,7 +56,8 @@ class SparseConvFn(torch.autograd.Function):
             wt, wt_b = ops.pack_conv_weights(wd.float(), want_fwd=tc_fwd, want_bwd=tc_bwd)   # one launch, both layouts
         if tc_fwd:
             x = ops.cast(feats, torch.bfloat16)
-        out_dt = torch.bfloat16 if (tc_fwd and BF16_ACTIVATIONS) else torch.float32
+        # bf16 hand-over also for the CUDA-core stem (its [N2, 64] output is the largest activation of the network)
+        out_dt = torch.bfloat16 if (BF16_ACTIVATIONS and (tc_fwd or (tc_on and cout % 8 == 0))) else torch.float32
         out = ops.sparse_conv(x, wd, kmap, n_out, wt_bf16=wt, out_dtype=out_dt)
         ctx.save_for_backward(x, wd, wt_b)
         ctx.kmap, ctx.kmap_t, ctx.n_in = kmap, kmap_t, int(feats.shape[0])
@@ -84,7 +85,8 @@ class SparseConvFn(torch.autograd.Function):
                 d_feats = ops.sparse_conv(g.float(), w_back, ctx.kmap_t, ctx.n_in, out_dtype=torch.float32)
             d_feats = d_feats.to(ctx.in_dtype)
         if want_w:
-            d_w = conv_wgrad(x, gb if x.dtype == torch.bfloat16 else g.float(), ctx.kmap, kvol, cin, cout)
+            gw = gb if x.dtype == torch.bfloat16 else (g if g.dtype in DT else g.float())   # fp32 x bf16 is a kernel flavour
+            d_w = conv_wgrad(x, gw, ctx.kmap, kvol, cin, cout)
         return d_feats, d_w, None, None, None, None
 
 
