@@ -21,8 +21,16 @@ def make_optimizer(model, lr=1e-3, weight_decay=1e-4):
 
 def wrap_ddp(model, device):
     if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
-        return torch.nn.parallel.DistributedDataParallel(model, device_ids=[device.index], broadcast_buffers=False,
-                                                         gradient_as_bucket_view=True)
+        import os
+        ddp = torch.nn.parallel.DistributedDataParallel(model, device_ids=[device.index], broadcast_buffers=False,
+                                                        gradient_as_bucket_view=True,
+                                                        bucket_cap_mb=int(os.environ.get("B2_DDP_BUCKET_MB", "100")))
+        # measured at N=2: 100 MB buckets 480 scenes/s, 25 MB 460-474; the bf16 compression hook 320-360 (its cast kernels
+        # cost more than NVLink saves), so it stays opt-in
+        if os.environ.get("B2_DDP_BF16", "0") == "1":
+            from torch.distributed.algorithms.ddp_comm_hooks import default_hooks
+            ddp.register_comm_hook(None, default_hooks.bf16_compress_hook)
+        return ddp
     return model
 
 
