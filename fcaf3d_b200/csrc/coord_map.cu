@@ -383,6 +383,7 @@ __global__ void k_scatter_rows_f32(const float* __restrict__ in, const int* __re
   if (t >= n * c) return;
   const long long i = t / c;
   const int ch = (int)(t - i * c);
+  if (dst[i] < 0) return;
   const long long o = (long long)dst[i] * c + ch;
   out[o] = accumulate ? out[o] + in[t] : in[t];
 }
@@ -393,6 +394,7 @@ __global__ void k_scatter_rows_bf16(const __nv_bfloat16* __restrict__ in, const 
   if (t >= n * c) return;
   const long long i = t / c;
   const int ch = (int)(t - i * c);
+  if (dst[i] < 0) return;
   const long long o = (long long)dst[i] * c + ch;
   out[o] = accumulate ? __float2bfloat16(__bfloat162float(out[o]) + __bfloat162float(in[t])) : in[t];
 }
@@ -404,6 +406,7 @@ __global__ void k_scatter_rows_bf16x8(const uint4* __restrict__ in, const int* _
   if (t >= n * vpr) return;
   const long long i = t / vpr;
   const int v = (int)(t - i * vpr);
+  if (dst[i] < 0) return;
   const long long o = (long long)dst[i] * vpr + v;
   uint4 a = __ldg(in + t);
   if (accumulate) {

@@ -347,6 +347,54 @@ __global__ void k_head_post(const float* __restrict__ feat, int n, int feat_ld, 
   if (max_score) max_score[i] = mscore;
 }
 
+// Same arithmetic with coalesced traffic: a CTA stages 256 rows of feat in shared memory (row pitch feat_ld + 1 words),
+// one thread per row does the per-row scalars from there, and the [rows, n_reg] / [rows, n_cls] blocks - contiguous in
+// the outputs - are written with consecutive threads on consecutive words.
+#define HP_ROWS 256
+__global__ void __launch_bounds__(256) k_head_post_tiled(const float* __restrict__ feat, int n, int feat_ld, int n_reg,
+                                                         int n_cls, const float* __restrict__ scale_ptr,
+                                                         float* __restrict__ centerness, float* __restrict__ bbox_pred,
+                                                         float* __restrict__ cls, float* __restrict__ prune_score,
+                                                         float* __restrict__ max_score) {
+  extern __shared__ float s_feat[];
+  const int row0 = blockIdx.x * HP_ROWS;
+  const int rows = min(HP_ROWS, n - row0);
+  const int ldp = feat_ld + 1;
+  const float* src = feat + (long long)row0 * feat_ld;
+  for (int t = threadIdx.x; t < rows * feat_ld; t += 256) {
+    const int r = t / feat_ld;
+    s_feat[r * ldp + (t - r * feat_ld)] = __ldg(src + t);
+  }
+  __syncthreads();
+  const float scale = scale_ptr ? __ldg(scale_ptr) : 1.f;
+  if (threadIdx.x < rows) {
+    const float* f = s_feat + threadIdx.x * ldp;
+    const int i = row0 + threadIdx.x;
+    const float ctr = f[0];
+    centerness[i] = ctr;
+    const float sc = 1.f / (1.f + expf(-ctr));
+    float mlogit = -INFINITY, mscore = -INFINITY;
+    for (int k = 0; k < n_cls; ++k) {
+      const float v = f[1 + n_reg + k];
+      mlogit = fmaxf(mlogit, v);
+      mscore = fmaxf(mscore, (1.f / (1.f + expf(-v))) * sc);
+    }
+    prune_score[i] = mlogit;
+    if (max_score) max_score[i] = mscore;
+  }
+  float* bp = bbox_pred + (long long)row0 * n_reg;
+  for (int t = threadIdx.x; t < rows * n_reg; t += 256) {
+    const int r = t / n_reg, k = t - r * n_reg;
+    const float v = s_feat[r * ldp + 1 + k];
+    bp[t] = (k < 6) ? expf(scale * v) : v;
+  }
+  float* cp = cls + (long long)row0 * n_cls;
+  for (int t = threadIdx.x; t < rows * n_cls; t += 256) {
+    const int r = t / n_cls, k = t - r * n_cls;
+    cp[t] = s_feat[r * ldp + 1 + n_reg + k];
+  }
+}
+
 // distances -> box (_bbox_pred_to_bbox :281-330).  yaw_mode: 0 none(6), 1 naive, 2 sin-cos, 3 fcaf3d (Mobius)
 __device__ __forceinline__ void decode_box(const float* __restrict__ p, const float* __restrict__ bp, int n_reg,
                                            int yaw_mode, float* __restrict__ o) {
@@ -541,8 +589,14 @@ int b2_head_post(const float* feat, long long n, int feat_ld, int n_reg, int n_c
                  float* bbox_pred, float* cls, float* prune_score, float* max_score, void* stream) {
   if (n == 0) return B2_OK;
   B2_CHECK_ARG(feat_ld >= 1 + n_reg + n_cls, "feat_ld smaller than 1 + n_reg + n_cls");
-  k_head_post<<<b2_div_up(n, 256), 256, 0, (cudaStream_t)stream>>>(feat, (int)n, feat_ld, n_reg, n_cls, scale, centerness,
-                                                                 bbox_pred, cls, prune_score, max_score);
+  const size_t smem = (size_t)HP_ROWS * (feat_ld + 1) * sizeof(float);
+  if (smem <= 48 * 1024)
+    k_head_post_tiled<<<b2_div_up(n, HP_ROWS), 256, smem, (cudaStream_t)stream>>>(feat, (int)n, feat_ld, n_reg, n_cls, scale,
+                                                                                centerness, bbox_pred, cls, prune_score,
+                                                                                max_score);
+  else
+    k_head_post<<<b2_div_up(n, 256), 256, 0, (cudaStream_t)stream>>>(feat, (int)n, feat_ld, n_reg, n_cls, scale, centerness,
+                                                                   bbox_pred, cls, prune_score, max_score);
   B2_LAUNCH_CHECK();
   return B2_OK;
 }

@@ -45,6 +45,56 @@ __global__ void __launch_bounds__(128) k_kernel_map(const B2Slot* __restrict__ t
   if (threadIdx.x == 0) tile_mask[blockIdx.x] = m;
 }
 
+// Stride-2 table (out map = in coordinates floored to 2*step) built from the INPUT side: an input voxel at u*step is the
+// offset-k neighbour of the output voxels at u*step - d_k*step that are multiples of 2*step - per axis one candidate
+// when u is even (d = 0), two when it is odd (d = -1, +1; even kernels: exactly one) - so ~3.4 probes of the OUT table
+// per input row instead of 27 probes of the input table per output row.  Every (k, o) entry has at most one writer
+// (input coordinates are unique), so the table equals k_kernel_map's bit for bit.  nbr is pre-filled with -1 and
+// tile_mask with 0 by the caller (b2_kernel_map_strided).
+template <int KS>
+__global__ void __launch_bounds__(256) k_kernel_map_strided_in(const B2Slot* __restrict__ out_table, unsigned int cap_mask,
+                                                               const int* __restrict__ in_coords, int n_in, int step,
+                                                               int* __restrict__ nbr, int ld,
+                                                               unsigned int* __restrict__ tile_mask) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_in) return;
+  const int4 c = __ldg(reinterpret_cast<const int4*>(in_coords) + i);
+  const int v[3] = {c.y, c.z, c.w};
+  int cnt[3], idx[3][2], q[3][2];
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    const bool odd = b2_floor_div(v[a], step) & 1;
+    if (KS & 1) {                 // centred: offset index = d + KS/2, d in -KS/2 .. KS/2 (KS = 3: -1, 0, 1)
+      if (!odd) {
+        cnt[a] = 1; idx[a][0] = KS / 2; q[a][0] = v[a];
+        idx[a][1] = 0; q[a][1] = 0;
+      } else {
+        cnt[a] = 2;
+        idx[a][0] = KS / 2 - 1; q[a][0] = v[a] + step;    // d = -1
+        idx[a][1] = KS / 2 + 1; q[a][1] = v[a] - step;    // d = +1
+      }
+    } else {                      // even kernels start at the voxel itself: d in 0 .. KS-1 (KS = 2: 0, 1)
+      cnt[a] = 1; idx[a][1] = 0; q[a][1] = 0;
+      idx[a][0] = odd ? 1 : 0;
+      q[a][0] = odd ? v[a] - step : v[a];
+    }
+  }
+  for (int az = 0; az < cnt[2]; ++az)
+    for (int ay = 0; ay < cnt[1]; ++ay)
+      for (int ax = 0; ax < cnt[0]; ++ax) {
+        const int x = q[0][ax], y = q[1][ay], z = q[2][az];
+        if (!b2_coord_in_range(c.x, x, y, z)) continue;
+        const int o = b2_table_find(out_table, cap_mask, b2_pack_key(c.x, x, y, z));
+        if (o < 0) continue;
+        const int k = idx[0][ax] + KS * idx[1][ay] + KS * KS * idx[2][az];
+        nbr[(long long)k * ld + o] = i;
+        // a tile's bit is set by its first writer only: ~440 rows x offsets land on every word, same-address atomics
+        // serialise in L2, a plain (L1-bypassing) read of the word does not
+        unsigned int* word = tile_mask + (o >> 7);
+        if (!((*reinterpret_cast<volatile unsigned int*>(word) >> k) & 1u)) atomicOr(word, 1u << k);
+      }
+}
+
 // Neighbour table of a CHILDREN map (rows 8*i + c, c = cx + 2*cy + 4*cz, all eight children of every parent present)
 // derived from the parent's 3^3 table without touching the hash: the neighbour of child c at offset d lies in the parent
 // at offset e = floor((c + d) / 2) and is that parent's child c' = (c + d) - 2e.
@@ -72,6 +122,76 @@ __global__ void k_kernel_map_children(const int* __restrict__ pnbr, int pld, int
   }
   nbr[(long long)k * ld + t] = out;
   if (k == 0 && (t & 127) == 0) tile_mask[t >> 7] = 0x7FFFFFFu;  // dense blocks: every offset is in use (conservative)
+}
+
+// Pruning right behind a children map (fcaf3d_neck_with_head.py:99-102): the rows that survive the prune are known from
+// the coarser level's scores before the 3^3 convolution of the up-block runs, and in eval mode that convolution is
+// followed by per-row work only, so it is enough to evaluate it at the surviving rows.  Step 1: where every row of the
+// children map ("gen" rows 8 i + c) and every backbone row goes in the pruned map (-1 = dropped), and which gen row
+// feeds each pruned row.  dst_b / dst_a are the union's row maps, mask / pos the prune mask and its exclusive scan.
+__global__ void k_prune_plan(const int* __restrict__ dst_b, int n_gen, const int* __restrict__ dst_a, int n_a,
+                             const uint8_t* __restrict__ mask, const int* __restrict__ pos, int* __restrict__ gen_to_kept,
+                             int* __restrict__ a_to_kept, int* __restrict__ kept_src) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n_gen) {
+    const int u = dst_b[t];
+    const int r = mask[u] ? pos[u] : -1;
+    gen_to_kept[t] = r;
+    if (r >= 0) kept_src[r] = t;
+  } else if (t < n_gen + n_a) {
+    const int u = dst_a[t - n_gen];
+    a_to_kept[t - n_gen] = mask[u] ? pos[u] : -1;
+  }
+}
+
+// Step 2: both 3^3 tables of the pruned rows from the PARENT's table (same index arithmetic as k_kernel_map_children):
+// nbr_up[k][r] = gen row next to pruned row r (input of the up-block convolution = all gen rows),
+// nbr_out[k][r] = the same neighbour as a pruned row, -1 if it was dropped (table of the pruned map itself).
+// One 128-row tile per CTA; exact tile masks.
+__global__ void __launch_bounds__(128) k_kernel_map_children_pruned(
+    const int* __restrict__ pnbr, int pld, const int* __restrict__ kept_src, const int* __restrict__ gen_to_kept,
+    int n_keep, int ld, int* __restrict__ nbr_up, unsigned int* __restrict__ mask_up, int* __restrict__ nbr_out,
+    unsigned int* __restrict__ mask_out) {
+  __shared__ unsigned int s_up, s_out;
+  if (threadIdx.x == 0) s_up = s_out = 0u;
+  __syncthreads();
+  const int r = blockIdx.x * 128 + threadIdx.x;
+  const int t = (r < n_keep) ? kept_src[r] : -1;
+  const int i = t >> 3, c = t & 7;
+  unsigned int bits_up = 0u, bits_out = 0u;
+#pragma unroll
+  for (int k = 0; k < 27; ++k) {
+    int g = -1, o = -1;
+    if (t >= 0) {
+      const int d[3] = {k % 3 - 1, (k / 3) % 3 - 1, k / 9 - 1};
+      int ke = 0, cnew = 0;
+#pragma unroll
+      for (int a = 0; a < 3; ++a) {
+        const int s = ((c >> a) & 1) + d[a];     // -1 .. 2
+        const int e = (s < 0) ? -1 : (s > 1 ? 1 : 0);
+        ke += (e + 1) * (a == 0 ? 1 : (a == 1 ? 3 : 9));
+        cnew += (s - 2 * e) << a;
+      }
+      const int p = __ldg(pnbr + (long long)ke * pld + i);
+      if (p >= 0) {
+        g = 8 * p + cnew;
+        o = __ldg(gen_to_kept + g);
+      }
+    }
+    nbr_up[(long long)k * ld + r] = g;
+    nbr_out[(long long)k * ld + r] = o;
+    if (__any_sync(0xffffffffu, g >= 0)) bits_up |= 1u << k;
+    if (__any_sync(0xffffffffu, o >= 0)) bits_out |= 1u << k;
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicOr(&s_up, bits_up);
+    atomicOr(&s_out, bits_out);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    mask_up[blockIdx.x] = s_up;
+    mask_out[blockIdx.x] = s_out;
+  }
 }
 
 // ---------------------------------------------------------------------------
@@ -415,6 +535,59 @@ __global__ void k_maxpool_bf16x8(const uint4* __restrict__ in, const int* __rest
   out[t] = make_uint4(r4[0], r4[1], r4[2], r4[3]);
 }
 
+// Max pool over act(x * scale[s] + shift[s]) (s = scene of the output row) without materialising the normalised rows:
+// every gathered value is normalised, activated and rounded to bf16 exactly as k_affine_act_bf16x8 would store it, then
+// the maximum is taken, so the result equals b2_affine_act followed by b2_maxpool bit for bit.
+__global__ void k_maxpool_affine_bf16x8(const uint4* __restrict__ in, const int* __restrict__ nbr, int ld, int kvol,
+                                        int n_out, int vpr, const int* __restrict__ out_coords,
+                                        const float* __restrict__ scale, const float* __restrict__ shift, int act,
+                                        uint4* __restrict__ out) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long long)n_out * vpr) return;
+  const int o = (int)(t / vpr), v = (int)(t - (long long)o * vpr);
+  const int s = out_coords ? __ldg(out_coords + 4ll * o) : 0;
+  const float* sc = scale + ((long long)s * vpr + v) * 8;
+  const float* sh = shift + ((long long)s * vpr + v) * 8;
+  float a[8], b[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    a[e] = __ldg(sc + e);
+    b[e] = __ldg(sh + e);
+  }
+  float best[8];
+  bool any = false;
+  for (int k = 0; k < kvol; ++k) {
+    const int r = nbr[(long long)k * ld + o];
+    if (r < 0) continue;
+    const uint4 u = __ldg(in + (long long)r * vpr + v);
+    const unsigned w4[4] = {u.x, u.y, u.z, u.w};
+    float f[8];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      f[2 * e] = __uint_as_float(w4[e] << 16);
+      f[2 * e + 1] = __uint_as_float(w4[e] & 0xFFFF0000u);
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) f[e] = f[e] * a[e] + b[e];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const __nv_bfloat162 h = __floats2bfloat162_rn(b2_apply_act(f[2 * e], act), b2_apply_act(f[2 * e + 1], act));
+      const unsigned w = *reinterpret_cast<const unsigned*>(&h);
+      const float lo = __uint_as_float(w << 16), hi = __uint_as_float(w & 0xFFFF0000u);
+      best[2 * e] = (!any || lo > best[2 * e]) ? lo : best[2 * e];
+      best[2 * e + 1] = (!any || hi > best[2 * e + 1]) ? hi : best[2 * e + 1];
+    }
+    any = true;
+  }
+  unsigned r4[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(any ? best[2 * e] : 0.f, any ? best[2 * e + 1] : 0.f);
+    r4[e] = *reinterpret_cast<const unsigned*>(&h);
+  }
+  out[t] = make_uint4(r4[0], r4[1], r4[2], r4[3]);
+}
+
 __global__ void k_affine_act_bf16x8(const uint4* __restrict__ x, const int* __restrict__ coords, long long n, int c,
                                     const float* __restrict__ scale, const float* __restrict__ shift,
                                     const uint4* __restrict__ residual, int act, uint4* __restrict__ y) {
@@ -569,6 +742,26 @@ int b2_kernel_map(const void* in_table, long long cap, const int* out_coords, lo
   return B2_OK;
 }
 
+int b2_kernel_map_strided(const void* out_table, long long cap, const int* in_coords, long long n_in, int ksize, int step,
+                          int* nbr, long long ld, unsigned int* tile_mask, void* stream) {
+  B2_CHECK_ARG(ld % 128 == 0, "ld must be n_out rounded up to 128");
+  B2_CHECK_ARG(ksize == 2 || ksize == 3, "kernel size %d unsupported (2, 3)", ksize);
+  B2_CHECK_ARG(step >= 1, "step must be positive");
+  if (ld == 0) return B2_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int kvol = ksize * ksize * ksize;
+  B2_CUDA(cudaMemsetAsync(nbr, 0xFF, sizeof(int) * (size_t)kvol * (size_t)ld, st));
+  B2_CUDA(cudaMemsetAsync(tile_mask, 0, sizeof(unsigned int) * (size_t)(ld / 128), st));
+  if (n_in == 0) return B2_OK;
+  const B2Slot* t = (const B2Slot*)out_table;
+  const unsigned m = (unsigned)(cap - 1);
+  const int G = (int)b2_div_up(n_in, 256);
+  if (ksize == 2) k_kernel_map_strided_in<2><<<G, 256, 0, st>>>(t, m, in_coords, (int)n_in, step, nbr, (int)ld, tile_mask);
+  else k_kernel_map_strided_in<3><<<G, 256, 0, st>>>(t, m, in_coords, (int)n_in, step, nbr, (int)ld, tile_mask);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
 // 3^3 stride-1 table of a children map (b2_map_children order) from the parent map's 3^3 stride-1 table
 int b2_kernel_map_children(const int* parent_nbr, long long parent_ld, long long n_parent, int* nbr, long long ld,
                            unsigned int* tile_mask, void* stream) {
@@ -577,6 +770,27 @@ int b2_kernel_map_children(const int* parent_nbr, long long parent_ld, long long
   dim3 grid(b2_div_up(ld, 256), 27);
   k_kernel_map_children<<<grid, 256, 0, (cudaStream_t)stream>>>(parent_nbr, (int)parent_ld, (int)n_parent, nbr, (int)ld,
                                                                tile_mask);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_prune_plan(const int* dst_b, long long n_gen, const int* dst_a, long long n_a, const uint8_t* mask, const int* pos,
+                  int* gen_to_kept, int* a_to_kept, int* kept_src, void* stream) {
+  B2_CHECK_ARG(n_gen >= 0 && n_a >= 0 && n_gen + n_a < (1ll << 31), "row counts out of range");
+  if (n_gen + n_a == 0) return B2_OK;
+  k_prune_plan<<<b2_div_up(n_gen + n_a, 256), 256, 0, (cudaStream_t)stream>>>(dst_b, (int)n_gen, dst_a, (int)n_a, mask, pos,
+                                                                             gen_to_kept, a_to_kept, kept_src);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_kernel_map_children_pruned(const int* parent_nbr, long long parent_ld, const int* kept_src, const int* gen_to_kept,
+                                  long long n_keep, long long ld, int* nbr_up, unsigned int* mask_up, int* nbr_out,
+                                  unsigned int* mask_out, void* stream) {
+  B2_CHECK_ARG(ld % 128 == 0 && ld >= n_keep, "ld must be n_keep rounded up to 128");
+  if (ld == 0) return B2_OK;
+  k_kernel_map_children_pruned<<<(int)(ld / 128), 128, 0, (cudaStream_t)stream>>>(
+      parent_nbr, (int)parent_ld, kept_src, gen_to_kept, (int)n_keep, (int)ld, nbr_up, mask_up, nbr_out, mask_out);
   B2_LAUNCH_CHECK();
   return B2_OK;
 }
@@ -629,6 +843,17 @@ int b2_maxpool(const void* in, int dtype, const int* nbr, long long ld, int kvol
   else
     k_maxpool<__nv_bfloat16><<<G, 256, 0, st>>>((const __nv_bfloat16*)in, nbr, (int)ld, kvol, (int)n_out, c,
                                                 (__nv_bfloat16*)out, argmax);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+int b2_maxpool_affine(const void* in, const int* nbr, long long ld, int kvol, long long n_out, int c, const int* out_coords,
+                      const float* scale, const float* shift, int act, void* out, void* stream) {
+  B2_CHECK_ARG(c % 8 == 0, "channel count must be a multiple of 8");
+  B2_CHECK_ARG(scale != nullptr && shift != nullptr, "scale and shift are required");
+  if (n_out == 0) return B2_OK;
+  k_maxpool_affine_bf16x8<<<b2_div_up(n_out * (c / 8), 256), 256, 0, (cudaStream_t)stream>>>(
+      (const uint4*)in, nbr, (int)ld, kvol, (int)n_out, c / 8, out_coords, scale, shift, act, (uint4*)out);
   B2_LAUNCH_CHECK();
   return B2_OK;
 }

@@ -11,6 +11,7 @@ Two execution modes over the same modules and weights:
                             fused head, batched top-k / decode / NMS with one host sync at the end.
 """
 import math
+import os
 
 import torch
 import torch.nn as nn
@@ -167,12 +168,17 @@ class MEResNet3D(nn.Module):
         f = ops.sparse_conv(x.F.contiguous(), conv._w3(), km, cm.size(key), out_dtype=dt)
         m = cm.get_map(key)
         scale, shift = inorm.scale_shift(f, m)
-        f = ops.affine_act(f, scale, shift, coords=m.coords, act=ops.ACT_RELU, out=f)
         pkey = cm.stride(key, pool.stride)
         first = getattr(self, "layer1")[0]
         if isinstance(first, BasicBlock):
             cm.stride_prefetch(pkey, first.conv1.stride)
-        f = ops.maxpool(f, cm.kernel_map(key, pkey, pool.kernel_size, pool.dilation))
+        pkm = cm.kernel_map(key, pkey, pool.kernel_size, pool.dilation)
+        if f.dtype == torch.bfloat16 and f.shape[1] % 8 == 0:
+            # InstanceNorm + ReLU applied to the rows as the pooling gathers them (same bf16 values, one pass less)
+            f = ops.maxpool_affine(f, pkm, cm.get_map(pkey).coords, scale, shift, ops.ACT_RELU)
+        else:
+            f = ops.affine_act(f, scale, shift, coords=m.coords, act=ops.ACT_RELU, out=f)
+            f = ops.maxpool(f, pkm)
         key = pkey
         outs = []
         for i in range(self.n_outs):
@@ -236,6 +242,11 @@ def _fused_block(block, f, key, cm):
 
 
 # =============================================================================================== neck + head
+# forward_fused, eval: evaluate the up-block's 3^3 convolution at the rows that survive the prune only (B2_PRUNE_FIRST=0
+# restores convolve-everything-then-prune for A/B runs; both give the same rows, tests/test_surface_gpu.py)
+PRUNE_BEFORE_CONV = os.environ.get("B2_PRUNE_FIRST", "1") != "0"
+
+
 class Fcaf3DNeckWithHead(nn.Module):
     def __init__(self, n_classes, in_channels, out_channels, n_reg_outs, voxel_size, pts_threshold, assigner=None,
                  yaw_parametrization="fcaf3d", loss_centerness=None, loss_bbox=None, loss_cls=None, train_cfg=None,
@@ -570,26 +581,44 @@ class Fcaf3DNeckWithHead(nn.Module):
                 else:
                     s, b = bn1.scale_shift(None)
                     g = gen.generate(f, scale=s.reshape(-1), shift=b.reshape(-1), act=ops.ACT_ELU)
-                km = cm.kernel_map(gkey, gkey, conv.kernel_size, conv.dilation)
-                g = conv_bn_act(conv, bn2, g, km, cm.size(gkey), ops.ACT_ELU)
                 # inputs[i] + x  (union of the backbone map and the generated map)
                 ukey, dst_a, dst_b = cm.union(inputs[i].coordinate_map_key, gkey)
                 nu = cm.size(ukey)
-                f = torch.zeros((nu, g.shape[1]), dtype=g.dtype, device=g.device)
-                ops.scatter_rows(inputs[i].F.contiguous(), dst_a, f, accumulate=False)
-                ops.scatter_rows(g, dst_b, f, accumulate=True)
-                key = ukey
-                # prune by the coarser level's interpolated max-class score
-                um = cm.get_map(key)
-                if self.pts_threshold >= 0 and max(um.off_host[b + 1] - um.off_host[b]
-                                                   for b in range(um.num_batches)) > self.pts_threshold:
+                um = cm.get_map(ukey)
+                need_prune = self.pts_threshold >= 0 and max(um.off_host[b + 1] - um.off_host[b]
+                                                             for b in range(um.num_batches)) > self.pts_threshold
+                if need_prune:
+                    # prune by the coarser level's interpolated max-class score: the mask depends on the coordinates and
+                    # on the previous level only, so it is ready before the up-block's 3^3 convolution runs
                     pm = cm.get_map(prev["key"])
                     table, cap = pm.ensure_table()
                     sc = ops.interp(table, cap, prev["prune"], pm.ts, um.coords.float())
                     mask = ops.topk_mask(sc.reshape(-1), um.off_dev, um.num_batches, self.pts_threshold)
                     keep = [min(um.off_host[b + 1] - um.off_host[b], self.pts_threshold) for b in range(um.num_batches)]
-                    key, m8, pos, n_keep = cm.prune(key, mask, keep_counts=keep)   # top-k keeps exactly min(N_b, k) rows
-                    f = ops.gather_rows(f, m8, pos, n_keep)
+                    key, m8, pos, n_keep = cm.prune(ukey, mask, keep_counts=keep)   # top-k keeps exactly min(N_b, k) rows
+                if (need_prune and PRUNE_BEFORE_CONV and not bn2.bn.training and nu == cm.size(gkey)
+                        and int(conv.kernel_size) == 3 and int(conv.dilation) == 1):
+                    # Eval: behind the convolution there is per-row work only (folded BatchNorm, ELU, + backbone row), so
+                    # it is evaluated at the surviving rows alone; its table and the pruned map's own 3^3 table (the
+                    # out_block's) both come from the parent's table by index arithmetic - no children-wide table, no
+                    # hash of the pruned map.  Same values on the surviving rows as convolving everything and pruning.
+                    self.prune_first_levels = getattr(self, "prune_first_levels", 0) + 1     # (tests look at this)
+                    g2k, a2k, ksrc = ops.prune_plan(dst_b, dst_a, m8, pos, n_keep)
+                    parent = cm.get_map(gkey).children_of
+                    km_up, km_out = ops.kernel_map_children_pruned(cm.kernel_map(parent, parent, 3, 1), ksrc, g2k, n_keep)
+                    cm.set_kernel_map(key, key, 3, 1, km_out)
+                    f = conv_bn_act(conv, bn2, g, km_up, n_keep, ops.ACT_ELU)
+                    ops.scatter_rows(inputs[i].F.contiguous(), a2k, f, accumulate=True)
+                else:
+                    km = cm.kernel_map(gkey, gkey, conv.kernel_size, conv.dilation)
+                    g = conv_bn_act(conv, bn2, g, km, cm.size(gkey), ops.ACT_ELU)
+                    f = torch.zeros((nu, g.shape[1]), dtype=g.dtype, device=g.device)
+                    ops.scatter_rows(inputs[i].F.contiguous(), dst_a, f, accumulate=False)
+                    ops.scatter_rows(g, dst_b, f, accumulate=True)
+                    if need_prune:
+                        f = ops.gather_rows(f, m8, pos, n_keep)
+                    else:
+                        key = ukey
             if i > 0:
                 # the next (finer) level's generated map and its union with the backbone map depend on coordinates only:
                 # enqueue them before this level's out_block / heads so that the union's row count is not waited for idle

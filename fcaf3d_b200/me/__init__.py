@@ -6,6 +6,7 @@ detectors/single_stage_sparse.py) import it unchanged.  Surface and semantics fo
 as used by those files; only CUDA tensors are accepted (no CPU backend).
 """
 import math
+import os
 
 import torch
 import torch.nn as nn
@@ -50,6 +51,10 @@ class CoordinateMapKey:
 
     def __repr__(self):
         return "coordinate map key:%s%s" % (list(self._ts), (":" + self._id) if self._id else "")
+
+
+# stride-2 kernel maps from the input side (ops.kernel_map_strided); B2_KMAP_STRIDED=0 = hash probes per output row
+STRIDED_FROM_INPUT = os.environ.get("B2_KMAP_STRIDED", "1") != "0"
 
 
 class _Map:
@@ -252,11 +257,24 @@ class CoordinateManager:
                 # map of ALL children of `parent` (generative transpose): derive the table from the parent's, no hash
                 pkm = self.kernel_map(parent, parent, 3, 1)
                 km = ops.kernel_map_children(pkm, self._maps[parent].n)
+            elif (STRIDED_FROM_INPUT and in_key != out_key and dst.ts == 2 * src.ts and int(kernel_size) in (2, 3)
+                  and int(dilation) == 1):
+                # stride 2: a few probes of the OUT table per input row instead of kvol probes per output row
+                table, cap = dst.ensure_table()
+                km = ops.kernel_map_strided(table, cap, src.coords, dst.n, int(kernel_size), src.ts)
             else:
                 table, cap = src.ensure_table()
                 km = ops.kernel_map(table, cap, dst.coords, int(kernel_size), src.ts * int(dilation))
             self._kmaps[ck] = km
         return km
+
+
+def _set_kernel_map(self, in_key, out_key, kernel_size, dilation, km):
+    """Registers a neighbour table a caller derived by other means (e.g. ops.kernel_map_children_pruned)."""
+    self._kmaps[(in_key, out_key, int(kernel_size), int(dilation))] = km
+
+
+CoordinateManager.set_kernel_map = _set_kernel_map
 
 
 def _kernel_map_transposed(self, in_key, out_key, kernel_size, dilation=1):

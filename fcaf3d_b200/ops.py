@@ -290,6 +290,23 @@ def kernel_map(in_table, in_cap, out_coords, ksize, step):
     return KernelMap(nbr, ld, tile_mask, n_out, kvol)
 
 
+def kernel_map_strided(out_table, out_cap, in_coords, n_out, ksize, step):
+    """Table of a stride-2 convolution / pooling built from the input rows (probes of the OUT map's hash table)."""
+    n_in = int(in_coords.shape[0])
+    dev = in_coords.device
+    n_out = int(n_out)
+    ld = (n_out + 127) // 128 * 128
+    kvol = ksize ** 3
+    nbr = torch.empty((kvol, ld), dtype=I32, device=dev)
+    tile_mask = torch.empty((max(ld // 128, 1),), dtype=I32, device=dev)
+    t0 = _prof_start()
+    call("b2_kernel_map_strided", ptr(out_table), out_cap, ptr(in_coords), n_in, int(ksize), int(step), ptr(nbr), ld,
+         ptr(tile_mask))
+    probes = 3.375 if ksize == 3 else 1.0
+    _prof_stop(t0, "kernel_map", 0.0, 16.0 * n_in + (20.0 + 4.0) * probes * n_in + 4.0 * kvol * ld)
+    return KernelMap(nbr, ld, tile_mask, n_out, kvol)
+
+
 def kernel_map_children(parent_km, n_parent):
     """3^3 table of the map of all children (rows 8 i + c) from the parent's 3^3 table, without hash probes."""
     dev = parent_km.nbr.device
@@ -301,6 +318,34 @@ def kernel_map_children(parent_km, n_parent):
     call("b2_kernel_map_children", ptr(parent_km.nbr), parent_km.ld, int(n_parent), ptr(nbr), ld, ptr(tile_mask))
     _prof_stop(t0, "kernel_map_children", 0.0, 4.0 * 27 * (n_parent + n_out))
     return KernelMap(nbr, ld, tile_mask, n_out, 27)
+
+
+def prune_plan(dst_b, dst_a, mask, pos, n_keep):
+    """Row maps of a prune that directly follows a children map + union: (children row -> pruned row or -1,
+    backbone row -> pruned row or -1, pruned row -> children row)."""
+    dev = dst_b.device
+    gen_to_kept = torch.empty((dst_b.shape[0],), dtype=I32, device=dev)
+    a_to_kept = torch.empty((dst_a.shape[0],), dtype=I32, device=dev)
+    kept_src = torch.empty((max(int(n_keep), 1),), dtype=I32, device=dev)
+    call("b2_prune_plan", ptr(dst_b), dst_b.shape[0], ptr(dst_a), dst_a.shape[0], ptr(mask), ptr(pos), ptr(gen_to_kept),
+         ptr(a_to_kept), ptr(kept_src))
+    return gen_to_kept, a_to_kept, kept_src
+
+
+def kernel_map_children_pruned(parent_km, kept_src, gen_to_kept, n_keep):
+    """(table from the pruned rows into all children rows, 3^3 table of the pruned map) from the parent's 3^3 table."""
+    dev = parent_km.nbr.device
+    n_keep = int(n_keep)
+    ld = (n_keep + 127) // 128 * 128
+    nbr_up = torch.empty((27, ld), dtype=I32, device=dev)
+    nbr_out = torch.empty((27, ld), dtype=I32, device=dev)
+    mask_up = torch.empty((max(ld // 128, 1),), dtype=I32, device=dev)
+    mask_out = torch.empty((max(ld // 128, 1),), dtype=I32, device=dev)
+    t0 = _prof_start()
+    call("b2_kernel_map_children_pruned", ptr(parent_km.nbr), parent_km.ld, ptr(kept_src), ptr(gen_to_kept), n_keep, ld,
+         ptr(nbr_up), ptr(mask_up), ptr(nbr_out), ptr(mask_out))
+    _prof_stop(t0, "kernel_map_children", 0.0, 4.0 * n_keep * (1 + 27 + 27 + 2 * 27))
+    return KernelMap(nbr_up, ld, mask_up, n_keep, 27), KernelMap(nbr_out, ld, mask_out, n_keep, 27)
 
 
 _TC_ENABLED = True
@@ -392,6 +437,16 @@ def maxpool(x, kmap, want_argmax=False):
     call("b2_maxpool", ptr(x), DT[x.dtype], ptr(kmap.nbr), kmap.ld, kmap.kvol, kmap.n_out, x.shape[1], ptr(out),
          ptr(arg))
     return (out, arg) if want_argmax else out
+
+
+def maxpool_affine(x, kmap, out_coords, scale, shift, act):
+    """maxpool(affine_act(x, scale, shift, act)) in one pass (bf16 rows, per-scene scale / shift [B, C])."""
+    if x.dtype != torch.bfloat16 or x.shape[1] % 8:
+        raise B2Error("maxpool_affine: bf16 rows with a multiple of 8 channels")
+    out = torch.empty((kmap.n_out, x.shape[1]), dtype=x.dtype, device=x.device)
+    call("b2_maxpool_affine", ptr(x), ptr(kmap.nbr), kmap.ld, kmap.kvol, kmap.n_out, x.shape[1], ptr(out_coords),
+         ptr(scale), ptr(shift), int(act), ptr(out))
+    return out
 
 
 def segment_stats(x, seg_off, nseg):

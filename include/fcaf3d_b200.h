@@ -75,6 +75,7 @@ int b2_gather_coords(const int* coords, const uint8_t* mask, const int* pos, lon
 int b2_gather_rows(const void* in, const uint8_t* mask, const int* pos, long long n, int row_bytes, void* out,
                    void* stream);
 int b2_index_rows(const void* in, const int* idx, long long n, int row_bytes, void* out, void* stream);
+/* out[dst[i]] = in[i] (accumulate: +=); rows with dst[i] < 0 are skipped */
 int b2_scatter_rows(const void* in, const int* dst, long long n, int c, int dtype, int accumulate, void* out,
                     void* stream);
 
@@ -85,10 +86,27 @@ int b2_scatter_rows(const void* in, const int* dst, long long n, int c, int dtyp
  * tile_mask[o/128] bit k = some row of the 128-row tile has neighbour k.  ld = n_out rounded up to 128. */
 int b2_kernel_map(const void* in_table, long long cap, const int* out_coords, long long n_out, int ksize, int step,
                   int* nbr, long long ld, unsigned int* tile_mask, void* stream);
+/* The same table for a stride-2 convolution / pooling (out map = in coordinates floored to 2*step, kernel 2 or 3, offsets
+ * step apart), built from the input rows by probing the OUT map's hash table (~3.4 probes per input row for kernel 3,
+ * one for kernel 2, instead of kvol probes per output row); identical table and tile masks.  ld = n_out rounded to 128. */
+int b2_kernel_map_strided(const void* out_table, long long cap, const int* in_coords, long long n_in, int ksize, int step,
+                          int* nbr, long long ld, unsigned int* tile_mask, void* stream);
 /* 3^3 stride-1 table of a children map (rows 8*i + c as made by b2_map_children, all children present) derived from
  * the parent map's 3^3 stride-1 table by index arithmetic, no hash probes; tile_mask is set to "all offsets" */
 int b2_kernel_map_children(const int* parent_nbr, long long parent_ld, long long n_parent, int* nbr, long long ld,
                            unsigned int* tile_mask, void* stream);
+/* Prune directly behind a children map (fcaf3d_neck_with_head.py:99-102, eval mode): the up-block's 3^3 convolution is
+ * evaluated at the rows that survive the prune only.  b2_prune_plan: for the union's row maps dst_b (children row ->
+ * union row, n_gen rows) and dst_a (backbone row -> union row, n_a rows), the prune mask and its exclusive scan pos:
+ * gen_to_kept / a_to_kept = row in the pruned map or -1, kept_src[pruned row] = children row (every pruned row must be
+ * a children row, i.e. union size == n_gen).  b2_kernel_map_children_pruned: from the parent's 3^3 table, nbr_up =
+ * table from pruned rows into ALL children rows (the convolution's map), nbr_out = 3^3 table of the pruned map itself
+ * (what b2_kernel_map gives on its coordinates), with exact tile masks; ld = n_keep rounded up to 128. */
+int b2_prune_plan(const int* dst_b, long long n_gen, const int* dst_a, long long n_a, const uint8_t* mask, const int* pos,
+                  int* gen_to_kept, int* a_to_kept, int* kept_src, void* stream);
+int b2_kernel_map_children_pruned(const int* parent_nbr, long long parent_ld, const int* kept_src, const int* gen_to_kept,
+                                  long long n_keep, long long ld, int* nbr_up, unsigned int* mask_up, int* nbr_out,
+                                  unsigned int* mask_out, void* stream);
 /* CUDA-core implicit GEMM (fp32 accumulate):
  *   out[o,:] = act((sum_k in[nbr[k][o],:] @ w[k] + bias) * scale + shift + residual[o,:]);  w: [kvol, cin, cout] fp32.
  * nbr == NULL: identity map (kvol == 1).  ch_mod > 0: epilogue channel = column % ch_mod. */
@@ -117,6 +135,10 @@ int b2_kmap_sort(const int* nbr, long long ld, long long n_out, int kvol, int* p
  *      me_resnet.py:22-24,63; fcaf3d_neck_with_head.py:53-54,67-71) ------------------------------ */
 int b2_maxpool(const void* in, int dtype, const int* nbr, long long ld, int kvol, long long n_out, int c, void* out,
                int* argmax, void* stream);
+/* b2_affine_act (per-scene scale / shift [B, c], scene = out_coords[o][0], or scene 0 when NULL) followed by b2_maxpool
+ * in one pass over bf16 rows (c % 8 == 0): the stem's InstanceNorm + ReLU + pooling, me_resnet.py:22-24 */
+int b2_maxpool_affine(const void* in, const int* nbr, long long ld, int kvol, long long n_out, int c, const int* out_coords,
+                      const float* scale, const float* shift, int act, void* out, void* stream);
 size_t b2_segment_stats_ws_bytes(int nseg, int c);
 /* per-segment (contiguous row ranges) channel mean and biased variance, two-pass, deterministic */
 int b2_segment_stats(const void* x, int dtype, const int* seg_off, int nseg, int c, float* mean, float* var, void* ws,

@@ -193,6 +193,24 @@ def test_pool_norms_activations(dev):
         assert torch.equal(ME.MinkowskiReLU()(x).F.cpu(), torch.relu(o.F))
 
 
+def test_maxpool_with_normalisation_applied_on_the_fly(dev):
+    """b2_maxpool_affine (the stem's InstanceNorm + ReLU folded into the pooling gather) against b2_affine_act followed
+    by b2_maxpool on bf16 rows: bit-identical."""
+    x, _ = _tensors(dev, 64, batch=3)
+    cm, key = x.coordinate_manager, x.coordinate_map_key
+    pkey = cm.stride(key, 2)
+    km = cm.kernel_map(key, pkey, 2)
+    m = cm.get_map(key)
+    f = (x.F * 3).to(torch.bfloat16)
+    g = torch.Generator().manual_seed(4)
+    scale = torch.randn(3, 64, generator=g).to(dev)                 # negative scales included: the max moves rows
+    shift = torch.randn(3, 64, generator=g).to(dev)
+    for act in (ops.ACT_RELU, ops.ACT_NONE, ops.ACT_ELU):
+        want = ops.maxpool(ops.affine_act(f, scale, shift, coords=m.coords, act=act), km)
+        got = ops.maxpool_affine(f, km, cm.get_map(pkey).coords, scale, shift, act)
+        assert torch.equal(got, want), act
+
+
 def test_basic_block_and_union_add(dev):
     from fcaf3d_b200.me.modules.resnet_block import BasicBlock
     x, o = _tensors(dev, 16)

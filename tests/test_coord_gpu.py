@@ -115,6 +115,26 @@ def test_kernel_map_bit_exact(dev, ksize, stride):
         assert torch.equal(km.nbr[13, :n_out].cpu(), torch.arange(n_out, dtype=torch.int32))  # centre = identity
 
 
+@pytest.mark.parametrize("ksize", [2, 3])
+def test_strided_kernel_map_from_the_input_side_equals_hashed(dev, ksize):
+    """Stride-2 tables built from the input rows (probes of the OUT table) against the per-output-row hash probes:
+    same table, same tile masks, at tensor strides 1 -> 2 and 2 -> 4, negative coordinates included."""
+    from util import random_coords
+    c = np.concatenate([surface_coords(3000, batch=2, seed=7), random_coords(2000, batch=3, extent=30, seed=9)[4000:]])
+    x, _ = _pair(c, dev)
+    cm = x.coordinate_manager
+    k1 = x.coordinate_map_key
+    k2 = cm.stride(k1, 2)
+    k4 = cm.stride(k2, 2)
+    for ik, ok_ in ((k1, k2), (k2, k4)):
+        km = cm.kernel_map(ik, ok_, ksize)                          # input-driven path
+        src, dst = cm.get_map(ik), cm.get_map(ok_)
+        table, cap = src.ensure_table()
+        hashed = ops.kernel_map(table, cap, dst.coords, ksize, src.ts)
+        assert torch.equal(km.nbr, hashed.nbr) and torch.equal(km.tile_mask, hashed.tile_mask)
+        assert int((km.nbr >= 0).sum()) >= src.n                    # every input row feeds at least its own parent
+
+
 def test_children_kernel_map_derived_equals_hashed(dev):
     """3^3 table of a generated (all-children) map: the table derived from the parent's table must equal the
     hash-probed one and the oracle's; the derived tile mask is conservative (all 27 offsets)."""

@@ -142,3 +142,57 @@ def test_mefpn3d_matches_reference_golden(dev):
         want = torch.from_numpy(g["grad/" + key])
         err = ((flat[::step].cpu() - want).abs().max() / want.abs().max().clamp(min=1e-12)).item()
         assert err < 1e-2, (key, err)
+
+
+@pytest.mark.parametrize("dtype,thr", [(torch.float32, 4000), (torch.bfloat16, 4000), (torch.float32, 700)])
+def test_prune_before_up_block_convolution_gives_the_same_rows(dev, dtype, thr):
+    """forward_fused, eval: the up-block's 3^3 convolution evaluated at the surviving rows only (tables derived from the
+    parent's) against convolve-everything-then-prune: same coordinates, bit-identical head outputs; the derived table of
+    the pruned map equals the hash-built one; and the op-by-op reference-style path agrees within the fp32 tolerance.
+    thr = 4000: only the finest level prunes (the shape of the real workloads); thr = 700: the ts16 level prunes too, after
+    which backbone rows whose parents were dropped reach the union and the finest level takes the general path."""
+    from fcaf3d_b200 import detector as D
+    from fcaf3d_b200 import ops
+    det = deterministic_init(build_fcaf3d("scannet", pts_threshold=thr), 0, cls_bias=0.0).to(dev).eval()
+    assert det.neck_with_head.pts_threshold == thr
+    pts = [torch.from_numpy(make_scene("tiny", s, 3000)[0]).to(dev) for s in (1, 2, 3)]
+    ME.set_compute_dtype(dtype)
+    outs = {}
+    try:
+        for flag in (True, False):
+            D.PRUNE_BEFORE_CONV = flag
+            with torch.no_grad():
+                levels, cm = det.forward_features_fused(pts)
+            outs[flag] = (levels, cm)
+        with torch.no_grad():
+            ref = det.extract_feat(pts) if dtype == torch.float32 else None
+    finally:
+        D.PRUNE_BEFORE_CONV = True
+        ME.set_compute_dtype(torch.float32)
+    (la, cma), (lb, cmb) = outs[True], outs[False]
+    pruned_levels = 0
+    for a, b in zip(la, lb):
+        ma, mb = cma.get_map(a["key"]), cmb.get_map(b["key"])
+        assert torch.equal(ma.coords, mb.coords) and ma.off_host == mb.off_host
+        for name in ("centerness", "bbox_pred", "cls", "prune"):
+            assert torch.equal(a[name], b[name]), name
+        ka = cma._kmaps.get((a["key"], a["key"], 3, 1))
+        kb = cmb._kmaps.get((b["key"], b["key"], 3, 1))
+        assert torch.equal(ka.nbr[:, :ka.n_out], kb.nbr[:, :kb.n_out])
+        assert torch.equal(ka.tile_mask, kb.tile_mask)
+        if max(ma.off_host[i + 1] - ma.off_host[i] for i in range(3)) == thr:
+            pruned_levels += 1
+            table, cap = ma.ensure_table()
+            hashed = ops.kernel_map(table, cap, ma.coords, 3, ma.ts)
+            assert torch.equal(hashed.nbr[:, :ka.n_out], ka.nbr[:, :ka.n_out])
+            assert torch.equal(hashed.tile_mask, ka.tile_mask)
+    assert pruned_levels >= 1 and det.neck_with_head.prune_first_levels >= 1
+    if ref is not None:
+        centernesses, bbox_preds, cls_scores, points = [list(x) for x in ref]
+        for lvl, a in enumerate(la):
+            m = cma.get_map(a["key"])
+            for b in range(3):
+                sl = slice(m.off_host[b], m.off_host[b + 1])
+                assert torch.equal(torch.round(points[lvl][b] / det.voxel_size).int(), m.coords[sl, 1:])
+                want = cls_scores[lvl][b]
+                assert ((a["cls"][sl] - want).abs().max() / want.abs().max().clamp(min=1e-6)).item() < 2e-3
