@@ -324,7 +324,17 @@ extern "C" int b2_conv_tc(const void* in_bf16, long long n_in, const void* wt_bf
   // is used only when it still yields at least half an SM wave of CTAs.  B2_TC_BN256=0 / 1 forces it off / on.
   static const int bn256_env = getenv("B2_TC_BN256") ? atoi(getenv("B2_TC_BN256")) : -1;
   const long long cta256 = (long long)b2_div_up(n_out, TC_BM) * (cout / 256);
-  if (cout % 256 == 0 && bn256_env != 0 && (bn256_env == 1 || cta256 >= 74)) {
+  // dense GEMMs (identity map: generative transposes, heads) have a main loop of cin / 64 stages only and are bound by
+  // the epilogue, which two resident CTAs per SM overlap better than one: 128-column tiles by default (generative
+  // transposes of one step 249 -> 193 us against 256-column tiles; 64 columns are no better).  B2_TC_DENSE_BN = 64 /
+  // 128 / 256 picks the tile width for A/B runs.
+  static const int dense_bn = getenv("B2_TC_DENSE_BN") ? atoi(getenv("B2_TC_DENSE_BN")) : 128;
+  const bool dense = (nbr == nullptr);
+  if (dense && dense_bn == 64 && out_dtype == 1 && cout % 64 == 0)
+    return launch_tc<64, 4, __nv_bfloat16>(in_bf16, wt_bf16, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias,
+                                           scale, shift, residual, act, ch_mod, out, st);
+  const bool no256 = dense && (dense_bn == 64 || dense_bn == 128);
+  if (cout % 256 == 0 && bn256_env != 0 && !no256 && (bn256_env == 1 || cta256 >= 74)) {
     if (out_dtype == 1)
       return launch_tc<256, 3, __nv_bfloat16>(in_bf16, wt_bf16, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias,
                                               scale, shift, residual, act, ch_mod, out, st);

@@ -541,38 +541,51 @@ __global__ void __launch_bounds__(NT) k_nms_greedy(const float* __restrict__ box
     const int nk = s_nk;
     kept += nk;
     if (t < rows) keep[beg + blk * NMS_TILE + t] = (uint8_t)(((~s_remv[blk]) >> t) & 1ull);
-    // (3) rows of the boxes kept in this block against every later column
+    // (3) rows of the boxes kept in this block against every later column.  A thread owns columns (col0 + t, + NT, ...):
+    // the column's box is loaded once per block, the kept rows come from shared memory (broadcast), and the walk over
+    // the kept rows stops at the first one that suppresses the column - further bits cannot change the outcome.
     const int col0 = (blk + 1) * NMS_TILE;
-    const int rem = n - col0;
-    if (rem > 0 && nk > 0) {
-      const long long total = (long long)nk * rem;
-      for (long long e = t; e < total; e += blockDim.x) {
-        const int a = s_klist[(int)(e / rem)];
-        const int j = col0 + (int)(e % rem);
-        if ((s_remv[j >> 6] >> (j & 63)) & 1ull) continue;  // already suppressed: the bit cannot change the outcome
-        float iou;
+    if (nk > 0) {
+      for (int j = col0 + t; j < n; j += NT) {
+        if ((s_remv[j >> 6] >> (j & 63)) & 1ull) continue;  // suppressed by an earlier block
+        bool sup = false;
         if (ROTATED) {
-          const BoxPrep& A = s_row[a];
-          const BoxPrep B = prep[beg + j];
-          const float ddx = A.cx - B.cx, ddy = A.cy - B.cy;
-          const float reach = A.rad + B.rad + 0.05f;
-          if (thresh >= 0.f && ddx * ddx + ddy * ddy > reach * reach) continue;
-          iou = iou_rotated(A, B);
+          BoxPrep B = prep[beg + j];
+#pragma unroll 1
+          for (int ai = 0; ai < nk; ++ai) {
+            // B stays in registers across the walk, but the compiler must not hoist B-only sub-expressions out of the
+            // loop: that would change how the pair arithmetic is contracted into FMAs (tools/check_nms_codegen.py)
+            asm volatile("" : "+f"(B.cx), "+f"(B.cy), "+f"(B.dx), "+f"(B.dy), "+f"(B.cosm), "+f"(B.sinm), "+f"(B.c[0].x),
+                         "+f"(B.c[0].y), "+f"(B.c[1].x), "+f"(B.c[1].y), "+f"(B.c[2].x), "+f"(B.c[2].y), "+f"(B.c[3].x),
+                         "+f"(B.c[3].y), "+f"(B.rad));
+            const BoxPrep& A = s_row[s_klist[ai]];
+            const float ddx = A.cx - B.cx, ddy = A.cy - B.cy;
+            const float reach = A.rad + B.rad + 0.05f;
+            if (thresh >= 0.f && ddx * ddx + ddy * ddy > reach * reach) continue;
+            if (iou_rotated(A, B) > thresh) {
+              sup = true;
+              break;
+            }
+          }
         } else {
           const float* b = boxes + (long long)(beg + j) * 7;
-          const float4 ae = s_rowedge[a];
-          const float2 as = s_rowsize[a];
-          const float4 be = make_float4(b[0] - b[3] / 2, b[0] + b[3] / 2, b[1] - b[4] / 2, b[1] + b[4] / 2);
-          const float left = fmaxf(ae.x, be.x), right = fminf(ae.y, be.y);
-          const float top = fmaxf(ae.z, be.z), bottom = fminf(ae.w, be.w);
-          const float width = fmaxf(right - left, 0.f), height = fmaxf(bottom - top, 0.f);
-          if (thresh >= 0.f && !(width > 0.f && height > 0.f)) continue;
-          const float inter = width * height;
-          const float Sa = as.x * as.y;
-          const float Sb = b[3] * b[4];
-          iou = inter / fmaxf(Sa + Sb - inter, NMS_EPS);
+          const float b3 = b[3], b4 = b[4];
+          const float4 be = make_float4(b[0] - b3 / 2, b[0] + b3 / 2, b[1] - b4 / 2, b[1] + b4 / 2);
+          const float Sb = b3 * b4;
+          for (int ai = 0; ai < nk && !sup; ++ai) {
+            const int a = s_klist[ai];
+            const float4 ae = s_rowedge[a];
+            const float left = fmaxf(ae.x, be.x), right = fminf(ae.y, be.y);
+            const float top = fmaxf(ae.z, be.z), bottom = fminf(ae.w, be.w);
+            const float width = fmaxf(right - left, 0.f), height = fmaxf(bottom - top, 0.f);
+            if (thresh >= 0.f && !(width > 0.f && height > 0.f)) continue;
+            const float2 as = s_rowsize[a];
+            const float inter = width * height;
+            const float Sa = as.x * as.y;
+            sup = inter / fmaxf(Sa + Sb - inter, NMS_EPS) > thresh;
+          }
         }
-        if (iou > thresh) atomicOr(&s_remv[j >> 6], 1ull << (j & 63));
+        if (sup) atomicOr(&s_remv[j >> 6], 1ull << (j & 63));
       }
     }
     __syncthreads();
@@ -696,7 +709,13 @@ int b2_nms_greedy_batched(const float* boxes, const float* scores, const int* se
     }
     k_nms_greedy<true, 512><<<nseg, 512, 0, st>>>(sb, prep, seg_off, thresh, keep, counts);
   } else {
-    k_nms_greedy<false, 256><<<nseg, 256, 0, st>>>(sb, prep, seg_off, thresh, keep, counts);
+    // threads per segment: the update phase is one independent walk per column, so a segment of thousands of boxes
+    // feeds 1024 threads (B2_NMS_NT=256 / 512 / 1024 for A/B runs)
+    static const int nt_env = getenv("B2_NMS_NT") ? atoi(getenv("B2_NMS_NT")) : 0;
+    const int nt = nt_env ? nt_env : (max_seg > 1024 ? 1024 : (max_seg > 256 ? 512 : 256));
+    if (nt >= 1024) k_nms_greedy<false, 1024><<<nseg, 1024, 0, st>>>(sb, prep, seg_off, thresh, keep, counts);
+    else if (nt >= 512) k_nms_greedy<false, 512><<<nseg, 512, 0, st>>>(sb, prep, seg_off, thresh, keep, counts);
+    else k_nms_greedy<false, 256><<<nseg, 256, 0, st>>>(sb, prep, seg_off, thresh, keep, counts);
   }
   B2_LAUNCH_CHECK();
   return B2_OK;

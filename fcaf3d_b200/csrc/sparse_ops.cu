@@ -556,10 +556,18 @@ __global__ void k_maxpool_affine_bf16x8(const uint4* __restrict__ in, const int*
   }
   float best[8];
   bool any = false;
-  for (int k = 0; k < kvol; ++k) {
-    const int r = nbr[(long long)k * ld + o];
-    if (r < 0) continue;
-    const uint4 u = __ldg(in + (long long)r * vpr + v);
+  // kvol <= 8 (2^3 pooling): all neighbour indices first, then all row loads, so that up to 8 loads are in flight
+  int rr[8];
+  uint4 uu[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) rr[k] = (k < kvol) ? __ldg(nbr + (long long)k * ld + o) : -1;
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    uu[k] = (rr[k] >= 0) ? __ldg(in + (long long)rr[k] * vpr + v) : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    if (rr[k] < 0) continue;
+    const uint4 u = uu[k];
     const unsigned w4[4] = {u.x, u.y, u.z, u.w};
     float f[8];
 #pragma unroll
@@ -850,6 +858,7 @@ int b2_maxpool(const void* in, int dtype, const int* nbr, long long ld, int kvol
 int b2_maxpool_affine(const void* in, const int* nbr, long long ld, int kvol, long long n_out, int c, const int* out_coords,
                       const float* scale, const float* shift, int act, void* out, void* stream) {
   B2_CHECK_ARG(c % 8 == 0, "channel count must be a multiple of 8");
+  B2_CHECK_ARG(kvol >= 1 && kvol <= 8, "kernel volume %d unsupported (1..8)", kvol);
   B2_CHECK_ARG(scale != nullptr && shift != nullptr, "scale and shift are required");
   if (n_out == 0) return B2_OK;
   k_maxpool_affine_bf16x8<<<b2_div_up(n_out * (c / 8), 256), 256, 0, (cudaStream_t)stream>>>(

@@ -53,8 +53,9 @@ class CoordinateMapKey:
         return "coordinate map key:%s%s" % (list(self._ts), (":" + self._id) if self._id else "")
 
 
-# stride-2 kernel maps from the input side (ops.kernel_map_strided); B2_KMAP_STRIDED=0 = hash probes per output row
-STRIDED_FROM_INPUT = os.environ.get("B2_KMAP_STRIDED", "1") != "0"
+# stride-2 kernel maps from the input side (ops.kernel_map_strided): 0 = never (hash probes per output row), 1 = where
+# there are few inputs per output row, 2 = always
+STRIDED_FROM_INPUT = int(os.environ.get("B2_KMAP_STRIDED", "1"))
 
 
 class _Map:
@@ -257,9 +258,12 @@ class CoordinateManager:
                 # map of ALL children of `parent` (generative transpose): derive the table from the parent's, no hash
                 pkm = self.kernel_map(parent, parent, 3, 1)
                 km = ops.kernel_map_children(pkm, self._maps[parent].n)
-            elif (STRIDED_FROM_INPUT and in_key != out_key and dst.ts == 2 * src.ts and int(kernel_size) in (2, 3)
-                  and int(dilation) == 1):
-                # stride 2: a few probes of the OUT table per input row instead of kvol probes per output row
+            elif (STRIDED_FROM_INPUT and in_key != out_key and dst.ts == 2 * src.ts and int(kernel_size) == 3
+                  and int(dilation) == 1 and (STRIDED_FROM_INPUT > 1 or 2 * src.n < 3 * dst.n)):
+                # stride 2, few inputs per output (the stem: 786 k -> 738 k rows): ~3.4 probes of the OUT table per input
+                # row instead of 27 probes per output row (188 -> 95 us).  Deeper levels (548 k -> 218 k rows) have ~8
+                # inputs per output, every 128-row tile's mask word is then hit ~3.7 k times (a hot spot in L2, atomics
+                # or plain reads alike) and the per-output kernel wins (45 vs 148 us), so those stay on it.
                 table, cap = dst.ensure_table()
                 km = ops.kernel_map_strided(table, cap, src.coords, dst.n, int(kernel_size), src.ts)
             else:

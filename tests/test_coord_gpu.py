@@ -116,10 +116,10 @@ def test_kernel_map_bit_exact(dev, ksize, stride):
 
 
 @pytest.mark.parametrize("ksize", [2, 3])
-def test_strided_kernel_map_from_the_input_side_equals_hashed(dev, ksize):
+def test_strided_kernel_map_from_the_input_side_equals_hashed(dev, ksize, monkeypatch):
     """Stride-2 tables built from the input rows (probes of the OUT table) against the per-output-row hash probes:
     same table, same tile masks, at tensor strides 1 -> 2 and 2 -> 4, negative coordinates included."""
-    from util import random_coords
+    monkeypatch.setattr(ME, "STRIDED_FROM_INPUT", 2)                  # every stride-2 map, whatever its in/out ratio
     c = np.concatenate([surface_coords(3000, batch=2, seed=7), random_coords(2000, batch=3, extent=30, seed=9)[4000:]])
     x, _ = _pair(c, dev)
     cm = x.coordinate_manager
@@ -127,8 +127,12 @@ def test_strided_kernel_map_from_the_input_side_equals_hashed(dev, ksize):
     k2 = cm.stride(k1, 2)
     k4 = cm.stride(k2, 2)
     for ik, ok_ in ((k1, k2), (k2, k4)):
-        km = cm.kernel_map(ik, ok_, ksize)                          # input-driven path
         src, dst = cm.get_map(ik), cm.get_map(ok_)
+        if ksize == 3:
+            km = cm.kernel_map(ik, ok_, ksize)                      # input-driven path
+        else:                                                       # kernel 2 (pooling) is not routed there: call it directly
+            t2, c2 = dst.ensure_table()
+            km = ops.kernel_map_strided(t2, c2, src.coords, dst.n, 2, src.ts)
         table, cap = src.ensure_table()
         hashed = ops.kernel_map(table, cap, dst.coords, ksize, src.ts)
         assert torch.equal(km.nbr, hashed.nbr) and torch.equal(km.tile_mask, hashed.tile_mask)
