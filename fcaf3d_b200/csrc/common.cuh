@@ -105,3 +105,21 @@ __device__ __forceinline__ float b2_apply_act(float v, int act) {
   if (act == B2_ACT_ELU) return v > 0.f ? v : expm1f(v);
   return v;
 }
+
+// ELU of a value that is stored as bf16 right afterwards.  expm1f costs ~40 instructions per element, which made the
+// epilogues of the neck's short-K tcgen05 layers (a 128 x 256 tile has 32 k elements for 8 warps: ~17 us per tile
+// whatever K was) and the bf16 normalisation passes arithmetic-bound.  exp(v) - 1 through ex2.approx away from zero and
+// the cubic Taylor polynomial near zero stays within 1e-5 relative of expm1f, three orders of magnitude below the bf16
+// rounding that follows.  fp32 outputs keep expm1f (b2_apply_act).
+__device__ __forceinline__ float b2_elu_bf16(float v) {
+  const float e = __expf(v) - 1.f;
+  const float p = v * (1.f + v * (0.5f + v * (1.f / 6.f)));
+  const float neg = (v > -0.03f) ? p : e;
+  return v > 0.f ? v : neg;
+}
+
+__device__ __forceinline__ float b2_apply_act_bf16(float v, int act) {
+  if (act == B2_ACT_RELU) return v > 0.f ? v : 0.f;
+  if (act == B2_ACT_ELU) return b2_elu_bf16(v);
+  return v;
+}

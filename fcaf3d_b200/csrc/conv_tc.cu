@@ -14,18 +14,6 @@
 #include "tc_common.cuh"
 #include <stdlib.h>
 
-// ELU of a value that is stored as bf16 right afterwards.  expm1f costs ~40 instructions per element, and a 128 x 256
-// tile has 32 k of them for 8 epilogue warps: on the neck's short-K layers (generative transposes, K = 2-8 stages) the
-// epilogue arithmetic, not the stores, set the CTA time (~17 us per 128 x 256 tile whatever K was).  exp(v) - 1 through
-// ex2.approx away from zero and the cubic Taylor polynomial near zero is within 1e-5 relative of expm1f, three orders of
-// magnitude below the bf16 rounding that follows.  fp32 outputs keep expm1f (b2_apply_act).
-__device__ __forceinline__ float tc_elu_bf16(float v) {
-  const float e = __expf(v) - 1.f;
-  const float p = v * (1.f + v * (0.5f + v * (1.f / 6.f)));
-  const float neg = (v > -0.03f) ? p : e;
-  return v > 0.f ? v : neg;
-}
-
 template <int BN, int ST>
 struct TcCfg {
   static constexpr int STAGES = ST;
@@ -200,7 +188,7 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __rest
           }
           if (sizeof(TOut) == 2 && act == B2_ACT_ELU) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] = tc_elu_bf16(f[j]);
+            for (int j = 0; j < 32; ++j) f[j] = b2_elu_bf16(f[j]);
           } else {
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = b2_apply_act(f[j], act);

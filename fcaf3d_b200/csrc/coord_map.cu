@@ -176,7 +176,9 @@ __global__ void k_hash_insert(const int* __restrict__ coords, int n, int quant, 
   for (;;) {
     unsigned long long old = atomicCAS(&table[h].key, B2_EMPTY_KEY, key);
     if (old == B2_EMPTY_KEY || old == key) {
-      atomicMin(&table[h].val, (unsigned int)i);  // lowest input row wins (ME CPU first-occurrence rule)
+      // lowest input row wins (ME CPU first-occurrence rule).  The input row lives in the slot's second word; the
+      // first one (what lookups return) receives the compacted row id from the winner in k_build_finalize
+      atomicMin(&table[h].pad, (unsigned int)i);
       row_slot[i] = (int)h;
       return;
     }
@@ -189,11 +191,12 @@ __global__ void k_winner_flags(const B2Slot* __restrict__ table, const int* __re
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int s = row_slot[i];
-  flags[i] = (s >= 0 && table[s].val == (unsigned int)i) ? 1 : 0;
+  flags[i] = (s >= 0 && table[s].pad == (unsigned int)i) ? 1 : 0;
 }
 
-// winners write the compacted coordinate row + unique_index; everybody records the winner row of its voxel
-__global__ void k_build_finalize(const int* __restrict__ coords, int n, int quant, const B2Slot* __restrict__ table,
+// winners write the compacted coordinate row + unique_index and turn their slot's value into the compacted row id;
+// everybody records the winner row of its voxel (read from the slot's second word, which nobody writes here)
+__global__ void k_build_finalize(const int* __restrict__ coords, int n, int quant, B2Slot* __restrict__ table,
                                  const int* __restrict__ row_slot, const uint8_t* __restrict__ flags,
                                  const int* __restrict__ pos, int* __restrict__ out_coords,
                                  int* __restrict__ unique_index, int* __restrict__ inverse_map) {
@@ -204,7 +207,7 @@ __global__ void k_build_finalize(const int* __restrict__ coords, int n, int quan
     inverse_map[i] = -1;
     return;
   }
-  const int w = (int)table[s].val;  // original row of the representative
+  const int w = (int)table[s].pad;  // original row of the representative
   inverse_map[i] = pos[w];
   if (flags[i]) {
     int4 c = load_coord(coords, i);
@@ -216,15 +219,8 @@ __global__ void k_build_finalize(const int* __restrict__ coords, int n, int quan
     const int p = pos[i];
     reinterpret_cast<int4*>(out_coords)[p] = c;
     unique_index[p] = i;
+    table[s].val = (unsigned int)p;
   }
-}
-
-// second phase: table values become compacted row ids
-__global__ void k_table_relabel(B2Slot* table, const int* __restrict__ row_slot, const uint8_t* __restrict__ flags,
-                                const int* __restrict__ pos, int n) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  if (flags[i]) table[row_slot[i]].val = (unsigned int)pos[i];
 }
 
 // plain insert of already-unique coordinates (value = row)
@@ -479,10 +475,8 @@ int b2_map_build(const int* coords, long long n, int quant, void* table, long lo
   B2_LAUNCH_CHECK();
   int rc = b2_scan_flags_launch(flags, n, pos, n_out, scan_ws, scan_bytes, st);
   if (rc) return rc;
-  k_build_finalize<<<G, T, 0, st>>>(coords, (int)n, quant, (const B2Slot*)table, row_slot, flags, pos, out_coords,
-                                    unique_index, inverse_map);
-  B2_LAUNCH_CHECK();
-  k_table_relabel<<<G, T, 0, st>>>((B2Slot*)table, row_slot, flags, pos, (int)n);
+  k_build_finalize<<<G, T, 0, st>>>(coords, (int)n, quant, (B2Slot*)table, row_slot, flags, pos, out_coords, unique_index,
+                                    inverse_map);
   B2_LAUNCH_CHECK();
   return B2_OK;
 }

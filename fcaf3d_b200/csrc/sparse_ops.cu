@@ -579,7 +579,7 @@ __global__ void k_maxpool_affine_bf16x8(const uint4* __restrict__ in, const int*
     for (int e = 0; e < 8; ++e) f[e] = f[e] * a[e] + b[e];
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
-      const __nv_bfloat162 h = __floats2bfloat162_rn(b2_apply_act(f[2 * e], act), b2_apply_act(f[2 * e + 1], act));
+      const __nv_bfloat162 h = __floats2bfloat162_rn(b2_apply_act_bf16(f[2 * e], act), b2_apply_act_bf16(f[2 * e + 1], act));
       const unsigned w = *reinterpret_cast<const unsigned*>(&h);
       const float lo = __uint_as_float(w << 16), hi = __uint_as_float(w & 0xFFFF0000u);
       best[2 * e] = (!any || lo > best[2 * e]) ? lo : best[2 * e];
@@ -631,7 +631,7 @@ __global__ void k_affine_act_bf16x8(const uint4* __restrict__ x, const int* __re
   unsigned r4[4];
 #pragma unroll
   for (int e = 0; e < 4; ++e) {
-    const __nv_bfloat162 h = __floats2bfloat162_rn(b2_apply_act(f[2 * e], act), b2_apply_act(f[2 * e + 1], act));
+    const __nv_bfloat162 h = __floats2bfloat162_rn(b2_apply_act_bf16(f[2 * e], act), b2_apply_act_bf16(f[2 * e + 1], act));
     r4[e] = *reinterpret_cast<const unsigned*>(&h);
   }
   y[t] = make_uint4(r4[0], r4[1], r4[2], r4[3]);
@@ -688,6 +688,87 @@ __global__ void k_colsum_final(const float* __restrict__ partial, const int* __r
   for (int j = 0; j < ST_CHUNKS; ++j) acc += partial[((long long)s * ST_CHUNKS + j) * c + ch];
   const int n = seg_off[s + 1] - seg_off[s];
   out[t] = n > 0 ? acc / (float)n : 0.f;
+}
+
+// InstanceNorm statistics in ONE pass over the rows (the two-pass kernels above read the largest tensor of the network
+// twice with 2-byte loads): per scene and channel, sums of (x - pivot) and (x - pivot)^2 with pivot = the scene's first
+// row (shifted sums: no cancellation for the magnitudes a convolution output has), 16-byte loads, IN_CHUNKS x nseg CTAs,
+// partials added in a fixed order (deterministic).  k_instnorm_final turns them into the folded (scale, shift) of
+// MinkowskiInstanceNorm directly: biased variance, eps inside the square root (ME App. A.6; me_resnet.py:22).
+#define IN_CHUNKS 74
+template <typename T>
+__global__ void __launch_bounds__(256) k_instnorm_partial(const T* __restrict__ x, const int* __restrict__ seg_off, int c,
+                                                          float* __restrict__ partial) {
+  constexpr int E = 16 / (int)sizeof(T);
+  __shared__ float red[256 * 2 * E];
+  const int s = blockIdx.y, chunk = blockIdx.x;
+  const int r0 = seg_off[s], r1 = seg_off[s + 1];
+  const int n = r1 - r0;
+  const int V = c / E, rows_par = 256 / V;
+  const int vl = threadIdx.x % V, rl = threadIdx.x / V;
+  const int per = (n + IN_CHUNKS - 1) / IN_CHUNKS;
+  const int a = r0 + chunk * per, b = min(a + per, r1);
+  float piv[E], s1[E], s2[E];
+#pragma unroll
+  for (int e = 0; e < E; ++e) piv[e] = s1[e] = s2[e] = 0.f;
+  if (n > 0) {
+#pragma unroll
+    for (int e = 0; e < E; ++e) piv[e] = to_f32<T>(x[(long long)r0 * c + vl * E + e]);
+  }
+  for (int r = a + rl; r < b; r += rows_par) {
+    const uint4 u = __ldg(reinterpret_cast<const uint4*>(x + (long long)r * c) + vl);
+    const T* v = reinterpret_cast<const T*>(&u);
+#pragma unroll
+    for (int e = 0; e < E; ++e) {
+      const float d = to_f32<T>(v[e]) - piv[e];
+      s1[e] += d;
+      s2[e] += d * d;
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    red[(threadIdx.x * 2) * E + e] = s1[e];
+    red[(threadIdx.x * 2 + 1) * E + e] = s2[e];
+  }
+  __syncthreads();
+  if (rl == 0) {
+    float* out = partial + ((long long)s * IN_CHUNKS + chunk) * 2 * c;
+#pragma unroll
+    for (int e = 0; e < E; ++e) {
+      float t1 = 0.f, t2 = 0.f;
+      for (int j = 0; j < rows_par; ++j) {
+        t1 += red[((j * V + vl) * 2) * E + e];
+        t2 += red[((j * V + vl) * 2 + 1) * E + e];
+      }
+      out[vl * E + e] = t1;
+      out[c + vl * E + e] = t2;
+    }
+  }
+}
+
+template <typename T>
+__global__ void k_instnorm_final(const T* __restrict__ x, const float* __restrict__ partial, const int* __restrict__ seg_off,
+                                 int c, int nseg, const float* __restrict__ weight, const float* __restrict__ bias, float eps,
+                                 float* __restrict__ scale, float* __restrict__ shift) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nseg * c) return;
+  const int s = t / c, ch = t - s * c;
+  const int r0 = seg_off[s], n = seg_off[s + 1] - r0;
+  double mean = 0.0, var = 0.0;
+  if (n > 0) {
+    double a1 = 0.0, a2 = 0.0;
+    for (int j = 0; j < IN_CHUNKS; ++j) {
+      a1 += (double)partial[((long long)s * IN_CHUNKS + j) * 2 * c + ch];
+      a2 += (double)partial[((long long)s * IN_CHUNKS + j) * 2 * c + c + ch];
+    }
+    const double m = a1 / n;
+    mean = (double)to_f32<T>(x[(long long)r0 * c + ch]) + m;
+    var = a2 / n - m * m;
+    if (var < 0.0) var = 0.0;
+  }
+  const float sc = (weight ? weight[ch] : 1.f) / sqrtf((float)var + eps);
+  scale[t] = sc;
+  shift[t] = (bias ? bias[ch] : 0.f) - (float)mean * sc;
 }
 
 // y = act(x * scale[s, c] + shift[s, c] + residual); s = batch index of the row (coords) or 0
@@ -893,6 +974,35 @@ int b2_segment_stats(const void* x, int dtype, const int* seg_off, int nseg, int
     k_colsum_final<<<GF, 256, 0, st>>>(partial, seg_off, c, nseg, var);
   }
   b2_count_launches(3);  // four kernels behind one check
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+size_t b2_instnorm_ws_bytes(int nseg, int c) { return (size_t)nseg * IN_CHUNKS * 2 * c * sizeof(float); }
+
+int b2_instnorm_scale_shift(const void* x, int dtype, const int* seg_off, int nseg, int c, const float* weight,
+                            const float* bias, float eps, float* scale, float* shift, void* ws, size_t ws_bytes,
+                            void* stream) {
+  const int E = dtype == 0 ? 4 : 8;
+  B2_CHECK_ARG(nseg > 0 && c > 0 && c % E == 0 && c / E <= 256 && 256 % (c / E) == 0,
+               "channel count %d unsupported (vectors per row must divide 256)", c);
+  if (ws_bytes < b2_instnorm_ws_bytes(nseg, c)) {
+    b2_set_error("b2_instnorm_scale_shift workspace too small");
+    return B2_ERR_WS;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  float* partial = (float*)ws;
+  dim3 grid(IN_CHUNKS, nseg);
+  const int GF = b2_div_up((long long)nseg * c, 256);
+  if (dtype == 0) {
+    k_instnorm_partial<float><<<grid, 256, 0, st>>>((const float*)x, seg_off, c, partial);
+    k_instnorm_final<float><<<GF, 256, 0, st>>>((const float*)x, partial, seg_off, c, nseg, weight, bias, eps, scale, shift);
+  } else {
+    k_instnorm_partial<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, seg_off, c, partial);
+    k_instnorm_final<__nv_bfloat16><<<GF, 256, 0, st>>>((const __nv_bfloat16*)x, partial, seg_off, c, nseg, weight, bias, eps,
+                                                       scale, shift);
+  }
+  b2_count_launches(1);
   B2_LAUNCH_CHECK();
   return B2_OK;
 }

@@ -702,6 +702,9 @@ class MinkowskiInstanceNorm(MinkowskiModuleBase):
         self.bias = nn.Parameter(torch.zeros(1, num_features))
 
     def scale_shift(self, feats, m):
+        w, b = self.weight.detach(), self.bias.detach()
+        if ops.instnorm_supported(feats) and w.dtype == torch.float32 and w.is_contiguous() and b.is_contiguous():
+            return ops.instnorm_scale_shift(feats, m.off_dev, m.num_batches, w.reshape(-1), b.reshape(-1), self.eps)
         mean, var = ops.segment_stats(feats, m.off_dev, m.num_batches)
         scale = self.weight.detach() / torch.sqrt(var + self.eps)
         shift = self.bias.detach() - mean * scale

@@ -458,6 +458,23 @@ def segment_stats(x, seg_off, nseg):
     return mean, var
 
 
+def instnorm_supported(x):
+    e = 16 // x.element_size()
+    c = int(x.shape[1])
+    return x.dtype in DT and c % e == 0 and c // e <= 256 and 256 % (c // e) == 0
+
+
+def instnorm_scale_shift(x, seg_off, nseg, weight, bias, eps):
+    """Per-scene folded InstanceNorm (scale, shift) [nseg, C] in one pass over the rows."""
+    c = int(x.shape[1])
+    scale = torch.empty((nseg, c), dtype=torch.float32, device=x.device)
+    shift = torch.empty((nseg, c), dtype=torch.float32, device=x.device)
+    ws = workspace(_lib.lib().b2_instnorm_ws_bytes(nseg, c), x.device, slot=1)
+    call("b2_instnorm_scale_shift", ptr(x), DT[x.dtype], ptr(seg_off), nseg, c, ptr(weight), ptr(bias), float(eps),
+         ptr(scale), ptr(shift), ptr(ws), ws.numel())
+    return scale, shift
+
+
 def affine_act(x, scale=None, shift=None, coords=None, residual=None, act=ACT_NONE, out=None):
     out = torch.empty_like(x) if out is None else out
     call("b2_affine_act", ptr(x), DT[x.dtype], ptr(coords), x.shape[0], x.shape[1], ptr(scale), ptr(shift),

@@ -143,6 +143,13 @@ size_t b2_segment_stats_ws_bytes(int nseg, int c);
 /* per-segment (contiguous row ranges) channel mean and biased variance, two-pass, deterministic */
 int b2_segment_stats(const void* x, int dtype, const int* seg_off, int nseg, int c, float* mean, float* var, void* ws,
                      size_t ws_bytes, void* stream);
+/* MinkowskiInstanceNorm (me_resnet.py:22) folded to per-scene (scale, shift) [nseg, c] in one pass over the rows:
+ * scale = weight / sqrt(var + eps), shift = bias - mean * scale with the per-segment biased variance (shifted sums,
+ * deterministic).  dtype 0: c % 4 == 0, dtype 1: c % 8 == 0, and the 16-byte vectors of a row must divide 256. */
+size_t b2_instnorm_ws_bytes(int nseg, int c);
+int b2_instnorm_scale_shift(const void* x, int dtype, const int* seg_off, int nseg, int c, const float* weight,
+                            const float* bias, float eps, float* scale, float* shift, void* ws, size_t ws_bytes,
+                            void* stream);
 /* y = act(x * scale[s,:] + shift[s,:] + residual), s = batch index of the row (coords) or 0 when coords == NULL */
 int b2_affine_act(const void* x, int dtype, const int* coords, long long n, int c, const float* scale,
                   const float* shift, const void* residual, int act, void* y, void* stream);

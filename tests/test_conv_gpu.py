@@ -5,6 +5,7 @@ Tolerances (relative to the max |reference| of the tensor):
   fp32 path  : 2e-5  (fp32 FMA accumulation in a different order than the oracle's index_add)
   bf16 path  : 1.5e-2 (operands rounded to bf16 = 2^-8 relative, fp32 accumulate, bf16 output rounding)
 """
+import numpy as np
 import pytest
 import torch
 
@@ -209,6 +210,30 @@ def test_maxpool_with_normalisation_applied_on_the_fly(dev):
         want = ops.maxpool(ops.affine_act(f, scale, shift, coords=m.coords, act=act), km)
         got = ops.maxpool_affine(f, km, cm.get_map(pkey).coords, scale, shift, act)
         assert torch.equal(got, want), act
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_instance_norm_statistics_in_one_pass(dev, dtype):
+    """b2_instnorm_scale_shift (shifted one-pass sums) against torch: per-scene mean / biased variance folded into
+    (scale, shift); an empty scene and a large common offset (the case a naive one-pass sum of squares gets wrong)."""
+    g = torch.Generator().manual_seed(8)
+    sizes = [5000, 0, 777, 12345]
+    off = torch.tensor([0] + list(np.cumsum(sizes)), dtype=torch.int32, device=dev)
+    x = (torch.randn(sum(sizes), 64, generator=g) * 0.7 + 40.0).to(dev).to(dtype)
+    w = torch.randn(64, generator=g).to(dev)
+    b = torch.randn(64, generator=g).to(dev)
+    scale, shift = ops.instnorm_scale_shift(x, off, len(sizes), w, b, 1e-8)
+    lo = 0
+    for i, n in enumerate(sizes):
+        if n:
+            xs = x[lo:lo + n].double()
+            mean, var = xs.mean(0), xs.var(0, unbiased=False)
+            want_scale = w.double() / torch.sqrt(var + 1e-8)
+            want_shift = b.double() - mean * want_scale
+            assert rel_err(scale[i], want_scale.float()) < 1e-4
+            assert ((shift[i].double() - want_shift).abs().max() / want_shift.abs().max()).item() < 1e-4
+        lo += n
+    assert torch.isfinite(scale).all() and torch.isfinite(shift).all()
 
 
 def test_basic_block_and_union_add(dev):
