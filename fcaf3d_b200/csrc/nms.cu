@@ -465,7 +465,8 @@ __global__ void __launch_bounds__(NT) k_nms_greedy(const float* __restrict__ box
   __shared__ float4 s_rowedge[NMS_TILE];
   __shared__ float2 s_rowsize[NMS_TILE];
   __shared__ int s_klist[NMS_TILE];
-  __shared__ int s_nk;
+  __shared__ int s_alive[NMS_TILE];
+  __shared__ int s_nk, s_na;
   const int q = blockIdx.x;
   const int beg = seg_off[q], n = seg_off[q + 1] - beg;
   const int T = (n + NMS_TILE - 1) / NMS_TILE;
@@ -477,6 +478,13 @@ __global__ void __launch_bounds__(NT) k_nms_greedy(const float* __restrict__ box
     const int rows = min(n - blk * NMS_TILE, NMS_TILE);
     if (t < NMS_TILE) {
       s_diag[t] = 0ull;
+      if (t == 0) {          // boxes of this block that no earlier block suppressed, in visiting order
+        const unsigned long long dead = s_remv[blk];
+        int m = 0;
+        for (int i = 0; i < rows; ++i)
+          if (!((dead >> i) & 1ull)) s_alive[m++] = i;
+        s_na = m;
+      }
       if (t < rows) {
         const int gi = beg + blk * NMS_TILE + t;
         if (ROTATED) {
@@ -489,45 +497,45 @@ __global__ void __launch_bounds__(NT) k_nms_greedy(const float* __restrict__ box
       }
     }
     __syncthreads();
-    // (1) diagonal tile: thread (row r, part) -> 64 / (NT / 64) columns of the same block, only c > r
-    {
-      constexpr int PARTS = NT / 64, CPP = 64 / PARTS;
-      const int r = t & 63, part = t >> 6;
-      if (r < rows) {
-        unsigned long long bits = 0ull;
-        const int c1 = min(part * CPP + CPP, rows);
-        for (int c = max(part * CPP, r + 1); c < c1; ++c) {
-          float iou;
-          if (ROTATED) {
-            const BoxPrep& A = s_row[r];
-            const BoxPrep& B = s_row[c];
-            const float ddx = A.cx - B.cx, ddy = A.cy - B.cy;
-            const float reach = A.rad + B.rad + 0.05f;
-            if (thresh >= 0.f && ddx * ddx + ddy * ddy > reach * reach) continue;
-            iou = iou_rotated(A, B);
-          } else {
-            const float4 ae = s_rowedge[r], be = s_rowedge[c];
-            const float2 as = s_rowsize[r], bs = s_rowsize[c];
-            const float left = fmaxf(ae.x, be.x), right = fminf(ae.y, be.y);
-            const float top = fmaxf(ae.z, be.z), bottom = fminf(ae.w, be.w);
-            const float width = fmaxf(right - left, 0.f), height = fmaxf(bottom - top, 0.f);
-            if (thresh >= 0.f && !(width > 0.f && height > 0.f)) continue;
-            const float inter = width * height;
-            const float Sa = as.x * as.y;
-            const float Sb = bs.x * bs.y;
-            iou = inter / fmaxf(Sa + Sb - inter, NMS_EPS);
-          }
-          if (iou > thresh) bits |= 1ull << c;
-        }
-        if (bits) atomicOr(&s_diag[r], bits);
+    // (1) diagonal tile.  Only pairs of boxes that are still alive at the start of the block can matter: the resolve
+    // below never reads the row of a box that an earlier block suppressed, and a bit for an already suppressed column
+    // changes nothing.  With a few dozen survivors per thousands of boxes that is a handful of pairs per block instead
+    // of 2016 - and on the rotated path one pair is a polygon clip with an angular sort (tens of thousands of
+    // instructions), which made this phase ~90 % of the kernel.  The alive pairs are spread evenly over the threads.
+    const int na = s_na;
+    for (int p = t; p < na * na; p += NT) {
+      const int ia = p / na, ib = p - ia * na;
+      if (ia >= ib) continue;
+      const int r = s_alive[ia], c = s_alive[ib];
+      float iou;
+      if (ROTATED) {
+        const BoxPrep& A = s_row[r];
+        const BoxPrep& B = s_row[c];
+        const float ddx = A.cx - B.cx, ddy = A.cy - B.cy;
+        const float reach = A.rad + B.rad + 0.05f;
+        if (thresh >= 0.f && ddx * ddx + ddy * ddy > reach * reach) continue;
+        iou = iou_rotated(A, B);
+      } else {
+        const float4 ae = s_rowedge[r], be = s_rowedge[c];
+        const float2 as = s_rowsize[r], bs = s_rowsize[c];
+        const float left = fmaxf(ae.x, be.x), right = fminf(ae.y, be.y);
+        const float top = fmaxf(ae.z, be.z), bottom = fminf(ae.w, be.w);
+        const float width = fmaxf(right - left, 0.f), height = fmaxf(bottom - top, 0.f);
+        if (thresh >= 0.f && !(width > 0.f && height > 0.f)) continue;
+        const float inter = width * height;
+        const float Sa = as.x * as.y;
+        const float Sb = bs.x * bs.y;
+        iou = inter / fmaxf(Sa + Sb - inter, NMS_EPS);
       }
+      if (iou > thresh) atomicOr(&s_diag[r], 1ull << c);
     }
     __syncthreads();
     // (2) serial resolve of this block (same visiting order as the reference's host loop)
     if (t == 0) {
       unsigned long long cur = s_remv[blk], kw = 0ull;
       int nk = 0;
-      for (int i = 0; i < rows; ++i) {
+      for (int ia = 0; ia < na; ++ia) {   // rows dead at the start of the block cannot be kept: walk the alive ones
+        const int i = s_alive[ia];
         if (!((cur >> i) & 1ull)) {
           kw |= 1ull << i;
           cur |= s_diag[i];
@@ -551,8 +559,23 @@ __global__ void __launch_bounds__(NT) k_nms_greedy(const float* __restrict__ box
         bool sup = false;
         if (ROTATED) {
           BoxPrep B = prep[beg + j];
-#pragma unroll 1
+          // Any kept row that overlaps enough suppresses the column, so the visiting order is free: the kept row whose
+          // centre is nearest goes first - it is the likeliest suppressor, and a column that this block suppresses then
+          // costs one polygon clip instead of one per kept row up to the first hit.
+          int first = 0;
+          float dmin = 3.0e38f;
           for (int ai = 0; ai < nk; ++ai) {
+            const BoxPrep& A = s_row[s_klist[ai]];
+            const float ex = A.cx - B.cx, ey = A.cy - B.cy;
+            const float d = ex * ex + ey * ey;
+            if (d < dmin) {
+              dmin = d;
+              first = ai;
+            }
+          }
+#pragma unroll 1
+          for (int it = 0; it < nk; ++it) {
+            const int ai = (it == 0) ? first : (it <= first ? it - 1 : it);
             // B stays in registers across the walk, but the compiler must not hoist B-only sub-expressions out of the
             // loop: that would change how the pair arithmetic is contracted into FMAs (tools/check_nms_codegen.py)
             asm volatile("" : "+f"(B.cx), "+f"(B.cy), "+f"(B.dx), "+f"(B.dy), "+f"(B.cosm), "+f"(B.sinm), "+f"(B.c[0].x),
@@ -707,7 +730,12 @@ int b2_nms_greedy_batched(const float* boxes, const float* scores, const int* se
       k_nms_prep<<<b2_div_up(n, 128), 128, 0, st>>>(sb, (int)n, prep);
       B2_LAUNCH_CHECK();
     }
-    k_nms_greedy<true, 512><<<nseg, 512, 0, st>>>(sb, prep, seg_off, thresh, keep, counts);
+    // 57 registers per thread: 1024 threads per segment fit, and the per-column walk of the update phase uses them
+    // (B2_NMS_NT_ROT=512 for A/B runs)
+    static const int ntr_env = getenv("B2_NMS_NT_ROT") ? atoi(getenv("B2_NMS_NT_ROT")) : 0;
+    const int ntr = ntr_env ? ntr_env : (max_seg > 1024 ? 1024 : 512);
+    if (ntr >= 1024) k_nms_greedy<true, 1024><<<nseg, 1024, 0, st>>>(sb, prep, seg_off, thresh, keep, counts);
+    else k_nms_greedy<true, 512><<<nseg, 512, 0, st>>>(sb, prep, seg_off, thresh, keep, counts);
   } else {
     // threads per segment: the update phase is one independent walk per column, so a segment of thousands of boxes
     // feeds 1024 threads (B2_NMS_NT=256 / 512 / 1024 for A/B runs)

@@ -49,23 +49,26 @@ def main():
     inbox_lo, inbox_hi = find("int corner_in_box("), find("float bev_overlap(")    # lines whose attribution may shift
     k = op_table()
     get = lambda pat: next(v for n, v in k.items() if pat in n)
-    mask, greedy, prep = get("k_nms_maskILb1E"), get("k_nms_greedyILb1E"), get("k_nms_prep")
+    mask, prep = get("k_nms_maskILb1E"), get("k_nms_prep")
+    greedies = [(n, v) for n, v in k.items() if "k_nms_greedyILb1E" in n]      # every thread-count instantiation
     ops = ("FMUL", "FFMA", "FADD")
     bad = []
-    inbox = {name: collections.Counter() for name in ("mask", "greedy")}
-    for ln in range(pair_lo, pair_hi):
-        if prep_lo <= ln < prep_hi:
-            continue
-        for op in ops:
-            m, g = mask.get((ln, op), 0), greedy.get((ln, op), 0)
-            if inbox_lo <= ln < inbox_hi:
-                inbox["mask"][op] += m
-                inbox["greedy"][op] += g
-            elif g != 2 * m:
-                bad.append(("greedy", ln, op, m, g))
-    for op in ops:  # the corner-in-box lines are compared as a group (the same FMA may be attributed to a neighbouring line)
-        if inbox["greedy"][op] != 2 * inbox["mask"][op]:
-            bad.append(("greedy corner_in_box", 0, op, inbox["mask"][op], inbox["greedy"][op]))
+    for gname, greedy in greedies:
+        tag = "greedy<%s>" % re.search(r"ILb1ELi(\d+)E", gname).group(1)
+        inbox = {name: collections.Counter() for name in ("mask", "greedy")}
+        for ln in range(pair_lo, pair_hi):
+            if prep_lo <= ln < prep_hi:
+                continue
+            for op in ops:
+                m, g = mask.get((ln, op), 0), greedy.get((ln, op), 0)
+                if inbox_lo <= ln < inbox_hi:
+                    inbox["mask"][op] += m
+                    inbox["greedy"][op] += g
+                elif g != 2 * m:
+                    bad.append((tag, ln, op, m, g))
+        for op in ops:  # the corner-in-box lines are compared as a group (the same FMA may be attributed to a neighbouring line)
+            if inbox["greedy"][op] != 2 * inbox["mask"][op]:
+                bad.append((tag + " corner_in_box", 0, op, inbox["mask"][op], inbox["greedy"][op]))
     for ln in range(prep_lo, prep_hi):
         if "hx" in src[ln - 1] or "/ 2" in src[ln - 1]:
             continue  # half extents: x * 0.5 is exact, so fusing it into the following add cannot change a bit
