@@ -14,6 +14,9 @@
 #include "tc_common.cuh"
 #include <stdlib.h>
 
+// 8 producer / epilogue warps, the MMA warp, and (GRP == 2) the warp whose lane 0 issues the weight-tile TMA loads
+#define CT_THREADS 320
+
 template <int BN, int ST>
 struct TcCfg {
   static constexpr int STAGES = ST;
@@ -28,8 +31,14 @@ struct TcCfg {
 // Warp roles: warps 0..7 = producers (cp.async gathers), then epilogue; warp 8 = TMEM owner + MMA issuer.
 // Producer thread t: 16-byte chunk (t & 7) of rows (t >> 3) + 32 p; everything that does not depend on the stage is
 // hoisted (the producers are instruction-latency bound: a stage must cost them as few dependent instructions as possible).
-template <int BN, int ST, typename TOut>
-__global__ void __launch_bounds__(TC_THREADS)
+// GRP == 2: the producer warps work as two groups of four that fill alternate pipeline stages (each thread copies 8 rows'
+// chunks of a stage instead of 4, every other stage).  A producer warp needs ~120 dependent instructions per stage it
+// takes part in (wait, address arithmetic, copies, arrive) at ~8 cycles each, and that chain - not the L2 fabric or the
+// tensor pipe - paced the C = 64 layers (ncu source view: 2/3 of the stall samples in the producer loop and its per-offset
+// set-up); with two groups the per-stage fixed part of the chain is paid half as often per warp.  The weight tile's TMA
+// load moves from thread 0 of the producers to lane 0 of a warp of its own.
+template <int BN, int ST, typename TOut, int GRP>
+__global__ void __launch_bounds__(CT_THREADS)
 k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __restrict__ in, const int* __restrict__ nbr,
           int ld,
           const unsigned int* __restrict__ tile_mask, const int* __restrict__ out_rows, int n_out, int cin, int cout,
@@ -56,7 +65,7 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __rest
 
   if (tid == 0) {
     for (int s = 0; s < S; ++s) {
-      mbar_init(&full_bar[s], TC_PRODUCERS + 1);  // producers' cp.async arrivals + the weight tile's expect_tx
+      mbar_init(&full_bar[s], TC_PRODUCERS / GRP + 1);  // one group's cp.async arrivals + the weight tile's expect_tx
       mbar_init(&empty_bar[s], 1);
     }
     mbar_init(accum_bar, 1);
@@ -71,22 +80,22 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __rest
   // stage the tile's neighbour rows in shared memory once (coalesced, independent loads in flight)
   if (nbr != nullptr) {
     const int total = kvol * TC_BM;
-    for (int i0 = tid; i0 < total; i0 += TC_THREADS * 4) {
+    for (int i0 = tid; i0 < total; i0 += CT_THREADS * 4) {
       int v[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        const int i = i0 + u * TC_THREADS;
+        const int i = i0 + u * CT_THREADS;
         const int k = i >> 7, r = i & (TC_BM - 1);
         v[u] = (i < total && ((kmask >> k) & 1u)) ? __ldg(nbr + (long long)k * ld + row0 + r) : -1;
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u)
-        if (i0 + u * TC_THREADS < total) s_nbr[i0 + u * TC_THREADS] = v[u];
+        if (i0 + u * CT_THREADS < total) s_nbr[i0 + u * CT_THREADS] = v[u];
     }
   } else {
-    for (int r = tid; r < TC_BM; r += TC_THREADS) s_nbr[r] = (row0 + r < n_out) ? row0 + r : -1;
+    for (int r = tid; r < TC_BM; r += CT_THREADS) s_nbr[r] = (row0 + r < n_out) ? row0 + r : -1;
   }
-  for (int j = tid; j < BN; j += TC_THREADS) {
+  for (int j = tid; j < BN; j += CT_THREADS) {
     const int n = col0 + j;
     const int ch = ch_mod > 0 ? (n % ch_mod) : n;
     s_epi[j] = bias ? __ldg(bias + ch) : 0.f;
@@ -100,6 +109,40 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __rest
 
   if (warp < TC_PRODUCERS / 32) {
     // ===================== producers ======================================================
+    if (GRP == 2) {
+      const int group = warp >> 2, gt = tid & 127;
+      const int chunk16 = gt & 7, rsub = gt >> 3;  // rsub 0..15; rows rsub + 16 p keep (row & 7) == (rsub & 7)
+      const uint32_t dst_off = (uint32_t)(rsub * 128 + ((chunk16 ^ (rsub & 7)) << 4));  // + 2048 per pass (16 rows)
+      const __nv_bfloat16* in_thr = in + chunk16 * 8;
+      const uint32_t smem_base = smem_u32(smem);
+      int it = 0;
+      for (int k = 0; k < kvol; ++k) {
+        if (!((kmask >> k) & 1u)) continue;
+        const int mine = it + ((it & 1) != group);   // this group's first stage of the offset
+        if (mine >= it + chunks) {
+          it += chunks;
+          continue;
+        }
+        const int* nb = s_nbr + k * TC_BM + rsub;
+        const __nv_bfloat16* src[TC_BM / 16];
+        uint32_t nbytes[TC_BM / 16];
+#pragma unroll
+        for (int p = 0; p < TC_BM / 16; ++p) {
+          const int r = nb[p * 16];
+          src[p] = in_thr + (r >= 0 ? (long long)r * cin : 0ll);
+          nbytes[p] = r >= 0 ? 16u : 0u;
+        }
+        for (int c = 0; c < chunks; ++c, ++it) {
+          if ((it & 1) != group) continue;
+          const int s = it % S;
+          mbar_wait(&empty_bar[s], ((uint32_t)(it / S) & 1u) ^ 1u);
+          const uint32_t a_dst = smem_base + s * Cfg::STAGE_BYTES + dst_off;
+#pragma unroll
+          for (int p = 0; p < TC_BM / 16; ++p) cp_async16(a_dst + p * 2048, src[p] + c * TC_BK, nbytes[p]);
+          cp_async_arrive_noinc(&full_bar[s]);
+        }
+      }
+    } else {
     const int chunk16 = tid & 7, rsub = tid >> 3;  // rsub 0..31
     const uint32_t dst_off = (uint32_t)(rsub * 128 + ((chunk16 ^ (rsub & 7)) << 4));  // + 4096 per pass (32 rows)
     const __nv_bfloat16* in_thr = in + chunk16 * 8;
@@ -131,6 +174,7 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __rest
         // asynchronous completion: nobody waits here, so all S stages can be in flight
         cp_async_arrive_noinc(&full_bar[s]);
       }
+    }
     }
 
     // ===================== epilogue: TMEM -> registers -> global ===========================
@@ -214,6 +258,22 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __rest
       }
     }
     tc_fence_before();
+  } else if (warp == TC_PRODUCERS / 32 + 1) {
+    // ===================== weight tiles (GRP == 2): one thread, one TMA tile load per stage ===
+    if (GRP == 2 && lane == 0) {
+      const uint32_t smem_base = smem_u32(smem);
+      int it = 0;
+      for (int k = 0; k < kvol; ++k) {
+        if (!((kmask >> k) & 1u)) continue;
+        for (int c = 0; c < chunks; ++c, ++it) {
+          const int s = it % S;
+          mbar_wait(&empty_bar[s], ((uint32_t)(it / S) & 1u) ^ 1u);
+          mbar_expect_tx(&full_bar[s], (uint32_t)Cfg::B_BYTES);
+          tma_tile_2d(smem_base + s * Cfg::STAGE_BYTES + Cfg::A_BYTES, &map_b, &full_bar[s], c * TC_BK, k * cout + col0);
+        }
+      }
+    }
+    __syncwarp();
   } else {
     // ===================== MMA issuer (one thread) ==========================================
     if (lane == 0 && nstage > 0) {
@@ -245,12 +305,12 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __rest
   }
 }
 
-template <int BN, int ST, typename TOut>
-static int launch_tc(const void* in, const void* wt, const int* nbr, long long ld, const unsigned int* tile_mask,
+template <int BN, int ST, typename TOut, int GRP>
+static int launch_tc_g(const void* in, const void* wt, const int* nbr, long long ld, const unsigned int* tile_mask,
                      const int* out_rows, long long n_out, int cin, int cout, int kvol, const float* bias, const float* scale,
                      const float* shift, const void* residual, int act, int ch_mod, void* out, cudaStream_t st) {
   using Cfg = TcCfg<BN, ST>;
-  auto kern = k_conv_tc<BN, ST, TOut>;
+  auto kern = k_conv_tc<BN, ST, TOut, GRP>;
   static bool configured = false;  // per template instance; attribute is per device function
   if (!configured) {
     B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
@@ -260,11 +320,25 @@ static int launch_tc(const void* in, const void* wt, const int* nbr, long long l
   const int rc = b2_make_bf16_map(&map_b, wt, (long long)kvol * cout, cin, BN);
   if (rc) return rc;
   dim3 grid(b2_div_up(n_out, TC_BM), cout / BN);
-  kern<<<grid, TC_THREADS, Cfg::SMEM, st>>>(map_b, (const __nv_bfloat16*)in, nbr, (int)ld, tile_mask, out_rows,
+  kern<<<grid, CT_THREADS, Cfg::SMEM, st>>>(map_b, (const __nv_bfloat16*)in, nbr, (int)ld, tile_mask, out_rows,
                                             (int)n_out, cin, cout, kvol, bias, scale, shift, (const TOut*)residual, act,
                                             ch_mod, (TOut*)out);
   B2_LAUNCH_CHECK();
   return B2_OK;
+}
+
+// producer organisation: 2 = two groups on alternate stages + a weight-loader warp, 1 = all eight warps on every stage
+// (B2_TC_GROUPS=1 / 2 for A/B runs)
+template <int BN, int ST, typename TOut>
+static int launch_tc(const void* in, const void* wt, const int* nbr, long long ld, const unsigned int* tile_mask,
+                     const int* out_rows, long long n_out, int cin, int cout, int kvol, const float* bias, const float* scale,
+                     const float* shift, const void* residual, int act, int ch_mod, void* out, cudaStream_t st) {
+  static const int groups = getenv("B2_TC_GROUPS") ? atoi(getenv("B2_TC_GROUPS")) : 2;
+  if (groups == 2)
+    return launch_tc_g<BN, ST, TOut, 2>(in, wt, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, shift,
+                                        residual, act, ch_mod, out, st);
+  return launch_tc_g<BN, ST, TOut, 1>(in, wt, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, shift,
+                                      residual, act, ch_mod, out, st);
 }
 
 int b2_conv_tc2_dispatch(const void* in, const void* wt, const int* nbr, long long ld, const unsigned int* tile_mask,
