@@ -455,44 +455,57 @@ __global__ void k_nms_prep(const float* __restrict__ boxes, int n, BoxPrep* __re
 
 // NT threads per segment: 256 for the cheap axis-aligned pairs, 512 for the rotated ones (their update phase is the
 // long pole: a few kept rows x thousands of columns of polygon clipping per round)
-template <bool ROTATED, int NT>
+// STAGED (axis-aligned only): the edges and sizes of ALL boxes of the segment are put in dynamic shared memory once
+// (24 bytes per box), so neither the row staging nor the per-column walk of a block waits for global loads.
+template <bool ROTATED, int NT, bool STAGED>
 __global__ void __launch_bounds__(NT) k_nms_greedy(const float* __restrict__ boxes, const BoxPrep* __restrict__ prep,
                                                     const int* __restrict__ seg_off, float thresh,
-                                                    uint8_t* __restrict__ keep, int* __restrict__ counts) {
+                                                    uint8_t* __restrict__ keep, int* __restrict__ counts, int cap) {
+  extern __shared__ __align__(16) unsigned char s_dyn[];
   __shared__ unsigned long long s_remv[RED_MAX_WORDS];
   __shared__ unsigned long long s_diag[NMS_TILE];
   __shared__ BoxPrep s_row[ROTATED ? NMS_TILE : 1];
-  __shared__ float4 s_rowedge[NMS_TILE];
-  __shared__ float2 s_rowsize[NMS_TILE];
+  __shared__ float4 s_rowedge_blk[STAGED ? 1 : NMS_TILE];
+  __shared__ float2 s_rowsize_blk[STAGED ? 1 : NMS_TILE];
   __shared__ int s_klist[NMS_TILE];
   __shared__ int s_alive[NMS_TILE];
-  __shared__ int s_nk, s_na;
+  __shared__ int s_nk;
+  float4* s_alledge = reinterpret_cast<float4*>(s_dyn);                 // [cap]
+  float2* s_allsize = reinterpret_cast<float2*>(s_dyn + (size_t)cap * sizeof(float4));
   const int q = blockIdx.x;
   const int beg = seg_off[q], n = seg_off[q + 1] - beg;
   const int T = (n + NMS_TILE - 1) / NMS_TILE;
   const int t = threadIdx.x;
   for (int j = t; j < T; j += blockDim.x) s_remv[j] = 0ull;
+  if (STAGED) {
+    for (int j = t; j < n; j += NT) {
+      const float* b = boxes + (long long)(beg + j) * 7;
+      const float b0 = b[0], b1 = b[1], b3 = b[3], b4 = b[4];
+      s_alledge[j] = make_float4(b0 - b3 / 2, b0 + b3 / 2, b1 - b4 / 2, b1 + b4 / 2);
+      s_allsize[j] = make_float2(b3, b4);
+    }
+  }
   int kept = 0;
   __syncthreads();
   for (int blk = 0; blk < T; ++blk) {
     const int rows = min(n - blk * NMS_TILE, NMS_TILE);
+    const float4* s_rowedge = STAGED ? s_alledge + blk * NMS_TILE : s_rowedge_blk;
+    const float2* s_rowsize = STAGED ? s_allsize + blk * NMS_TILE : s_rowsize_blk;
+    // boxes of this block that no earlier block suppressed, in visiting order (every thread knows the mask)
+    const unsigned long long alive =
+        ~s_remv[blk] & (rows == NMS_TILE ? ~0ull : ((1ull << rows) - 1ull));
+    const int na = __popcll(alive);
     if (t < NMS_TILE) {
       s_diag[t] = 0ull;
-      if (t == 0) {          // boxes of this block that no earlier block suppressed, in visiting order
-        const unsigned long long dead = s_remv[blk];
-        int m = 0;
-        for (int i = 0; i < rows; ++i)
-          if (!((dead >> i) & 1ull)) s_alive[m++] = i;
-        s_na = m;
-      }
+      if ((alive >> t) & 1ull) s_alive[__popcll(alive & ((1ull << t) - 1ull))] = t;
       if (t < rows) {
         const int gi = beg + blk * NMS_TILE + t;
         if (ROTATED) {
           s_row[t] = prep[gi];
-        } else {
+        } else if (!STAGED) {
           const float* b = boxes + (long long)gi * 7;
-          s_rowedge[t] = make_float4(b[0] - b[3] / 2, b[0] + b[3] / 2, b[1] - b[4] / 2, b[1] + b[4] / 2);
-          s_rowsize[t] = make_float2(b[3], b[4]);
+          s_rowedge_blk[t] = make_float4(b[0] - b[3] / 2, b[0] + b[3] / 2, b[1] - b[4] / 2, b[1] + b[4] / 2);
+          s_rowsize_blk[t] = make_float2(b[3], b[4]);
         }
       }
     }
@@ -502,7 +515,7 @@ __global__ void __launch_bounds__(NT) k_nms_greedy(const float* __restrict__ box
     // changes nothing.  With a few dozen survivors per thousands of boxes that is a handful of pairs per block instead
     // of 2016 - and on the rotated path one pair is a polygon clip with an angular sort (tens of thousands of
     // instructions), which made this phase ~90 % of the kernel.  The alive pairs are spread evenly over the threads.
-    const int na = s_na;
+#pragma unroll 1
     for (int p = t; p < na * na; p += NT) {
       const int ia = p / na, ib = p - ia * na;
       if (ia >= ib) continue;
@@ -591,10 +604,18 @@ __global__ void __launch_bounds__(NT) k_nms_greedy(const float* __restrict__ box
             }
           }
         } else {
-          const float* b = boxes + (long long)(beg + j) * 7;
-          const float b3 = b[3], b4 = b[4];
-          const float4 be = make_float4(b[0] - b3 / 2, b[0] + b3 / 2, b[1] - b4 / 2, b[1] + b4 / 2);
-          const float Sb = b3 * b4;
+          float4 be;
+          float Sb;
+          if (STAGED) {
+            be = s_alledge[j];
+            const float2 bs = s_allsize[j];
+            Sb = bs.x * bs.y;
+          } else {
+            const float* b = boxes + (long long)(beg + j) * 7;
+            const float b3 = b[3], b4 = b[4];
+            be = make_float4(b[0] - b3 / 2, b[0] + b3 / 2, b[1] - b4 / 2, b[1] + b4 / 2);
+            Sb = b3 * b4;
+          }
           for (int ai = 0; ai < nk && !sup; ++ai) {
             const int a = s_klist[ai];
             const float4 ae = s_rowedge[a];
@@ -734,16 +755,31 @@ int b2_nms_greedy_batched(const float* boxes, const float* scores, const int* se
     // (B2_NMS_NT_ROT=512 for A/B runs)
     static const int ntr_env = getenv("B2_NMS_NT_ROT") ? atoi(getenv("B2_NMS_NT_ROT")) : 0;
     const int ntr = ntr_env ? ntr_env : (max_seg > 1024 ? 1024 : 512);
-    if (ntr >= 1024) k_nms_greedy<true, 1024><<<nseg, 1024, 0, st>>>(sb, prep, seg_off, thresh, keep, counts);
-    else k_nms_greedy<true, 512><<<nseg, 512, 0, st>>>(sb, prep, seg_off, thresh, keep, counts);
+    if (ntr >= 1024) k_nms_greedy<true, 1024, false><<<nseg, 1024, 0, st>>>(sb, prep, seg_off, thresh, keep, counts, 0);
+    else k_nms_greedy<true, 512, false><<<nseg, 512, 0, st>>>(sb, prep, seg_off, thresh, keep, counts, 0);
   } else {
     // threads per segment: the update phase is one independent walk per column, so a segment of thousands of boxes
     // feeds 1024 threads (B2_NMS_NT=256 / 512 / 1024 for A/B runs)
     static const int nt_env = getenv("B2_NMS_NT") ? atoi(getenv("B2_NMS_NT")) : 0;
     const int nt = nt_env ? nt_env : (max_seg > 1024 ? 1024 : (max_seg > 256 ? 512 : 256));
-    if (nt >= 1024) k_nms_greedy<false, 1024><<<nseg, 1024, 0, st>>>(sb, prep, seg_off, thresh, keep, counts);
-    else if (nt >= 512) k_nms_greedy<false, 512><<<nseg, 512, 0, st>>>(sb, prep, seg_off, thresh, keep, counts);
-    else k_nms_greedy<false, 256><<<nseg, 256, 0, st>>>(sb, prep, seg_off, thresh, keep, counts);
+    // all boxes of a segment staged in shared memory (24 B per box) when the longest segment fits (B2_NMS_STAGED=0: off)
+    static const bool staged_ok = !(getenv("B2_NMS_STAGED") && atoi(getenv("B2_NMS_STAGED")) == 0);
+    const size_t dyn = (size_t)max_seg * (sizeof(float4) + sizeof(float2));
+    if (nt >= 1024 && staged_ok && max_seg > 0 && dyn <= 160 * 1024) {
+      auto kern = k_nms_greedy<false, 1024, true>;
+      static bool configured = false;
+      if (!configured) {
+        B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        configured = true;
+      }
+      kern<<<nseg, 1024, dyn, st>>>(sb, prep, seg_off, thresh, keep, counts, max_seg);
+    } else if (nt >= 1024) {
+      k_nms_greedy<false, 1024, false><<<nseg, 1024, 0, st>>>(sb, prep, seg_off, thresh, keep, counts, 0);
+    } else if (nt >= 512) {
+      k_nms_greedy<false, 512, false><<<nseg, 512, 0, st>>>(sb, prep, seg_off, thresh, keep, counts, 0);
+    } else {
+      k_nms_greedy<false, 256, false><<<nseg, 256, 0, st>>>(sb, prep, seg_off, thresh, keep, counts, 0);
+    }
   }
   B2_LAUNCH_CHECK();
   return B2_OK;

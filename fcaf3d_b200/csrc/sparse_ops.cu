@@ -45,6 +45,39 @@ __global__ void __launch_bounds__(128) k_kernel_map(const B2Slot* __restrict__ t
   if (threadIdx.x == 0) tile_mask[blockIdx.x] = m;
 }
 
+// The same table with the offsets spread over blockIdx.y (KPB offsets per CTA): a thread does KPB independent probes
+// instead of KS^3 sequential ones, so the small maps of the deep levels (21 - 423 tiles), which were pure probe latency
+// (27 dependent L2 round trips, ~21 - 35 us whatever the size), finish in a few microseconds.  tile_mask is zeroed by the
+// caller; a CTA ORs in the bits of its offsets (one atomic per CTA).
+template <int KS, int KPB>
+__global__ void __launch_bounds__(128) k_kernel_map_par(const B2Slot* __restrict__ table, unsigned int cap_mask,
+                                                        const int* __restrict__ out_coords, int n_out, int step,
+                                                        int* __restrict__ nbr, int ld, unsigned int* __restrict__ tile_mask) {
+  const int o = blockIdx.x * 128 + threadIdx.x;
+  const int k0 = blockIdx.y * KPB;
+  int res[KPB];
+#pragma unroll
+  for (int j = 0; j < KPB; ++j) res[j] = -1;
+  if (o < n_out) {
+    const int4 c = __ldg(reinterpret_cast<const int4*>(out_coords) + o);
+#pragma unroll
+    for (int j = 0; j < KPB; ++j) {
+      const int k = k0 + j;
+      const int ix = k % KS, iy = (k / KS) % KS, iz = k / (KS * KS);
+      const int base = (KS & 1) ? -(KS / 2) : 0;
+      const int x = c.y + (ix + base) * step, y = c.z + (iy + base) * step, z = c.w + (iz + base) * step;
+      if (b2_coord_in_range(c.x, x, y, z)) res[j] = b2_table_find(table, cap_mask, b2_pack_key(c.x, x, y, z));
+    }
+  }
+  unsigned int m = 0;
+#pragma unroll
+  for (int j = 0; j < KPB; ++j) {
+    nbr[(long long)(k0 + j) * ld + o] = res[j];
+    if (__syncthreads_or(res[j] >= 0)) m |= (1u << (k0 + j));
+  }
+  if (threadIdx.x == 0 && m) atomicOr(tile_mask + blockIdx.x, m);
+}
+
 // Stride-2 table (out map = in coordinates floored to 2*step) built from the INPUT side: an input voxel at u*step is the
 // offset-k neighbour of the output voxels at u*step - d_k*step that are multiples of 2*step - per axis one candidate
 // when u is even (d = 0), two when it is odd (d = -1, +1; even kernels: exactly one) - so ~3.4 probes of the OUT table
@@ -824,9 +857,18 @@ int b2_kernel_map(const void* in_table, long long cap, const int* out_coords, lo
   const int G = (int)(ld / 128);
   const B2Slot* t = (const B2Slot*)in_table;
   const unsigned m = (unsigned)(cap - 1);
+  static const bool par = !(getenv("B2_KMAP_PAR") && atoi(getenv("B2_KMAP_PAR")) == 0);   // A/B switch
   if (ksize == 1) k_kernel_map<1><<<G, 128, 0, st>>>(t, m, out_coords, (int)n_out, step, nbr, (int)ld, tile_mask);
-  if (ksize == 2) k_kernel_map<2><<<G, 128, 0, st>>>(t, m, out_coords, (int)n_out, step, nbr, (int)ld, tile_mask);
-  if (ksize == 3) k_kernel_map<3><<<G, 128, 0, st>>>(t, m, out_coords, (int)n_out, step, nbr, (int)ld, tile_mask);
+  if (ksize >= 2 && par) {
+    B2_CUDA(cudaMemsetAsync(tile_mask, 0, sizeof(unsigned int) * (size_t)G, st));
+    if (ksize == 2)
+      k_kernel_map_par<2, 2><<<dim3(G, 4), 128, 0, st>>>(t, m, out_coords, (int)n_out, step, nbr, (int)ld, tile_mask);
+    else
+      k_kernel_map_par<3, 3><<<dim3(G, 9), 128, 0, st>>>(t, m, out_coords, (int)n_out, step, nbr, (int)ld, tile_mask);
+  } else {
+    if (ksize == 2) k_kernel_map<2><<<G, 128, 0, st>>>(t, m, out_coords, (int)n_out, step, nbr, (int)ld, tile_mask);
+    if (ksize == 3) k_kernel_map<3><<<G, 128, 0, st>>>(t, m, out_coords, (int)n_out, step, nbr, (int)ld, tile_mask);
+  }
   B2_LAUNCH_CHECK();
   return B2_OK;
 }

@@ -46,7 +46,9 @@ def main():
     find = lambda s: next(i for i, l in enumerate(src) if s in l) + 1
     pair_lo, pair_hi = find("float cross3("), find("float iou_aligned(")          # per-pair arithmetic
     prep_lo, prep_hi = find("void rotate_about("), find("int seg_intersect(")      # per-box arithmetic
-    inbox_lo, inbox_hi = find("int corner_in_box("), find("float bev_overlap(")    # lines whose attribution may shift
+    # lines whose attribution may shift between each other: corner_in_box and the corner loops of bev_overlap that inline it
+    inbox_lo, inbox_hi = find("int corner_in_box("), find("float bev_overlap(")
+    loop_lo, loop_hi = find("for (int k = 0; k < 4; ++k) {"), find("ctr.x /= cnt;")
     k = op_table()
     get = lambda pat: next(v for n, v in k.items() if pat in n)
     mask, prep = get("k_nms_maskILb1E"), get("k_nms_prep")
@@ -61,14 +63,26 @@ def main():
                 continue
             for op in ops:
                 m, g = mask.get((ln, op), 0), greedy.get((ln, op), 0)
-                if inbox_lo <= ln < inbox_hi:
+                if inbox_lo <= ln < inbox_hi or loop_lo <= ln < loop_hi:
                     inbox["mask"][op] += m
                     inbox["greedy"][op] += g
                 elif g != 2 * m:
                     bad.append((tag, ln, op, m, g))
-        for op in ops:  # the corner-in-box lines are compared as a group (the same FMA may be attributed to a neighbouring line)
-            if inbox["greedy"][op] != 2 * inbox["mask"][op]:
-                bad.append((tag + " corner_in_box", 0, op, inbox["mask"][op], inbox["greedy"][op]))
+        # the corner-in-box lines are compared as a group (the same FMA may be attributed to a neighbouring line), and
+        # nvcc may unroll the 4-corner loops of one call site, so the group must hold a whole number (>= 2) of copies of
+        # the mask kernel's mix - the same multiple for every opcode, i.e. the same contraction in every copy
+        ratios = set()
+        for op in ops:
+            m, g = inbox["mask"][op], inbox["greedy"][op]
+            if m == 0:
+                if g:
+                    bad.append((tag + " corner_in_box", 0, op, m, g))
+            elif g % m or g // m < 2:
+                bad.append((tag + " corner_in_box", 0, op, m, g))
+            else:
+                ratios.add(g // m)
+        if len(ratios) > 1:
+            bad.append((tag + " corner_in_box mix", 0, "ratio", 0, len(ratios)))
     for ln in range(prep_lo, prep_hi):
         if "hx" in src[ln - 1] or "/ 2" in src[ln - 1]:
             continue  # half extents: x * 0.5 is exact, so fusing it into the following add cannot change a bit
