@@ -92,13 +92,25 @@ def ptr(t):
     return t.data_ptr()
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def stream():
+    """cudaStream_t of torch's current stream (the raw-handle query is ~10x cheaper than building a Stream object, and
+    every entry point asks for it: ~200 calls per inference step)."""
+    if _raw_stream is not None:
+        return _raw_stream(torch.cuda.current_device())
     return torch.cuda.current_stream().cuda_stream
+
+
+_fns = {}
 
 
 def call(name, *args):
     """Calls an int-returning entry point on the current torch stream (appended as last argument)."""
-    fn = getattr(lib(), name)
+    fn = _fns.get(name)
+    if fn is None:
+        fn = _fns[name] = getattr(lib(), name)
     rc = fn(*args, stream())
     if rc != 0:
         raise B2Error("%s failed (%d): %s" % (name, rc, last_error()))
