@@ -396,6 +396,20 @@ extern "C" int b2_conv_tc(const void* in_bf16, long long n_in, const void* wt_bf
     return launch_tc<64, 4, __nv_bfloat16>(in_bf16, wt_bf16, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias,
                                            scale, shift, residual, act, ch_mod, out, st);
   const bool no256 = dense && (dense_bn == 64 || dense_bn == 128);
+  // Deep pipelines for grids of at most one CTA per SM (the deep levels: 84 - 99 CTAs): such a CTA has the whole shared
+  // memory of its SM, and the layer is bound by latency x bytes in flight, so it takes 6 stages of 32 KB (128 columns) or
+  // 4 of 48 KB (256 columns) instead of 3.  B2_TC_DEEP=0 keeps 3 stages.
+  static const bool deep_ok = !(getenv("B2_TC_DEEP") && atoi(getenv("B2_TC_DEEP")) == 0);
+  const long long tiles = b2_div_up(n_out, TC_BM);
+  if (deep_ok && nbr != nullptr && out_dtype == 1 && kvol * (cin / TC_BK) >= 24) {
+    const bool use256 = cout % 256 == 0 && bn256_env != 0 && (bn256_env == 1 || cta256 >= 74);
+    if (use256 && cta256 <= 148)
+      return launch_tc<256, 4, __nv_bfloat16>(in_bf16, wt_bf16, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias,
+                                              scale, shift, residual, act, ch_mod, out, st);
+    if (!use256 && wide && tiles * (cout / 128) <= 148)
+      return launch_tc<128, 6, __nv_bfloat16>(in_bf16, wt_bf16, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias,
+                                              scale, shift, residual, act, ch_mod, out, st);
+  }
   if (cout % 256 == 0 && bn256_env != 0 && !no256 && (bn256_env == 1 || cta256 >= 74)) {
     if (out_dtype == 1)
       return launch_tc<256, 3, __nv_bfloat16>(in_bf16, wt_bf16, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias,
