@@ -1,11 +1,12 @@
 // tcgen05 implicit-GEMM sparse convolution for sm_100a (bf16 operands, fp32 accumulators in TMEM).
 //
 // Output-stationary: one CTA owns a 128-row x BN-column output tile and walks the kernel offsets
-// that the tile actually uses (tile_mask).  For every (offset k, 64-channel slice) stage, four
-// producer warps gather the 128 neighbour rows (cp.async, 16 B per request, zero-fill for missing
-// neighbours) and the matching [BN x 64] slice of W_k^T into 128B-swizzled shared memory; a single
-// thread of warp 4 issues tcgen05.mma (M=128, N=BN, K=16) and releases the stage with
-// tcgen05.commit.  The accumulator never leaves TMEM until the fused epilogue
+// that the tile actually uses (tile_mask).  For every (offset k, 64-channel slice) stage, one of two
+// groups of four producer warps gathers the 128 neighbour rows (cp.async, 16 B per request, zero-fill
+// for missing neighbours) into 128B-swizzled shared memory - the groups take alternate stages -, lane 0
+// of warp 9 fetches the matching [BN x 64] slice of W_k^T with one TMA tile load, and a single thread
+// of warp 8 issues tcgen05.mma (M=128, N=BN, K=16) and releases the stage with tcgen05.commit
+// (3, 4 or 6 stages).  The accumulator never leaves TMEM until the fused epilogue
 // (bias, folded BatchNorm scale/shift, residual, ReLU/ELU), so there are no atomics, no scatter and
 // no intermediate [pairs x C] buffers as in MinkowskiEngine's gather-GEMM-scatter
 // (reference call sites: me_resnet.py:66-78 BasicBlock convs, fcaf3d_neck_with_head.py:52,60-69).
