@@ -9,6 +9,7 @@ N > 1 (torchrun): every rank runs its own batch of 8 scenes (scene sharding, no 
 Prints ONE JSON line (rank 0).  See DESIGN.md §Measurement for every field.
 """
 import argparse
+import atexit
 import json
 import os
 import statistics
@@ -39,13 +40,18 @@ class ClockSampler:
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index):
-        self.rows, self.proc, self.index = [], None, index
+    def __init__(self, index, period_ms=100):
+        self.rows, self.proc, self.index, self.period_ms = [], None, index, period_ms
+        self.first = 0
+
+    def mark(self):
+        """Samples taken before this call (process start-up, warm-up) are not reported."""
+        self.first = len(self.rows)
 
     def __enter__(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                          "--format=csv,noheader,nounits", "-lms", str(self.period_ms)], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
@@ -68,7 +74,7 @@ class ClockSampler:
     def summary(self):
         sm, mx, reasons = [], 0, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        for r in self.rows[self.first:]:
             try:
                 sm.append(float(r[0]))
                 mx = max(mx, float(r[1]))
@@ -380,14 +386,19 @@ def main():
         return t.item() / steps, out
 
     lib = ops._lib.lib()
+    # The sampler process is started before the warm-up (nvidia-smi needs ~0.1 s to deliver its first line) and its samples
+    # are counted from the start of the first timed bracket to the end of the second one: K device-resident steps are only
+    # ~6.4 ms each, so one bracket alone would see one or two 50 ms samples.
+    clk = ClockSampler(local, period_ms=50)
+    clk.__enter__()
+    atexit.register(clk.__exit__)      # the sampler process must not outlive a failed run
     for _ in range(args.warmup):
         step_device()
     torch.cuda.synchronize()
     launches0 = lib.b2_launch_count()
-    with ClockSampler(local) as clk:
-        ms, dets = timed(step_device, args.steps, 0)
+    clk.mark()
+    ms, dets = timed(step_device, args.steps, 0)
     launches = lib.b2_launch_count() - launches0  # kernels of libfcaf3d_b200.so inside the timed region
-    clocks = clk.summary()
     def timed_e2e(steps, warmup):
         """End to end through the public API: every step copies ITS inputs from pinned host memory and reads ITS
         detections back, all inside one timed bracket; the copy of step i+1 is double-buffered on a side stream
@@ -418,6 +429,8 @@ def main():
         return t.item() / steps, out
 
     ms_e2e, res = timed_e2e(max(3, args.steps // 2), 1)
+    clk.__exit__()
+    clocks = clk.summary()
     n_det = int(dets["count"].item())
     # bytes actually copied per step by DetectionRead: the count + the first CAP packed rows (box, score, label, scene)
     d2h = 8 + min(DetectionRead.CAP, int(dets["boxes"].shape[0])) * (int(dets["box_dim"]) + 3) * 4
