@@ -19,7 +19,12 @@
 #define ST_AGG 1ull
 #define ST_PREFIX 2ull
 
-__global__ void __launch_bounds__(SCAN_THREADS) k_scan_flags(const uint8_t* __restrict__ flags, int n,
+// WINNER: the flags are not read from memory but computed in place - row i is flagged when it is the winning (lowest)
+// input row of its hash slot (b2_map_build: saves the pass that wrote the flags and the one that read them back).
+template <bool WINNER>
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_flags(const uint8_t* __restrict__ flags,
+                                                             const int* __restrict__ row_slot,
+                                                             const B2Slot* __restrict__ table, int n,
                                                              int* __restrict__ pos, int* __restrict__ total,
                                                              unsigned long long* status, unsigned int* ticket,
                                                              int nblocks) {
@@ -33,7 +38,25 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_flags(const uint8_t* __re
   const long long base = (long long)bid * SCAN_TILE + (long long)threadIdx.x * SCAN_ITEMS;
 
   int f[SCAN_ITEMS];
-  if (base + SCAN_ITEMS <= n) {
+  if (WINNER) {
+    int sl[SCAN_ITEMS];
+    if (base + SCAN_ITEMS <= n) {
+#pragma unroll
+      for (int i = 0; i < SCAN_ITEMS / 4; ++i) {
+        const int4 v = __ldg(reinterpret_cast<const int4*>(row_slot + base) + i);
+        sl[4 * i] = v.x;
+        sl[4 * i + 1] = v.y;
+        sl[4 * i + 2] = v.z;
+        sl[4 * i + 3] = v.w;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < SCAN_ITEMS; ++i) sl[i] = (base + i < n) ? row_slot[base + i] : -1;
+    }
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i)
+      f[i] = (sl[i] >= 0 && table[sl[i]].pad == (unsigned int)(base + i)) ? 1 : 0;
+  } else if (base + SCAN_ITEMS <= n) {
     const uint4 v = *reinterpret_cast<const uint4*>(flags + base);
     const unsigned w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
@@ -142,7 +165,24 @@ int b2_scan_flags_launch(const uint8_t* flags, long long n, int* pos, int* total
   B2_CUDA(cudaMemsetAsync(ws, 0, need, st));
   unsigned int* ticket = reinterpret_cast<unsigned int*>(ws);
   unsigned long long* status = reinterpret_cast<unsigned long long*>(ws) + 1;
-  k_scan_flags<<<nblocks, SCAN_THREADS, 0, st>>>(flags, (int)n, pos, total, status, ticket, nblocks);
+  k_scan_flags<false><<<nblocks, SCAN_THREADS, 0, st>>>(flags, nullptr, nullptr, (int)n, pos, total, status, ticket, nblocks);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+// exclusive positions of the winning rows of a hash build (see k_scan_flags<true>); row_slot must be 16-byte aligned
+static int b2_scan_winners_launch(const int* row_slot, const B2Slot* table, long long n, int* pos, int* total, void* ws,
+                                  size_t ws_bytes, cudaStream_t st) {
+  const size_t need = b2_scan_ws_bytes_impl(n);
+  if (ws_bytes < need) {
+    b2_set_error("scan workspace too small: %zu < %zu", ws_bytes, need);
+    return B2_ERR_WS;
+  }
+  const int nblocks = (int)((n + SCAN_TILE - 1) / SCAN_TILE);
+  B2_CUDA(cudaMemsetAsync(ws, 0, need, st));
+  unsigned int* ticket = reinterpret_cast<unsigned int*>(ws);
+  unsigned long long* status = reinterpret_cast<unsigned long long*>(ws) + 1;
+  k_scan_flags<true><<<nblocks, SCAN_THREADS, 0, st>>>(nullptr, row_slot, table, (int)n, pos, total, status, ticket, nblocks);
   B2_LAUNCH_CHECK();
   return B2_OK;
 }
@@ -186,18 +226,10 @@ __global__ void k_hash_insert(const int* __restrict__ coords, int n, int quant, 
   }
 }
 
-__global__ void k_winner_flags(const B2Slot* __restrict__ table, const int* __restrict__ row_slot, int n,
-                               uint8_t* __restrict__ flags) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const int s = row_slot[i];
-  flags[i] = (s >= 0 && table[s].pad == (unsigned int)i) ? 1 : 0;
-}
-
 // winners write the compacted coordinate row + unique_index and turn their slot's value into the compacted row id;
 // everybody records the winner row of its voxel (read from the slot's second word, which nobody writes here)
 __global__ void k_build_finalize(const int* __restrict__ coords, int n, int quant, B2Slot* __restrict__ table,
-                                 const int* __restrict__ row_slot, const uint8_t* __restrict__ flags,
+                                 const int* __restrict__ row_slot,
                                  const int* __restrict__ pos, int* __restrict__ out_coords,
                                  int* __restrict__ unique_index, int* __restrict__ inverse_map) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -209,7 +241,7 @@ __global__ void k_build_finalize(const int* __restrict__ coords, int n, int quan
   }
   const int w = (int)table[s].pad;  // original row of the representative
   inverse_map[i] = pos[w];
-  if (flags[i]) {
+  if (w == i) {  // this row is the representative of its voxel
     int4 c = load_coord(coords, i);
     if (quant > 0) {
       c.y = b2_floor_div(c.y, quant) * quant;
@@ -464,18 +496,16 @@ int b2_map_build(const int* coords, long long n, int quant, void* table, long lo
   p += align_up((size_t)n * 4, 256);
   int* pos = reinterpret_cast<int*>(p);
   p += align_up((size_t)n * 4, 256);
-  uint8_t* flags = reinterpret_cast<uint8_t*>(p);
-  p += align_up((size_t)n, 256);
+  p += align_up((size_t)n, 256);   // (formerly one flag byte per row; the workspace layout is unchanged)
   void* scan_ws = p;
   const size_t scan_bytes = ws_bytes - (size_t)(p - reinterpret_cast<char*>(ws));
   const int T = 256, G = b2_div_up(n, T);
   k_hash_insert<<<G, T, 0, st>>>(coords, (int)n, quant, (B2Slot*)table, (unsigned)(cap - 1), row_slot, err);
   B2_LAUNCH_CHECK();
-  k_winner_flags<<<G, T, 0, st>>>((const B2Slot*)table, row_slot, (int)n, flags);
-  B2_LAUNCH_CHECK();
-  int rc = b2_scan_flags_launch(flags, n, pos, n_out, scan_ws, scan_bytes, st);
+  // the scan computes "row i won its slot" itself (k_scan_flags<true>), and so does the finalize kernel
+  int rc = b2_scan_winners_launch(row_slot, (const B2Slot*)table, n, pos, n_out, scan_ws, scan_bytes, st);
   if (rc) return rc;
-  k_build_finalize<<<G, T, 0, st>>>(coords, (int)n, quant, (B2Slot*)table, row_slot, flags, pos, out_coords, unique_index,
+  k_build_finalize<<<G, T, 0, st>>>(coords, (int)n, quant, (B2Slot*)table, row_slot, pos, out_coords, unique_index,
                                     inverse_map);
   B2_LAUNCH_CHECK();
   return B2_OK;
