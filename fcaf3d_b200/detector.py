@@ -5,10 +5,13 @@ Mirrors (same module tree, attribute names and state-dict keys, same hyper-param
   Fcaf3DNeckWithHead              mmdet3d/models/dense_heads/fcaf3d_neck_with_head.py:13-374
   SingleStageSparse3DDetector     mmdet3d/models/detectors/single_stage_sparse.py:9-62
 
-Two execution modes over the same modules and weights:
-  * `forward(...)`        – op by op through the ME-surface modules, like the reference code does;
-  * `forward_fused(...)`  – the B200 path: conv + folded BN + activation + residual in one kernel,
-                            fused head, batched top-k / decode / NMS with one host sync at the end.
+Only the module tree (attribute names = state-dict keys, so released checkpoints load) and the hyper-parameters are
+mirrored; the execution paths here are this package's own:
+  * `simple_test_fused(...)`  – inference: conv + folded BN + activation + residual in one kernel, fused head, batched
+                                top-k / decode / NMS with one host sync at the end;
+  * `forward_train(...)`      – training: autograd through the ME-surface modules, whole-batch assigner and losses.
+The reference's op-by-op execution (python loops over scenes / levels / classes) is not re-typed here: it is the
+reference's own three files, loaded unmodified on this package's surfaces by `fcaf3d_b200.compat`.
 """
 import math
 import os
@@ -18,34 +21,9 @@ import torch.nn as nn
 
 from . import me as ME
 from . import ops
-from .losses import Fcaf3DAssigner, build_loss
+from .compat import Scale, bias_init_with_prob, reduce_mean
+from .losses import Fcaf3DAssigner, build_loss, decoded_box_iou
 from .me.modules.resnet_block import BasicBlock, Bottleneck
-from .pcdet_nms import pcdet_nms_gpu, pcdet_nms_normal_gpu
-
-
-class Scale(nn.Module):
-    """mmcv.cnn.Scale: a learnable scalar multiplier."""
-
-    def __init__(self, scale=1.0):
-        super().__init__()
-        self.scale = nn.Parameter(torch.tensor(scale, dtype=torch.float))
-
-    def forward(self, x):
-        return x * self.scale
-
-
-def reduce_mean(t):
-    """mmdet.core.reduce_mean: identity on one process, all-reduce mean under torch.distributed"""
-    import torch.distributed as dist
-    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
-        return t
-    t = t.clone()
-    dist.all_reduce(t.div_(dist.get_world_size()), op=dist.ReduceOp.SUM)
-    return t
-
-
-def bias_init_with_prob(prior_prob):
-    return float(-math.log((1 - prior_prob) / prior_prob))
 
 
 # =============================================================================================== backbone
@@ -302,23 +280,6 @@ class Fcaf3DNeckWithHead(nn.Module):
         c = self.test_cfg
         return c[name] if isinstance(c, dict) else getattr(c, name)
 
-    # ---- reference-style execution -------------------------------------------------------------
-    def forward(self, x):
-        outs = []
-        inputs = x
-        x = inputs[-1]
-        scores = None
-        for i in range(len(inputs) - 1, -1, -1):
-            if i < len(inputs) - 1:
-                x = getattr(self, f"up_block_{i + 1}")(x)
-                x = inputs[i] + x
-                x = self._prune(x, scores)
-            out = getattr(self, f"out_block_{i}")(x)
-            out = self.forward_single(out, self.scales[i])
-            scores = out[-1]
-            outs.append(out[:-1])
-        return zip(*outs[::-1])
-
     def _prune(self, x, scores):
         if self.pts_threshold < 0:
             return x
@@ -327,73 +288,6 @@ class Fcaf3DNeckWithHead(nn.Module):
             m = x._map()
             mask = ops.topk_mask(interpolated.reshape(-1).contiguous(), m.off_dev, m.num_batches, self.pts_threshold)
         return self.pruning(x, mask.bool())
-
-    def forward_single(self, x, scale):
-        if torch.is_grad_enabled() and x.F.requires_grad and x.F.dtype == self.cls_conv.kernel.dtype:
-            # training: the three 1x1 heads (ME: three F.mm calls) as ONE GEMM over the concatenated kernels, so the
-            # backward is two GEMMs over the level's rows instead of six
-            w = torch.cat((self.centerness_conv.kernel, self.reg_conv.kernel, self.cls_conv.kernel), dim=1)
-            h = x.F @ w
-            centerness, reg_final = h[:, :1], h[:, 1:1 + self.n_reg_outs]
-            cls_score = h[:, 1 + self.n_reg_outs:] + self.cls_conv.bias
-            ck, cmgr = x.coordinate_map_key, x.coordinate_manager
-        else:
-            centerness = self.centerness_conv(x).features
-            scores = self.cls_conv(x)
-            cls_score = scores.features
-            ck, cmgr = scores.coordinate_map_key, scores.coordinate_manager
-            reg_final = self.reg_conv(x).features
-        prune_scores = ME.SparseTensor(cls_score.max(dim=1, keepdim=True).values, coordinate_map_key=ck,
-                                       coordinate_manager=cmgr)
-        reg_distance = torch.exp(scale(reg_final[:, :6]))
-        bbox_pred = torch.cat((reg_distance, reg_final[:, 6:]), dim=1)
-        centernesses, bbox_preds, cls_scores = [], [], []
-        m = x._map()
-        for b in range(m.num_batches):   # rows of a scene are contiguous: slices instead of index tensors
-            sl = slice(m.off_host[b], m.off_host[b + 1])
-            centernesses.append(centerness[sl])
-            bbox_preds.append(bbox_pred[sl])
-            cls_scores.append(cls_score[sl])
-        points = [p * self.voxel_size for p in x.decomposed_coordinates]
-        return centernesses, bbox_preds, cls_scores, points, prune_scores
-
-    # ---- training (fcaf3d_neck_with_head.py:128-203) ---------------------------------------------
-    def loss(self, centernesses, bbox_preds, cls_scores, points, gt_bboxes, gt_labels, img_metas=None):
-        """gt_bboxes: list over scenes of [B_i, 7] tensors (gravity centre, size, yaw); gt_labels: int64 [B_i]."""
-        n = len(gt_bboxes)
-        per_scene = [self._loss_single([x[i] for x in centernesses], [x[i] for x in bbox_preds],
-                                       [x[i] for x in cls_scores], [x[i] for x in points], gt_bboxes[i], gt_labels[i])
-                     for i in range(n)]
-        return dict(loss_centerness=torch.mean(torch.stack([p[0] for p in per_scene])),
-                    loss_bbox=torch.mean(torch.stack([p[1] for p in per_scene])),
-                    loss_cls=torch.mean(torch.stack([p[2] for p in per_scene])))
-
-    def _loss_single(self, centernesses, bbox_preds, cls_scores, points, gt_bboxes, gt_labels):
-        centerness_targets, bbox_targets, labels = self.assigner.assign(points, gt_bboxes, gt_labels)
-        centerness = torch.cat(centernesses)
-        bbox_preds = torch.cat(bbox_preds)
-        cls_scores = torch.cat(cls_scores)
-        points = torch.cat(points)
-        pos_inds = torch.nonzero(labels >= 0).squeeze(1)
-        n_pos = torch.tensor(len(pos_inds), dtype=torch.float, device=centerness.device)
-        n_pos = torch.clamp(reduce_mean(n_pos), min=1.)
-        loss_cls = self.loss_cls(cls_scores, labels, avg_factor=n_pos)
-        pos_centerness = centerness[pos_inds]
-        pos_bbox_preds = bbox_preds[pos_inds]
-        pos_centerness_targets = centerness_targets[pos_inds].unsqueeze(1)
-        pos_bbox_targets = bbox_targets[pos_inds]
-        centerness_denorm = torch.clamp(reduce_mean(pos_centerness_targets.sum().detach()), min=1e-6)
-        if len(pos_inds) > 0:
-            pos_points = points[pos_inds]
-            loss_centerness = self.loss_centerness(pos_centerness, pos_centerness_targets, avg_factor=n_pos)
-            pred = self._bbox_pred_to_bbox_train(pos_points, pos_bbox_preds)
-            target = pos_bbox_targets if pred.shape[1] == 7 else pos_bbox_targets[:, :6]
-            loss_bbox = self.loss_bbox(pred, target, weight=pos_centerness_targets.squeeze(1),
-                                       avg_factor=centerness_denorm)
-        else:
-            loss_centerness = pos_centerness.sum()
-            loss_bbox = pos_bbox_preds.sum()
-        return loss_centerness, loss_bbox, loss_cls
 
     # ---- batched training path (SURVEY 8f N1): no python loop over scenes ------------------------------
     def forward_train_batched(self, inputs, gt_bboxes, gt_labels):
@@ -454,100 +348,19 @@ class Fcaf3DNeckWithHead(nn.Module):
         if len(pos_inds) > 0:
             loss_centerness = self.loss_centerness(pos_centerness, pos_ct.unsqueeze(1),
                                                    weight=w_scene[pos_scene].unsqueeze(1), avg_factor=1.0)
-            pred = self._bbox_pred_to_bbox_train(points[pos_inds], pos_bbox_preds)
-            target = bbox_targets[pos_inds]
-            target = target if pred.shape[1] == 7 else target[:, :6]
-            loss_bbox = self.loss_bbox(pred, target, weight=pos_ct / (S * denorm[pos_scene]), avg_factor=1.0,
-                                       check_weight=False)
+            # decode + IoU (rotated or axis-aligned, as the configured IoU3DLoss) + their gradient: one launch
+            iou = decoded_box_iou(points[pos_inds], pos_bbox_preds, bbox_targets[pos_inds],
+                                  self._yaw_mode(pos_bbox_preds.shape[1]), self.loss_bbox.with_yaw)
+            loss_bbox = self.loss_bbox.loss_weight * ((1 - iou) * (pos_ct / (S * denorm[pos_scene]))).sum()
         else:
             loss_centerness = pos_centerness.sum()
             loss_bbox = pos_bbox_preds.sum()
         return dict(loss_centerness=loss_centerness, loss_bbox=loss_bbox, loss_cls=loss_cls)
 
-    def _bbox_pred_to_bbox_train(self, points, bbox_pred):
-        """differentiable twin of _bbox_pred_to_bbox (:281-330); the inference path uses the fused kernel"""
-        xc = points[:, 0] + (bbox_pred[:, 1] - bbox_pred[:, 0]) / 2
-        yc = points[:, 1] + (bbox_pred[:, 3] - bbox_pred[:, 2]) / 2
-        zc = points[:, 2] + (bbox_pred[:, 5] - bbox_pred[:, 4]) / 2
-        base = torch.stack([xc, yc, zc, bbox_pred[:, 0] + bbox_pred[:, 1], bbox_pred[:, 2] + bbox_pred[:, 3],
-                            bbox_pred[:, 4] + bbox_pred[:, 5]], -1)
-        if bbox_pred.shape[1] == 6:
-            return base
-        if self.yaw_parametrization == "naive":
-            return torch.cat((base, bbox_pred[:, 6:7]), -1)
-        if self.yaw_parametrization == "sin-cos":
-            norm = torch.pow(torch.pow(bbox_pred[:, 6:7], 2) + torch.pow(bbox_pred[:, 7:8], 2), 0.5)
-            return torch.cat((base, torch.atan2(bbox_pred[:, 6:7] / norm, bbox_pred[:, 7:8] / norm)), -1)
-        scale = bbox_pred[:, 0] + bbox_pred[:, 1] + bbox_pred[:, 2] + bbox_pred[:, 3]
-        q = torch.exp(torch.sqrt(torch.pow(bbox_pred[:, 6], 2) + torch.pow(bbox_pred[:, 7], 2)))
-        alpha = 0.5 * torch.atan2(bbox_pred[:, 6], bbox_pred[:, 7])
-        return torch.stack((xc, yc, zc, scale / (1 + q), scale / (1 + q) * q, bbox_pred[:, 5] + bbox_pred[:, 4], alpha),
-                           dim=-1)
-
-    def get_bboxes(self, centernesses, bbox_preds, cls_scores, points, img_metas, rescale=False):
-        results = []
-        for i in range(len(img_metas)):
-            results.append(self._get_bboxes_single([x[i] for x in centernesses], [x[i] for x in bbox_preds],
-                                                   [x[i] for x in cls_scores], [x[i] for x in points], img_metas[i]))
-        return results
-
-    def _get_bboxes_single(self, centernesses, bbox_preds, cls_scores, points, img_meta):
-        nms_pre = self._cfg("nms_pre")
-        mlvl_bboxes, mlvl_scores = [], []
-        for centerness, bbox_pred, cls_score, point in zip(centernesses, bbox_preds, cls_scores, points):
-            scores = cls_score.sigmoid() * centerness.sigmoid()
-            max_scores, _ = scores.max(dim=1)
-            if len(scores) > nms_pre > 0:
-                _, ids = max_scores.topk(nms_pre)
-                bbox_pred, scores, point = bbox_pred[ids], scores[ids], point[ids]
-            mlvl_bboxes.append(self._bbox_pred_to_bbox(point, bbox_pred))
-            mlvl_scores.append(scores)
-        return self._nms(torch.cat(mlvl_bboxes), torch.cat(mlvl_scores), img_meta)
-
     def _yaw_mode(self, n_reg):
         if n_reg == 6:
             return ops.YAW_MODES["none"]
         return ops.YAW_MODES[self.yaw_parametrization]
-
-    def _bbox_pred_to_bbox(self, points, bbox_pred):
-        if bbox_pred.shape[0] == 0:
-            return bbox_pred
-        n_reg = bbox_pred.shape[1]
-        out = ops.decode_boxes(points.float(), bbox_pred.float(), self._yaw_mode(n_reg))
-        return out[:, :6] if n_reg == 6 else out
-
-    def _nms(self, bboxes, scores, img_meta):
-        n_classes = scores.shape[1]
-        yaw_flag = bboxes.shape[1] == 7
-        score_thr, iou_thr = self._cfg("score_thr"), self._cfg("iou_thr")
-        nms_bboxes, nms_scores, nms_labels = [], [], []
-        for i in range(n_classes):
-            ids = scores[:, i] > score_thr
-            if not ids.any():
-                continue
-            class_scores = scores[ids, i]
-            class_bboxes = bboxes[ids]
-            if yaw_flag:
-                nms_function = pcdet_nms_gpu
-            else:
-                class_bboxes = torch.cat((class_bboxes, torch.zeros_like(class_bboxes[:, :1])), dim=1)
-                nms_function = pcdet_nms_normal_gpu
-            nms_ids, _ = nms_function(class_bboxes, class_scores, iou_thr)
-            nms_bboxes.append(class_bboxes[nms_ids])
-            nms_scores.append(class_scores[nms_ids])
-            nms_labels.append(bboxes.new_full(class_scores[nms_ids].shape, i, dtype=torch.long))
-        if len(nms_bboxes):
-            nms_bboxes, nms_scores, nms_labels = torch.cat(nms_bboxes), torch.cat(nms_scores), torch.cat(nms_labels)
-        else:
-            nms_bboxes = bboxes.new_zeros((0, bboxes.shape[1]))
-            nms_scores = bboxes.new_zeros((0,))
-            nms_labels = bboxes.new_zeros((0,), dtype=torch.long)
-        if not yaw_flag:
-            nms_bboxes = nms_bboxes[:, :6]
-        box_type = img_meta.get("box_type_3d") if isinstance(img_meta, dict) else None
-        if box_type is not None:
-            nms_bboxes = box_type(nms_bboxes, box_dim=nms_bboxes.shape[1], with_yaw=yaw_flag, origin=(.5, .5, .5))
-        return nms_bboxes, nms_scores, nms_labels
 
     # ---- fused execution -----------------------------------------------------------------------
     def _head_weights(self):
@@ -722,7 +535,11 @@ def split_detections(dets, num_scenes):
     host = buf[:n]
     host.copy_(packed_dev, non_blocking=True)
     torch.cuda.current_stream().synchronize()
-    packed = host.clone()                      # the pinned buffer is reused by the next call
+    return _split_packed(host.clone(), d, num_scenes)       # the pinned buffer is reused by the next call
+
+
+def _split_packed(packed, d, num_scenes):
+    n = packed.shape[0]
     boxes, scores, labels, scene = packed[:, :d], packed[:, d], packed[:, d + 1].long(), packed[:, d + 2].long()
     cnt = torch.bincount(scene, minlength=num_scenes).tolist() if n else [0] * num_scenes
     out, lo = [], 0
@@ -735,31 +552,37 @@ def split_detections(dets, num_scenes):
 class DetectionRead:
     """Asynchronous read-back of one step's detections: the packed copy (count + the first `cap` rows) is enqueued on a side
     stream behind the step's last kernel, so the caller can enqueue the NEXT step before it looks at the result
-    (`finish()`); the GPU never waits for the host between two steps."""
-    _stream = None
-    _ring = {}
-    _next = 0
+    (`finish()`); the GPU never waits for the host between two steps.
+
+    Staging: per (device, box width, count dtype) a ring of SLOTS pinned buffers; read k uses slot k % SLOTS, so up to
+    SLOTS reads may be in flight before a buffer is reused, and `finish()` hands out a copy, never the pinned rows."""
+    SLOTS = 4
     CAP = 16384
+    _streams = {}      # device index -> side stream
+    _rings = {}        # (device index, box width, count dtype) -> [slots, next read number]
 
     def __init__(self, dets, num_scenes):
         self.dets, self.num_scenes, self.d = dets, num_scenes, dets["box_dim"]
         dev = dets["boxes"].device
-        if DetectionRead._stream is None:
-            DetectionRead._stream = torch.cuda.Stream(device=dev)
+        di = dev.index if dev.index is not None else torch.cuda.current_device()
+        stream = DetectionRead._streams.get(di)
+        if stream is None:
+            stream = DetectionRead._streams[di] = torch.cuda.Stream(device=dev)
+        ring = DetectionRead._rings.setdefault((di, self.d, str(dets["count"].dtype)), [[None] * self.SLOTS, 0])
+        slot = ring[1] % self.SLOTS
+        ring[1] += 1
+        if ring[0][slot] is None:
+            ring[0][slot] = (torch.empty((self.CAP, self.d + 3), dtype=torch.float32).pin_memory(),
+                             torch.empty((1,), dtype=dets["count"].dtype).pin_memory())
+        full, self.count_host = ring[0][slot]
         done = torch.cuda.Event()
         done.record()
         cap = min(self.CAP, int(dets["boxes"].shape[0]))
         self.cap = cap
-        with torch.cuda.stream(DetectionRead._stream):
-            DetectionRead._stream.wait_event(done)
+        with torch.cuda.stream(stream):
+            stream.wait_event(done)
             packed = torch.cat((dets["boxes"][:cap, :self.d], dets["scores"][:cap, None], dets["labels"][:cap, None].float(),
                                 dets["scene"][:cap, None].float()), dim=1)
-            ring = DetectionRead._ring.setdefault((self.d, str(dets["count"].dtype)), [])
-            if len(ring) < 4:                 # four pinned staging buffers, reused round-robin
-                ring.append((torch.empty((self.CAP, self.d + 3), dtype=torch.float32).pin_memory(),
-                             torch.empty((1,), dtype=dets["count"].dtype).pin_memory()))
-            DetectionRead._next = (DetectionRead._next + 1) % 4
-            full, self.count_host = ring[DetectionRead._next % len(ring)]
             self.host = full[:cap]
             if cap:
                 self.host.copy_(packed, non_blocking=True)
@@ -773,15 +596,7 @@ class DetectionRead:
         n = int(self.count_host[0])
         if n > self.cap:                      # more detections than the staged rows: fall back to the blocking read
             return split_detections(self.dets, self.num_scenes)
-        d = self.d
-        packed = self.host[:n]
-        boxes, scores, labels, scene = packed[:, :d], packed[:, d], packed[:, d + 1].long(), packed[:, d + 2].long()
-        cnt = torch.bincount(scene, minlength=self.num_scenes).tolist() if n else [0] * self.num_scenes
-        out, lo = [], 0
-        for b in range(self.num_scenes):
-            out.append((boxes[lo:lo + cnt[b]], scores[lo:lo + cnt[b]], labels[lo:lo + cnt[b]]))
-            lo += cnt[b]
-        return out
+        return _split_packed(self.host[:n].clone(), self.d, self.num_scenes)
 
 
 # =============================================================================================== detector
@@ -797,7 +612,6 @@ class SingleStageSparse3DDetector(nn.Module):
         self.neck_with_head = Fcaf3DNeckWithHead(**neck_with_head)
         self.voxel_size = voxel_size
         self.train_cfg, self.test_cfg = train_cfg, test_cfg
-        self.batched_loss = True   # forward_train: whole-batch assigner + losses (False: the reference's per-scene loop)
         self.init_weights()
 
     def init_weights(self, pretrained=None):
@@ -810,30 +624,17 @@ class SingleStageSparse3DDetector(nn.Module):
         coords._b2_prefetch_stride = int(stem.stride) if isinstance(stem.stride, int) else int(stem.stride[0])
         return ME.SparseTensor(coordinates=coords, features=feats)
 
-    def extract_feat(self, points, img_metas=None):
-        x = self._input_tensor(points)
-        x = self.backbone(x)
-        return self.neck_with_head(x)
-
     def prepare(self, points, training=True):
         """Input tensor of a batch with all backbone coordinate / kernel maps already built (MEResNet3D.prebuild_maps);
         forward_train / extract_feat accept it in place of the point list."""
         return self.backbone.prebuild_maps(self._input_tensor(points), training=training)
 
     def forward_train(self, points, gt_bboxes_3d, gt_labels_3d, img_metas=None):
-        """single_stage_sparse.py:42-49.  gt_bboxes_3d: list of [B_i, 7] (gravity centre, size, yaw) tensors.
-        `points`: list of [N_i, 6] tensors, or the tensor returned by prepare()."""
+        """Losses of one batch (the call single_stage_sparse.py:42-49 makes), computed for all scenes at once.
+        gt_bboxes_3d: list of [B_i, 7] (gravity centre, size, yaw) tensors.  `points`: list of [N_i, 6] tensors, or the
+        tensor returned by prepare()."""
         x0 = points if isinstance(points, ME.SparseTensor) else self._input_tensor(points)
-        if self.batched_loss:
-            return self.neck_with_head.forward_train_batched(self.backbone(x0), gt_bboxes_3d, gt_labels_3d)
-        x = self.neck_with_head(self.backbone(x0))
-        return self.neck_with_head.loss(*x, gt_bboxes_3d, gt_labels_3d, img_metas)
-
-    @torch.no_grad()
-    def simple_test(self, points, img_metas, imgs=None, rescale=False):
-        """Reference-style inference (op by op, python loops over scenes / levels / classes)."""
-        x = self.extract_feat(points, img_metas)
-        return self.neck_with_head.get_bboxes(*x, img_metas, rescale=rescale)
+        return self.neck_with_head.forward_train_batched(self.backbone(x0), gt_bboxes_3d, gt_labels_3d)
 
     @torch.no_grad()
     def simple_test_fused(self, points, to_host=True):
@@ -851,21 +652,23 @@ class SingleStageSparse3DDetector(nn.Module):
         return self.neck_with_head.forward_fused(feats, want_max_score=True), x.coordinate_manager
 
 
-def build_fcaf3d(dataset="scannet", **overrides):
-    """FCAF3D detector with the hyper-parameters of configs/fcaf3d/fcaf3d.py:3-28 and the per-dataset overrides
-    (fcaf3d_scannet-3d-18class.py:4-8, fcaf3d_sunrgbd-3d-10class.py:4-7, fcaf3d_s3dis-3d-5class.py:4-8)."""
+def fcaf3d_config(dataset="scannet", **overrides):
+    """Constructor arguments of the detector with the hyper-parameters of configs/fcaf3d/fcaf3d.py:3-28 and the per-dataset
+    overrides (fcaf3d_scannet-3d-18class.py:4-8, fcaf3d_sunrgbd-3d-10class.py:4-7, fcaf3d_s3dis-3d-5class.py:4-8)."""
     heads = {"scannet": (18, 6), "sunrgbd": (10, 8), "s3dis": (5, 6)}
     n_classes, n_reg = heads[dataset]
     voxel_size = overrides.pop("voxel_size", 0.01)
+    n_outs = overrides.pop("n_outs", 4)
     cfg = dict(
-        backbone=dict(in_channels=3, depth=overrides.pop("depth", 34), n_outs=overrides.pop("n_outs", 4)),
-        neck_with_head=dict(n_classes=n_classes, in_channels=(64, 128, 256, 512), out_channels=128, n_reg_outs=n_reg,
-                            voxel_size=voxel_size, pts_threshold=overrides.pop("pts_threshold", 100000),
-                            assigner=dict(type="Fcaf3DAssigner", limit=27, topk=18, n_scales=4),
+        backbone=dict(in_channels=3, depth=overrides.pop("depth", 34), n_outs=n_outs),
+        neck_with_head=dict(n_classes=n_classes, in_channels=(64, 128, 256, 512)[:n_outs], out_channels=128,
+                            n_reg_outs=n_reg, voxel_size=voxel_size, pts_threshold=overrides.pop("pts_threshold", 100000),
+                            assigner=dict(type="Fcaf3DAssigner", limit=27, topk=18, n_scales=n_outs),
                             loss_bbox=dict(type="IoU3DLoss", loss_weight=1.0, with_yaw=(dataset == "sunrgbd"))),
         voxel_size=voxel_size, train_cfg=dict(), test_cfg=dict(nms_pre=1000, iou_thr=.5, score_thr=.01))
-    n_outs = cfg["backbone"]["n_outs"]
-    cfg["neck_with_head"]["in_channels"] = cfg["neck_with_head"]["in_channels"][:n_outs]
-    cfg["neck_with_head"]["assigner"]["n_scales"] = n_outs
     assert not overrides, f"unknown overrides {overrides}"
-    return SingleStageSparse3DDetector(**cfg)
+    return cfg
+
+
+def build_fcaf3d(dataset="scannet", **overrides):
+    return SingleStageSparse3DDetector(**fcaf3d_config(dataset, **overrides))

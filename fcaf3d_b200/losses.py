@@ -9,9 +9,8 @@ Mirrors the callables the reference builds by registry name (fcaf3d_neck_with_he
 """
 import torch
 import torch.nn as nn
-import torch.nn.functional as F
 
-from ._lib import call, ptr
+from ._lib import B2Error, call, ptr
 
 
 # ------------------------------------------------------------------------------------------- focal
@@ -51,6 +50,29 @@ class FocalLoss(nn.Module):
         return self.loss_weight * (loss.sum() / avg_factor if avg_factor is not None else loss.mean())
 
 
+class _BCEFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, target):
+        logits = logits.contiguous().float()
+        target = target.detach().contiguous().float()
+        loss, grad = torch.empty_like(logits), torch.empty_like(logits)
+        call("b2_bce_logits", ptr(logits), ptr(target), logits.numel(), ptr(loss), ptr(grad))
+        ctx.save_for_backward(grad)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        (grad,) = ctx.saved_tensors
+        return g * grad, None
+
+
+def bce_with_logits(logits, target):
+    """element-wise binary cross entropy with logits (value + gradient from one launch of b2_bce_logits)"""
+    if logits.shape != target.shape:
+        raise B2Error("bce_with_logits: logits %s and target %s differ in shape" % (tuple(logits.shape), tuple(target.shape)))
+    return _BCEFn.apply(logits, target)
+
+
 class CrossEntropyLoss(nn.Module):
     def __init__(self, use_sigmoid=False, use_mask=False, reduction="mean", class_weight=None, loss_weight=1.0):
         super().__init__()
@@ -59,7 +81,7 @@ class CrossEntropyLoss(nn.Module):
 
     def forward(self, cls_score, label, weight=None, avg_factor=None, reduction_override=None, **kw):
         reduction = reduction_override if reduction_override else self.reduction     # mmdet weight_reduce_loss rules
-        loss = F.binary_cross_entropy_with_logits(cls_score, label.float(), reduction="none")
+        loss = bce_with_logits(cls_score, label.float())
         if weight is not None:
             loss = loss * weight.reshape(loss.shape[0], -1)
         if avg_factor is None:
@@ -95,81 +117,56 @@ def axis_aligned_iou_3d(pred, target):
     return _AxisAlignedIoUFn.apply(pred, target)
 
 
-def _box2corners(box):
-    """(n, 5) x, y, w, h, alpha -> (n, 4, 2) corners (oriented_iou_loss.py:6-35)"""
-    x, y, w, h, alpha = box[:, 0:1], box[:, 1:2], box[:, 2:3], box[:, 3:4], box[:, 4:5]
-    x4 = box.new_tensor([0.5, -0.5, -0.5, 0.5]) * w
-    y4 = box.new_tensor([0.5, 0.5, -0.5, -0.5]) * h
-    corners = torch.stack([x4, y4], dim=-1)
-    sin, cos = torch.sin(alpha), torch.cos(alpha)
-    rot_t = torch.stack([torch.cat([cos, sin], -1), torch.cat([-sin, cos], -1)], dim=-2)
-    rotated = torch.bmm(corners, rot_t)
-    return rotated + torch.stack([x, y], dim=-1)
+class _RotatedIoUFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pred, target):
+        pred = pred.contiguous().float()
+        target = target.detach().contiguous().float()
+        n = pred.shape[0]
+        iou = torch.empty((n,), dtype=torch.float32, device=pred.device)
+        dpred = torch.empty_like(pred)
+        call("b2_rot_iou3d", ptr(pred), ptr(target), n, ptr(iou), ptr(dpred))
+        ctx.save_for_backward(dpred)
+        return iou
+
+    @staticmethod
+    def backward(ctx, g):
+        (dpred,) = ctx.saved_tensors
+        return g.unsqueeze(1) * dpred, None
 
 
-def _sort_vertices(vertices, mask):
-    """the un-vendored cuda_op.sort_v (box_intersection_2d.py:131-147) on our kernel"""
-    num_valid = mask.sum(dim=1).int()
-    mean = (vertices * mask.unsqueeze(-1).float()).sum(dim=1, keepdim=True) / num_valid.view(-1, 1, 1)
-    vn = (vertices - mean).detach().contiguous().float()
-    idx = torch.empty((vertices.shape[0], 9), dtype=torch.int32, device=vertices.device)
-    m8 = mask.to(torch.uint8).contiguous()
-    call("b2_sort_vertices", ptr(vn), ptr(m8), ptr(num_valid.contiguous()), vertices.shape[0], ptr(idx))
-    return idx.long()
+def rotated_iou_3d(pred, target):
+    """cal_iou_3d (oriented_iou_loss.py:86-109) for aligned pairs (n, 7) x, y, z, w, l, h, alpha: value and the gradient
+    w.r.t. `pred` from one kernel launch (b2_rot_iou3d); `target` is treated as constant, as the head uses it."""
+    if pred.shape[-1] != 7 or target.shape[-1] != 7:
+        raise B2Error("rotated_iou_3d takes (n, 7) boxes")
+    return _RotatedIoUFn.apply(pred, target)
 
 
-def rotated_iou_2d(box1, box2):
-    """differentiable IoU of aligned pairs of rotated rectangles (n, 5); follows box_intersection_2d.py:13-183 and
-    oriented_iou_loss.py:38-58 (torch composition + angular sort kernel).  Returns (iou, union)."""
-    eps = 1e-8
-    c1, c2 = _box2corners(box1), _box2corners(box2)
-    # edge intersections (box_intersection_th)
-    l1 = torch.cat([c1, c1[:, [1, 2, 3, 0], :]], dim=2)
-    l2 = torch.cat([c2, c2[:, [1, 2, 3, 0], :]], dim=2)
-    e1 = l1.unsqueeze(2).expand(-1, -1, 4, -1)
-    e2 = l2.unsqueeze(1).expand(-1, 4, -1, -1)
-    x1, y1, x2, y2 = e1[..., 0], e1[..., 1], e1[..., 2], e1[..., 3]
-    x3, y3, x4, y4 = e2[..., 0], e2[..., 1], e2[..., 2], e2[..., 3]
-    num = (x1 - x2) * (y3 - y4) - (y1 - y2) * (x3 - x4)
-    den_t = (x1 - x3) * (y3 - y4) - (y1 - y3) * (x3 - x4)
-    t = torch.where(num == 0, torch.full_like(num, -1.), den_t / num)
-    mask_t = (t > 0) & (t < 1)
-    den_u = (x1 - x2) * (y1 - y3) - (y1 - y2) * (x1 - x3)
-    u = torch.where(num == 0, torch.full_like(num, -1.), -den_u / num)
-    mask_u = (u > 0) & (u < 1)
-    mask_inter = mask_t & mask_u
-    t = den_t / (num + eps)
-    inters = torch.stack([x1 + t * (x2 - x1), y1 + t * (y2 - y1)], dim=-1) * mask_inter.float().unsqueeze(-1)
+class _DecodedIoUFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, points, bbox_pred, target, yaw_mode, rotated):
+        points = points.detach().contiguous().float()
+        bbox_pred = bbox_pred.contiguous().float()
+        target = target.detach().contiguous().float()
+        n, n_reg = bbox_pred.shape
+        iou = torch.empty((n,), dtype=torch.float32, device=bbox_pred.device)
+        dbbox = torch.empty_like(bbox_pred)
+        call("b2_box_iou_decoded", ptr(points), ptr(bbox_pred), n_reg, int(yaw_mode), ptr(target), int(bool(rotated)), n,
+             ptr(iou), ptr(dbbox))
+        ctx.save_for_backward(dbbox)
+        return iou
 
-    def in_box(ca, cb):  # corners of a inside b (box1_in_box2)
-        a, b, d = cb[:, 0:1, :], cb[:, 1:2, :], cb[:, 3:4, :]
-        ab, am, ad = b - a, ca - a, d - a
-        p_ab, n_ab = (ab * am).sum(-1), (ab * ab).sum(-1)
-        p_ad, n_ad = (ad * am).sum(-1), (ad * ad).sum(-1)
-        return (p_ab / n_ab > -1e-6) & (p_ab / n_ab < 1 + 1e-6) & (p_ad / n_ad > -1e-6) & (p_ad / n_ad < 1 + 1e-6)
-
-    c12, c21 = in_box(c1, c2), in_box(c2, c1)
-    n = box1.shape[0]
-    vertices = torch.cat([c1, c2, inters.reshape(n, 16, 2)], dim=1)
-    mask = torch.cat([c12, c21, mask_inter.reshape(n, 16)], dim=1)
-    idx = _sort_vertices(vertices, mask)
-    sel = torch.gather(vertices, 1, idx.unsqueeze(-1).expand(-1, -1, 2))
-    total = (sel[:, :-1, 0] * sel[:, 1:, 1] - sel[:, :-1, 1] * sel[:, 1:, 0]).sum(dim=1)
-    inter_area = total.abs() / 2
-    union = box1[:, 2] * box1[:, 3] + box2[:, 2] * box2[:, 3] - inter_area
-    return inter_area / union, union
+    @staticmethod
+    def backward(ctx, g):
+        (dbbox,) = ctx.saved_tensors
+        return None, g.unsqueeze(1) * dbbox, None, None, None
 
 
-def rotated_iou_3d(b1, b2):
-    """cal_iou_3d (oriented_iou_loss.py:86-109) for aligned pairs (n, 7) x, y, z, w, h, l, alpha"""
-    zmax1, zmin1 = b1[:, 2] + b1[:, 5] * 0.5, b1[:, 2] - b1[:, 5] * 0.5
-    zmax2, zmin2 = b2[:, 2] + b2[:, 5] * 0.5, b2[:, 2] - b2[:, 5] * 0.5
-    z_overlap = (torch.min(zmax1, zmax2) - torch.max(zmin1, zmin2)).clamp_min(0.)
-    iou_2d, u = rotated_iou_2d(b1[:, [0, 1, 3, 4, 6]], b2[:, [0, 1, 3, 4, 6]])
-    inter3d = iou_2d * u * z_overlap
-    v1 = b1[:, 3] * b1[:, 4] * b1[:, 5]
-    v2 = b2[:, 3] * b2[:, 4] * b2[:, 5]
-    return inter3d / (v1 + v2 - inter3d)
+def decoded_box_iou(points, bbox_pred, target, yaw_mode, rotated):
+    """IoU [n] between the boxes `bbox_pred` [n, 6|7|8] decodes to at `points` [n, 3] (_bbox_pred_to_bbox,
+    fcaf3d_neck_with_head.py:281-330) and `target` [n, 7]; decode, IoU and the gradient w.r.t. bbox_pred in one launch."""
+    return _DecodedIoUFn.apply(points, bbox_pred, target, yaw_mode, rotated)
 
 
 class IoU3DLoss(nn.Module):

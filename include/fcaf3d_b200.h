@@ -277,6 +277,20 @@ int b2_aa_iou3d(const float* pred, const float* tgt, long long n, int stride, fl
 /* Rotated_IoU cuda_op.sort_v (box_intersection_2d.py:147): vertices [n,24,2], mask [n,24] u8, num_valid [n] -> idx [n,9] */
 int b2_sort_vertices(const float* vertices, const uint8_t* mask, const int* num_valid, long long n, int* idx,
                      void* stream);
+/* Rotated 3-D IoU of aligned pairs of (x, y, z, w, l, h, alpha) boxes and d iou / d pred [n,7] (NULL = value only), one
+   launch: cal_iou_3d (oriented_iou_loss.py:86-109 -> :38-58, :6-35) -> oriented_box_intersection_2d
+   (box_intersection_2d.py:13-183) with the angular sort of the un-vendored cuda_op.sort_v done in-thread.  The gradient
+   is the one torch autograd gives for that graph (iou3d_loss.py:11-13 wraps it as 1 - iou). */
+int b2_rot_iou3d(const float* pred, const float* tgt, long long n, float* iou, float* dpred, void* stream);
+/* The head's regression loss in one launch: decode bbox_pred [n, n_reg] at points [n,3] (_bbox_pred_to_bbox,
+   fcaf3d_neck_with_head.py:281-330; yaw_mode 0 none, 1 naive, 2 sin-cos, 3 fcaf3d), IoU with tgt [n,7] (rotated != 0:
+   as b2_rot_iou3d; 0: axis-aligned, iou3d_loss.py:21-35 -> iou3d_calculator.py:279-312) -> iou [n] and
+   d iou / d bbox_pred [n, n_reg]. */
+int b2_box_iou_decoded(const float* points, const float* bbox_pred, int n_reg, int yaw_mode, const float* tgt,
+                       int rotated, long long n, float* iou, float* dbbox_pred, void* stream);
+/* element-wise binary cross entropy with logits and d/dx (fcaf3d_neck_with_head.py:191-193 -> mmdet 2.14
+   CrossEntropyLoss(use_sigmoid=True) -> F.binary_cross_entropy_with_logits) */
+int b2_bce_logits(const float* x, const float* t, long long n, float* loss, float* grad, void* stream);
 
 #ifdef __cplusplus
 }

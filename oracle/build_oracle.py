@@ -3,14 +3,21 @@
   oracle/_build/libnms_oracle.so   gcc, from oracle/nms_oracle.c (our C restatement)          -- always
   oracle/_ref/libpcdet_ref_cpu.so  g++, the reference's iou3d_cpu.cpp where it lies            -- if /root/reference exists
   oracle/_ref/libpcdet_ref_cuda.so nvcc sm_100a, the reference's iou3d_nms_kernel.cu           -- if /root/reference exists
-Reference sources are never copied; _ref/ holds binaries only (git-ignored, shipped to the GPU box).
+  oracle/_ref/py/mmdet3d/models/…  the reference's three FCAF3D model files, byte for byte       -- if /root/reference exists
+Reference sources never enter the repository: _ref/ is git-ignored build output that ships to the GPU box with the
+snapshot, like the two libraries.  The staged .py files exist so that the `-m gpu` tests can run the reference's own model
+code, unmodified, on the product's operator surfaces (fcaf3d_b200.compat) on a box that has no /root/reference.
 """
 import os
+import shutil
 import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 REF = os.environ.get("FCAF3D_REFERENCE", "/root/reference")
 REF_SRC = os.path.join(REF, "mmdet3d", "ops", "pcdet_nms", "src")
+REF_PY = ("mmdet3d/models/backbones/me_resnet.py", "mmdet3d/models/dense_heads/fcaf3d_neck_with_head.py",
+          "mmdet3d/models/detectors/single_stage_sparse.py")
+STAGED_PY = os.path.join(HERE, "_ref", "py")
 
 
 def _run(cmd):
@@ -47,11 +54,19 @@ def build(force=False):
             _run(["/usr/local/cuda/bin/nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-w", "-shared",
                   "-Xcompiler", "-fPIC", '-DREF_CUDA_SRC="%s"' % cuda_src, "-o", out, wrap])
         built["ref_cuda"] = out
+        for rel in REF_PY:                      # unmodified copies next to the binaries (never tracked by git)
+            src, dst = os.path.join(REF, rel), os.path.join(STAGED_PY, rel)
+            if force or _stale(dst, [src]):
+                os.makedirs(os.path.dirname(dst), exist_ok=True)
+                shutil.copyfile(src, dst)
+        built["ref_py"] = STAGED_PY
     else:
         for name in ("libpcdet_ref_cpu.so", "libpcdet_ref_cuda.so"):
             p = os.path.join(rdir, name)
             if os.path.exists(p):
                 built["ref_cpu" if "cpu" in name else "ref_cuda"] = p
+        if all(os.path.exists(os.path.join(STAGED_PY, rel)) for rel in REF_PY):
+            built["ref_py"] = STAGED_PY
     return built
 
 

@@ -1,6 +1,8 @@
 """GPU end-to-end parity against the committed golden vectors, which tests/golden/make_golden.py produced by running
 the reference's own model files (me_resnet.py, fcaf3d_neck_with_head.py, single_stage_sparse.py) on the CPU oracle
-with identical (name-keyed) weights and identical points.
+with identical (name-keyed) weights and identical points.  "Both modes": (1) the SAME three reference files, unmodified,
+executed on the GPU on the product's MinkowskiEngine / pcdet_nms / loss surfaces (`ref_models`, fcaf3d_b200.compat), and
+(2) the product's fused path.
 
 Tolerances: head outputs after ~45 fp32 sparse convolutions — 2e-3 of the column's max |value| (fp32 path, both
 execution modes); bf16 tensor-core path — 6e-2.  Coordinates / row counts are exact."""
@@ -14,6 +16,7 @@ from conftest import GOLDEN
 from fcaf3d_b200 import me as ME
 from fcaf3d_b200.detector import build_fcaf3d
 from fcaf3d_b200.testing import canonical_order, deterministic_init
+from util import reference_detections, reference_twin
 
 pytestmark = pytest.mark.gpu
 
@@ -70,11 +73,12 @@ def _levels_from_fused(levels, cm):
 
 
 @pytest.mark.parametrize("name,dataset", [("fcaf3d_tiny_scannet.npz", "scannet"), ("fcaf3d_tiny_sunrgbd.npz", "sunrgbd")])
-def test_forward_matches_golden_both_modes(dev, name, dataset):
+def test_forward_matches_golden_both_modes(dev, ref_models, name, dataset):
     g, det, pts = _load(name, dataset, dev)
+    ref = reference_twin(ref_models, det, dataset)
     ME.set_compute_dtype(torch.float32)
     with torch.no_grad():
-        x = det.extract_feat(pts)
+        x = ref.extract_feat(pts, None)
         _check_levels(g, _levels_from_reference_style(x, det.voxel_size), len(pts), 2e-3)
         levels, cm = det.forward_features_fused(pts)
         _check_levels(g, _levels_from_fused(levels, cm), len(pts), 2e-3)
@@ -107,11 +111,12 @@ def _match(boxes, scores, labels, g, b, box_tol=2e-3):
 
 
 @pytest.mark.parametrize("name,dataset", [("fcaf3d_tiny_scannet.npz", "scannet"), ("fcaf3d_tiny_sunrgbd.npz", "sunrgbd")])
-def test_detections_match_golden_both_modes(dev, name, dataset):
+def test_detections_match_golden_both_modes(dev, ref_models, name, dataset):
     g, det, pts = _load(name, dataset, dev)
+    ref = reference_twin(ref_models, det, dataset)
     ME.set_compute_dtype(torch.float32)
-    metas = [dict() for _ in pts]
-    ref_style = det.simple_test(pts, metas)
+    with torch.no_grad():
+        ref_style = reference_detections(ref, [list(a) for a in ref.extract_feat(pts, None)], len(pts))
     fused = det.simple_test_fused(pts)
     for b in range(len(pts)):
         _match(*ref_style[b], g, b)
@@ -120,10 +125,13 @@ def test_detections_match_golden_both_modes(dev, name, dataset):
         assert abs(len(ref_style[b][0]) - len(fused[b][0])) <= 2
 
 
-def test_fused_tail_equals_reference_style_tail_on_same_head_outputs(dev):
-    """Same head outputs in, same detections out (bit-exact keep-sets): isolates top-k / decode / NMS batching."""
+def test_fused_tail_equals_reference_tail_on_same_head_outputs(dev, ref_models):
+    """Same head outputs in, same detections out (bit-exact keep-sets): the product's batched top-k / decode / NMS against
+    the reference's own `_get_bboxes_single` (fcaf3d_neck_with_head.py:227-253, python loops, per-class pcdet NMS)."""
+    from fcaf3d_b200 import compat
     g, det, pts = _load("fcaf3d_tiny_scannet.npz", "scannet", dev)
     head = det.neck_with_head
+    ref_head = reference_twin(ref_models, det, "scannet").neck_with_head
     with torch.no_grad():
         levels, cm = det.forward_features_fused(pts)
         dets = head.get_bboxes_fused(levels, cm)
@@ -141,6 +149,6 @@ def test_fused_tail_equals_reference_style_tail_on_same_head_outputs(dev):
                 sl = slice(m.off_host[b], m.off_host[b + 1])
                 cs.append(l["centerness"][sl]), bs.append(l["bbox_pred"][sl]), ss.append(l["cls"][sl])
                 ps.append(m.coords[sl, 1:] * det.voxel_size)
-            boxes, scores, labels = head._get_bboxes_single(cs, bs, ss, ps, dict())
+            boxes, scores, labels = ref_head._get_bboxes_single(cs, bs, ss, ps, dict(box_type_3d=compat.DepthInstance3DBoxes))
             key = lambda B, S, L: sorted(zip(L.tolist(), [round(float(s), 6) for s in S.tolist()]))
-            assert key(boxes.cpu(), scores.cpu(), labels.cpu()) == key(*fused[b])
+            assert key(boxes.tensor.cpu(), scores.cpu(), labels.cpu()) == key(*fused[b])

@@ -63,38 +63,49 @@ def test_state_dict_and_config_match_the_reference_files():
         assert c["test_cfg"] == ours.neck_with_head.test_cfg and c["voxel_size"] == ours.voxel_size
 
 
-@pytest.mark.skipif(not ref_loader.available(), reason="reference tree absent (GPU box)")
-def test_reference_backbone_file_builds_on_our_me_surface(lib_built):
-    """Drop-in check that needs no GPU: the reference's me_resnet.py, imported unmodified with fcaf3d_b200.me
-    registered as `MinkowskiEngine`, constructs the same module tree (forward needs a GPU)."""
-    import importlib.util
+def _reference_root():
+    from fcaf3d_b200 import compat
+    from oracle import build_oracle
+    for root in (ref_loader.REF, build_oracle.STAGED_PY):
+        if compat.reference_files_present(root):
+            return root
+    return None
+
+
+@pytest.mark.skipif(_reference_root() is None, reason="reference model files neither checked out nor staged")
+def test_reference_model_files_build_on_the_product_surfaces(lib_built):
+    """Drop-in check that needs no GPU: the reference's three model files, imported unmodified by fcaf3d_b200.compat
+    (product ME surface, pcdet_nms, loss registry), construct the same module tree as the product's mirror, with the
+    product's loss / NMS callables bound where the reference looks them up (a forward needs a GPU)."""
     import sys
-    import types
-    import fcaf3d_b200
-    saved = {k: sys.modules.get(k) for k in ("MinkowskiEngine", "MinkowskiEngine.modules",
-                                              "MinkowskiEngine.modules.resnet_block", "mmdet", "mmdet.models")}
+    from fcaf3d_b200 import compat, losses, me, pcdet_nms
+    from fcaf3d_b200.detector import build_fcaf3d
+    saved = dict(sys.modules)
     try:
-        me = fcaf3d_b200.install_as_minkowski_engine()
-        reg = types.SimpleNamespace(register_module=lambda *a, **k: (lambda cls: cls))
-        sys.modules["mmdet"] = types.ModuleType("mmdet")
-        sys.modules["mmdet.models"] = types.SimpleNamespace(BACKBONES=reg, DETECTORS=reg)
-        path = os.path.join(ref_loader.REF, "mmdet3d/models/backbones/me_resnet.py")
-        spec = importlib.util.spec_from_file_location("ref_me_resnet_on_b200", path)
-        mod = importlib.util.module_from_spec(spec)
-        spec.loader.exec_module(mod)
-        net = mod.MEResNet3D(3, 34)
-        net.init_weights()
-        from fcaf3d_b200.detector import MEResNet3D
-        ours = MEResNet3D(3, 34)
-        assert list(net.state_dict().keys()) == list(ours.state_dict().keys())
+        ns = compat.load_reference_models(_reference_root())
+        for dataset in ("scannet", "sunrgbd", "s3dis"):
+            ref = compat.reference_detector(ns, dataset)
+            ours = build_fcaf3d(dataset)
+            rs, os_ = ref.state_dict(), ours.state_dict()
+            assert list(rs.keys()) == list(os_.keys())
+            assert all(rs[k].shape == os_[k].shape for k in rs)
+            ref.load_state_dict(os_, strict=True)
+            head = ref.neck_with_head
+            assert isinstance(head.loss_cls, losses.FocalLoss) and isinstance(head.loss_bbox, losses.IoU3DLoss)
+            assert head.loss_bbox.with_yaw == (dataset == "sunrgbd")
+            assert type(head.assigner).__module__.endswith("fcaf3d_neck_with_head")     # the reference's own assigner
+        net = ref.backbone
         assert isinstance(net.conv1[0], me.MinkowskiConvolution) and net.conv1[0].kernel.shape == (27, 3, 64)
         assert net.layer1[0].downsample[0].kernel.shape == (1, 64, 64)      # K == 1 but stride 2 -> [1, in, out]
+        mod = sys.modules["mmdet3d.models.dense_heads.fcaf3d_neck_with_head"]
+        assert mod.pcdet_nms_gpu is pcdet_nms.pcdet_nms_gpu and mod.ME is me
+        assert open(mod.__file__, "rb").read() == open(
+            os.path.join(_reference_root(), "mmdet3d/models/dense_heads/fcaf3d_neck_with_head.py"), "rb").read()
     finally:
-        for k, v in saved.items():
-            if v is None:
-                sys.modules.pop(k, None)
-            else:
-                sys.modules[k] = v
+        for k in list(sys.modules):
+            if k not in saved:
+                del sys.modules[k]
+        sys.modules.update(saved)
 
 
 def test_checkpoint_round_trip_in_the_reference_format(tmp_path):

@@ -9,7 +9,7 @@ from fcaf3d_b200 import me as ME
 from fcaf3d_b200.detector import MEResNet3D, build_fcaf3d
 from fcaf3d_b200.scenes import make_scene
 from fcaf3d_b200.testing import deterministic_init
-from util import rel_err
+from util import reference_detections, reference_twin, rel_err
 
 pytestmark = pytest.mark.gpu
 
@@ -32,14 +32,15 @@ def test_tensor_field_quantise_and_slice(dev):
 
 
 @pytest.mark.parametrize("n_outs,voxel", [(2, 0.02), (3, 0.01)])
-def test_two_and_three_scale_variants(dev, n_outs, voxel):
+def test_two_and_three_scale_variants(dev, ref_models, n_outs, voxel):
     """configs/fcaf3d/fcaf3d_{2,3}scales_scannet-3d-18class.py: fewer levels (and 2 cm voxels for the 2-scale one)"""
     det = deterministic_init(build_fcaf3d("scannet", n_outs=n_outs, voxel_size=voxel), 0, cls_bias=0.0).to(dev).eval()
     pts = [torch.from_numpy(make_scene("tiny", s, 3000)[0]).to(dev) for s in (1, 2)]
     ME.set_compute_dtype(torch.float32)
     with torch.no_grad():
         fused = det.simple_test_fused(pts)
-        ref = det.simple_test(pts, [dict(), dict()])
+        twin = reference_twin(ref_models, det, "scannet", n_outs=n_outs, voxel_size=voxel)
+        ref = reference_detections(twin, [list(a) for a in twin.extract_feat(pts, None)], 2)
     assert len(fused) == 2
     for (b, s, l), (rb, rs, rl) in zip(fused, ref):
         assert b.shape[1] == 6 and abs(len(b) - len(rb)) <= 2 and len(b) > 0
@@ -145,10 +146,10 @@ def test_mefpn3d_matches_reference_golden(dev):
 
 
 @pytest.mark.parametrize("dtype,thr", [(torch.float32, 4000), (torch.bfloat16, 4000), (torch.float32, 700)])
-def test_prune_before_up_block_convolution_gives_the_same_rows(dev, dtype, thr):
+def test_prune_before_up_block_convolution_gives_the_same_rows(dev, ref_models, dtype, thr):
     """forward_fused, eval: the up-block's 3^3 convolution evaluated at the surviving rows only (tables derived from the
     parent's) against convolve-everything-then-prune: same coordinates, bit-identical head outputs; the derived table of
-    the pruned map equals the hash-built one; and the op-by-op reference-style path agrees within the fp32 tolerance.
+    the pruned map equals the hash-built one; and the reference's own files, run op by op, agree within the fp32 tolerance.
     thr = 4000: only the finest level prunes (the shape of the real workloads); thr = 700: the ts16 level prunes too, after
     which backbone rows whose parents were dropped reach the union and the finest level takes the general path."""
     from fcaf3d_b200 import detector as D
@@ -165,7 +166,8 @@ def test_prune_before_up_block_convolution_gives_the_same_rows(dev, dtype, thr):
                 levels, cm = det.forward_features_fused(pts)
             outs[flag] = (levels, cm)
         with torch.no_grad():
-            ref = det.extract_feat(pts) if dtype == torch.float32 else None
+            ref = (reference_twin(ref_models, det, "scannet", pts_threshold=thr).extract_feat(pts, None)
+                   if dtype == torch.float32 else None)
     finally:
         D.PRUNE_BEFORE_CONV = True
         ME.set_compute_dtype(torch.float32)

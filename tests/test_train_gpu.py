@@ -191,18 +191,28 @@ def test_batched_assigner_equals_per_scene(dev):
     assert int(n_pos[1]) == 0 and int(n_pos.sum()) > 0
 
 
-@pytest.mark.parametrize("batched", [True, False], ids=["batched_loss", "per_scene_loss"])
+@pytest.mark.parametrize("mode", ["product_batched_loss", "reference_files"])
 @pytest.mark.parametrize("name,dataset", [("train_tiny_scannet.npz", "scannet"), ("train_tiny_sunrgbd.npz", "sunrgbd")])
-def test_training_step_matches_reference_golden(dev, name, dataset, batched):
+def test_training_step_matches_reference_golden(dev, ref_models, name, dataset, mode):
+    """One training step (losses + sampled parameter gradients) against the golden the reference's own files produced on
+    the CPU oracle: (1) the product's whole-batch path, (2) the reference's three files themselves (`forward_train`
+    of single_stage_sparse.py:42-49 -> per-scene `_loss_single` + `Fcaf3DAssigner.assign`, unmodified) running on the GPU
+    through the product's autograd-enabled ME surface and loss kernels."""
+    from fcaf3d_b200 import compat
+    from util import reference_twin
     g = np.load(os.path.join(GOLDEN, name))
     det = deterministic_init(build_fcaf3d(dataset), seed=1).to(dev).train()
-    det.batched_loss = batched
     nb = len(g["seeds"])
     pts = [torch.from_numpy(g["points_%d" % i]).to(dev) for i in range(nb)]
     gtb = [torch.from_numpy(g["gt_%d" % i]).to(dev) for i in range(nb)]
     gtl = [torch.from_numpy(g["gt_labels_%d" % i]).to(dev) for i in range(nb)]
     ME.set_compute_dtype(torch.float32)
-    losses = det.forward_train(pts, gtb, gtl)
+    if mode == "reference_files":
+        det = reference_twin(ref_models, det, dataset)
+        boxes = [compat.DepthInstance3DBoxes(b, origin=(.5, .5, .5)) for b in gtb]
+        losses = det.forward_train(pts, boxes, gtl, [dict() for _ in pts])
+    else:
+        losses = det.forward_train(pts, gtb, gtl)
     for k, v in losses.items():
         assert abs(v.item() - float(g[k])) < 2e-3 * abs(float(g[k])), (k, v.item(), float(g[k]))
     sum(losses.values()).backward()

@@ -37,3 +37,26 @@ def sort_rows(coords, *others):
 def rel_err(a, b):
     a, b = a.float().cpu(), b.float().cpu()
     return ((a - b).abs().max() / b.abs().max().clamp(min=1e-12)).item()
+
+
+def reference_twin(ref_models, det, dataset, **overrides):
+    """The REFERENCE's detector class (its own three files, fcaf3d_b200.compat) with the same hyper-parameters, weights,
+    device and train / eval mode as the product detector `det`."""
+    from fcaf3d_b200 import compat
+    ref = compat.reference_detector(ref_models, dataset, **overrides)
+    missing = ref.load_state_dict(det.state_dict(), strict=True)
+    assert not missing.missing_keys and not missing.unexpected_keys
+    ref = ref.to(next(det.parameters()).device)
+    return ref.train() if det.training else ref.eval()
+
+
+def reference_detections(ref, x, n_scenes):
+    """get_bboxes of the reference head -> [(boxes [n, 6|7] gravity centre, scores, labels)] like the fused path returns"""
+    from fcaf3d_b200 import compat
+    metas = [dict(box_type_3d=compat.DepthInstance3DBoxes)] * n_scenes
+    out = []
+    for boxes, scores, labels in ref.neck_with_head.get_bboxes(*x, metas):
+        t = boxes.tensor.clone()
+        t[:, 2] += t[:, 5] * 0.5
+        out.append((t if boxes.with_yaw else t[:, :6], scores, labels))
+    return out
