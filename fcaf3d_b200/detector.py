@@ -236,6 +236,7 @@ class Fcaf3DNeckWithHead(nn.Module):
         self.train_cfg = train_cfg
         self.test_cfg = test_cfg or dict(nms_pre=1000, iou_thr=.5, score_thr=.01)
         self.n_classes, self.n_reg_outs = n_classes, n_reg_outs
+        self.trace = None          # set to a dict to record every level's prune scores / mask in forward_fused
         assigner = dict(assigner or dict(limit=27, topk=18, n_scales=len(in_channels)))
         assigner.pop("type", None)
         self.assigner = Fcaf3DAssigner(**assigner)
@@ -407,6 +408,8 @@ class Fcaf3DNeckWithHead(nn.Module):
                     table, cap = pm.ensure_table()
                     sc = ops.interp(table, cap, prev["prune"], pm.ts, um.coords.float())
                     mask = ops.topk_mask(sc.reshape(-1), um.off_dev, um.num_batches, self.pts_threshold)
+                    if self.trace is not None:     # tests: the prune decision (scores, mask) of this level
+                        self.trace[i] = dict(union_key=ukey, scores=sc, mask=mask)
                     keep = [min(um.off_host[b + 1] - um.off_host[b], self.pts_threshold) for b in range(um.num_batches)]
                     key, m8, pos, n_keep = cm.prune(ukey, mask, keep_counts=keep)   # top-k keeps exactly min(N_b, k) rows
                 if (need_prune and PRUNE_BEFORE_CONV and not bn2.bn.training and nu == cm.size(gkey)
@@ -420,6 +423,7 @@ class Fcaf3DNeckWithHead(nn.Module):
                     parent = cm.get_map(gkey).children_of
                     km_up, km_out = ops.kernel_map_children_pruned(cm.kernel_map(parent, parent, 3, 1), ksrc, g2k, n_keep)
                     cm.set_kernel_map(key, key, 3, 1, km_out)
+                    cm.set_kernel_map(gkey, key, 3, 1, km_up)
                     f = conv_bn_act(conv, bn2, g, km_up, n_keep, ops.ACT_ELU)
                     ops.scatter_rows(inputs[i].F.contiguous(), a2k, f, accumulate=True)
                 else:

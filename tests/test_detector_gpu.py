@@ -152,3 +152,26 @@ def test_fused_tail_equals_reference_tail_on_same_head_outputs(dev, ref_models):
             boxes, scores, labels = ref_head._get_bboxes_single(cs, bs, ss, ps, dict(box_type_3d=compat.DepthInstance3DBoxes))
             key = lambda B, S, L: sorted(zip(L.tolist(), [round(float(s), 6) for s in S.tolist()]))
             assert key(boxes.tensor.cpu(), scores.cpu(), labels.cpu()) == key(*fused[b])
+
+
+def test_two_detection_reads_in_flight_from_a_cold_start(dev):
+    """the pinned staging ring of DetectionRead must hand every in-flight read its own buffer from the first
+    call on, and finish() must return rows that a later read cannot overwrite."""
+    from fcaf3d_b200.detector import DetectionRead, split_detections
+    DetectionRead._rings.clear()                           # cold start: no staging buffer exists yet
+    g, det, pts = _load("fcaf3d_tiny_scannet.npz", "scannet", dev)
+    with torch.no_grad():
+        d1 = det.simple_test_fused(pts, to_host=False)
+        d2 = det.simple_test_fused([pts[1], pts[0]], to_host=False)
+        want1, want2 = split_detections(d1, len(pts)), split_detections(d2, len(pts))
+        r1 = DetectionRead(d1, len(pts))
+        r2 = DetectionRead(d2, len(pts))                   # enqueued before the first one is looked at
+        got1 = r1.finish()
+        later = [DetectionRead(d2, len(pts)) for _ in range(5)]     # more reads than ring slots after got1 was handed out
+        got2 = r2.finish()
+        for r in later:
+            r.finish()
+    assert len(want1[0][0]) != len(want2[0][0]) or not torch.equal(want1[0][0], want2[0][0])
+    for got, want in ((got1, want1), (got2, want2)):
+        for (b1, s1, l1), (b2, s2, l2) in zip(got, want):
+            assert torch.equal(b1, b2) and torch.equal(s1, s2) and torch.equal(l1, l2)
