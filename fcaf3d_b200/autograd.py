@@ -44,7 +44,7 @@ class SparseConvFn(torch.autograd.Function):
     """
 
     @staticmethod
-    def forward(ctx, feats, w, kmap, kmap_t, n_out, use_bf16):
+    def forward(ctx, feats, w, kmap, kmap_t, n_out, use_bf16, out_dtype=None):
         feats = feats.contiguous()
         wd = w.detach().contiguous()
         kvol, cin, cout = wd.shape
@@ -58,11 +58,13 @@ class SparseConvFn(torch.autograd.Function):
             x = ops.cast(feats, torch.bfloat16)
         # bf16 hand-over also for the CUDA-core stem (its [N2, 64] output is the largest activation of the network)
         out_dt = torch.bfloat16 if (BF16_ACTIVATIONS and (tc_fwd or (tc_on and cout % 8 == 0))) else torch.float32
+        if out_dtype is not None:             # e.g. the head's logits: fp32 out of the bf16 operands
+            out_dt = out_dtype
         out = ops.sparse_conv(x, wd, kmap, n_out, wt_bf16=wt, out_dtype=out_dt)
         ctx.save_for_backward(x, wd, wt_b)
         ctx.kmap, ctx.kmap_t, ctx.n_in = kmap, kmap_t, int(feats.shape[0])
         ctx.in_dtype = feats.dtype
-        if out_dt == torch.bfloat16:
+        if out_dt == torch.bfloat16 or out_dtype is not None:
             return out
         return out.to(feats.dtype) if feats.dtype != torch.float32 else out
 
@@ -87,7 +89,7 @@ class SparseConvFn(torch.autograd.Function):
         if want_w:
             gw = gb if x.dtype == torch.bfloat16 else (g if g.dtype in DT else g.float())   # fp32 x bf16 is a kernel flavour
             d_w = conv_wgrad(x, gw, ctx.kmap, kvol, cin, cout)
-        return d_feats, d_w, None, None, None, None
+        return d_feats, d_w, None, None, None, None, None
 
 
 class MaxPoolFn(torch.autograd.Function):

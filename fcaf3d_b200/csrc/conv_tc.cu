@@ -312,11 +312,8 @@ static int launch_tc_g(const void* in, const void* wt, const int* nbr, long long
                      const float* shift, const void* residual, int act, int ch_mod, void* out, cudaStream_t st) {
   using Cfg = TcCfg<BN, ST>;
   auto kern = k_conv_tc<BN, ST, TOut, GRP>;
-  static bool configured = false;  // per template instance; attribute is per device function
-  if (!configured) {
-    B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM));
-    configured = true;
-  }
+  static unsigned long long configured = 0;  // per template instance, one bit per device
+  if (int rc0 = b2_optin_smem((const void*)kern, Cfg::SMEM, &configured)) return rc0;
   CUtensorMap map_b;
   const int rc = b2_make_bf16_map(&map_b, wt, (long long)kvol * cout, cin, BN);
   if (rc) return rc;
@@ -342,16 +339,6 @@ static int launch_tc(const void* in, const void* wt, const int* nbr, long long l
                                       residual, act, ch_mod, out, st);
 }
 
-int b2_conv_tc2_dispatch(const void* in, const void* wt, const int* nbr, long long ld, const unsigned int* tile_mask,
-                         long long n_out, int cin, int cout, int kvol, const float* bias, const float* scale,
-                         const float* shift, const void* residual, int act, int ch_mod, void* out, int out_dtype,
-                         cudaStream_t st);
-
-int b2_conv_tma_dispatch(const void* in, long long n_in, const void* wt, const int* nbr, long long ld,
-                         const unsigned int* tile_mask, long long n_out, int cin, int cout, int kvol, const float* bias,
-                         const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
-                         int out_dtype, cudaStream_t st);
-
 extern "C" int b2_conv_tc(const void* in_bf16, long long n_in, const void* wt_bf16, const int* nbr, long long ld,
                           const unsigned int* tile_mask, const int* out_rows, long long n_out, int cin, int cout, int kvol, const float* bias,
                           const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
@@ -365,18 +352,6 @@ extern "C" int b2_conv_tc(const void* in_bf16, long long n_in, const void* wt_bf
   B2_CHECK_ARG(out_rows == nullptr || nbr != nullptr, "a row permutation needs a neighbour table");
   if (n_out == 0) return B2_OK;
   cudaStream_t st = (cudaStream_t)stream;
-  // two row tiles per CTA sharing each weight tile (conv_tc2.cu) halve the weight traffic but also halve the CTA count;
-  // measured on B200 it is 10-100 % SLOWER on every FCAF3D layer shape (profiles/r01_step2_summary.md), so it is
-  // opt-in (B2_TC2=1) and kept for the A/B record only
-  static const bool use_tc2 = (getenv("B2_TC2") && atoi(getenv("B2_TC2")) == 1);
-  if (use_tc2 && out_rows == nullptr && cout % 64 == 0 && n_out > TC_BM)
-    return b2_conv_tc2_dispatch(in_bf16, wt_bf16, nbr, ld, tile_mask, n_out, cin, cout, kvol, bias, scale, shift,
-                                residual, act, ch_mod, out, out_dtype, st);
-  // operand staging by TMA (gather4 + tile loads, conv_tma.cu) instead of per-thread cp.async; B2_TC_TMA=0/1 for A/B runs
-  static const bool use_tma = (getenv("B2_TC_TMA") && atoi(getenv("B2_TC_TMA")) == 1);
-  if (use_tma && out_rows == nullptr)
-    return b2_conv_tma_dispatch(in_bf16, n_in, wt_bf16, nbr, ld, tile_mask, n_out, cin, cout, kvol, bias, scale, shift,
-                                residual, act, ch_mod, out, out_dtype, st);
   const bool wide = (cout % 128 == 0);
   const bool mid = (cout % 64 == 0);
 #define TC_GO(BN, T)                                                                                               \

@@ -767,10 +767,14 @@ int b2_nms_greedy_batched(const float* boxes, const float* scores, const int* se
     const size_t dyn = (size_t)max_seg * (sizeof(float4) + sizeof(float2));
     if (nt >= 1024 && staged_ok && max_seg > 0 && dyn <= 160 * 1024) {
       auto kern = k_nms_greedy<false, 1024, true>;
-      static bool configured = false;
-      if (!configured) {
-        B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-        configured = true;
+      static unsigned long long configured = 0;   // one bit per device: the attribute is per device
+      {
+        int dev = 0;
+        B2_CUDA(cudaGetDevice(&dev));
+        if (dev >= 64 || !((configured >> dev) & 1ull)) {
+          B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+          if (dev < 64) configured |= 1ull << dev;
+        }
       }
       kern<<<nseg, 1024, dyn, st>>>(sb, prep, seg_off, thresh, keep, counts, max_seg);
     } else if (nt >= 1024) {

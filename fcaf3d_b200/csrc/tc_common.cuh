@@ -103,5 +103,8 @@ __device__ __forceinline__ void tma_tile_2d(uint32_t dst, const CUtensorMap* map
 }
 
 
-// host: 2-D bf16 tensor map [rows, cols], box [box_rows x 64 cols], 128B swizzle, zero fill (defined in conv_tma.cu)
+// host (tc_map.cu): 2-D tensor maps [rows, cols], box [box_rows x 128 bytes], 128B swizzle, zero fill
 int b2_make_bf16_map(CUtensorMap* map, const void* base, long long rows, int cols, int box_rows);
+int b2_make_tf32_map(CUtensorMap* map, const void* base, long long rows, int cols, int box_rows);
+// host: opt-in of one kernel to `bytes` of dynamic shared memory on the CURRENT device, once per device
+int b2_optin_smem(const void* func, int bytes, unsigned long long* done);

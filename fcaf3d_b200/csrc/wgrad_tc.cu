@@ -249,11 +249,8 @@ static int launch_wgrad_tc(const void* in, const void* dout, const int* nbr, lon
                            int cout, int kvol, float* dw, cudaStream_t st) {
   using Cfg = WgCfg<BN>;
   auto kern = k_wgrad_tc<BN, SHARE>;
-  static bool configured = false;
-  if (!configured) {
-    B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::smem_bytes(Cfg::STAGES)));
-    configured = true;
-  }
+  static unsigned long long configured = 0;   // one bit per device
+  if (int rc0 = b2_optin_smem((const void*)kern, Cfg::smem_bytes(Cfg::STAGES), &configured)) return rc0;
   constexpr int stages = Cfg::STAGES;  // measured: 3, 4 and 5 stages give the same time (not latency bound)
   static const int dbg = getenv("B2_WG_DEBUG") ? atoi(getenv("B2_WG_DEBUG")) : 0;  // timing experiments only
   const int nsub = kvol * (cin / 64);

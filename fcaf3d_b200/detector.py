@@ -19,6 +19,7 @@ import os
 import torch
 import torch.nn as nn
 
+from . import autograd as AG
 from . import me as ME
 from . import ops
 from .compat import Scale, bias_init_with_prob, reduce_mean
@@ -306,11 +307,14 @@ class Fcaf3DNeckWithHead(nn.Module):
                 cm = x.coordinate_manager
                 cm.union_prefetch(inputs[i - 1].coordinate_map_key, cm.generate_children(x.coordinate_map_key))
             out = getattr(self, f"out_block_{i}")(x)
+            # the three 1x1 heads (ME: three F.mm calls, fcaf3d_neck_with_head.py:257-264) as ONE GEMM over the concatenated
+            # kernels on the library's convolution kernels (identity map; tcgen05 forward / input gradient / weight
+            # gradient with bf16 rows, CUDA-core fp32 otherwise), fp32 logits in both modes like forward_fused
             w = torch.cat((self.centerness_conv.kernel, self.reg_conv.kernel, self.cls_conv.kernel), dim=1)
-            if out.F.dtype == torch.bfloat16:    # bf16 rows: tensor-core GEMM (fp32 accumulate), logits back to fp32
-                h = (out.F @ w.to(torch.bfloat16)).float()
-            else:
-                h = out.F @ w
+            n_col = w.shape[1]
+            wp = torch.nn.functional.pad(w, (0, (-n_col) % 64)).unsqueeze(0)
+            h = AG.SparseConvFn.apply(out.F, wp, None, None, out.F.shape[0], out.F.dtype == torch.bfloat16,
+                                      torch.float32)[:, :n_col]
             reg = h[:, 1:1 + self.n_reg_outs]
             bbox = torch.cat((torch.exp(self.scales[i](reg[:, :6])), reg[:, 6:]), dim=1)
             cls = h[:, 1 + self.n_reg_outs:] + self.cls_conv.bias

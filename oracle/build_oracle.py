@@ -2,7 +2,8 @@
 
   oracle/_build/libnms_oracle.so   gcc, from oracle/nms_oracle.c (our C restatement)          -- always
   oracle/_ref/libpcdet_ref_cpu.so  g++, the reference's iou3d_cpu.cpp where it lies            -- if /root/reference exists
-  oracle/_ref/libpcdet_ref_cuda.so nvcc sm_100a, the reference's iou3d_nms_kernel.cu           -- if /root/reference exists
+  oracle/_ref/libpcdet_ref_cuda.so nvcc sm_100a, the reference's iou3d_nms_kernel.cu + its host   -- if /root/reference exists
+                                   side iou3d_nms.cpp (on a pointer-only at::Tensor stand-in)
   oracle/_ref/py/mmdet3d/models/…  the reference's three FCAF3D model files, byte for byte       -- if /root/reference exists
 Reference sources never enter the repository: _ref/ is git-ignored build output that ships to the GPU box with the
 snapshot, like the two libraries.  The staged .py files exist so that the `-m gpu` tests can run the reference's own model
@@ -50,9 +51,11 @@ def build(force=False):
         built["ref_cpu"] = out
         out = os.path.join(rdir, "libpcdet_ref_cuda.so")
         wrap = os.path.join(HERE, "ref_wrap_cuda.cu")
-        if force or _stale(out, [wrap, cuda_src]):
+        host_wrap, host_src = os.path.join(HERE, "ref_wrap_nms_host.cpp"), os.path.join(REF_SRC, "iou3d_nms.cpp")
+        if force or _stale(out, [wrap, cuda_src, host_wrap, host_src]):
             _run(["/usr/local/cuda/bin/nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-w", "-shared",
-                  "-Xcompiler", "-fPIC", '-DREF_CUDA_SRC="%s"' % cuda_src, "-o", out, wrap])
+                  "-Xcompiler", "-fPIC", '-DREF_CUDA_SRC="%s"' % cuda_src, '-DREF_NMS_SRC="%s"' % host_src,
+                  "-I", os.path.join(HERE, "ref_stubs_host"), "-o", out, wrap, host_wrap])
         built["ref_cuda"] = out
         for rel in REF_PY:                      # unmodified copies next to the binaries (never tracked by git)
             src, dst = os.path.join(REF, rel), os.path.join(STAGED_PY, rel)

@@ -10,6 +10,7 @@ import os
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
 SCALE = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-3, "us": 1.0, "ms": 1e3, "usecond": 1.0,
          "nsecond": 1e-3, "msecond": 1e3}
 
@@ -43,7 +44,8 @@ def main(raw, out_csv, note):
                     "tensor_pipe_active_pct", "registers"])
         w.writerows(out)
     n = len(out)
-    js = {"kernel": "k_conv_tc (all instantiations)", "launches": n, "dram_bytes_read": tot["rd"], "dram_bytes_write": tot["wr"],
+    from bench import kernel_digest       # bench.py refuses a capture taken from another version of the kernel source
+    js = {"kernel": "k_conv_tc (all instantiations)", "kernel_digest": kernel_digest(), "launches": n, "dram_bytes_read": tot["rd"], "dram_bytes_write": tot["wr"],
           "dram_bytes_per_launch": (tot["rd"] + tot["wr"]) / n, "lts_bytes_per_launch": tot["lts"] / n,
           "time_us_cold": round(tot["t"], 2), "tensor_pipe_active_pct_time_weighted": tot["tw"] / tot["t"],
           "source": "ncu --set full --clock-control none -k regex:k_conv_tc, one inference step (BENCH_PROFILE=1 python bench.py); "

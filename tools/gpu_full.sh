@@ -8,7 +8,7 @@ for t in test_coord_gpu test_head_gpu test_nms_gpu test_conv_gpu test_detector_g
   r=$?; echo "$t exit $r: $(tail -n 1 gpurun_out/$t.log)"; [ $r -ne 0 ] && rc=1
 done
 timeout 300 python __graft_entry__.py --smoke > gpurun_out/smoke.log 2>&1; echo "smoke exit $?"
-timeout 600 python bench.py > gpurun_out/bench.log 2> gpurun_out/bench.err; echo "bench exit $?"
+timeout 900 python bench.py > gpurun_out/bench.log 2> gpurun_out/bench.err; echo "bench exit $?"
 timeout 600 python bench.py --workload sunrgbd > gpurun_out/bench_sun.log 2>> gpurun_out/bench.err; echo "bench sunrgbd exit $?"
 timeout 600 python bench.py --workload s3dis1m > gpurun_out/bench_s3dis.log 2>> gpurun_out/bench.err; echo "bench s3dis exit $?"
 timeout 600 python bench.py --mode train > gpurun_out/bench_train.log 2>> gpurun_out/bench.err; echo "bench train exit $?"

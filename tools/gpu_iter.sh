@@ -10,7 +10,7 @@ for t in ${TESTS:-test_coord_gpu test_conv_gpu test_head_gpu test_surface_gpu te
 done
 while read -r name envs args; do
   [ -z "$name" ] && continue
-  env $(echo "$envs" | tr ',' ' ') timeout 300 python bench.py --no-cpu-baseline $args > gpurun_out/bench_$name.log 2> gpurun_out/bench_$name.err
+  env $(echo "$envs" | tr ',' ' ') timeout 300 python bench.py --no-cpu-baseline --configs none $args > gpurun_out/bench_$name.log 2> gpurun_out/bench_$name.err
   echo "bench $name exit $?: $(python - <<P
 import json
 try:
