@@ -300,7 +300,7 @@ def bench_infer(ctx, args, workload, dtype_name, steps, warmup, clk=None, brief=
         # End to end through the public API: every step copies ITS inputs from pinned host memory and reads ITS detections
         # back, all inside one timed bracket; the copy of step i+1 is double-buffered on a side stream
         # (fcaf3d_b200.data.ScenePrefetcher) and overlaps the compute of step i; L2 is flushed inside the loop.
-        k_e2e = max(3, steps // 2)
+        k_e2e = max(5, steps)
         for pts in ScenePrefetcher((host_pts for _ in range(5)), dev):       # warm-up through the SAME path
             DetectionRead(det.simple_test_fused(pts, to_host=False), batch).finish()
         ctx.barrier()

@@ -620,6 +620,8 @@ class SingleStageSparse3DDetector(nn.Module):
         self.neck_with_head = Fcaf3DNeckWithHead(**neck_with_head)
         self.voxel_size = voxel_size
         self.train_cfg, self.test_cfg = train_cfg, test_cfg
+        self.use_engine = os.environ.get("B2_ENGINE", "1") != "0"     # native executor for eval-mode inference
+        self._engine = None
         self.init_weights()
 
     def init_weights(self, pretrained=None):
@@ -646,12 +648,29 @@ class SingleStageSparse3DDetector(nn.Module):
 
     @torch.no_grad()
     def simple_test_fused(self, points, to_host=True):
-        """B200 inference path: fused backbone / neck / head and the batched tail."""
+        """B200 inference path: fused backbone / neck / head and the batched tail.  In eval mode the whole step is handed to
+        the native executor (fcaf3d_b200.engine: the same library calls issued from C++, bit-identical results);
+        `use_engine = False`, per-kernel profiling, a prune trace or a Bottleneck backbone keep the python driver."""
+        if self._engine_ok():
+            dets = self._engine(points)
+            return split_detections(dets, len(points)) if to_host else dets
         x = self._input_tensor(points)
         feats = self.backbone.forward_fused(x)
         levels = self.neck_with_head.forward_fused(feats, want_max_score=True)
         dets = self.neck_with_head.get_bboxes_fused(levels, x.coordinate_manager)
         return split_detections(dets, len(points)) if to_host else dets
+
+    def _engine_ok(self):
+        from . import engine as E
+        if not (self.use_engine and not self.training and ops.PROFILE is None and ops._TC_ENABLED and PRUNE_BEFORE_CONV
+                and self.neck_with_head.trace is None and ops.SORT_MIN_ROWS == 0 and ME.STRIDED_FROM_INPUT == 1):
+            return False
+        if self._engine is None:
+            if not E.supported(self):
+                self.use_engine = False
+                return False
+            self._engine = E.InferenceEngine(self)
+        return True
 
     @torch.no_grad()
     def forward_features_fused(self, points):

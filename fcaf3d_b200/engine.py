@@ -1,0 +1,162 @@
+"""Native executor of the fused inference step (csrc/engine.cu) bound to a detector's weights.
+
+`detector.simple_test_fused` drives one step as ~200 C-ABI calls from python; on a B200 the interpreter then needs as long
+per batch as the GPU.  `InferenceEngine(det)` hands the SAME sequence of library calls to one C++ entry point
+(`b2_engine_infer`): same kernels, same arguments, bit-identical detections, a host cost of the launches alone.
+Eval mode only (BatchNorm folded), BasicBlock backbones (depth 14 / 18 / 34); anything else stays on the python path.
+"""
+import ctypes
+
+import torch
+
+from . import me as ME
+from . import ops
+from ._lib import B2Error, last_error, lib, ptr, stream
+from .me.modules.resnet_block import BasicBlock
+
+
+def supported(det):
+    bb = det.backbone
+    return all(isinstance(b, BasicBlock) for i in range(bb.n_outs) for b in getattr(bb, "layer%d" % (i + 1))) and \
+        det.neck_with_head._cfg("nms_pre") > 0 and bb.n_outs <= 4
+
+
+class InferenceEngine:
+    def __init__(self, det):
+        if not supported(det):
+            raise B2Error("InferenceEngine: BasicBlock backbones with nms_pre > 0 only")
+        self.det = det
+        self._handle = None
+        self._sig = None
+        self._arena = None
+        self._keep = []
+        self._tensors = None
+
+    # ---- weight table -------------------------------------------------------------------------------------------------
+    def _signature(self):
+        if self._tensors is None:
+            self._tensors = list(self.det.parameters()) + list(self.det.buffers())
+        return tuple((t._version, t.data_ptr()) for t in self._tensors)
+
+    def _rec(self, words, conv=None, bn=None, wt=None, w32=None, bias=None, kvol=None, cin=None, cout=None):
+        """one 8-word record: wt bf16, w fp32, scale, shift, bias, kvol, cin, cout"""
+        scale = shift = None
+        if conv is not None:
+            w32 = conv._w3()
+            wt = conv._wt_bf16() if (w32.shape[1] % 64 == 0 and w32.shape[2] % 32 == 0) else None
+            kvol, cin, cout = (int(v) for v in w32.shape)
+            bias = conv.bias.detach().reshape(-1).contiguous() if conv.bias is not None else None
+        if bn is not None:
+            s, b = bn.scale_shift(None)
+            scale, shift = s.reshape(-1).contiguous(), b.reshape(-1).contiguous()
+        self._keep += [wt, w32, scale, shift, bias]
+        words += [ptr(t) or 0 for t in (wt, w32, scale, shift, bias)] + [int(kvol or 0), int(cin or 0), int(cout or 0)]
+
+    def _build(self):
+        det, head, bb = self.det, self.det.neck_with_head, self.det.backbone
+        if any(m.training for m in det.modules() if isinstance(m, torch.nn.BatchNorm1d)):
+            raise B2Error("InferenceEngine runs the eval-mode network (call det.eval())")
+        self._destroy()
+        self._keep = []
+        L = bb.n_outs
+        conv, inorm, _, pool = bb.conv1
+        blocks = [len(getattr(bb, "layer%d" % (i + 1))) for i in range(L)] + [0] * (4 - L)
+        w, b, wt = head._head_weights()
+        yaw_mode = head._yaw_mode(head.n_reg_outs)
+        words = [0xB2E1, L, head.n_classes, head.n_reg_outs, yaw_mode, int(head.pts_threshold), int(head._cfg("nms_pre")),
+                 3 + conv.in_channels, int(w.shape[2])] + blocks + [0, 0, 0]
+        assert len(words) == 16
+        self._rec(words, conv=conv)
+        iw, ib = inorm.weight.detach().reshape(-1).contiguous(), inorm.bias.detach().reshape(-1).contiguous()
+        self._rec(words, wt=iw, w32=ib)
+        for i in range(L):
+            layer = getattr(bb, "layer%d" % (i + 1))
+            for blk in layer:
+                self._rec(words, conv=blk.conv1, bn=blk.norm1)
+                self._rec(words, conv=blk.conv2, bn=blk.norm2)
+            if layer[0].downsample is None:
+                raise B2Error("InferenceEngine: the first block of every stage must have a downsample branch")
+            self._rec(words, conv=layer[0].downsample[0], bn=layer[0].downsample[1])
+        for i in range(L):
+            c, bn, _ = getattr(head, "out_block_%d" % i)
+            self._rec(words, conv=c, bn=bn)
+        for i in range(1, L):
+            gen, bn1, _, c, bn2, _ = getattr(head, "up_block_%d" % i)
+            wp, wpt = gen._packed()
+            gb = gen.bias.detach().reshape(-1).contiguous() if gen.bias is not None else None
+            s, sh = bn1.scale_shift(None)
+            s, sh = s.reshape(-1).contiguous(), sh.reshape(-1).contiguous()
+            self._keep += [wp, wpt, gb, s, sh]
+            words += [ptr(wpt) or 0, ptr(wp), ptr(s), ptr(sh), ptr(gb) or 0, 1, gen.in_channels, 8 * gen.out_channels]
+            self._rec(words, conv=c, bn=bn2)
+        self._rec(words, wt=wt, w32=w, bias=b, kvol=1, cin=int(w.shape[1]), cout=int(w.shape[2]))
+        for i in range(L):
+            sc = head.scales[i].scale.detach().reshape(1)
+            self._rec(words, wt=sc)
+        self._yaw_rotated = head.n_reg_outs != 6
+        desc = (ctypes.c_longlong * len(words))(*words)
+        fl = (ctypes.c_double * 4)(float(head.voxel_size), float(head._cfg("score_thr")), float(head._cfg("iou_thr")),
+                                   float(inorm.eps))
+        h = lib().b2_engine_create(desc, len(words), fl)
+        if not h:
+            raise B2Error("b2_engine_create failed: %s" % last_error())
+        self._handle = ctypes.c_void_p(h)
+        self._sig = self._signature()
+
+    def _destroy(self):
+        if self._handle is not None:
+            lib().b2_engine_destroy(self._handle)
+            self._handle = None
+
+    def __del__(self):
+        try:
+            self._destroy()
+        except Exception:
+            pass
+
+    # ---- one step -------------------------------------------------------------------------------------------------------
+    @torch.no_grad()
+    def __call__(self, points):
+        """points: list of [N_i, 6] fp32 CUDA tensors.  Returns the device-side result dict of get_bboxes_fused
+        (boxes [n,7], scores, labels, scene, count, box_dim); detector.split_detections / DetectionRead bring it to the host."""
+        if self._handle is None or self._sig != self._signature():
+            self._build()
+        dev = points[0].device
+        n = len(points)
+        pts = [p if (p.is_contiguous() and p.dtype == torch.float32) else p.contiguous().float() for p in points]
+        for p in pts:
+            if not p.is_cuda:
+                raise B2Error("InferenceEngine needs CUDA points (no CPU path)")
+        ptrs = (ctypes.c_void_p * n)(*[p.data_ptr() for p in pts])
+        counts = (ctypes.c_longlong * n)(*[int(p.shape[0]) for p in pts])
+        total = sum(int(p.shape[0]) for p in pts)
+        l = lib()
+        cap = int(l.b2_engine_out_rows(self._handle, n))
+        boxes = torch.empty((cap, 7), dtype=torch.float32, device=dev)
+        scores = torch.empty((cap,), dtype=torch.float32, device=dev)
+        labels = torch.empty((cap,), dtype=torch.int32, device=dev)
+        scene = torch.empty((cap,), dtype=torch.int32, device=dev)
+        count = torch.empty((1,), dtype=torch.int32, device=dev)
+        need = (4096 * total + (256 << 20)) if self._arena is None else 0
+        rows, used = ctypes.c_longlong(0), ctypes.c_size_t(0)
+        dt = 1 if ME.get_compute_dtype() == torch.bfloat16 else 0
+        for _ in range(6):
+            if self._arena is None or self._arena.numel() < need or self._arena.device != dev:
+                self._arena = None
+                self._arena = torch.empty(max(need, 1 << 20), dtype=torch.uint8, device=dev)
+            rc = l.b2_engine_infer(self._handle, ptrs, counts, n, dt, ptr(self._arena), self._arena.numel(), ptr(boxes),
+                                   ptr(scores), ptr(labels), ptr(scene), ptr(count), cap, ctypes.byref(rows),
+                                   ctypes.byref(used), stream())
+            if rc == -3:            # arena too small: the launches so far wrote only into the arena - grow it and redo the step
+                torch.cuda.current_stream().synchronize()
+                need = 2 * self._arena.numel()
+                continue
+            if rc != 0:
+                raise B2Error("b2_engine_infer failed (%d): %s" % (rc, last_error()))
+            break
+        else:
+            raise B2Error("b2_engine_infer: arena kept overflowing: %s" % last_error())
+        self.arena_used = int(used.value)
+        nr = int(rows.value)
+        return dict(boxes=boxes[:nr], scores=scores[:nr], labels=labels[:nr], scene=scene[:nr], count=count,
+                    box_dim=7 if self._yaw_rotated else 6)

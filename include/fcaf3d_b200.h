@@ -292,6 +292,28 @@ int b2_box_iou_decoded(const float* points, const float* bbox_pred, int n_reg, i
    CrossEntropyLoss(use_sigmoid=True) -> F.binary_cross_entropy_with_logits) */
 int b2_bce_logits(const float* x, const float* t, long long n, float* loss, float* grad, void* stream);
 
+/* ---- native executor of one fused inference step ------------------------------------------------------------------
+ * What the reference does per batch through python - SingleStageSparse3DDetector.simple_test -> extract_feat ->
+ * MEResNet3D.forward -> Fcaf3DNeckWithHead.forward / get_bboxes (single_stage_sparse.py:32-59, me_resnet.py:66-99,
+ * fcaf3d_neck_with_head.py:94-126,205-253,256-279,332-374), eval mode - as ONE host call that enqueues the entry points
+ * above in C++ (bit-identical results to calling them one by one; the python host needed as long per step as the GPU).
+ * b2_engine_create (set-up, not per step): parses the weight table `desc` (int64 words, layout documented at the
+ * definition in csrc/engine.cu and written by fcaf3d_b200/engine.py; pointers are device pointers owned by the caller, which
+ * must outlive the engine) and fl = {voxel_size, score_thr, iou_thr, InstanceNorm eps}; allocates a small pinned staging
+ * ring and events.  Returns NULL on error.  One engine per device; calls on one engine must not overlap on the host.
+ * b2_engine_infer (per step, allocates nothing): points_host / n_points_host are HOST arrays of n_scenes device pointers
+ * ([n_i, dim] fp32 rows xyz + colour) and row counts; dtype = activation storage (0 fp32, 1 bf16); every intermediate is
+ * taken from `arena` (-3 if too small; *arena_used_host reports the bytes used); detections come back in the caller's
+ * buffers of out_cap >= b2_engine_out_rows() rows: out_boxes [.,7], out_scores, out_labels, out_scene, grouped by
+ * (scene, class), *out_count (device) of them valid; *n_rows_host = rows the tail worked on.  The call blocks on the few
+ * row-count reads of the coordinate maps (each queued behind GPU work that was enqueued earlier). */
+void* b2_engine_create(const long long* desc, int n_words, const double* fl);
+int b2_engine_destroy(void* engine);
+long long b2_engine_out_rows(void* engine, int n_scenes);
+int b2_engine_infer(void* engine, const float* const* points_host, const long long* n_points_host, int n_scenes, int dtype,
+                    void* arena, size_t arena_bytes, float* out_boxes, float* out_scores, int* out_labels, int* out_scene,
+                    int* out_count, long long out_cap, long long* n_rows_host, size_t* arena_used_host, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,59 @@
+"""GPU: the native executor (csrc/engine.cu, one host call per inference step) against the python driver of the same
+kernels (detector.simple_test_fused with use_engine = False): identical detections, bit for bit, in both dtypes, on the
+ScanNet / SUN RGB-D / S3DIS heads, with an empty scene in the batch, with a prune threshold that takes the general
+(convolve, union, prune) path at the finest level, and at benchmark size."""
+import pytest
+import torch
+
+from fcaf3d_b200 import me as ME
+from fcaf3d_b200.detector import build_fcaf3d
+from fcaf3d_b200.scenes import make_scene
+from fcaf3d_b200.testing import deterministic_init
+
+pytestmark = pytest.mark.gpu
+
+
+def _both(det, pts, dtype):
+    ME.set_compute_dtype(dtype)
+    try:
+        det.use_engine = True
+        a = det.simple_test_fused(pts, to_host=False)
+        assert det._engine is not None and det._engine.arena_used > 0, "the native executor did not run"
+        det.use_engine = False
+        b = det.simple_test_fused(pts, to_host=False)
+    finally:
+        det.use_engine = True
+        ME.set_compute_dtype(torch.float32)
+    na, nb = int(a["count"].item()), int(b["count"].item())
+    assert na == nb and na > 0
+    assert a["box_dim"] == b["box_dim"]
+    for k in ("boxes", "scores", "labels", "scene"):
+        assert torch.equal(a[k][:na], b[k][:nb]), k
+    return na
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["fp32", "bf16"])
+@pytest.mark.parametrize("dataset,thr", [("scannet", 100000), ("sunrgbd", 100000), ("s3dis", 4000), ("scannet", 700)])
+def test_engine_equals_python_driver(dev, dataset, thr, dtype):
+    det = deterministic_init(build_fcaf3d(dataset, pts_threshold=thr), 0, cls_bias=0.0).to(dev).eval()
+    pts = [torch.from_numpy(make_scene("tiny", s, 3000)[0]).to(dev) for s in (1, 2, 3)]
+    _both(det, pts, dtype)
+
+
+def test_engine_with_an_empty_scene_and_changed_weights(dev):
+    det = deterministic_init(build_fcaf3d("scannet", depth=14), 0, cls_bias=0.0).to(dev).eval()
+    full = torch.from_numpy(make_scene("tiny", 4, 3000)[0]).to(dev)
+    n1 = _both(det, [full, full[:0].contiguous(), full[:40].contiguous()], torch.float32)
+    with torch.no_grad():                                   # the engine must notice new weights
+        det.neck_with_head.cls_conv.bias.add_(0.5)
+    n2 = _both(det, [full, full[:0].contiguous(), full[:40].contiguous()], torch.float32)
+    assert n1 > 0 and n2 > 0
+
+
+def test_engine_at_benchmark_size(dev):
+    det = deterministic_init(build_fcaf3d("scannet"), 0, cls_bias=0.0).to(dev).eval()
+    pts = [torch.from_numpy(make_scene("S0", 100 * i)[0]).to(dev) for i in range(8)]
+    n = _both(det, pts, torch.bfloat16)
+    assert n > 10000
+    big = deterministic_init(build_fcaf3d("s3dis"), 0, cls_bias=0.0).to(dev).eval()
+    _both(big, [torch.from_numpy(make_scene("S2", 0, n_classes=5)[0]).to(dev)], torch.bfloat16)
