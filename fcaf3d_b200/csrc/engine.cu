@@ -16,6 +16,7 @@
 #include "common.cuh"
 #include "../../include/fcaf3d_b200.h"
 
+#include <stdlib.h>
 #include <string.h>
 
 #include <vector>
@@ -50,6 +51,7 @@ struct Engine {
   cudaEvent_t events[RING];
   int next_slot = 0;
   int device = -1;
+  long long sort_min_rows = 32768;   // B2_SORT_MIN_ROWS (0 = never sort)
 };
 
 struct Map {
@@ -70,6 +72,10 @@ struct KMap {
   unsigned int* tmask;
   long long n_out;
   int kvol;
+  // sparsity-grouped copy for the tcgen05 convolutions (b2_kmap_sort), NULL = walk the table as built
+  int* perm = nullptr;
+  int* nbr_sorted = nullptr;
+  unsigned int* tmask_sorted = nullptr;
 };
 
 struct Pending {  // a map build / union whose row count is still in flight
@@ -315,6 +321,18 @@ struct Run {
     return B2_OK;
   }
 
+  // rows grouped by the kernel slabs they use (kmap_sort.cu): pays for tables that several tcgen05 convolutions walk
+  int sort_kmap(KMap* k) {
+    if (k->perm || k->kvol != 27 || k->ld == 0) return B2_OK;
+    k->perm = (int*)take((size_t)k->ld * 4);
+    k->nbr_sorted = (int*)take((size_t)k->kvol * k->ld * 4);
+    k->tmask_sorted = (unsigned int*)take((size_t)(k->ld / 128) * 4);
+    const size_t wsb = b2_kmap_sort_ws_bytes(k->n_out, k->kvol);
+    void* ws = take(wsb);
+    if (!k->perm || !k->nbr_sorted || !k->tmask_sorted || !ws) return B2_ERR_WS;
+    return b2_kmap_sort(k->nbr, k->ld, k->n_out, k->kvol, k->perm, k->nbr_sorted, k->tmask_sorted, ws, wsb, stv);
+  }
+
   // ---- convolution (the dispatch of ops.sparse_conv) ---------------------------------------------------------------
   int conv(const ConvW& w, const void* x, int x_dt, long long n_in, const KMap* km, long long n_out, const void* residual,
            int act, int ch_mod, int out_dt, void** out) {
@@ -323,9 +341,13 @@ struct Run {
     const int* nbr = km ? km->nbr : nullptr;
     const long long ld = km ? km->ld : 0;
     const unsigned int* tm = km ? km->tmask : nullptr;
-    if (x_dt == 1 && w.wt && w.cin % 64 == 0 && w.cout % 32 == 0)
+    if (x_dt == 1 && w.wt && w.cin % 64 == 0 && w.cout % 32 == 0) {
+      if (km && km->perm && w.kvol == 27)
+        return b2_conv_tc(x, n_in, w.wt, km->nbr_sorted, ld, km->tmask_sorted, km->perm, n_out, w.cin, w.cout, w.kvol,
+                          w.bias, w.scale, w.shift, residual, act, ch_mod, *out, out_dt, stv);
       return b2_conv_tc(x, n_in, w.wt, nbr, ld, tm, nullptr, n_out, w.cin, w.cout, w.kvol, w.bias, w.scale, w.shift,
                         residual, act, ch_mod, *out, out_dt, stv);
+    }
     return b2_conv_cc(x, x_dt, w.w32, nbr, ld, tm, n_out, w.cin, w.cout, w.kvol, w.bias, w.scale, w.shift, residual, act,
                       ch_mod, *out, out_dt, stv);
   }
@@ -428,6 +450,8 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
       }
       KMap* km2;
       CK(r.kernel_map(out, out, 3, &km2));
+      // the stage's stride-1 table is walked by 2 * blocks - 1 convolutions: group its rows once (bit-identical results)
+      if (r.dt == 1 && e.sort_min_rows > 0 && e.blocks[i] >= 2 && n_out >= e.sort_min_rows) CK(r.sort_kmap(km2));
       void* o;
       CK(r.conv(e.conv2[i][j], h, r.dt, n_out, km2, n_out, res, B2_ACT_RELU, 0, r.dt, &o));
       f = o;
@@ -669,6 +693,7 @@ void* b2_engine_create(const long long* desc, int n_words, const double* fl) {
     return nullptr;
   }
   Engine* e = new Engine();
+  if (const char* v = getenv("B2_SORT_MIN_ROWS")) e->sort_min_rows = atoll(v);
   e->n_outs = (int)desc[1], e->n_cls = (int)desc[2], e->n_reg = (int)desc[3], e->yaw_mode = (int)desc[4];
   e->pts_threshold = (int)desc[5], e->nms_pre = (int)desc[6], e->dim = (int)desc[7], e->head_cols = (int)desc[8];
   if (e->n_outs < 1 || e->n_outs > MAX_LEVELS) {

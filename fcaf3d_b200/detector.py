@@ -663,7 +663,7 @@ class SingleStageSparse3DDetector(nn.Module):
     def _engine_ok(self):
         from . import engine as E
         if not (self.use_engine and not self.training and ops.PROFILE is None and ops._TC_ENABLED and PRUNE_BEFORE_CONV
-                and self.neck_with_head.trace is None and ops.SORT_MIN_ROWS == 0 and ME.STRIDED_FROM_INPUT == 1):
+                and self.neck_with_head.trace is None and ME.STRIDED_FROM_INPUT == 1):
             return False
         if self._engine is None:
             if not E.supported(self):

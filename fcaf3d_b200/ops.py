@@ -252,12 +252,15 @@ class KernelMap:
         self.tc_uses = 0        # tcgen05 convolutions that walked this table so far
 
 
-# Sparsity-sorted walk of the tcgen05 convolution (kmap_sort.cu), OPT-IN (B2_SORT_MIN_ROWS=65536).  Measured on B200:
-# in isolation (tools/bench_conv.py) the sorted walk saves 25 % of a 218 k-row 64->64 convolution (111 -> 83 us), 14 % at
-# 54 k rows, 8 % at 12 k rows, but building it costs ~90-115 us per table (row masks, 4 radix passes, table permutation);
-# in the full step (bench.py, inference and training) the two cancel (827 vs 819 scenes/s, 167 vs 166 scenes/s), so the
-# default is off.  When on, a table is sorted once its SECOND tcgen05 convolution arrives and it has >= SORT_MIN_ROWS rows.
-SORT_MIN_ROWS = int(os.environ.get("B2_SORT_MIN_ROWS", "0"))
+# Sparsity-grouped walk of the tcgen05 convolution (kmap_sort.cu): the rows of a 3^3 table are grouped by the kernel slabs
+# they use (counting sort on a 6-bit key), a 128-row tile then walks ~16 instead of 27 offsets at tensor stride 8.  Round 1
+# measured the walk itself (-25 % at 218 k rows of 64 channels, -14 % at 54 k x 128) but its full 27-bit radix sort cost
+# 90-115 us per table and cancelled the gain; the counting sort is a fraction of that, so tables with >= SORT_MIN_ROWS rows
+# are now grouped when their SORT_MIN_USES-th tcgen05 convolution arrives (the backbone's stride-1 tables serve 5-11
+# convolutions each).  Measured (B200, 8 x S0): ts8 64->64 108 -> 78 us per convolution, ts16 128->128 60 -> 47 us, ts32 no gain
+# (49 -> 48 us, hence the 32 k-row threshold); grouping costs ~35 us per table inside the step.  B2_SORT_MIN_ROWS=0 switches
+# it off.  Results are bit-identical either way.
+SORT_MIN_ROWS = int(os.environ.get("B2_SORT_MIN_ROWS", "32768"))
 SORT_MIN_USES = int(os.environ.get("B2_SORT_MIN_USES", "2"))
 
 
