@@ -38,15 +38,19 @@ struct TcCfg {
 // tensor pipe - paced the C = 64 layers (ncu source view: 2/3 of the stall samples in the producer loop and its per-offset
 // set-up); with two groups the per-stage fixed part of the chain is paid half as often per warp.  The weight tile's TMA
 // load moves from thread 0 of the producers to lane 0 of a warp of its own.
-template <int BN, int ST, typename TOut, int GRP>
+// TIn = __nv_bfloat16 (kind::f16, 64 channels per 128-byte stage row) or float (kind::tf32: fp32 rows and weights read as
+// TF32 operands, 32 channels per stage row, fp32 accumulation - the fp32-storage mode of the tensor-core path).
+template <int BN, int ST, typename TOut, int GRP, typename TIn = __nv_bfloat16>
 __global__ void __launch_bounds__(CT_THREADS)
-k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __restrict__ in, const int* __restrict__ nbr,
+k_conv_tc(const __grid_constant__ CUtensorMap map_b, const TIn* __restrict__ in, const int* __restrict__ nbr,
           int ld,
           const unsigned int* __restrict__ tile_mask, const int* __restrict__ out_rows, int n_out, int cin, int cout,
           int kvol, const float* __restrict__ bias, const float* __restrict__ scale, const float* __restrict__ shift,
           const TOut* __restrict__ residual, int act, int ch_mod, TOut* __restrict__ out) {
   using Cfg = TcCfg<BN, ST>;
   constexpr int S = Cfg::STAGES;
+  constexpr int BKE = 128 / (int)sizeof(TIn);   // channels per stage row (128 bytes)
+  constexpr int CH16 = 16 / (int)sizeof(TIn);   // channels per 16-byte copy
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // stays a shared-space pointer
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S * Cfg::STAGE_BYTES);
@@ -61,7 +65,7 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __rest
   const int tile = (out_rows != nullptr) ? (int)(gridDim.x - 1 - blockIdx.x) : (int)blockIdx.x;
   const int row0 = tile * TC_BM, col0 = blockIdx.y * BN;
   const unsigned int kmask = (nbr != nullptr) ? tile_mask[tile] : 1u;
-  const int chunks = cin / TC_BK;
+  const int chunks = cin / BKE;
   const int nstage = __popc(kmask & ((1u << kvol) - 1u)) * chunks;
 
   if (tid == 0) {
@@ -114,7 +118,7 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __rest
       const int group = warp >> 2, gt = tid & 127;
       const int chunk16 = gt & 7, rsub = gt >> 3;  // rsub 0..15; rows rsub + 16 p keep (row & 7) == (rsub & 7)
       const uint32_t dst_off = (uint32_t)(rsub * 128 + ((chunk16 ^ (rsub & 7)) << 4));  // + 2048 per pass (16 rows)
-      const __nv_bfloat16* in_thr = in + chunk16 * 8;
+      const TIn* in_thr = in + chunk16 * CH16;
       const uint32_t smem_base = smem_u32(smem);
       int it = 0;
       for (int k = 0; k < kvol; ++k) {
@@ -125,7 +129,7 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __rest
           continue;
         }
         const int* nb = s_nbr + k * TC_BM + rsub;
-        const __nv_bfloat16* src[TC_BM / 16];
+        const TIn* src[TC_BM / 16];
         uint32_t nbytes[TC_BM / 16];
 #pragma unroll
         for (int p = 0; p < TC_BM / 16; ++p) {
@@ -139,20 +143,20 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __rest
           mbar_wait(&empty_bar[s], ((uint32_t)(it / S) & 1u) ^ 1u);
           const uint32_t a_dst = smem_base + s * Cfg::STAGE_BYTES + dst_off;
 #pragma unroll
-          for (int p = 0; p < TC_BM / 16; ++p) cp_async16(a_dst + p * 2048, src[p] + c * TC_BK, nbytes[p]);
+          for (int p = 0; p < TC_BM / 16; ++p) cp_async16(a_dst + p * 2048, src[p] + c * BKE, nbytes[p]);
           cp_async_arrive_noinc(&full_bar[s]);
         }
       }
     } else {
     const int chunk16 = tid & 7, rsub = tid >> 3;  // rsub 0..31
     const uint32_t dst_off = (uint32_t)(rsub * 128 + ((chunk16 ^ (rsub & 7)) << 4));  // + 4096 per pass (32 rows)
-    const __nv_bfloat16* in_thr = in + chunk16 * 8;
+    const TIn* in_thr = in + chunk16 * CH16;
     const uint32_t smem_base = smem_u32(smem);
     int it = 0;
     for (int k = 0; k < kvol; ++k) {
       if (!((kmask >> k) & 1u)) continue;
       const int* nb = s_nbr + k * TC_BM + rsub;
-      const __nv_bfloat16* src[TC_BM / 32];
+      const TIn* src[TC_BM / 32];
       uint32_t nbytes[TC_BM / 32];
 #pragma unroll
       for (int p = 0; p < TC_BM / 32; ++p) {
@@ -166,11 +170,11 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __rest
         const uint32_t a_dst = smem_base + s * Cfg::STAGE_BYTES + dst_off;
         const uint32_t b_dst = smem_base + s * Cfg::STAGE_BYTES + Cfg::A_BYTES;
 #pragma unroll
-        for (int p = 0; p < TC_BM / 32; ++p) cp_async16(a_dst + p * 4096, src[p] + c * TC_BK, nbytes[p]);
+        for (int p = 0; p < TC_BM / 32; ++p) cp_async16(a_dst + p * 4096, src[p] + c * BKE, nbytes[p]);
         // the weight slice W_k^T[col0 : col0+BN, c*64 : c*64+64] is ONE TMA tile load (completion counted in bytes)
         if (tid == 0) {
           mbar_expect_tx(&full_bar[s], (uint32_t)Cfg::B_BYTES);
-          tma_tile_2d(b_dst, &map_b, &full_bar[s], c * TC_BK, k * cout + col0);
+          tma_tile_2d(b_dst, &map_b, &full_bar[s], c * BKE, k * cout + col0);
         }
         // asynchronous completion: nobody waits here, so all S stages can be in flight
         cp_async_arrive_noinc(&full_bar[s]);
@@ -270,7 +274,7 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __rest
           const int s = it % S;
           mbar_wait(&empty_bar[s], ((uint32_t)(it / S) & 1u) ^ 1u);
           mbar_expect_tx(&full_bar[s], (uint32_t)Cfg::B_BYTES);
-          tma_tile_2d(smem_base + s * Cfg::STAGE_BYTES + Cfg::A_BYTES, &map_b, &full_bar[s], c * TC_BK, k * cout + col0);
+          tma_tile_2d(smem_base + s * Cfg::STAGE_BYTES + Cfg::A_BYTES, &map_b, &full_bar[s], c * BKE, k * cout + col0);
         }
       }
     }
@@ -278,7 +282,9 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __rest
   } else {
     // ===================== MMA issuer (one thread) ==========================================
     if (lane == 0 && nstage > 0) {
-      constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((128u >> 4) << 24);
+      // instruction descriptor: D = F32; A / B format 1 = BF16 (kind::f16) or 2 = TF32 (kind::tf32); N >> 3; M >> 4
+      constexpr uint32_t fmt = sizeof(TIn) == 2 ? 1u : 2u;
+      constexpr uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((128u >> 4) << 24);
       const uint32_t smem_base = smem_u32(smem);
       for (int it = 0; it < nstage; ++it) {
         const int s = it % S;
@@ -291,7 +297,10 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __rest
         for (int kk = 0; kk < TC_BK / 16; ++kk) {
           const uint64_t da = umma_desc_sw128(a_base + kk * 32);
           const uint64_t db = umma_desc_sw128(b_base + kk * 32);
-          umma_bf16(tmem_base, da, db, idesc, (it > 0 || kk > 0) ? 1u : 0u);
+          if (sizeof(TIn) == 2)
+            umma_bf16(tmem_base, da, db, idesc, (it > 0 || kk > 0) ? 1u : 0u);
+          else
+            umma_tf32(tmem_base, da, db, idesc, (it > 0 || kk > 0) ? 1u : 0u);
         }
         umma_commit(&empty_bar[s]);  // frees the smem stage once these MMAs have read it
       }
@@ -337,6 +346,51 @@ static int launch_tc(const void* in, const void* wt, const int* nbr, long long l
                                         residual, act, ch_mod, out, st);
   return launch_tc_g<BN, ST, TOut, 1>(in, wt, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, shift,
                                       residual, act, ch_mod, out, st);
+}
+
+template <int BN, int ST>
+static int launch_tf32(const void* in, const void* wt, const int* nbr, long long ld, const unsigned int* tile_mask,
+                       const int* out_rows, long long n_out, int cin, int cout, int kvol, const float* bias,
+                       const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
+                       cudaStream_t st) {
+  using Cfg = TcCfg<BN, ST>;
+  auto kern = k_conv_tc<BN, ST, float, 2, float>;
+  static unsigned long long configured = 0;
+  if (int rc0 = b2_optin_smem((const void*)kern, Cfg::SMEM, &configured)) return rc0;
+  CUtensorMap map_b;
+  const int rc = b2_make_tf32_map(&map_b, wt, (long long)kvol * cout, cin, BN);
+  if (rc) return rc;
+  dim3 grid(b2_div_up(n_out, TC_BM), cout / BN);
+  kern<<<grid, CT_THREADS, Cfg::SMEM, st>>>(map_b, (const float*)in, nbr, (int)ld, tile_mask, out_rows, (int)n_out, cin, cout,
+                                            kvol, bias, scale, shift, (const float*)residual, act, ch_mod, (float*)out);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+// fp32 rows and fp32 weights [kvol, cout, cin] through the tensor cores as TF32 operands (10-bit mantissa products, fp32
+// accumulation in TMEM), fp32 output: the fp32-storage mode of b2_conv_tc.  cin % 32 == 0, cout % 32 == 0.
+extern "C" int b2_conv_tc_tf32(const void* in_f32, long long n_in, const void* wt_f32, const int* nbr, long long ld,
+                               const unsigned int* tile_mask, const int* out_rows, long long n_out, int cin, int cout,
+                               int kvol, const float* bias, const float* scale, const float* shift, const void* residual,
+                               int act, int ch_mod, void* out, void* stream) {
+  (void)n_in;
+  B2_CHECK_ARG(cin % 32 == 0 && cin > 0, "b2_conv_tc_tf32 needs cin %% 32 == 0 (got %d)", cin);
+  B2_CHECK_ARG(cout % 32 == 0 && cout > 0, "b2_conv_tc_tf32 needs cout %% 32 == 0 (got %d)", cout);
+  B2_CHECK_ARG(nbr != nullptr || kvol == 1, "identity map requires kernel volume 1");
+  B2_CHECK_ARG(nbr == nullptr || (tile_mask != nullptr && kvol <= 27 && ld % TC_BM == 0),
+               "neighbour table needs a tile mask, kvol <= 27 and ld %% 128 == 0");
+  B2_CHECK_ARG((scale == nullptr) == (shift == nullptr), "scale and shift come together");
+  B2_CHECK_ARG(out_rows == nullptr || nbr != nullptr, "a row permutation needs a neighbour table");
+  if (n_out == 0) return B2_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (cout % 128 == 0)
+    return launch_tf32<128, 3>(in_f32, wt_f32, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, shift,
+                               residual, act, ch_mod, out, st);
+  if (cout % 64 == 0)
+    return launch_tf32<64, 4>(in_f32, wt_f32, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, shift,
+                              residual, act, ch_mod, out, st);
+  return launch_tf32<32, 4>(in_f32, wt_f32, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, shift,
+                            residual, act, ch_mod, out, st);
 }
 
 extern "C" int b2_conv_tc(const void* in_bf16, long long n_in, const void* wt_bf16, const int* nbr, long long ld,

@@ -112,6 +112,7 @@ struct Run {
   void* stv;
   int nb = 0;
   int dt = 1;  // activation dtype: 1 bf16, 0 fp32
+  bool tf32 = false;   // fp32 rows, wide convolutions as TF32 tensor-core operands (ConvW::wt then holds fp32 [kvol, cout, cin])
   std::vector<Map> maps;
   std::vector<KMap> kmaps;
 
@@ -341,6 +342,12 @@ struct Run {
     const int* nbr = km ? km->nbr : nullptr;
     const long long ld = km ? km->ld : 0;
     const unsigned int* tm = km ? km->tmask : nullptr;
+    if (tf32 && x_dt == 0 && out_dt == 0 && w.wt && w.cin % 32 == 0 && w.cout % 32 == 0) {
+      const bool sorted = km && km->perm && w.kvol == 27;
+      return b2_conv_tc_tf32(x, n_in, w.wt, sorted ? km->nbr_sorted : nbr, ld, sorted ? km->tmask_sorted : tm,
+                             sorted ? km->perm : nullptr, n_out, w.cin, w.cout, w.kvol, w.bias, w.scale, w.shift, residual,
+                             act, ch_mod, *out, stv);
+    }
     if (x_dt == 1 && w.wt && w.cin % 64 == 0 && w.cout % 32 == 0) {
       if (km && km->perm && w.kvol == 27)
         return b2_conv_tc(x, n_in, w.wt, km->nbr_sorted, ld, km->tmask_sorted, km->perm, n_out, w.cin, w.cout, w.kvol,
@@ -371,7 +378,8 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
                  float* out_boxes, float* out_scores, int* out_labels, int* out_scene, int* out_count, long long out_cap,
                  long long* n_rows_out) {
   r.nb = n_scenes;
-  r.dt = dtype;
+  r.dt = dtype == 1 ? 1 : 0;
+  r.tf32 = dtype == 2;
   const int nb = n_scenes, L = e.n_outs, dim = e.dim, fdim = e.dim - 3;
   B2_CHECK_ARG(nb >= 1 && nb + 3 <= SLOT_INTS && nb * (L + 1) + 1 <= SLOT_INTS, "engine: too many scenes per call (%d)", nb);
   long long total = 0;
@@ -451,7 +459,7 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
       KMap* km2;
       CK(r.kernel_map(out, out, 3, &km2));
       // the stage's stride-1 table is walked by 2 * blocks - 1 convolutions: group its rows once (bit-identical results)
-      if (r.dt == 1 && e.sort_min_rows > 0 && e.blocks[i] >= 2 && n_out >= e.sort_min_rows) CK(r.sort_kmap(km2));
+      if ((r.dt == 1 || r.tf32) && e.sort_min_rows > 0 && e.blocks[i] >= 2 && n_out >= e.sort_min_rows) CK(r.sort_kmap(km2));
       void* o;
       CK(r.conv(e.conv2[i][j], h, r.dt, n_out, km2, n_out, res, B2_ACT_RELU, 0, r.dt, &o));
       f = o;
@@ -769,7 +777,7 @@ int b2_engine_infer(void* engine, const float* const* points_host, const long lo
   Engine* e = (Engine*)engine;
   B2_CHECK_ARG(e && points_host && n_points_host && arena && out_boxes && out_scores && out_labels && out_scene && out_count,
                "b2_engine_infer: null argument");
-  B2_CHECK_ARG(dtype == 0 || dtype == 1, "b2_engine_infer: dtype 0 (fp32) or 1 (bf16)");
+  B2_CHECK_ARG(dtype >= 0 && dtype <= 2, "b2_engine_infer: dtype 0 (fp32), 1 (bf16) or 2 (fp32 rows, TF32 tensor cores)");
   int dev = -1;
   B2_CUDA(cudaGetDevice(&dev));
   B2_CHECK_ARG(dev == e->device, "b2_engine_infer: engine was created on device %d, current device is %d", e->device, dev);

@@ -193,12 +193,12 @@ def conv_bn_act(conv, bn, f, km, n_out, act, residual=None):
     """conv -> BatchNorm -> (+residual) -> activation.  Eval: one kernel (BN folded into the epilogue).
     Train: conv, batch statistics, then one fused normalise/residual/activation pass."""
     if bn.bn.training:
-        y = ops.sparse_conv(f, conv._w3(), km, n_out, wt_bf16=conv._wt_bf16())
+        y = ops.sparse_conv(f, conv._w3(), km, n_out, wt_bf16=conv._wt_bf16(), wt_tf32=conv._wt_tf32())
         scale, shift = bn.scale_shift(y)
         return ops.affine_act(y, scale, shift, residual=residual, act=act, out=y)
     scale, shift = bn.scale_shift(None)
     return ops.sparse_conv(f, conv._w3(), km, n_out, wt_bf16=conv._wt_bf16(), scale=scale.reshape(-1),
-                           shift=shift.reshape(-1), residual=residual, act=act)
+                           shift=shift.reshape(-1), residual=residual, act=act, wt_tf32=conv._wt_tf32())
 
 
 def _fused_block(block, f, key, cm):
@@ -378,8 +378,13 @@ class Fcaf3DNeckWithHead(nn.Module):
             pad = (-w.shape[1]) % 32                      # columns padded to a multiple of 32 for the tcgen05 path
             w = torch.nn.functional.pad(w, (0, pad)).unsqueeze(0).contiguous()
             b = torch.nn.functional.pad(b, (0, pad)).contiguous()
-            self._hw, self._hw_ver = (w, b, w.transpose(1, 2).contiguous().to(torch.bfloat16)), ver
-        return self._hw
+            wt = w.transpose(1, 2).contiguous()
+            self._hw, self._hw_ver = (w, b, wt.to(torch.bfloat16), wt), ver
+        return self._hw[:3]
+
+    def _head_weights_tf32(self):
+        self._head_weights()
+        return self._hw[3] if ME.get_tf32() else None
 
     def forward_fused(self, inputs, want_max_score=False):
         """Returns per level (fine -> coarse) dicts with centerness / bbox_pred / cls / prune score (+max score)
@@ -450,7 +455,8 @@ class Fcaf3DNeckWithHead(nn.Module):
             km = cm.kernel_map(key, key, conv.kernel_size, conv.dilation)
             o = conv_bn_act(conv, bn, f, km, cm.size(key), ops.ACT_ELU)
             w, b, wt = self._head_weights()
-            h = ops.sparse_conv(o, w, None, o.shape[0], wt_bf16=wt, bias=b, out_dtype=torch.float32)
+            h = ops.sparse_conv(o, w, None, o.shape[0], wt_bf16=wt, bias=b, out_dtype=torch.float32,
+                                wt_tf32=self._head_weights_tf32())
             ctr, bbox, cls, prune, mx = ops.head_post(h, self.n_reg_outs, self.n_classes,
                                                       self.scales[i].scale.detach().reshape(1), want_max_score)
             prev = dict(key=key, centerness=ctr, bbox_pred=bbox, cls=cls, prune=prune, max_score=mx)

@@ -36,14 +36,17 @@ class InferenceEngine:
     def _signature(self):
         if self._tensors is None:
             self._tensors = list(self.det.parameters()) + list(self.det.buffers())
-        return tuple((t._version, t.data_ptr()) for t in self._tensors)
+        return (ME.get_tf32(),) + tuple((t._version, t.data_ptr()) for t in self._tensors)
 
     def _rec(self, words, conv=None, bn=None, wt=None, w32=None, bias=None, kvol=None, cin=None, cout=None):
         """one 8-word record: wt bf16, w fp32, scale, shift, bias, kvol, cin, cout"""
         scale = shift = None
         if conv is not None:
             w32 = conv._w3()
-            wt = conv._wt_bf16() if (w32.shape[1] % 64 == 0 and w32.shape[2] % 32 == 0) else None
+            if ME.get_tf32():
+                wt = conv._wt_tf32() if (w32.shape[1] % 32 == 0 and w32.shape[2] % 32 == 0) else None
+            else:
+                wt = conv._wt_bf16() if (w32.shape[1] % 64 == 0 and w32.shape[2] % 32 == 0) else None
             kvol, cin, cout = (int(v) for v in w32.shape)
             bias = conv.bias.detach().reshape(-1).contiguous() if conv.bias is not None else None
         if bn is not None:
@@ -83,12 +86,16 @@ class InferenceEngine:
         for i in range(1, L):
             gen, bn1, _, c, bn2, _ = getattr(head, "up_block_%d" % i)
             wp, wpt = gen._packed()
+            if ME.get_tf32():
+                wpt = gen._packed_tf32()
             gb = gen.bias.detach().reshape(-1).contiguous() if gen.bias is not None else None
             s, sh = bn1.scale_shift(None)
             s, sh = s.reshape(-1).contiguous(), sh.reshape(-1).contiguous()
             self._keep += [wp, wpt, gb, s, sh]
             words += [ptr(wpt) or 0, ptr(wp), ptr(s), ptr(sh), ptr(gb) or 0, 1, gen.in_channels, 8 * gen.out_channels]
             self._rec(words, conv=c, bn=bn2)
+        if ME.get_tf32():
+            wt = head._head_weights_tf32()
         self._rec(words, wt=wt, w32=w, bias=b, kvol=1, cin=int(w.shape[1]), cout=int(w.shape[2]))
         for i in range(L):
             sc = head.scales[i].scale.detach().reshape(1)
@@ -139,7 +146,7 @@ class InferenceEngine:
         count = torch.empty((1,), dtype=torch.int32, device=dev)
         need = (4096 * total + (256 << 20)) if self._arena is None else 0
         rows, used = ctypes.c_longlong(0), ctypes.c_size_t(0)
-        dt = 1 if ME.get_compute_dtype() == torch.bfloat16 else 0
+        dt = 1 if ME.get_compute_dtype() == torch.bfloat16 else (2 if ME.get_tf32() else 0)
         for _ in range(6):
             if self._arena is None or self._arena.numel() < need or self._arena.device != dev:
                 self._arena = None

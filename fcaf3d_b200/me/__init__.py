@@ -519,13 +519,24 @@ SparseTensor.slice = _slice
 
 
 # ------------------------------------------------------------------------------------------- modules
-_POLICY = {"dtype": torch.float32}
+_POLICY = {"dtype": torch.float32, "tf32": False}
 
 
 def set_compute_dtype(dtype):
-    """torch.float32 (CUDA-core fp32 path) or torch.bfloat16 (tcgen05 path for wide layers)."""
+    """torch.float32 (CUDA-core fp32 path, or the TF32 tensor-core path with set_tf32) or torch.bfloat16 (tcgen05 path for
+    wide layers)."""
     assert dtype in (torch.float32, torch.bfloat16)
     _POLICY["dtype"] = dtype
+
+
+def set_tf32(flag):
+    """fp32 feature storage with the wide convolutions on the tensor cores as TF32 operands (b2_conv_tc_tf32; fp32
+    accumulation; ~1e-3 of max against the exact fp32 path, which stays the 2e-5 parity mode).  Inference / forward only."""
+    _POLICY["tf32"] = bool(flag)
+
+
+def get_tf32():
+    return _POLICY["tf32"]
 
 
 def get_compute_dtype():
@@ -552,6 +563,17 @@ class _ConvBase(MinkowskiModuleBase):
     def _w3(self):
         w = self.kernel.detach()
         return (w.unsqueeze(0) if w.dim() == 2 else w).contiguous()
+
+    def _wt_tf32(self):
+        """fp32 [K, Cout, Cin] copy of the kernel for the TF32 tensor-core path; None unless set_tf32(True)."""
+        if not _POLICY["tf32"]:
+            return None
+        k = self.kernel
+        ver = (k._version, k.data_ptr())
+        if getattr(self, "_wt32_ver", None) != ver:
+            self._wt32 = self._w3().transpose(1, 2).contiguous()
+            self._wt32_ver = ver
+        return self._wt32
 
 
 class MinkowskiConvolution(_ConvBase):
@@ -605,7 +627,8 @@ class MinkowskiConvolution(_ConvBase):
                 f = f + self.bias.to(f.dtype)
             return SparseTensor(f, coordinate_map_key=out_key, coordinate_manager=cm)
         bias = self.bias.detach().reshape(-1).contiguous() if self.bias is not None else None
-        f = ops.sparse_conv(x.F.contiguous(), self._w3(), km, n_out, wt_bf16=self._wt_bf16(), bias=bias)
+        f = ops.sparse_conv(x.F.contiguous(), self._w3(), km, n_out, wt_bf16=self._wt_bf16(), bias=bias,
+                            wt_tf32=self._wt_tf32())
         return SparseTensor(f, coordinate_map_key=out_key, coordinate_manager=x.coordinate_manager)
 
     def __repr__(self):
@@ -642,9 +665,14 @@ class MinkowskiGenerativeConvolutionTranspose(_ConvBase):
             w = k.detach()
             cin, cout = self.in_channels, self.out_channels
             wp = w.permute(1, 0, 2).reshape(1, cin, 8 * cout).contiguous()
-            self._pk = (wp, wp.transpose(1, 2).contiguous().to(torch.bfloat16))
+            wpt = wp.transpose(1, 2).contiguous()
+            self._pk = (wp, wpt.to(torch.bfloat16), wpt)
             self._pk_ver = ver
-        return self._pk
+        return self._pk[:2]
+
+    def _packed_tf32(self):
+        self._packed()
+        return self._pk[2] if _POLICY["tf32"] else None
 
     def forward(self, x):
         cm = x.coordinate_manager
@@ -661,7 +689,7 @@ class MinkowskiGenerativeConvolutionTranspose(_ConvBase):
         wp, wpt = self._packed()
         bias = self.bias.detach().reshape(-1).contiguous() if self.bias is not None else None
         out = ops.sparse_conv(feats, wp, None, feats.shape[0], wt_bf16=wpt, bias=bias, scale=scale, shift=shift, act=act,
-                              ch_mod=self.out_channels)
+                              ch_mod=self.out_channels, wt_tf32=self._packed_tf32())
         return out.view(feats.shape[0] * 8, self.out_channels)
 
 

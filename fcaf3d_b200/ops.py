@@ -392,10 +392,11 @@ def tc_eligible(x, cin, cout):
 
 
 def sparse_conv(x, w, kmap, n_out, wt_bf16=None, bias=None, scale=None, shift=None, residual=None, act=ACT_NONE,
-                ch_mod=0, out_dtype=None):
+                ch_mod=0, out_dtype=None, wt_tf32=None):
     """out[o] = act((sum_k x[nbr[k][o]] @ w[k] + bias) * scale + shift + residual[o]).
 
-    w: fp32 [K, Cin, Cout]; wt_bf16: optional bf16 [K, Cout, Cin] for the tcgen05 path; kmap None = identity (K = 1).
+    w: fp32 [K, Cin, Cout]; wt_bf16: optional bf16 [K, Cout, Cin] for the tcgen05 path; wt_tf32: optional fp32 [K, Cout, Cin]
+    for fp32 rows on the tensor cores as TF32 operands; kmap None = identity (K = 1).
     """
     require_cuda(x, "features")
     wshape = w.shape if torch.is_tensor(w) else w          # a bare (K, Cin, Cout) is enough for the tcgen05 path
@@ -408,7 +409,9 @@ def sparse_conv(x, w, kmap, n_out, wt_bf16=None, bias=None, scale=None, shift=No
     if residual is not None:
         assert residual.dtype == out_dtype and residual.shape == out.shape
     use_tc = wt_bf16 is not None and tc_eligible(x, cin, cout)
-    if not use_tc and not torch.is_tensor(w):
+    use_tf32 = (not use_tc and wt_tf32 is not None and _TC_ENABLED and x.dtype == torch.float32
+                and out_dtype == torch.float32 and cin % 32 == 0 and cout % 32 == 0)
+    if not use_tc and not use_tf32 and not torch.is_tensor(w):
         raise B2Error("sparse_conv: fp32 weights are required off the tcgen05 path")
     if PROFILE is not None:
         pairs = kmap_pairs(kmap, n_out)
@@ -416,12 +419,16 @@ def sparse_conv(x, w, kmap, n_out, wt_bf16=None, bias=None, scale=None, shift=No
         flops = 2.0 * pairs * cin * cout
         nbytes = esz * (x.shape[0] * cin + kvol * cin * cout) + out.element_size() * n_out * cout + 4.0 * kvol * ld
     t0 = _prof_start()
-    if use_tc:
+    if use_tc or use_tf32:
         perm = None
         if kmap is not None and kvol == 27:
             kmap.tc_uses += 1
             if kmap.sorted is not None or (0 < SORT_MIN_ROWS <= n_out and kmap.tc_uses >= SORT_MIN_USES):
                 perm, nbr, tmask = kmap_sorted(kmap)
+    if use_tf32:
+        call("b2_conv_tc_tf32", ptr(x), x.shape[0], ptr(wt_tf32), ptr(nbr), ld, ptr(tmask), ptr(perm), n_out, cin, cout,
+             kvol, ptr(bias), ptr(scale), ptr(shift), ptr(residual), act, ch_mod, ptr(out))
+    elif use_tc:
         call("b2_conv_tc", ptr(x), x.shape[0], ptr(wt_bf16), ptr(nbr), ld, ptr(tmask), ptr(perm), n_out, cin, cout, kvol,
              ptr(bias), ptr(scale), ptr(shift), ptr(residual), act, ch_mod, ptr(out), DT[out_dtype])
     else:
@@ -430,7 +437,7 @@ def sparse_conv(x, w, kmap, n_out, wt_bf16=None, bias=None, scale=None, shift=No
         call("b2_conv_cc", ptr(x), DT[x.dtype], ptr(w), ptr(nbr), ld, ptr(tmask), n_out, cin, cout, kvol, ptr(bias),
              ptr(scale), ptr(shift), ptr(residual), act, ch_mod, ptr(out), DT[out_dtype])
     if t0 is not None:
-        _prof_stop(t0, "conv_tc" if use_tc else "conv_cc", flops, nbytes)
+        _prof_stop(t0, "conv_tc" if (use_tc or use_tf32) else "conv_cc", flops, nbytes)
     return out
 
 

@@ -122,6 +122,14 @@ int b2_conv_tc(const void* in_bf16, long long n_in, const void* wt_bf16, const i
                const unsigned int* tile_mask, const int* out_rows,
                long long n_out, int cin, int cout, int kvol, const float* bias, const float* scale, const float* shift,
                const void* residual, int act, int ch_mod, void* out, int out_dtype, void* stream);
+/* The same kernel on fp32 rows and fp32 weights wt_f32 [kvol, cout, cin], read by the tensor cores as TF32 operands
+ * (products of 10-bit mantissas, fp32 accumulation), fp32 output: the fp32-storage mode of the tensor-core path (ME's own
+ * arithmetic is fp32 cuBLAS SGEMM; tolerance against it 1e-3 of the output's max, stated in tests/test_conv_gpu.py).
+ * cin % 32 == 0, cout % 32 == 0. */
+int b2_conv_tc_tf32(const void* in_f32, long long n_in, const void* wt_f32, const int* nbr, long long ld,
+                    const unsigned int* tile_mask, const int* out_rows, long long n_out, int cin, int cout, int kvol,
+                    const float* bias, const float* scale, const float* shift, const void* residual, int act, int ch_mod,
+                    void* out, void* stream);
 
 /* Sparsity-aware grouping of the rows of a neighbour table (no counterpart in ME 0.5.4, which runs one GEMM per kernel
  * offset; same idea as TorchSparse++'s sorted implicit GEMM): rows are ordered by their set of present offsets so that a
@@ -302,7 +310,8 @@ int b2_bce_logits(const float* x, const float* t, long long n, float* loss, floa
  * must outlive the engine) and fl = {voxel_size, score_thr, iou_thr, InstanceNorm eps}; allocates a small pinned staging
  * ring and events.  Returns NULL on error.  One engine per device; calls on one engine must not overlap on the host.
  * b2_engine_infer (per step, allocates nothing): points_host / n_points_host are HOST arrays of n_scenes device pointers
- * ([n_i, dim] fp32 rows xyz + colour) and row counts; dtype = activation storage (0 fp32, 1 bf16); every intermediate is
+ * ([n_i, dim] fp32 rows xyz + colour) and row counts; dtype = activation storage (0 fp32, 1 bf16, 2 fp32 with the wide
+ * convolutions as TF32 tensor-core operands: the table's `wt` pointers then hold fp32 [kvol, cout, cin]); every intermediate is
  * taken from `arena` (-3 if too small; *arena_used_host reports the bytes used); detections come back in the caller's
  * buffers of out_cap >= b2_engine_out_rows() rows: out_boxes [.,7], out_scores, out_labels, out_scene, grouped by
  * (scene, class), *out_count (device) of them valid; *n_rows_host = rows the tail worked on.  The call blocks on the few

@@ -254,3 +254,31 @@ def test_basic_block_and_union_add(dev):
                             up_o).to(dev)
         s, rs = x + up_g(y), o + up_o(ry)
         assert torch.equal(s.C.cpu(), rs.C) and rel_err(s.F, rs.F) < 1e-4
+
+
+@pytest.mark.parametrize("cin,cout,ksize,stride", [(64, 64, 3, 1), (128, 256, 3, 2), (512, 128, 3, 1), (256, 64, 1, 2), (32, 96, 3, 1)])
+def test_conv_tf32_tensor_core_path(dev, cin, cout, ksize, stride):
+    """b2_conv_tc_tf32 (fp32 rows and weights as TF32 tensor-core operands, fp32 accumulation) with the fused epilogue and a
+    residual against the exact fp32 CUDA-core kernel on the same operands.  Stated tolerance: 1e-3 of the output's largest
+    magnitude (TF32 keeps 10 mantissa bits of every operand: relative product error <= 2^-10, averaged down by the
+    accumulation over K * Cin >= 256 terms), and exactly the sparsity pattern of the exact path (a zero input gives zero)."""
+    from util import surface_coords
+    c = torch.from_numpy(surface_coords(6000, 2, seed=5)).to(dev)
+    x0 = ME.SparseTensor(torch.zeros(len(c), 1, device=dev), coordinates=c)
+    cm, key = x0.coordinate_manager, x0.coordinate_map_key
+    okey = key if stride == 1 else cm.stride(key, stride)
+    km = cm.kernel_map(key, okey, ksize)
+    n_in, n_out = cm.size(key), cm.size(okey)
+    torch.manual_seed(cin + cout)
+    f = torch.randn(n_in, cin, device=dev)
+    w = torch.randn(ksize ** 3, cin, cout, device=dev) * 0.05
+    wt = w.transpose(1, 2).contiguous()
+    scale, shift = torch.rand(cout, device=dev) + .5, torch.randn(cout, device=dev)
+    res = torch.randn(n_out, cout, device=dev)
+    kw = dict(scale=scale, shift=shift, residual=res, act=ops.ACT_ELU, out_dtype=torch.float32)
+    y_tc = ops.sparse_conv(f, w, km, n_out, wt_tf32=wt, **kw)
+    y_cc = ops.sparse_conv(f, w, km, n_out, **kw)
+    err = ((y_tc - y_cc).abs().max() / y_cc.abs().max()).item()
+    assert 0 < err < 1e-3, err                          # > 0: the tensor-core path really ran
+    z = ops.sparse_conv(torch.zeros_like(f), w, km, n_out, wt_tf32=wt, out_dtype=torch.float32)
+    assert float(z.abs().max()) == 0.0
