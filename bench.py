@@ -248,7 +248,7 @@ def bench_infer(ctx, args, workload, dtype_name, steps, warmup, clk=None, brief=
     from fcaf3d_b200 import me as ME
     from fcaf3d_b200 import ops
     from fcaf3d_b200.data import ScenePrefetcher
-    from fcaf3d_b200.detector import DetectionRead
+    from fcaf3d_b200.detector import DetectionRead, wait_ready
     dtype = torch.bfloat16 if dtype_name == "bf16" else torch.float32
     ME.set_compute_dtype(dtype)
     ME.set_tf32(dtype_name == "tf32")
@@ -289,6 +289,7 @@ def bench_infer(ctx, args, workload, dtype_name, steps, warmup, clk=None, brief=
         ctx.flush.fill_(1)
         dets = step_device()
     host_ms = 1000.0 * (time.perf_counter() - h0) / steps      # time the host needed to ENQUEUE a step (incl. its reads)
+    wait_ready(dets)            # the last step's NMS tail runs on the executor's side stream: the bracket closes behind it
     e.record()
     torch.cuda.synchronize()
     ctx.barrier()

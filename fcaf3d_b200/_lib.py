@@ -19,6 +19,7 @@ _SCALARS = {
     "float": ctypes.c_float,
     "size_t": ctypes.c_size_t,
     "unsigned int": ctypes.c_uint,
+    "double": ctypes.c_double,
 }
 
 

@@ -19,15 +19,20 @@
 #define ST_AGG 1ull
 #define ST_PREFIX 2ull
 
-// WINNER: the flags are not read from memory but computed in place - row i is flagged when it is the winning (lowest)
+// WINNER >= 1: the flags are not read from memory but computed in place - row i is flagged when it is the winning (lowest)
 // input row of its hash slot (b2_map_build: saves the pass that wrote the flags and the one that read them back).
-template <bool WINNER>
+// WINNER == 2 (map builds whose caller wants no inverse map): the scan also does the finalize step for the winners - it
+// writes their compacted coordinate row (floored to `quant`), optionally their input row (unique_index) and the compacted
+// row id into their hash slot - so the build is two kernels (insert, scan) and the positions never go to memory.
+template <int WINNER>
 __global__ void __launch_bounds__(SCAN_THREADS) k_scan_flags(const uint8_t* __restrict__ flags,
                                                              const int* __restrict__ row_slot,
-                                                             const B2Slot* __restrict__ table, int n,
+                                                             B2Slot* __restrict__ table, int n,
                                                              int* __restrict__ pos, int* __restrict__ total,
                                                              unsigned long long* status, unsigned int* ticket,
-                                                             int nblocks) {
+                                                             int nblocks, const int* __restrict__ coords = nullptr,
+                                                             int quant = 0, int* __restrict__ out_coords = nullptr,
+                                                             int* __restrict__ unique_index = nullptr) {
   __shared__ int s_bid;
   __shared__ int s_warp[SCAN_THREADS / 32];
   __shared__ int s_prefix;
@@ -38,8 +43,8 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_flags(const uint8_t* __re
   const long long base = (long long)bid * SCAN_TILE + (long long)threadIdx.x * SCAN_ITEMS;
 
   int f[SCAN_ITEMS];
+  int sl[WINNER ? SCAN_ITEMS : 1];
   if (WINNER) {
-    int sl[SCAN_ITEMS];
     if (base + SCAN_ITEMS <= n) {
 #pragma unroll
       for (int i = 0; i < SCAN_ITEMS / 4; ++i) {
@@ -125,6 +130,25 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_flags(const uint8_t* __re
   }
   __syncthreads();
   int run = s_prefix + warp_off + (incl - local);
+  if (WINNER == 2) {
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i) {
+      if (f[i]) {
+        const long long row = base + i;
+        int4 c = __ldg(reinterpret_cast<const int4*>(coords) + row);
+        if (quant > 0) {
+          c.y = b2_floor_div(c.y, quant) * quant;
+          c.z = b2_floor_div(c.z, quant) * quant;
+          c.w = b2_floor_div(c.w, quant) * quant;
+        }
+        reinterpret_cast<int4*>(out_coords)[run] = c;
+        if (unique_index) unique_index[run] = (int)row;
+        table[sl[i]].val = (unsigned int)run;
+        ++run;
+      }
+    }
+    return;
+  }
   if (base + SCAN_ITEMS <= n) {
     int o[SCAN_ITEMS];
 #pragma unroll
@@ -165,14 +189,15 @@ int b2_scan_flags_launch(const uint8_t* flags, long long n, int* pos, int* total
   B2_CUDA(cudaMemsetAsync(ws, 0, need, st));
   unsigned int* ticket = reinterpret_cast<unsigned int*>(ws);
   unsigned long long* status = reinterpret_cast<unsigned long long*>(ws) + 1;
-  k_scan_flags<false><<<nblocks, SCAN_THREADS, 0, st>>>(flags, nullptr, nullptr, (int)n, pos, total, status, ticket, nblocks);
+  k_scan_flags<0><<<nblocks, SCAN_THREADS, 0, st>>>(flags, nullptr, nullptr, (int)n, pos, total, status, ticket, nblocks);
   B2_LAUNCH_CHECK();
   return B2_OK;
 }
 
 // exclusive positions of the winning rows of a hash build (see k_scan_flags<true>); row_slot must be 16-byte aligned
-static int b2_scan_winners_launch(const int* row_slot, const B2Slot* table, long long n, int* pos, int* total, void* ws,
-                                  size_t ws_bytes, cudaStream_t st) {
+static int b2_scan_winners_launch(const int* row_slot, B2Slot* table, long long n, int* pos, int* total, void* ws,
+                                  size_t ws_bytes, cudaStream_t st, const int* coords = nullptr, int quant = 0,
+                                  int* out_coords = nullptr, int* unique_index = nullptr) {
   const size_t need = b2_scan_ws_bytes_impl(n);
   if (ws_bytes < need) {
     b2_set_error("scan workspace too small: %zu < %zu", ws_bytes, need);
@@ -182,7 +207,11 @@ static int b2_scan_winners_launch(const int* row_slot, const B2Slot* table, long
   B2_CUDA(cudaMemsetAsync(ws, 0, need, st));
   unsigned int* ticket = reinterpret_cast<unsigned int*>(ws);
   unsigned long long* status = reinterpret_cast<unsigned long long*>(ws) + 1;
-  k_scan_flags<true><<<nblocks, SCAN_THREADS, 0, st>>>(nullptr, row_slot, table, (int)n, pos, total, status, ticket, nblocks);
+  if (out_coords != nullptr)
+    k_scan_flags<2><<<nblocks, SCAN_THREADS, 0, st>>>(nullptr, row_slot, table, (int)n, nullptr, total, status, ticket, nblocks,
+                                                      coords, quant, out_coords, unique_index);
+  else
+    k_scan_flags<1><<<nblocks, SCAN_THREADS, 0, st>>>(nullptr, row_slot, table, (int)n, pos, total, status, ticket, nblocks);
   B2_LAUNCH_CHECK();
   return B2_OK;
 }
@@ -502,8 +531,11 @@ int b2_map_build(const int* coords, long long n, int quant, void* table, long lo
   const int T = 256, G = b2_div_up(n, T);
   k_hash_insert<<<G, T, 0, st>>>(coords, (int)n, quant, (B2Slot*)table, (unsigned)(cap - 1), row_slot, err);
   B2_LAUNCH_CHECK();
-  // the scan computes "row i won its slot" itself (k_scan_flags<true>), and so does the finalize kernel
-  int rc = b2_scan_winners_launch(row_slot, (const B2Slot*)table, n, pos, n_out, scan_ws, scan_bytes, st);
+  if (inverse_map == nullptr)   // nobody asked for the inverse map: insert + scan-with-finalize, two kernels
+    return b2_scan_winners_launch(row_slot, (B2Slot*)table, n, pos, n_out, scan_ws, scan_bytes, st, coords, quant, out_coords,
+                                  unique_index);
+  // the scan computes "row i won its slot" itself (k_scan_flags<1>), and so does the finalize kernel
+  int rc = b2_scan_winners_launch(row_slot, (B2Slot*)table, n, pos, n_out, scan_ws, scan_bytes, st);
   if (rc) return rc;
   k_build_finalize<<<G, T, 0, st>>>(coords, (int)n, quant, (B2Slot*)table, row_slot, pos, out_coords, unique_index,
                                     inverse_map);

@@ -166,17 +166,19 @@ struct Run {
   }
 
   // ---- coordinate maps -------------------------------------------------------------------------------------------
-  int build_start(const int* coords, long long n, int quant, int ts_out, Pending* p) {
+  // want_uidx: the input map (features are picked at the representatives' rows); nobody reads an inverse map in this pass,
+  // so every build is the two-kernel variant of b2_map_build
+  int build_start(const int* coords, long long n, int quant, int ts_out, Pending* p, bool want_uidx = false) {
     p->cap = table_cap(n);
     p->ts = ts_out;
     p->table = take((size_t)p->cap * 16);
     p->out_coords = (int*)take((size_t)(n > 0 ? n : 1) * 16);
-    p->uidx = (int*)take((size_t)(n > 0 ? n : 1) * 4);
-    p->inverse = (int*)take((size_t)(n > 0 ? n : 1) * 4);
+    p->uidx = want_uidx ? (int*)take((size_t)(n > 0 ? n : 1) * 4) : nullptr;
+    p->inverse = nullptr;
     p->status = (int*)take((size_t)(3 + nb) * 4);
     const size_t wsb = b2_map_build_ws_bytes(n);
     void* ws = take(wsb);
-    if (!p->table || !p->out_coords || !p->uidx || !p->inverse || !p->status || !ws) return B2_ERR_WS;
+    if (!p->table || !p->out_coords || (want_uidx && !p->uidx) || !p->status || !ws) return B2_ERR_WS;
     B2_CUDA(cudaMemsetAsync(p->status, 0, (size_t)(3 + nb) * 4, st));
     int rc = b2_map_build(coords, n, quant, p->table, p->cap, p->out_coords, p->uidx, p->inverse, p->status, p->status + 1,
                           ws, wsb, stv);
@@ -304,10 +306,10 @@ struct Run {
       rc = kernel_map(parent, parent, 3, &pk);
       if (rc) return rc;
       rc = b2_kernel_map_children(pk->nbr, pk->ld, maps[parent].n, k.nbr, k.ld, k.tmask, stv);
-    } else if (in != out && maps[out].ts == 2 * maps[in].ts && ks == 3 && 2 * maps[in].n < 3 * maps[out].n) {
+    } else if (in != out && maps[out].ts == 2 * maps[in].ts && ((ks == 3 && 2 * maps[in].n < 3 * maps[out].n) || ks == 2)) {
       rc = ensure_table(out);
       if (rc) return rc;
-      rc = b2_kernel_map_strided(maps[out].table, maps[out].cap, maps[in].coords, maps[in].n, 3, maps[in].ts, k.nbr, k.ld,
+      rc = b2_kernel_map_strided(maps[out].table, maps[out].cap, maps[in].coords, maps[in].n, ks, maps[in].ts, k.nbr, k.ld,
                                  k.tmask, stv);
     } else {
       rc = ensure_table(in);
@@ -376,7 +378,7 @@ struct Level {
 
 static int infer(Engine& e, Run& r, const float* const* points, const long long* n_points, int n_scenes, int dtype,
                  float* out_boxes, float* out_scores, int* out_labels, int* out_scene, int* out_count, long long out_cap,
-                 long long* n_rows_out) {
+                 long long* n_rows_out, void* tail_stream) {
   r.nb = n_scenes;
   r.dt = dtype == 1 ? 1 : 0;
   r.tf32 = dtype == 2;
@@ -395,7 +397,7 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
     row0 += n_points[b];
   }
   Pending p0, p1;
-  CK(r.build_start(coords, total, 0, 1, &p0));
+  CK(r.build_start(coords, total, 0, 1, &p0, true));
   CK(r.build_start(coords, total, 2, 2, &p1));
   int* uidx = p0.uidx;
   int m1;
@@ -592,6 +594,16 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
   }
 
   // ---- tail: per (scene, level) top-k -> decode -> per (scene, class) BEV NMS (fcaf3d_neck_with_head.py:205-253,332-374)
+  // The tail is a chain of small launches (one CTA per scene or per (scene, class) segment: ~0.4 ms at a few per cent of
+  // the SMs).  With a tail stream it is enqueued THERE, behind an event on the main stream, so the next step's
+  // quantise / hash / stem work on the main stream fills the GPU while this tail drains.
+  if (tail_stream != nullptr && tail_stream != r.stv) {
+    const int s = r.slot();
+    B2_CUDA(cudaEventRecord(e.events[s], r.st));
+    B2_CUDA(cudaStreamWaitEvent((cudaStream_t)tail_stream, e.events[s], 0));
+    r.st = (cudaStream_t)tail_stream;
+    r.stv = tail_stream;
+  }
   const int n_cls = e.n_cls, n_reg = e.n_reg;
   const int rotated = n_reg != 6;
   const int yaw_mode = rotated ? e.yaw_mode : 0;
@@ -773,7 +785,8 @@ long long b2_engine_out_rows(void* engine, int n_scenes) {
 
 int b2_engine_infer(void* engine, const float* const* points_host, const long long* n_points_host, int n_scenes, int dtype,
                     void* arena, size_t arena_bytes, float* out_boxes, float* out_scores, int* out_labels, int* out_scene,
-                    int* out_count, long long out_cap, long long* n_rows_host, size_t* arena_used_host, void* stream) {
+                    int* out_count, long long out_cap, long long* n_rows_host, size_t* arena_used_host, void* stream,
+                    void* tail_stream) {
   Engine* e = (Engine*)engine;
   B2_CHECK_ARG(e && points_host && n_points_host && arena && out_boxes && out_scores && out_labels && out_scene && out_count,
                "b2_engine_infer: null argument");
@@ -784,7 +797,7 @@ int b2_engine_infer(void* engine, const float* const* points_host, const long lo
   Run r(*e, arena, arena_bytes, stream);
   long long rows = 0;
   const int rc = infer(*e, r, points_host, n_points_host, n_scenes, dtype, out_boxes, out_scores, out_labels, out_scene,
-                       out_count, out_cap, &rows);
+                       out_count, out_cap, &rows, tail_stream);
   if (n_rows_host) *n_rows_host = rows;
   if (arena_used_host) *arena_used_host = r.off;
   return rc;

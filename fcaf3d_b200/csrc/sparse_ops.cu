@@ -6,6 +6,8 @@
 // mmdet3d/models/backbones/me_resnet.py:18-25,55-78 and
 // mmdet3d/models/dense_heads/fcaf3d_neck_with_head.py:49-72,83-85 (MinkowskiEngine v0.5.4, not vendored).
 #include "common.cuh"
+
+int b2_optin_smem(const void* func, int bytes, unsigned long long* done);   // tc_map.cu
 #include <stdlib.h>
 
 // ---------------------------------------------------------------------------
@@ -428,57 +430,59 @@ __global__ void __launch_bounds__(256) k_conv_flat(const TIn* __restrict__ in, c
 }
 
 // Narrow-input convolution that only touches the neighbours that exist (the stem: Cin = 3, 27 offsets, but a voxel of the
-// stride-2 map has ~3 of its 27 input neighbours: the dense 81-wide inner product above multiplies 90 % zeros).
-// CTA = 64 output rows per pass (persistent over row blocks); 16 threads per row x 4 output channels each; the whole
-// kernel [K][Cin<=4][64] sits in shared memory; per present neighbour: Cin broadcast loads + Cin LDS.128 + 4 Cin FMAs.
-// Accumulation order per output element is the same as in k_conv_flat (k ascending, then channel).
-#define CN_ROWS 64
+// stride-2 map has ~3 of its 27 input neighbours: a dense 81-wide inner product multiplies 90 % zeros).
+// Every WARP works on its own 32 output rows without block-wide barriers: phase 1, lane = row, reads the row's 27 table
+// entries (coalesced over the lanes, all loads independent) and keeps the present ones as (k << 26 | input row) in the
+// warp's shared list; phase 2, two rows at a time, 16 lanes x 4 output channels per row, walks the list (input loads of
+// four neighbours issued back to back, weights [K][Cin][64] from shared memory) and writes one 128-byte output row per
+// half warp.  Accumulation order per output element: k ascending, then channel (as in k_conv_flat).
+#define CN_WARPS 8
 template <typename TIn, typename TOut>
-__global__ void __launch_bounds__(256) k_conv_narrow(const TIn* __restrict__ in, const float* __restrict__ w,
-                                                     const int* __restrict__ nbr, int ld, int n_out, int cin, int cout,
-                                                     int kvol, const float* __restrict__ bias,
-                                                     const float* __restrict__ scale, const float* __restrict__ shift,
-                                                     const TOut* __restrict__ residual, int act, int ch_mod,
-                                                     TOut* __restrict__ out) {
-  __shared__ __align__(16) float s_w[27 * 4 * 64];
-  __shared__ int s_nbr[27][CN_ROWS];
-  __shared__ int s_cnt[CN_ROWS];
-  const int tid = threadIdx.x, tx = tid & 15, ry = tid >> 4;
-  for (int i = tid; i < kvol * 4 * 64; i += 256) {
-    const int n = i & 63, c = (i >> 6) & 3, k = i >> 8;
-    s_w[i] = (c < cin && n < cout) ? __ldg(w + ((long long)k * cin + c) * cout + n) : 0.f;
+__global__ void __launch_bounds__(CN_WARPS * 32) k_conv_narrow(const TIn* __restrict__ in, const float* __restrict__ w,
+                                                               const int* __restrict__ nbr, int ld, int n_out, int cin,
+                                                               int cout, int kvol, const float* __restrict__ bias,
+                                                               const float* __restrict__ scale,
+                                                               const float* __restrict__ shift,
+                                                               const TOut* __restrict__ residual, int act, int ch_mod,
+                                                               TOut* __restrict__ out) {
+  extern __shared__ __align__(16) unsigned char cn_smem[];
+  int* s_list = reinterpret_cast<int*>(cn_smem);                                    // [CN_WARPS][27][32]
+  float* s_w = reinterpret_cast<float*>(cn_smem + CN_WARPS * 27 * 32 * 4);          // [kvol][cin][64]
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int i = tid; i < kvol * cin * 64; i += CN_WARPS * 32) {
+    const int n = i & 63, kc = i >> 6;
+    s_w[i] = (n < cout) ? __ldg(w + (long long)kc * cout + n) : 0.f;
   }
-  for (int row0 = blockIdx.x * CN_ROWS; row0 < n_out; row0 += gridDim.x * CN_ROWS) {
-    __syncthreads();
-    for (int i = tid; i < kvol * CN_ROWS; i += 256) {
-      const int k = i / CN_ROWS, r = i - k * CN_ROWS;
-      s_nbr[k][r] = (row0 + r < n_out) ? __ldg(nbr + (long long)k * ld + row0 + r) : -1;
-    }
-    __syncthreads();
-    // one thread per row compacts its column in place: entry j = (k << 26) | row of the j-th PRESENT neighbour, so that
-    // the compute loop below issues the input loads of four neighbours back to back instead of one dependent global
-    // load per taken branch
-    if (tid < CN_ROWS) {
-      int cnt = 0;
-      for (int k = 0; k < kvol; ++k) {
-        const int src = s_nbr[k][tid];
-        if (src >= 0) s_nbr[cnt++][tid] = (k << 26) | src;
+  __syncthreads();
+  int* list = s_list + warp * 27 * 32;
+  const int half = lane >> 4, tx = lane & 15;
+  for (long long row0 = ((long long)blockIdx.x * CN_WARPS + warp) * 32; row0 < n_out;
+       row0 += (long long)gridDim.x * CN_WARPS * 32) {
+    int cnt = 0;
+    {
+      const long long o = row0 + lane;
+      if (o < n_out) {
+        int v[27];
+#pragma unroll
+        for (int k = 0; k < 27; ++k) v[k] = (k < kvol) ? __ldg(nbr + (long long)k * ld + o) : -1;
+#pragma unroll
+        for (int k = 0; k < 27; ++k)
+          if (v[k] >= 0) list[(cnt++) * 32 + lane] = (k << 26) | v[k];
       }
-      s_cnt[tid] = cnt;
     }
-    __syncthreads();
+    __syncwarp();
 #pragma unroll 1
-    for (int rr = 0; rr < CN_ROWS / 16; ++rr) {
-      const int r = ry + 16 * rr, o = row0 + r;
-      if (o >= n_out) continue;
+    for (int rr = 0; rr < 16; ++rr) {
+      const int r = rr * 2 + half;
+      const long long o = row0 + r;
+      const int n_e = __shfl_sync(0xffffffffu, cnt, r);
       float acc[4] = {0.f, 0.f, 0.f, 0.f};
-      const int cnt = s_cnt[r];
-      for (int j0 = 0; j0 < cnt; j0 += 4) {
+      for (int j0 = 0; j0 < n_e; j0 += 4) {
         int e[4];
         float a[4][4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-          e[u] = (j0 + u < cnt) ? s_nbr[j0 + u][r] : -1;
+          e[u] = (j0 + u < n_e) ? list[(j0 + u) * 32 + r] : -1;
           const TIn* p = in + (long long)(e[u] & 0x3FFFFFF) * cin;
 #pragma unroll
           for (int c = 0; c < 4; ++c) a[u][c] = (e[u] >= 0 && c < cin) ? to_f32<TIn>(p[c]) : 0.f;
@@ -490,7 +494,7 @@ __global__ void __launch_bounds__(256) k_conv_narrow(const TIn* __restrict__ in,
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
             if (c >= cin) continue;
-            const float4 wv = *reinterpret_cast<const float4*>(&s_w[((k * 4 + c) << 6) + tx * 4]);
+            const float4 wv = *reinterpret_cast<const float4*>(&s_w[((k * cin + c) << 6) + tx * 4]);
             acc[0] = fmaf(a[u][c], wv.x, acc[0]);
             acc[1] = fmaf(a[u][c], wv.y, acc[1]);
             acc[2] = fmaf(a[u][c], wv.z, acc[2]);
@@ -498,18 +502,21 @@ __global__ void __launch_bounds__(256) k_conv_narrow(const TIn* __restrict__ in,
           }
         }
       }
+      if (o < n_out) {
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int n = tx * 4 + j;
-        if (n >= cout) continue;
-        const int ch = ch_mod > 0 ? (n % ch_mod) : n;
-        float v = acc[j];
-        if (bias) v += bias[ch];
-        if (scale) v = v * scale[ch] + shift[ch];
-        if (residual) v += to_f32<TOut>(residual[(long long)o * cout + n]);
-        out[(long long)o * cout + n] = from_f32<TOut>(b2_apply_act(v, act));
+        for (int j = 0; j < 4; ++j) {
+          const int n = tx * 4 + j;
+          if (n >= cout) continue;
+          const int ch = ch_mod > 0 ? (n % ch_mod) : n;
+          float v = acc[j];
+          if (bias) v += bias[ch];
+          if (scale) v = v * scale[ch] + shift[ch];
+          if (residual) v += to_f32<TOut>(residual[o * cout + n]);
+          out[o * cout + n] = from_f32<TOut>(b2_apply_act(v, act));
+        }
       }
     }
+    __syncwarp();
   }
 }
 
@@ -940,13 +947,18 @@ int b2_conv_cc(const void* in, int in_dtype, const float* w, const int* nbr, lon
   const bool flat = (nbr != nullptr && cin <= 8 && kvol <= 27);
   static const bool narrow_ok = !(getenv("B2_CONV_NARROW") && atoi(getenv("B2_CONV_NARROW")) == 0);
   const bool narrow = narrow_ok && nbr != nullptr && cin <= 4 && cout <= 64 && kvol <= 27;
-  const int gn = (int)(b2_div_up(n_out, CN_ROWS) < 148 * 6 ? b2_div_up(n_out, CN_ROWS) : 148 * 6);
+  const int cn_rows = CN_WARPS * 32;
+  const int gn = (int)(b2_div_up(n_out, cn_rows) < 148 * 4 ? b2_div_up(n_out, cn_rows) : 148 * 4);
+  const int cn_smem_bytes = CN_WARPS * 27 * 32 * 4 + kvol * cin * 64 * 4;
 #define CC_LAUNCH(TI, TO)                                                                                          \
   do {                                                                                                             \
-    if (narrow)                                                                                                    \
-      k_conv_narrow<TI, TO><<<gn, 256, 0, st>>>((const TI*)in, w, nbr, (int)ld, (int)n_out, cin, cout, kvol, bias,  \
-                                                scale, shift, (const TO*)residual, act, ch_mod, (TO*)out);         \
-    else if (flat)                                                                                                 \
+    if (narrow) {                                                                                                  \
+      static unsigned long long cn_done = 0;                                                                       \
+      if (cn_smem_bytes > 48 * 1024)                                                                               \
+        if (int rc0 = b2_optin_smem((const void*)k_conv_narrow<TI, TO>, 56 * 1024, &cn_done)) return rc0;          \
+      k_conv_narrow<TI, TO><<<gn, CN_WARPS * 32, cn_smem_bytes, st>>>((const TI*)in, w, nbr, (int)ld, (int)n_out, cin, \
+                                                cout, kvol, bias, scale, shift, (const TO*)residual, act, ch_mod, (TO*)out); \
+    } else if (flat)                                                                                                 \
       k_conv_flat<TI, TO><<<grid, 256, 0, st>>>((const TI*)in, w, nbr, (int)ld, (int)n_out, cin, cout, kvol, bias,  \
                                                 scale, shift, (const TO*)residual, act, ch_mod, (TO*)out);         \
     else                                                                                                           \

@@ -534,10 +534,20 @@ class Fcaf3DNeckWithHead(nn.Module):
 _PINNED_OUT = {}
 
 
+def wait_ready(dets, stream=None):
+    """Results of the native executor may still be in flight on its tail stream: makes `stream` (default: the current one)
+    wait for them.  A no-op for results produced on the current stream."""
+    ev = dets.get("ready")
+    if ev is not None:
+        (stream or torch.cuda.current_stream()).wait_event(ev)
+    return dets
+
+
 def split_detections(dets, num_scenes):
     """Device-side result dict -> host list of (boxes, scores, labels) per scene: one read of the count, then ONE packed
     device->host copy of (box, score, label, scene) rows into a reused pinned buffer; the rows come out of the NMS in
     (scene, class) order, so the per-scene split is a slice."""
+    wait_ready(dets)
     n = int(dets["count"].item())
     d = dets["box_dim"]
     packed_dev = torch.cat((dets["boxes"][:n, :d], dets["scores"][:n, None], dets["labels"][:n, None].float(),
@@ -595,6 +605,7 @@ class DetectionRead:
         self.cap = cap
         with torch.cuda.stream(stream):
             stream.wait_event(done)
+            wait_ready(dets, stream)
             packed = torch.cat((dets["boxes"][:cap, :self.d], dets["scores"][:cap, None], dets["labels"][:cap, None].float(),
                                 dets["scene"][:cap, None].float()), dim=1)
             self.host = full[:cap]

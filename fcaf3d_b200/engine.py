@@ -6,6 +6,7 @@ per batch as the GPU.  `InferenceEngine(det)` hands the SAME sequence of library
 Eval mode only (BatchNorm folded), BasicBlock backbones (depth 14 / 18 / 34); anything else stays on the python path.
 """
 import ctypes
+import os
 
 import torch
 
@@ -28,7 +29,11 @@ class InferenceEngine:
         self.det = det
         self._handle = None
         self._sig = None
-        self._arena = None
+        self._arenas = [None, None]      # alternate: the tail of step i may still read arena i % 2 while step i + 1 runs
+        self._arena_free = [None, None]  # event after which the arena may be overwritten (its last tail has drained)
+        self._step = 0
+        self._tail = None                # side stream of the top-k / NMS tail (B2_ENGINE_OVERLAP=0: none)
+        self.overlap_tail = os.environ.get("B2_ENGINE_OVERLAP", "1") != "0"
         self._keep = []
         self._tensors = None
 
@@ -144,26 +149,45 @@ class InferenceEngine:
         labels = torch.empty((cap,), dtype=torch.int32, device=dev)
         scene = torch.empty((cap,), dtype=torch.int32, device=dev)
         count = torch.empty((1,), dtype=torch.int32, device=dev)
-        need = (4096 * total + (256 << 20)) if self._arena is None else 0
+        slot = self._step % 2
+        self._step += 1
+        main = torch.cuda.current_stream(dev)
+        if self.overlap_tail and self._tail is None:
+            self._tail = torch.cuda.Stream(device=dev)
+        tail = self._tail if self.overlap_tail else None
+        if self._arena_free[slot] is not None:
+            main.wait_event(self._arena_free[slot])       # the tail that last read this arena has finished
+        need = (4096 * total + (256 << 20)) if self._arenas[slot] is None else 0
         rows, used = ctypes.c_longlong(0), ctypes.c_size_t(0)
         dt = 1 if ME.get_compute_dtype() == torch.bfloat16 else (2 if ME.get_tf32() else 0)
         for _ in range(6):
-            if self._arena is None or self._arena.numel() < need or self._arena.device != dev:
-                self._arena = None
-                self._arena = torch.empty(max(need, 1 << 20), dtype=torch.uint8, device=dev)
-            rc = l.b2_engine_infer(self._handle, ptrs, counts, n, dt, ptr(self._arena), self._arena.numel(), ptr(boxes),
+            arena = self._arenas[slot]
+            if arena is None or arena.numel() < need or arena.device != dev:
+                self._arenas[slot] = arena = None
+                self._arenas[slot] = arena = torch.empty(max(need, 1 << 20), dtype=torch.uint8, device=dev)
+            rc = l.b2_engine_infer(self._handle, ptrs, counts, n, dt, ptr(arena), arena.numel(), ptr(boxes),
                                    ptr(scores), ptr(labels), ptr(scene), ptr(count), cap, ctypes.byref(rows),
-                                   ctypes.byref(used), stream())
+                                   ctypes.byref(used), stream(), tail.cuda_stream if tail is not None else None)
             if rc == -3:            # arena too small: the launches so far wrote only into the arena - grow it and redo the step
-                torch.cuda.current_stream().synchronize()
-                need = 2 * self._arena.numel()
+                torch.cuda.synchronize(dev)
+                need = 2 * arena.numel()
                 continue
             if rc != 0:
                 raise B2Error("b2_engine_infer failed (%d): %s" % (rc, last_error()))
             break
         else:
             raise B2Error("b2_engine_infer: arena kept overflowing: %s" % last_error())
+        ready = None
+        if tail is not None:
+            for t in (boxes, scores, labels, scene, count):
+                t.record_stream(tail)                     # allocated on the main stream, written on the tail stream
+            ready = torch.cuda.Event()
+            ready.record(tail)
+            self._arena_free[slot] = ready
         self.arena_used = int(used.value)
         nr = int(rows.value)
-        return dict(boxes=boxes[:nr], scores=scores[:nr], labels=labels[:nr], scene=scene[:nr], count=count,
-                    box_dim=7 if self._yaw_rotated else 6)
+        out = dict(boxes=boxes[:nr], scores=scores[:nr], labels=labels[:nr], scene=scene[:nr], count=count,
+                   box_dim=7 if self._yaw_rotated else 6)
+        if ready is not None:
+            out["ready"] = ready     # the detections are complete once this event has fired (detector.wait_ready)
+        return out

@@ -125,7 +125,8 @@ class CoordinateManager:
         # raw rows gives the same map as flooring the deduplicated ones): callers that know the stride of their first
         # convolution ask for it here and both row counts come back behind one wait.
         pre = int(getattr(coordinates, "_b2_prefetch_stride", 0) or 0)
-        p1 = ops.map_build_start(coords, ts * pre, self.num_batches) if pre > 1 and perm is None else None
+        p1 = (ops.map_build_start(coords, ts * pre, self.num_batches, want_index=False)
+              if pre > 1 and perm is None else None)
         out_coords, unique_index, inverse, table, cap, n_out, off = ops.map_build_finish(p0)
         key = CoordinateMapKey(ts, string_id)
         if key in self._maps:
@@ -150,7 +151,7 @@ class CoordinateManager:
         if ck in self._stride_cache or ("s", ck) in self._pending:
             return
         src = self._maps[in_key]
-        self._pending[("s", ck)] = ops.map_build_start(src.coords, src.ts * s, self.num_batches)
+        self._pending[("s", ck)] = ops.map_build_start(src.coords, src.ts * s, self.num_batches, want_index=False)
 
     def stride(self, in_key, stride):
         """Coordinates floored to multiples of ts*stride, deduplicated; cached per (key, stride) (ME A.3)."""
@@ -160,13 +161,13 @@ class CoordinateManager:
             return self._stride_cache[ck]
         src = self._maps[in_key]
         ts_out = src.ts * s
-        pending = self._pending.pop(("s", ck), None) or ops.map_build_start(src.coords, ts_out, self.num_batches)
-        out_coords, _, inverse, table, cap, _, off = ops.map_build_finish(pending)
+        pending = self._pending.pop(("s", ck), None) or ops.map_build_start(src.coords, ts_out, self.num_batches,
+                                                                             want_index=False)
+        out_coords, _, _, table, cap, _, off = ops.map_build_finish(pending)
         key = CoordinateMapKey(ts_out, "")
         if key in self._maps:
             key = self._fresh_id(ts_out)
         m = _Map(out_coords.contiguous(), ts_out, self.num_batches, table, cap, off=off)
-        m.parent_of = {in_key: inverse}
         self._maps[key] = m
         self._stride_cache[ck] = key
         return key
@@ -258,8 +259,11 @@ class CoordinateManager:
                 # map of ALL children of `parent` (generative transpose): derive the table from the parent's, no hash
                 pkm = self.kernel_map(parent, parent, 3, 1)
                 km = ops.kernel_map_children(pkm, self._maps[parent].n)
-            elif (STRIDED_FROM_INPUT and in_key != out_key and dst.ts == 2 * src.ts and int(kernel_size) == 3
-                  and int(dilation) == 1 and (STRIDED_FROM_INPUT > 1 or 2 * src.n < 3 * dst.n)):
+            elif (STRIDED_FROM_INPUT and in_key != out_key and dst.ts == 2 * src.ts and int(dilation) == 1
+                  and ((int(kernel_size) == 3 and (STRIDED_FROM_INPUT > 1 or 2 * src.n < 3 * dst.n))
+                       or int(kernel_size) == 2)):
+                # (kernel 2, the stem's pooling map: every input row has exactly ONE parent, so one probe per input row
+                # replaces eight per output row)
                 # stride 2, few inputs per output (the stem: 786 k -> 738 k rows): ~3.4 probes of the OUT table per input
                 # row instead of 27 probes per output row (188 -> 95 us).  Deeper levels (548 k -> 218 k rows) have ~8
                 # inputs per output, every 128-row tile's mask word is then hit ~3.7 k times (a hot spot in L2, atomics

@@ -96,15 +96,16 @@ def quantize_points(points_list, voxel_size, feat_div=255.0):
     return coords, feats
 
 
-def map_build_start(coords, quant=0, num_batches=0):
-    """Enqueues the dedup kernels and the asynchronous read of (n_out, err, batch offsets); see map_build_finish."""
+def map_build_start(coords, quant=0, num_batches=0, want_index=True):
+    """Enqueues the dedup kernels and the asynchronous read of (n_out, err, batch offsets); see map_build_finish.
+    want_index=False (strided maps inside a network): no unique_index / inverse map, two kernels instead of three."""
     require_cuda(coords, "coords")
     n = int(coords.shape[0])
     dev = coords.device
     table, cap = alloc_table(n, dev)
     out_coords = torch.empty((n, 4), dtype=I32, device=dev)
-    unique_index = torch.empty((n,), dtype=I32, device=dev)
-    inverse = torch.empty((n,), dtype=I32, device=dev)
+    unique_index = torch.empty((n,), dtype=I32, device=dev) if want_index else None
+    inverse = torch.empty((n,), dtype=I32, device=dev) if want_index else None
     status = torch.zeros((2 + num_batches + 1,), dtype=I32, device=dev)  # [n_out, err, offsets...]
     ws_bytes = _lib.lib().b2_map_build_ws_bytes(n)
     ws = workspace(ws_bytes, dev)
@@ -126,10 +127,11 @@ def map_build_finish(p):
     if err == 2:
         raise _lib.B2Error("coordinate rows must be grouped by ascending batch index")
     nb = p["num_batches"]
+    uidx = p["unique_index"][:n_out] if p["unique_index"] is not None else None
     if nb > 0:
-        return (p["out_coords"][:n_out], p["unique_index"][:n_out], p["inverse"], p["table"], p["cap"], n_out,
+        return (p["out_coords"][:n_out], uidx, p["inverse"], p["table"], p["cap"], n_out,
                 (p["status"][2:3 + nb], host[2:3 + nb]))
-    return p["out_coords"][:n_out], p["unique_index"][:n_out], p["inverse"], p["table"], p["cap"], n_out
+    return p["out_coords"][:n_out], uidx, p["inverse"], p["table"], p["cap"], n_out
 
 
 def map_build(coords, quant=0, num_batches=0):

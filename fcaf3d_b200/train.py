@@ -13,10 +13,14 @@ def shard_scenes(n_scenes, rank, world_size):
     return list(range(rank, n_scenes, world_size))
 
 
-def make_optimizer(model, lr=1e-3, weight_decay=1e-4):
-    params = list(model.parameters())
-    fused = bool(params) and all(p.is_cuda for p in params)      # one multi-tensor kernel chain instead of ~10 per step
-    return torch.optim.AdamW(params, lr=lr, weight_decay=weight_decay, fused=fused)
+def make_optimizer(model, lr=1e-3, weight_decay=1e-4, max_norm=10.0):
+    """AdamW + gradient clipping of the reference recipe on the library's kernels (fcaf3d_b200.optim.FusedAdamW: norm,
+    clip and update of all parameters in three launches).  CPU parameters (host-logic tests) get torch's AdamW."""
+    params = [p for p in model.parameters() if p.requires_grad]
+    if params and all(p.is_cuda for p in params):
+        from .optim import FusedAdamW
+        return FusedAdamW(params, lr=lr, weight_decay=weight_decay, max_norm=max_norm)
+    return torch.optim.AdamW(params, lr=lr, weight_decay=weight_decay)
 
 
 def wrap_ddp(model, device):
@@ -61,7 +65,10 @@ def train_step(module, optimizer, points, gt_boxes, gt_labels, max_norm=10.0, ne
         with torch.no_grad():
             nxt = det.prepare(next_points)
     total.backward()
-    torch.nn.utils.clip_grad_norm_(module.parameters(), max_norm)
+    if hasattr(optimizer, "max_norm"):
+        optimizer.max_norm = max_norm                    # clipping happens inside the fused update
+    else:
+        torch.nn.utils.clip_grad_norm_(module.parameters(), max_norm)
     optimizer.step()
     out = (total.detach(), {k: v.detach() for k, v in losses.items()})
     return out + (nxt,) if next_points is not None else out

@@ -50,7 +50,8 @@ size_t b2_map_build_ws_bytes(long long n);
 /* ME insert_and_map / stride: hash-insert n rows (optionally floored to multiples of `quant`), dedup with the
  * LOWEST input row as representative, rows in first-occurrence order (ME CPU rule).  table: cap slots of 16 B,
  * cap = power of two >= 2n.  Outputs: out_coords[*n_out,4], unique_index[*n_out], inverse_map[n],
- * *err != 0 if a coordinate is out of the packed range. */
+ * *err != 0 if a coordinate is out of the packed range.  inverse_map == NULL (strided maps inside a network: nobody reads
+ * it): the build is two kernels instead of three and unique_index may be NULL as well. */
 int b2_map_build(const int* coords, long long n, int quant, void* table, long long cap, int* out_coords,
                  int* unique_index, int* inverse_map, int* n_out, int* err, void* ws, size_t ws_bytes, void* stream);
 /* hash table over already-unique rows (value = row) */
@@ -299,6 +300,16 @@ int b2_box_iou_decoded(const float* points, const float* bbox_pred, int n_reg, i
 /* element-wise binary cross entropy with logits and d/dx (fcaf3d_neck_with_head.py:191-193 -> mmdet 2.14
    CrossEntropyLoss(use_sigmoid=True) -> F.binary_cross_entropy_with_logits) */
 int b2_bce_logits(const float* x, const float* t, long long n, float* loss, float* grad, void* stream);
+/* Optimiser of the reference recipe (configs/fcaf3d/fcaf3d.py:30-31: AdamW + grad_clip max_norm 10; mmcv OptimizerHook ->
+ * torch clip_grad_norm_ + torch.optim.AdamW) over ALL parameter tensors at once.  table: n records of 5 x int64 (param,
+ * grad, exp_avg, exp_avg_sq device pointers, element count); chunks: n_chunks int32 pairs (tensor index, chunk index) with
+ * b2_opt_chunk_elems() elements per chunk.  b2_grad_sqnorm: deterministic squared L2 norm of every gradient element
+ * (partial: n_chunks floats of scratch).  b2_adamw_step: gradient scaled by min(1, max_norm / (sqrt(*sqnorm) + 1e-6))
+ * (max_norm <= 0 or sqnorm NULL: unscaled), decoupled weight decay, moments, bias-corrected update of 1-based `step`. */
+int b2_opt_chunk_elems(void);
+int b2_grad_sqnorm(const void* table, const int* chunks, int n_chunks, float* partial, float* sqnorm_out, void* stream);
+int b2_adamw_step(const void* table, const int* chunks, int n_chunks, double lr, double beta1, double beta2, double eps,
+                  double wd, long long step, double max_norm, const float* sqnorm, void* stream);
 
 /* ---- native executor of one fused inference step ------------------------------------------------------------------
  * What the reference does per batch through python - SingleStageSparse3DDetector.simple_test -> extract_feat ->
@@ -315,13 +326,18 @@ int b2_bce_logits(const float* x, const float* t, long long n, float* loss, floa
  * taken from `arena` (-3 if too small; *arena_used_host reports the bytes used); detections come back in the caller's
  * buffers of out_cap >= b2_engine_out_rows() rows: out_boxes [.,7], out_scores, out_labels, out_scene, grouped by
  * (scene, class), *out_count (device) of them valid; *n_rows_host = rows the tail worked on.  The call blocks on the few
- * row-count reads of the coordinate maps (each queued behind GPU work that was enqueued earlier). */
+ * row-count reads of the coordinate maps (each queued behind GPU work that was enqueued earlier).
+ * tail_stream (NULL or == stream: everything on `stream`): the top-k / decode / NMS tail - small launches on a handful
+ * of SMs - is enqueued on that second stream behind an event, so the NEXT call's first kernels on `stream` overlap it; the
+ * outputs are then complete when tail_stream reaches the point the call left it at, and the caller must not hand the same
+ * arena to a later call before that (fcaf3d_b200/engine.py alternates two arenas and orders them with events). */
 void* b2_engine_create(const long long* desc, int n_words, const double* fl);
 int b2_engine_destroy(void* engine);
 long long b2_engine_out_rows(void* engine, int n_scenes);
 int b2_engine_infer(void* engine, const float* const* points_host, const long long* n_points_host, int n_scenes, int dtype,
                     void* arena, size_t arena_bytes, float* out_boxes, float* out_scores, int* out_labels, int* out_scene,
-                    int* out_count, long long out_cap, long long* n_rows_host, size_t* arena_used_host, void* stream);
+                    int* out_count, long long out_cap, long long* n_rows_host, size_t* arena_used_host, void* stream,
+                    void* tail_stream);
 
 #ifdef __cplusplus
 }

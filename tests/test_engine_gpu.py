@@ -6,7 +6,7 @@ import pytest
 import torch
 
 from fcaf3d_b200 import me as ME
-from fcaf3d_b200.detector import build_fcaf3d
+from fcaf3d_b200.detector import build_fcaf3d, wait_ready
 from fcaf3d_b200.scenes import make_scene
 from fcaf3d_b200.testing import deterministic_init
 
@@ -17,7 +17,7 @@ def _both(det, pts, dtype):
     ME.set_compute_dtype(dtype)
     try:
         det.use_engine = True
-        a = det.simple_test_fused(pts, to_host=False)
+        a = wait_ready(det.simple_test_fused(pts, to_host=False))     # (the tail may run on the executor's side stream)
         assert det._engine is not None and det._engine.arena_used > 0, "the native executor did not run"
         det.use_engine = False
         b = det.simple_test_fused(pts, to_host=False)

@@ -386,3 +386,32 @@ def test_fused_instance_norm_matches_torch_graph(dev, act):
             AG.FUSED_BN = old
     for a, b in zip(*outs):
         assert a.shape == b.shape and rel_err(a, b) < 5e-5
+
+
+def test_fused_adamw_with_clipping_matches_torch(dev):
+    """FusedAdamW (b2_grad_sqnorm + b2_adamw_step) against torch.nn.utils.clip_grad_norm_ + torch.optim.AdamW over four
+    steps on tensors from 1 element to ~1 M elements: parameters to 1e-6 of max, both moments to 1e-5 (summation order of
+    the norm and FMA contraction differ from torch's kernels by a few ulp), gradient norm to 1e-6 relative; two steps
+    clip (norm > max_norm), two do not."""
+    from fcaf3d_b200.optim import FusedAdamW
+    g = torch.Generator().manual_seed(0)
+    shapes = [(27,), (3, 9), (64,), (27, 64, 64), (1, 128, 25), (27, 128, 256), (1,)]
+    pa = [torch.nn.Parameter(torch.randn(s, generator=g).to(dev)) for s in shapes]
+    pb = [torch.nn.Parameter(p.detach().clone()) for p in pa]
+    oa = FusedAdamW(pa, lr=1e-3, weight_decay=1e-4, max_norm=10.0)
+    ob = torch.optim.AdamW(pb, lr=1e-3, weight_decay=1e-4)
+    for it, gscale in enumerate((1.0, 1e-3, 5.0, 0.1)):
+        grads = [torch.randn(s, generator=g).to(dev) * gscale for s in shapes]
+        for p, q, gr in zip(pa, pb, grads):
+            p.grad, q.grad = gr.clone(), gr.clone()
+        sq = oa.step()
+        norm = torch.nn.utils.clip_grad_norm_(pb, 10.0)
+        ob.step()
+        assert abs(float(sq.sqrt()) - float(norm)) < 1e-6 * float(norm)
+        assert (float(norm) > 10.0) == (gscale >= 1.0)
+        for i, (p, q) in enumerate(zip(pa, pb)):
+            assert rel_err(p, q) < 1e-6, (it, i)
+            st = ob.state[q]
+            assert rel_err(oa.exp_avg[i], st["exp_avg"]) < 1e-5 and rel_err(oa.exp_avg_sq[i], st["exp_avg_sq"]) < 1e-5
+    sd = oa.state_dict()
+    assert int(sd["state"][0]["step"]) == 4 and len(sd["state"]) == len(shapes)
