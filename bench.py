@@ -259,7 +259,9 @@ def bench_infer(ctx, args, workload, dtype_name, steps, warmup, clk=None, brief=
     lib = ops._lib.lib()
 
     def step_device():
-        return det.simple_test_fused(dev_pts, to_host=False)
+        # inputs_ready=True: the points are resident and complete (synchronised before the bracket), so the executor's
+        # coordinate stream may start on step i + 1 while step i's convolutions still run
+        return det.simple_test_fused(dev_pts, to_host=False, inputs_ready=True)
 
     if os.environ.get("BENCH_PROFILE"):
         # one step between cudaProfilerStart/Stop for `ncu --profile-from-start off` (numbers printed here are not bench values)

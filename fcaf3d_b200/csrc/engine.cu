@@ -33,7 +33,7 @@ struct ConvW {
 };
 
 constexpr int MAX_LEVELS = 4;
-constexpr int RING = 256;       // pinned staging slots
+constexpr int RING = 1024;      // pinned staging slots / events
 constexpr int SLOT_INTS = 128;  // ints per slot
 
 struct Engine {
@@ -52,9 +52,12 @@ struct Engine {
   int next_slot = 0;
   int device = -1;
   long long sort_min_rows = 32768;   // B2_SORT_MIN_ROWS (0 = never sort)
+  cudaStream_t coord_stream = nullptr;   // coordinate work (hash builds, kernel maps) runs here, ahead of the features
+  bool split = true;                     // B2_ENGINE_SPLIT=0: everything on the caller's stream
 };
 
 struct Map {
+  bool on_F = false;   // coordinates produced on the feature stream (a pruned map): whatever consumes it runs there too
   int* coords = nullptr;
   long long n = 0;
   int ts = 1;
@@ -80,6 +83,7 @@ struct KMap {
 
 struct Pending {  // a map build / union whose row count is still in flight
   bool valid = false;
+  bool on_F = false;
   int slot = 0;
   int* status = nullptr;
   int* out_coords = nullptr;
@@ -108,8 +112,11 @@ struct Run {
   Engine& e;
   char* base;
   size_t cap, off = 0;
-  cudaStream_t st;
+  cudaStream_t st;   // the stream ops are enqueued on right now (stF or stC)
   void* stv;
+  cudaStream_t stF, stC;
+  bool split = false;    // coordinate work on stC, features on stF, F waits for C by events
+  bool c_dirty = false;  // C work enqueued since F last waited for C
   int nb = 0;
   int dt = 1;  // activation dtype: 1 bf16, 0 fp32
   bool tf32 = false;   // fp32 rows, wide convolutions as TF32 tensor-core operands (ConvW::wt then holds fp32 [kvol, cout, cin])
@@ -117,7 +124,9 @@ struct Run {
   std::vector<KMap> kmaps;
 
   Run(Engine& eng, void* arena, size_t bytes, void* stream)
-      : e(eng), base((char*)arena), cap(bytes), st((cudaStream_t)stream), stv(stream) {
+      : e(eng), base((char*)arena), cap(bytes), st((cudaStream_t)stream), stv(stream), stF((cudaStream_t)stream),
+        stC(eng.coord_stream) {
+    split = eng.split && eng.coord_stream != nullptr;
     maps.reserve(256);
     kmaps.reserve(256);   // pointers into these vectors are handed out: they must never reallocate (checked below)
   }
@@ -132,6 +141,38 @@ struct Run {
     return base + a;
   }
   size_t esize() const { return dt == 1 ? 2 : 4; }
+
+  // Two streams: everything that depends on COORDINATES only (hash builds, kernel maps, table grouping, children / union
+  // maps) is enqueued on stC, the feature kernels on stF; before a feature op F waits (by event) for the coordinate work
+  // enqueued so far.  Nothing on C ever waits for F inside a call, and the host blocks on C events only, so while the GPU
+  // still runs the convolutions of this call on F the host is already enqueueing - and the GPU executing - the small,
+  // latency-bound coordinate kernels of the NEXT call on C.
+  void to_F() { st = stF, stv = (void*)stF; }
+  int fsync() {
+    if (!split || !c_dirty) return B2_OK;
+    const int s = slot();
+    B2_CUDA(cudaEventRecord(e.events[s], stC));
+    B2_CUDA(cudaStreamWaitEvent(stF, e.events[s], 0));
+    c_dirty = false;
+    return B2_OK;
+  }
+  struct CoordScope {   // ops of this scope go to C (or to F when they touch a map that was made on F)
+    Run& r;
+    int rc = B2_OK;
+    cudaStream_t old_st;
+    void* old_stv;
+    CoordScope(Run& r_, bool on_f) : r(r_), old_st(r_.st), old_stv(r_.stv) {
+      if (r.split && r.st == r.stC && !on_f) return;   // nested inside a coordinate scope: stay on C
+      if (on_f || !r.split) {
+        rc = r.fsync();
+        r.to_F();
+      } else {
+        r.st = r.stC, r.stv = (void*)r.stC;
+        r.c_dirty = true;
+      }
+    }
+    ~CoordScope() { r.st = old_st, r.stv = old_stv; }
+  };
 
   int slot() {
     const int s = e.next_slot;
@@ -169,6 +210,8 @@ struct Run {
   // want_uidx: the input map (features are picked at the representatives' rows); nobody reads an inverse map in this pass,
   // so every build is the two-kernel variant of b2_map_build
   int build_start(const int* coords, long long n, int quant, int ts_out, Pending* p, bool want_uidx = false) {
+    CoordScope sc(*this, false);
+    if (sc.rc) return sc.rc;
     p->cap = table_cap(n);
     p->ts = ts_out;
     p->table = take((size_t)p->cap * 16);
@@ -213,6 +256,8 @@ struct Run {
   int ensure_table(int mi) {
     Map& m = maps[mi];
     if (m.table) return B2_OK;
+    CoordScope sc(*this, m.on_F);
+    if (sc.rc) return sc.rc;
     m.cap = table_cap(m.n);
     m.table = take((size_t)m.cap * 16);
     int* err = (int*)take(4);
@@ -223,7 +268,10 @@ struct Run {
   int children(int mi, int* out_index) {
     const Map src = maps[mi];
     B2_CHECK_ARG(src.ts % 2 == 0, "generative transpose needs an even tensor stride");
+    CoordScope sc(*this, src.on_F);
+    if (sc.rc) return sc.rc;
     Map m;
+    m.on_F = src.on_F;
     m.n = src.n * 8;
     m.ts = src.ts / 2;
     m.coords = (int*)take((size_t)(m.n > 0 ? m.n : 1) * 16);
@@ -244,6 +292,9 @@ struct Run {
     if (rc) return rc;
     const Map &a = maps[ai], &b = maps[bi];
     B2_CHECK_ARG(a.ts == b.ts, "union of maps with different tensor strides");
+    p->on_F = a.on_F || b.on_F;
+    CoordScope sc(*this, p->on_F);
+    if (sc.rc) return sc.rc;
     p->ts = a.ts;
     p->out_coords = (int*)take((size_t)(a.n + b.n > 0 ? a.n + b.n : 1) * 16);
     p->dst_a = (int*)take((size_t)(a.n > 0 ? a.n : 1) * 4);
@@ -268,6 +319,7 @@ struct Run {
     int rc = read_wait(p->slot, &h);
     if (rc) return rc;
     Map m;
+    m.on_F = p->on_F;
     m.coords = p->out_coords;
     m.n = h[0];
     m.ts = p->ts;
@@ -300,6 +352,8 @@ struct Run {
     KMap k;
     int rc = alloc_kmap(in, out, ks, maps[out].n, &k);
     if (rc) return rc;
+    CoordScope sc(*this, maps[in].on_F || maps[out].on_F);
+    if (sc.rc) return sc.rc;
     if (in == out && maps[in].children_of >= 0 && ks == 3) {
       const int parent = maps[in].children_of;
       KMap* pk;
@@ -327,6 +381,8 @@ struct Run {
   // rows grouped by the kernel slabs they use (kmap_sort.cu): pays for tables that several tcgen05 convolutions walk
   int sort_kmap(KMap* k) {
     if (k->perm || k->kvol != 27 || k->ld == 0) return B2_OK;
+    CoordScope sc(*this, maps[k->in].on_F || maps[k->out].on_F);
+    if (sc.rc) return sc.rc;
     k->perm = (int*)take((size_t)k->ld * 4);
     k->nbr_sorted = (int*)take((size_t)k->kvol * k->ld * 4);
     k->tmask_sorted = (unsigned int*)take((size_t)(k->ld / 128) * 4);
@@ -341,6 +397,7 @@ struct Run {
            int act, int ch_mod, int out_dt, void** out) {
     *out = take((size_t)(n_out > 0 ? n_out : 1) * w.cout * (out_dt == 1 ? 2 : 4));
     if (!*out) return B2_ERR_WS;
+    if (int rcs = fsync()) return rcs;
     const int* nbr = km ? km->nbr : nullptr;
     const long long ld = km ? km->ld : 0;
     const unsigned int* tm = km ? km->tmask : nullptr;
@@ -372,13 +429,30 @@ struct Level {
     int rc_ = (call);       \
     if (rc_) return rc_;    \
   } while (0)
+#define FK(call)            \
+  do {                      \
+    CK(r.fsync());          \
+    CK(call);               \
+  } while (0)
 #define TAKE(var, type, count)                                      \
   type* var = (type*)r.take((size_t)((count) > 0 ? (count) : 1) * sizeof(type)); \
   if (!var) return B2_ERR_WS
 
 static int infer(Engine& e, Run& r, const float* const* points, const long long* n_points, int n_scenes, int dtype,
                  float* out_boxes, float* out_scores, int* out_labels, int* out_scene, int* out_count, long long out_cap,
-                 long long* n_rows_out, void* tail_stream) {
+                 long long* n_rows_out, void* tail_stream, void* inputs_ready_event, int inputs_ready,
+                 void* arena_free_event) {
+  if (r.split) {
+    // C starts as soon as the inputs are there and the arena is free - NOT behind the feature work still queued on F
+    if (inputs_ready_event != nullptr) {
+      B2_CUDA(cudaStreamWaitEvent(r.stC, (cudaEvent_t)inputs_ready_event, 0));
+    } else if (!inputs_ready) {   // unknown producer: the inputs are ordered on F only, so C has to wait for F's queue
+      const int s = r.slot();
+      B2_CUDA(cudaEventRecord(e.events[s], r.stF));
+      B2_CUDA(cudaStreamWaitEvent(r.stC, e.events[s], 0));
+    }
+    if (arena_free_event != nullptr) B2_CUDA(cudaStreamWaitEvent(r.stC, (cudaEvent_t)arena_free_event, 0));
+  }
   r.nb = n_scenes;
   r.dt = dtype == 1 ? 1 : 0;
   r.tf32 = dtype == 2;
@@ -391,10 +465,14 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
   // ---- input: quantise, dedup, the first strided map from the raw rows (both row counts come back behind one wait)
   TAKE(coords, int, total * 4);
   TAKE(feats, float, total * fdim);
-  long long row0 = 0;
-  for (int b = 0; b < nb; ++b) {
-    CK(b2_quantize_points(points[b], n_points[b], dim, b, e.voxel_size, 255.f, row0, coords, feats, r.stv));
-    row0 += n_points[b];
+  {
+    Run::CoordScope sc(r, false);
+    if (sc.rc) return sc.rc;
+    long long row0 = 0;
+    for (int b = 0; b < nb; ++b) {
+      CK(b2_quantize_points(points[b], n_points[b], dim, b, e.voxel_size, 255.f, row0, coords, feats, r.stv));
+      row0 += n_points[b];
+    }
   }
   Pending p0, p1;
   CK(r.build_start(coords, total, 0, 1, &p0, true));
@@ -403,7 +481,7 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
   int m1;
   CK(r.build_finish(&p0, &m1));
   TAKE(x0, float, r.maps[m1].n * fdim);
-  CK(b2_index_rows(feats, uidx, r.maps[m1].n, fdim * 4, x0, r.stv));
+  FK(b2_index_rows(feats, uidx, r.maps[m1].n, fdim * 4, x0, r.stv));
 
   // ---- stem: conv 3^3 s2 -> InstanceNorm + ReLU -> max-pool 2^3 s2 (me_resnet.py:18-25)
   int m2;
@@ -421,7 +499,7 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
     const size_t wsb = b2_instnorm_ws_bytes(nb, c0);
     void* ws = r.take(wsb);
     if (!ws) return B2_ERR_WS;
-    CK(b2_instnorm_scale_shift(f0, r.dt, r.maps[m2].off_dev, nb, c0, e.inorm_w, e.inorm_b, e.inorm_eps, in_scale, in_shift,
+    FK(b2_instnorm_scale_shift(f0, r.dt, r.maps[m2].off_dev, nb, c0, e.inorm_w, e.inorm_b, e.inorm_eps, in_scale, in_shift,
                                ws, wsb, r.stv));
   }
   int m4;
@@ -432,11 +510,11 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
   void* f = r.take((size_t)(r.maps[m4].n > 0 ? r.maps[m4].n : 1) * c0 * r.esize());
   if (!f) return B2_ERR_WS;
   if (r.dt == 1) {
-    CK(b2_maxpool_affine(f0, km->nbr, km->ld, km->kvol, km->n_out, c0, r.maps[m4].coords, in_scale, in_shift, B2_ACT_RELU,
+    FK(b2_maxpool_affine(f0, km->nbr, km->ld, km->kvol, km->n_out, c0, r.maps[m4].coords, in_scale, in_shift, B2_ACT_RELU,
                          f, r.stv));
   } else {
-    CK(b2_affine_act(f0, r.dt, r.maps[m2].coords, r.maps[m2].n, c0, in_scale, in_shift, nullptr, B2_ACT_RELU, f0, r.stv));
-    CK(b2_maxpool(f0, r.dt, km->nbr, km->ld, km->kvol, km->n_out, c0, f, nullptr, r.stv));
+    FK(b2_affine_act(f0, r.dt, r.maps[m2].coords, r.maps[m2].n, c0, in_scale, in_shift, nullptr, B2_ACT_RELU, f0, r.stv));
+    FK(b2_maxpool(f0, r.dt, km->nbr, km->ld, km->kvol, km->n_out, c0, f, nullptr, r.stv));
   }
 
   // ---- residual stages (me_resnet.py:27-41,66-78): conv + folded BatchNorm + ReLU (+ residual) = one launch each
@@ -502,21 +580,23 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
         const Level& prev = lv[i + 1];
         CK(r.ensure_table(prev.map));
         TAKE(q, float, nu * 4);
+        CK(r.fsync());
         k_coords_to_float<<<b2_div_up(nu * 4, 256), 256, 0, r.st>>>(r.maps[ukey].coords, nu * 4, q);
         B2_LAUNCH_CHECK();
         TAKE(sc, float, nu);
-        CK(b2_interp(r.maps[prev.map].table, r.maps[prev.map].cap, prev.prune, 1, r.maps[prev.map].ts, q, nu, sc, r.stv));
+        FK(b2_interp(r.maps[prev.map].table, r.maps[prev.map].cap, prev.prune, 1, r.maps[prev.map].ts, q, nu, sc, r.stv));
         mask = (uint8_t*)r.take((size_t)nu);
         pos = (int*)r.take((size_t)nu * 4);
         int* tot = (int*)r.take(4);
         if (!mask || !pos || !tot) return B2_ERR_WS;
-        CK(b2_topk_mask_n(sc, r.maps[ukey].off_dev, nb, e.pts_threshold, nu, mask, r.stv));
+        FK(b2_topk_mask_n(sc, r.maps[ukey].off_dev, nb, e.pts_threshold, nu, mask, r.stv));
         B2_CUDA(cudaMemsetAsync(tot, 0, 4, r.st));
         const size_t wsb = b2_scan_ws_bytes(nu);
         void* ws = r.take(wsb);
         if (!ws) return B2_ERR_WS;
-        CK(b2_scan_mask(mask, nu, pos, tot, ws, wsb, r.stv));
+        FK(b2_scan_mask(mask, nu, pos, tot, ws, wsb, r.stv));
         Map pm;  // top-k keeps exactly min(N_b, k) rows of every scene: the pruned map's offsets are known on the host
+        pm.on_F = true;
         pm.ts = r.maps[ukey].ts;
         pm.off.resize(nb + 1);
         pm.off[0] = 0;
@@ -526,7 +606,7 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
         CK(r.upload(pm.off.data(), nb + 1, &pm.off_dev));
         pm.coords = (int*)r.take((size_t)(n_keep > 0 ? n_keep : 1) * 16);
         if (!pm.coords) return B2_ERR_WS;
-        CK(b2_gather_coords(r.maps[ukey].coords, mask, pos, nu, pm.coords, r.stv));
+        FK(b2_gather_coords(r.maps[ukey].coords, mask, pos, nu, pm.coords, r.stv));
         r.maps.push_back(pm);
         pkey = (int)r.maps.size() - 1;
       }
@@ -536,17 +616,17 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
         TAKE(g2k, int, n_gen);
         TAKE(a2k, int, r.maps[stage_map[i]].n);
         TAKE(ksrc, int, n_keep);
-        CK(b2_prune_plan(dst_b, n_gen, dst_a, r.maps[stage_map[i]].n, mask, pos, g2k, a2k, ksrc, r.stv));
+        FK(b2_prune_plan(dst_b, n_gen, dst_a, r.maps[stage_map[i]].n, mask, pos, g2k, a2k, ksrc, r.stv));
         KMap* pk;
         CK(r.kernel_map(parent, parent, 3, &pk));
         KMap up, ko;
         CK(r.alloc_kmap(gkey, pkey, 3, n_keep, &up));
         CK(r.alloc_kmap(pkey, pkey, 3, n_keep, &ko));
-        CK(b2_kernel_map_children_pruned(pk->nbr, pk->ld, ksrc, g2k, n_keep, up.ld, up.nbr, up.tmask, ko.nbr, ko.tmask, r.stv));
+        FK(b2_kernel_map_children_pruned(pk->nbr, pk->ld, ksrc, g2k, n_keep, up.ld, up.nbr, up.tmask, ko.nbr, ko.tmask, r.stv));
         r.kmaps.push_back(ko);
         void* o;
         CK(r.conv(e.up_conv[i + 1], g, r.dt, n_gen, &up, n_keep, nullptr, B2_ACT_ELU, 0, r.dt, &o));
-        CK(b2_scatter_rows(stage_f[i], a2k, r.maps[stage_map[i]].n, cg, r.dt, 1, o, r.stv));
+        FK(b2_scatter_rows(stage_f[i], a2k, r.maps[stage_map[i]].n, cg, r.dt, 1, o, r.stv));
         f = o;
       } else {
         KMap* kg;
@@ -556,13 +636,13 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
         void* u = r.take((size_t)(nu > 0 ? nu : 1) * cg * r.esize());
         if (!u) return B2_ERR_WS;
         B2_CUDA(cudaMemsetAsync(u, 0, (size_t)nu * cg * r.esize(), r.st));
-        CK(b2_scatter_rows(stage_f[i], dst_a, r.maps[stage_map[i]].n, cg, r.dt, 0, u, r.stv));
-        CK(b2_scatter_rows(o, dst_b, n_gen, cg, r.dt, 1, u, r.stv));
+        FK(b2_scatter_rows(stage_f[i], dst_a, r.maps[stage_map[i]].n, cg, r.dt, 0, u, r.stv));
+        FK(b2_scatter_rows(o, dst_b, n_gen, cg, r.dt, 1, u, r.stv));
         f = u;
         if (need_prune) {
           void* pr = r.take((size_t)(n_keep > 0 ? n_keep : 1) * cg * r.esize());
           if (!pr) return B2_ERR_WS;
-          CK(b2_gather_rows(u, mask, pos, nu, (int)(cg * r.esize()), pr, r.stv));
+          FK(b2_gather_rows(u, mask, pos, nu, (int)(cg * r.esize()), pr, r.stv));
           f = pr;
         }
       }
@@ -589,7 +669,7 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
     l.prune = (float*)r.take((size_t)(n > 0 ? n : 1) * 4);
     l.max_score = (float*)r.take((size_t)(n > 0 ? n : 1) * 4);
     if (!l.centerness || !l.bbox || !l.cls || !l.prune || !l.max_score) return B2_ERR_WS;
-    CK(b2_head_post((const float*)h, n, e.head_cols, e.n_reg, e.n_cls, e.level_scale[i], l.centerness, l.bbox, l.cls, l.prune,
+    FK(b2_head_post((const float*)h, n, e.head_cols, e.n_reg, e.n_cls, e.level_scale[i], l.centerness, l.bbox, l.cls, l.prune,
                     l.max_score, r.stv));
   }
 
@@ -597,12 +677,14 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
   // The tail is a chain of small launches (one CTA per scene or per (scene, class) segment: ~0.4 ms at a few per cent of
   // the SMs).  With a tail stream it is enqueued THERE, behind an event on the main stream, so the next step's
   // quantise / hash / stem work on the main stream fills the GPU while this tail drains.
+  CK(r.fsync());
   if (tail_stream != nullptr && tail_stream != r.stv) {
     const int s = r.slot();
     B2_CUDA(cudaEventRecord(e.events[s], r.st));
     B2_CUDA(cudaStreamWaitEvent((cudaStream_t)tail_stream, e.events[s], 0));
-    r.st = (cudaStream_t)tail_stream;
+    r.st = r.stF = (cudaStream_t)tail_stream;   // from here on "F" is the tail stream (no coordinate work follows)
     r.stv = tail_stream;
+    r.split = false;
   }
   const int n_cls = e.n_cls, n_reg = e.n_reg;
   const int rotated = n_reg != 6;
@@ -643,10 +725,10 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
     const size_t wsb = b2_scan_ws_bytes(m.n);
     void* ws = r.take(wsb);
     if (!mask || !pos || !tot || !ws) return B2_ERR_WS;
-    CK(b2_topk_mask_n(lv[li].max_score, m.off_dev, nb, (int)k, m.n, mask, r.stv));
+    FK(b2_topk_mask_n(lv[li].max_score, m.off_dev, nb, (int)k, m.n, mask, r.stv));
     B2_CUDA(cudaMemsetAsync(tot, 0, 4, r.st));
-    CK(b2_scan_mask(mask, m.n, pos, tot, ws, wsb, r.stv));
-    CK(b2_emit_candidates(m.coords, lv[li].centerness, lv[li].bbox, lv[li].cls, mask, pos, m.off_dev,
+    FK(b2_scan_mask(mask, m.n, pos, tot, ws, wsb, r.stv));
+    FK(b2_emit_candidates(m.coords, lv[li].centerness, lv[li].bbox, lv[li].cls, mask, pos, m.off_dev,
                           meta_dev + nb + 1 + li * nb, m.n, n_reg, n_cls, yaw_mode, e.voxel_size, cand_boxes, cand_scores,
                           r.stv));
   }
@@ -666,7 +748,7 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
     const size_t wsb = b2_scan_ws_bytes(nf);
     void* ws = r.take(wsb);
     if (!ws) return B2_ERR_WS;
-    CK(b2_class_segments(cand_boxes, cand_scores, meta_dev, nb, n_cls, tot_c, e.score_thr, flags, fpos, seg_off + nseg + 1,
+    FK(b2_class_segments(cand_boxes, cand_scores, meta_dev, nb, n_cls, tot_c, e.score_thr, flags, fpos, seg_off + nseg + 1,
                          seg_boxes, seg_scores, seg_src, seg_off, ws, wsb, r.stv));
   }
   TAKE(keep, uint8_t, nf);
@@ -679,7 +761,7 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
     const size_t wsb = b2_nms_greedy_ws_bytes(nf, rotated);
     void* ws = r.take(wsb);
     if (!ws) return B2_ERR_WS;
-    CK(b2_nms_greedy_batched(seg_boxes, seg_scores, seg_off, nseg, nf, max_seg, e.iou_thr, rotated, 1, sorted_boxes, order,
+    FK(b2_nms_greedy_batched(seg_boxes, seg_scores, seg_off, nseg, nf, max_seg, e.iou_thr, rotated, 1, sorted_boxes, order,
                              ws, wsb, keep, counts, r.stv));
   }
   TAKE(kpos, int, nf);
@@ -688,9 +770,9 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
     const size_t wsb = b2_scan_ws_bytes(nf);
     void* ws = r.take(wsb);
     if (!ws) return B2_ERR_WS;
-    CK(b2_scan_mask(keep, nf, kpos, out_count, ws, wsb, r.stv));
+    FK(b2_scan_mask(keep, nf, kpos, out_count, ws, wsb, r.stv));
   }
-  CK(b2_collect_dets(sorted_boxes, seg_scores, order, seg_off, nseg, n_cls, keep, kpos, nf, out_boxes, out_scores, out_labels,
+  FK(b2_collect_dets(sorted_boxes, seg_scores, order, seg_off, nseg, n_cls, keep, kpos, nf, out_boxes, out_scores, out_labels,
                      out_scene, r.stv));
   return B2_OK;
 }
@@ -764,6 +846,11 @@ void* b2_engine_create(const long long* desc, int n_words, const double* fl) {
     return nullptr;
   }
   for (int i = 0; i < RING; ++i) cudaEventCreateWithFlags(&e->events[i], cudaEventDisableTiming);
+  if (const char* v = getenv("B2_ENGINE_SPLIT")) e->split = atoi(v) != 0;
+  if (e->split && cudaStreamCreateWithFlags(&e->coord_stream, cudaStreamNonBlocking) != cudaSuccess) {
+    e->coord_stream = nullptr;
+    e->split = false;
+  }
   return e;
 }
 
@@ -771,6 +858,7 @@ int b2_engine_destroy(void* engine) {
   Engine* e = (Engine*)engine;
   if (!e) return B2_OK;
   for (int i = 0; i < RING; ++i) cudaEventDestroy(e->events[i]);
+  if (e->coord_stream) cudaStreamDestroy(e->coord_stream);
   if (e->pinned) cudaFreeHost(e->pinned);
   delete e;
   return B2_OK;
@@ -786,7 +874,7 @@ long long b2_engine_out_rows(void* engine, int n_scenes) {
 int b2_engine_infer(void* engine, const float* const* points_host, const long long* n_points_host, int n_scenes, int dtype,
                     void* arena, size_t arena_bytes, float* out_boxes, float* out_scores, int* out_labels, int* out_scene,
                     int* out_count, long long out_cap, long long* n_rows_host, size_t* arena_used_host, void* stream,
-                    void* tail_stream) {
+                    void* tail_stream, void* inputs_ready_event, int inputs_ready, void* arena_free_event) {
   Engine* e = (Engine*)engine;
   B2_CHECK_ARG(e && points_host && n_points_host && arena && out_boxes && out_scores && out_labels && out_scene && out_count,
                "b2_engine_infer: null argument");
@@ -797,7 +885,7 @@ int b2_engine_infer(void* engine, const float* const* points_host, const long lo
   Run r(*e, arena, arena_bytes, stream);
   long long rows = 0;
   const int rc = infer(*e, r, points_host, n_points_host, n_scenes, dtype, out_boxes, out_scores, out_labels, out_scene,
-                       out_count, out_cap, &rows, tail_stream);
+                       out_count, out_cap, &rows, tail_stream, inputs_ready_event, inputs_ready, arena_free_event);
   if (n_rows_host) *n_rows_host = rows;
   if (arena_used_host) *arena_used_host = r.off;
   return rc;

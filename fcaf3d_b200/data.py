@@ -92,6 +92,11 @@ class DeviceAugment:
         return outs, (bouts if boxes_list is not None else None)
 
 
+class ReadyList(list):
+    """list of device tensors + `ready`: the event after which their host->device copies are complete"""
+    ready = None
+
+
 class ScenePrefetcher:
     """Iterates over `batches` (an iterable of lists of CPU tensors / numpy arrays, e.g. the raw scenes of one training
     step) and yields lists of CUDA tensors; while the consumer works on batch i, batch i+1 is staged through pinned
@@ -132,4 +137,6 @@ class ScenePrefetcher:
         for t in dev:
             t.record_stream(cur)
         self._preload()
-        return dev
+        out = ReadyList(dev)
+        out.ready = ev               # consumers with streams of their own (the native executor) wait for the copy directly
+        return out

@@ -664,12 +664,12 @@ class SingleStageSparse3DDetector(nn.Module):
         return self.neck_with_head.forward_train_batched(self.backbone(x0), gt_bboxes_3d, gt_labels_3d)
 
     @torch.no_grad()
-    def simple_test_fused(self, points, to_host=True):
+    def simple_test_fused(self, points, to_host=True, inputs_ready=None):
         """B200 inference path: fused backbone / neck / head and the batched tail.  In eval mode the whole step is handed to
         the native executor (fcaf3d_b200.engine: the same library calls issued from C++, bit-identical results);
         `use_engine = False`, per-kernel profiling, a prune trace or a Bottleneck backbone keep the python driver."""
         if self._engine_ok():
-            dets = self._engine(points)
+            dets = self._engine(points, inputs_ready=inputs_ready)   # (see InferenceEngine.__call__ for inputs_ready)
             return split_detections(dets, len(points)) if to_host else dets
         x = self._input_tensor(points)
         feats = self.backbone.forward_fused(x)

@@ -32,8 +32,10 @@ class InferenceEngine:
         self._arenas = [None, None]      # alternate: the tail of step i may still read arena i % 2 while step i + 1 runs
         self._arena_free = [None, None]  # event after which the arena may be overwritten (its last tail has drained)
         self._step = 0
+        self._hold = [None, None]
         self._tail = None                # side stream of the top-k / NMS tail (B2_ENGINE_OVERLAP=0: none)
         self.overlap_tail = os.environ.get("B2_ENGINE_OVERLAP", "1") != "0"
+        self.split_streams = os.environ.get("B2_ENGINE_SPLIT", "1") != "0"
         self._keep = []
         self._tensors = None
 
@@ -128,9 +130,12 @@ class InferenceEngine:
 
     # ---- one step -------------------------------------------------------------------------------------------------------
     @torch.no_grad()
-    def __call__(self, points):
+    def __call__(self, points, inputs_ready=None):
         """points: list of [N_i, 6] fp32 CUDA tensors.  Returns the device-side result dict of get_bboxes_fused
-        (boxes [n,7], scores, labels, scene, count, box_dim); detector.split_detections / DetectionRead bring it to the host."""
+        (boxes [n,7], scores, labels, scene, count, box_dim[, ready]); detector.split_detections / DetectionRead bring it to
+        the host.  inputs_ready: a torch.cuda.Event after which the points are complete (e.g. the end of their host->device
+        copy), or True when they are complete already; the executor's coordinate stream then starts on them right away
+        instead of waiting for everything queued on the current stream (default: it waits)."""
         if self._handle is None or self._sig != self._signature():
             self._build()
         dev = points[0].device
@@ -151,6 +156,12 @@ class InferenceEngine:
         count = torch.empty((1,), dtype=torch.int32, device=dev)
         slot = self._step % 2
         self._step += 1
+        self._hold[slot] = pts           # the coordinate stream reads them: alive until this slot's next turn
+        if inputs_ready is None:
+            inputs_ready = getattr(points, "ready", None)
+        in_ev = inputs_ready.cuda_event if isinstance(inputs_ready, torch.cuda.Event) else None
+        in_flag = 1 if inputs_ready is True else 0
+        free_ev = self._arena_free[slot].cuda_event if self._arena_free[slot] is not None else None
         main = torch.cuda.current_stream(dev)
         if self.overlap_tail and self._tail is None:
             self._tail = torch.cuda.Stream(device=dev)
@@ -167,7 +178,8 @@ class InferenceEngine:
                 self._arenas[slot] = arena = torch.empty(max(need, 1 << 20), dtype=torch.uint8, device=dev)
             rc = l.b2_engine_infer(self._handle, ptrs, counts, n, dt, ptr(arena), arena.numel(), ptr(boxes),
                                    ptr(scores), ptr(labels), ptr(scene), ptr(count), cap, ctypes.byref(rows),
-                                   ctypes.byref(used), stream(), tail.cuda_stream if tail is not None else None)
+                                   ctypes.byref(used), stream(), tail.cuda_stream if tail is not None else None, in_ev,
+                                   in_flag, free_ev)
             if rc == -3:            # arena too small: the launches so far wrote only into the arena - grow it and redo the step
                 torch.cuda.synchronize(dev)
                 need = 2 * arena.numel()
@@ -178,6 +190,11 @@ class InferenceEngine:
         else:
             raise B2Error("b2_engine_infer: arena kept overflowing: %s" % last_error())
         ready = None
+        if tail is None and self.split_streams:
+            ready = torch.cuda.Event()           # (arena reuse is then ordered behind the feature stream)
+            ready.record(main)
+            self._arena_free[slot] = ready
+            ready = None
         if tail is not None:
             for t in (boxes, scores, labels, scene, count):
                 t.record_stream(tail)                     # allocated on the main stream, written on the tail stream

@@ -330,14 +330,20 @@ int b2_adamw_step(const void* table, const int* chunks, int n_chunks, double lr,
  * tail_stream (NULL or == stream: everything on `stream`): the top-k / decode / NMS tail - small launches on a handful
  * of SMs - is enqueued on that second stream behind an event, so the NEXT call's first kernels on `stream` overlap it; the
  * outputs are then complete when tail_stream reaches the point the call left it at, and the caller must not hand the same
- * arena to a later call before that (fcaf3d_b200/engine.py alternates two arenas and orders them with events). */
+ * arena to a later call before that (fcaf3d_b200/engine.py alternates two arenas and orders them with events).
+ * Coordinate stream: the engine owns a third stream for everything that depends on coordinates only (hash builds, kernel
+ * maps); the feature kernels on `stream` wait for it by events, never the other way round, so the coordinate work of the
+ * next call runs while the GPU is still busy with this call's convolutions.  That stream must know when it may start:
+ * inputs_ready_event (a cudaEvent_t, e.g. the end of the host->device copy) or inputs_ready != 0 (the points are complete
+ * already) - with neither it waits for everything queued on `stream` so far; arena_free_event (cudaEvent_t or NULL): the
+ * event after which `arena` may be overwritten.  B2_ENGINE_SPLIT=0 keeps all of it on `stream`. */
 void* b2_engine_create(const long long* desc, int n_words, const double* fl);
 int b2_engine_destroy(void* engine);
 long long b2_engine_out_rows(void* engine, int n_scenes);
 int b2_engine_infer(void* engine, const float* const* points_host, const long long* n_points_host, int n_scenes, int dtype,
                     void* arena, size_t arena_bytes, float* out_boxes, float* out_scores, int* out_labels, int* out_scene,
                     int* out_count, long long out_cap, long long* n_rows_host, size_t* arena_used_host, void* stream,
-                    void* tail_stream);
+                    void* tail_stream, void* inputs_ready_event, int inputs_ready, void* arena_free_event);
 
 #ifdef __cplusplus
 }
