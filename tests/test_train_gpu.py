@@ -400,7 +400,7 @@ def test_fused_adamw_with_clipping_matches_torch(dev):
     pb = [torch.nn.Parameter(p.detach().clone()) for p in pa]
     oa = FusedAdamW(pa, lr=1e-3, weight_decay=1e-4, max_norm=10.0)
     ob = torch.optim.AdamW(pb, lr=1e-3, weight_decay=1e-4)
-    for it, gscale in enumerate((1.0, 1e-3, 5.0, 0.1)):
+    for it, gscale in enumerate((1.0, 1e-3, 5.0, 5e-3)):      # gradient norm ~ 1050 x gscale
         grads = [torch.randn(s, generator=g).to(dev) * gscale for s in shapes]
         for p, q, gr in zip(pa, pb, grads):
             p.grad, q.grad = gr.clone(), gr.clone()
@@ -408,7 +408,7 @@ def test_fused_adamw_with_clipping_matches_torch(dev):
         norm = torch.nn.utils.clip_grad_norm_(pb, 10.0)
         ob.step()
         assert abs(float(sq.sqrt()) - float(norm)) < 1e-6 * float(norm)
-        assert (float(norm) > 10.0) == (gscale >= 1.0)
+        assert (float(norm) > 10.0) == (gscale >= 0.1)
         for i, (p, q) in enumerate(zip(pa, pb)):
             assert rel_err(p, q) < 1e-6, (it, i)
             st = ob.state[q]
