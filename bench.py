@@ -287,11 +287,14 @@ def bench_infer(ctx, args, workload, dtype_name, steps, warmup, clk=None, brief=
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     s.record()
     h0 = time.perf_counter()
+    recent = []
     for _ in range(steps):
         ctx.flush.fill_(1)
         dets = step_device()
+        recent = (recent + [dets])[-4:]
     host_ms = 1000.0 * (time.perf_counter() - h0) / steps      # time the host needed to ENQUEUE a step (incl. its reads)
-    wait_ready(dets)            # the last step's NMS tail runs on the executor's side stream: the bracket closes behind it
+    for d in recent:            # the last steps' work runs on the executor's own streams: the bracket closes behind them
+        wait_ready(d)
     e.record()
     torch.cuda.synchronize()
     ctx.barrier()
@@ -311,14 +314,15 @@ def bench_infer(ctx, args, workload, dtype_name, steps, warmup, clk=None, brief=
         torch.cuda.synchronize()
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s.record()
-        pending = None
+        pending = []                                # as many reads in flight as the detector keeps steps in flight
+        depth = max(1, int(getattr(det, "lanes", 1)))
         for pts in ScenePrefetcher((host_pts for _ in range(k_e2e)), dev):
             ctx.flush.fill_(1)
-            read = DetectionRead(det.simple_test_fused(pts, to_host=False), batch)   # async packed copy, side stream
-            if pending is not None:
-                pending.finish()                    # the previous step's detections, read while this step runs
-            pending = read
-        pending.finish()
+            pending.append(DetectionRead(det.simple_test_fused(pts, to_host=False), batch))   # async packed copy, side stream
+            if len(pending) > depth:
+                pending.pop(0).finish()             # an earlier step's detections, read while the later ones run
+        for r_ in pending:
+            r_.finish()
         e.record()
         torch.cuda.synchronize()
         ms_e2e = ctx.max_over_ranks(s.elapsed_time(e)) / k_e2e
@@ -549,11 +553,14 @@ def nms_vs_reference(ctx, n_per_class=(1000, 4000), n_cls=18, n_scenes=8, thr=0.
                 num = ref.ref_nms_gpu_call(bs.data_ptr(), bs.size(0), kp.data_ptr(), thr, int(rotated))
                 return od[kp[:num].cuda()].contiguous()
             ref_segment(0)
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            ref_keep = [ref_segment(i) for i in range(nseg)]
-            torch.cuda.synchronize()
-            ref_ms = 1000.0 * (time.perf_counter() - t0)
+            ref_ms = None
+            for _ in range(2):       # best of two passes (the first cudaMalloc after a large free can take a second)
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                ref_keep = [ref_segment(i) for i in range(nseg)]
+                torch.cuda.synchronize()
+                dt_ms = 1000.0 * (time.perf_counter() - t0)
+                ref_ms = dt_ms if ref_ms is None else min(ref_ms, dt_ms)
             # ---- same keep-sets
             keep_h, order_h = keep.cpu().numpy().astype(bool), order.cpu().numpy()
             same = True

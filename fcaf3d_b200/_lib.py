@@ -130,8 +130,9 @@ _ws = {}
 
 
 def workspace(nbytes, device, slot=0):
-    """Cached, grow-only scratch buffer per (device, slot)."""
-    key = (device.index if device.index is not None else torch.cuda.current_device(), slot)
+    """Cached, grow-only scratch buffer per (device, slot, current stream): kernels enqueued on different streams (the
+    trainer builds the next batch's maps on a side stream) must not share scratch."""
+    key = (device.index if device.index is not None else torch.cuda.current_device(), slot, stream())
     buf = _ws.get(key)
     if buf is None or buf.numel() < nbytes:
         buf = torch.empty(max(int(nbytes), 1 << 16), dtype=torch.uint8, device=device)

@@ -562,6 +562,38 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
       const int gkey = pre_gen, parent = r.maps[gkey].children_of;
       const long long n_par = r.maps[parent].n, n_gen = r.maps[gkey].n;
       const int cg = e.up_gen[i + 1].cout / 8;  // channels of the finer level
+      // The prune chain of this level (interpolation, top-k, scan, row maps, tables of the pruned rows: ~0.25 ms of small
+      // launches) needs the previous level's scores only, the generative transpose needs its features only: with a tail
+      // stream the chain runs THERE, next to the transpose on the feature stream, and the feature stream waits for it
+      // right before the up-block convolution.
+      const bool can_aux = tail_stream != nullptr && r.split && tail_stream != (void*)r.stF;
+      int aux_ev = -1;
+      if (can_aux) {
+        aux_ev = r.slot();
+        B2_CUDA(cudaEventRecord(e.events[aux_ev], r.stF));
+      }
+      bool in_aux = false;
+      cudaStream_t f_orig = r.stF;
+      auto aux_begin = [&]() -> int {
+        B2_CUDA(cudaStreamWaitEvent((cudaStream_t)tail_stream, e.events[aux_ev], 0));
+        r.stF = (cudaStream_t)tail_stream;
+        r.to_F();
+        r.c_dirty = true;      // the aux stream has not seen any coordinate work yet
+        in_aux = true;
+        return r.fsync();
+      };
+      auto aux_end = [&]() -> int {
+        if (!in_aux) return B2_OK;
+        int rc_ = r.fsync();
+        if (rc_) return rc_;
+        const int s = r.slot();
+        B2_CUDA(cudaEventRecord(e.events[s], r.stF));
+        r.stF = f_orig;
+        r.to_F();
+        B2_CUDA(cudaStreamWaitEvent(f_orig, e.events[s], 0));
+        in_aux = false;
+        return B2_OK;
+      };
       void* g;
       CK(r.conv(e.up_gen[i + 1], f, r.dt, n_par, nullptr, n_par, nullptr, B2_ACT_ELU, cg, r.dt, &g));  // [n_par, 8 cg] = [n_gen, cg]
       int ukey;
@@ -577,6 +609,7 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
       int pkey = ukey;
       if (need_prune) {
         // prune by the coarser level's interpolated max-class score: ready before the up-block's 3^3 convolution runs
+        if (can_aux) CK(aux_begin());
         const Level& prev = lv[i + 1];
         CK(r.ensure_table(prev.map));
         TAKE(q, float, nu * 4);
@@ -623,12 +656,14 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
         CK(r.alloc_kmap(gkey, pkey, 3, n_keep, &up));
         CK(r.alloc_kmap(pkey, pkey, 3, n_keep, &ko));
         FK(b2_kernel_map_children_pruned(pk->nbr, pk->ld, ksrc, g2k, n_keep, up.ld, up.nbr, up.tmask, ko.nbr, ko.tmask, r.stv));
+        CK(aux_end());
         r.kmaps.push_back(ko);
         void* o;
         CK(r.conv(e.up_conv[i + 1], g, r.dt, n_gen, &up, n_keep, nullptr, B2_ACT_ELU, 0, r.dt, &o));
         FK(b2_scatter_rows(stage_f[i], a2k, r.maps[stage_map[i]].n, cg, r.dt, 1, o, r.stv));
         f = o;
       } else {
+        CK(aux_end());
         KMap* kg;
         CK(r.kernel_map(gkey, gkey, 3, &kg));
         void* o;

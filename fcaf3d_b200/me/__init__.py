@@ -277,6 +277,27 @@ class CoordinateManager:
         return km
 
 
+def _record_stream(self, stream):
+    """Marks every tensor of the manager as used on `stream` (torch's allocator then keeps their memory until that stream
+    has passed the point of their release): for maps that were built on one stream and are consumed on another."""
+    def rec(t):
+        if torch.is_tensor(t) and t.is_cuda:
+            t.record_stream(stream)
+    for m in self._maps.values():
+        for t in (m.coords, m.table, m.off_dev):
+            rec(t)
+    for km in self._kmaps.values():
+        rec(km.nbr), rec(km.tile_mask)
+        for t in (km.sorted or ()):
+            rec(t)
+    for p in self._pending.values():
+        for t in p.values():
+            rec(t)
+
+
+CoordinateManager.record_stream = _record_stream
+
+
 def _set_kernel_map(self, in_key, out_key, kernel_size, dilation, km):
     """Registers a neighbour table a caller derived by other means (e.g. ops.kernel_map_children_pruned)."""
     self._kmaps[(in_key, out_key, int(kernel_size), int(dilation))] = km
