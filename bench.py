@@ -273,7 +273,7 @@ def bench_infer(ctx, args, workload, dtype_name, steps, warmup, clk=None, brief=
         torch.cuda.profiler.stop()
         return {"profile_step": "done"}
 
-    for _ in range(warmup):
+    for _ in range(max(warmup, 2 * int(getattr(det, "lanes", 1)) + 1)):   # every executor lane sees both of its arenas
         step_device()
     torch.cuda.synchronize()
     launches0 = lib.b2_launch_count()

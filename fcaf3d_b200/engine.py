@@ -176,6 +176,12 @@ class InferenceEngine:
             if arena is None or arena.numel() < need or arena.device != dev:
                 self._arenas[slot] = arena = None
                 self._arenas[slot] = arena = torch.empty(max(need, 1 << 20), dtype=torch.uint8, device=dev)
+                other = self._arenas[1 - slot]            # both arenas at once: no allocation in a later (timed) call
+                if other is None or other.numel() < arena.numel() or other.device != dev:
+                    if self._arena_free[1 - slot] is not None:
+                        self._arena_free[1 - slot].synchronize()
+                    self._arenas[1 - slot] = None
+                    self._arenas[1 - slot] = torch.empty(arena.numel(), dtype=torch.uint8, device=dev)
             rc = l.b2_engine_infer(self._handle, ptrs, counts, n, dt, ptr(arena), arena.numel(), ptr(boxes),
                                    ptr(scores), ptr(labels), ptr(scene), ptr(count), cap, ctypes.byref(rows),
                                    ctypes.byref(used), stream(), tail.cuda_stream if tail is not None else None, in_ev,
