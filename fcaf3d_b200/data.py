@@ -102,10 +102,17 @@ class ScenePrefetcher:
     step) and yields lists of CUDA tensors; while the consumer works on batch i, batch i+1 is staged through pinned
     memory and copied on a side stream."""
 
+    _streams = {}
+
     def __init__(self, batches, device):
         self.batches = iter(batches)
         self.device = torch.device(device)
-        self.stream = torch.cuda.Stream(device=self.device)
+        # one copy stream per device for the life of the process: torch's allocator keeps a pool per stream, so a fresh
+        # stream per prefetcher would cudaMalloc its first batches again (inside whatever loop is being timed)
+        key = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        if key not in ScenePrefetcher._streams:
+            ScenePrefetcher._streams[key] = torch.cuda.Stream(device=self.device)
+        self.stream = ScenePrefetcher._streams[key]
         self._next = None
         self._preload()
 
