@@ -38,15 +38,30 @@ struct TcCfg {
 // tensor pipe - paced the C = 64 layers (ncu source view: 2/3 of the stall samples in the producer loop and its per-offset
 // set-up); with two groups the per-stage fixed part of the chain is paid half as often per warp.  The weight tile's TMA
 // load moves from thread 0 of the producers to lane 0 of a warp of its own.
+// Head epilogue (EPI == 1, BN == 32: the fused 128 -> 1 + n_reg + n_cls head GEMM): instead of storing the [rows, 32] logits
+// and running b2_head_post over them, every epilogue thread - it holds all 32 columns of its row - writes the head's outputs
+// directly (forward_single, fcaf3d_neck_with_head.py:256-279: centerness, exp(scale * distances), class logits, row max for
+// the pruning score; and max_c sigmoid(cls) * sigmoid(centerness) for the candidate top-k, :237-238).  Same expressions as
+// k_head_post_tiled, hence bit-identical values.
+struct TcHeadEpi {
+  float* centerness = nullptr;
+  float* bbox_pred = nullptr;
+  float* cls = nullptr;
+  float* prune_score = nullptr;
+  float* max_score = nullptr;
+  const float* scale = nullptr;
+  int n_reg = 0, n_cls = 0;
+};
+
 // TIn = __nv_bfloat16 (kind::f16, 64 channels per 128-byte stage row) or float (kind::tf32: fp32 rows and weights read as
 // TF32 operands, 32 channels per stage row, fp32 accumulation - the fp32-storage mode of the tensor-core path).
-template <int BN, int ST, typename TOut, int GRP, typename TIn = __nv_bfloat16>
+template <int BN, int ST, typename TOut, int GRP, typename TIn = __nv_bfloat16, int EPI = 0>
 __global__ void __launch_bounds__(CT_THREADS)
 k_conv_tc(const __grid_constant__ CUtensorMap map_b, const TIn* __restrict__ in, const int* __restrict__ nbr,
           int ld,
           const unsigned int* __restrict__ tile_mask, const int* __restrict__ out_rows, int n_out, int cin, int cout,
           int kvol, const float* __restrict__ bias, const float* __restrict__ scale, const float* __restrict__ shift,
-          const TOut* __restrict__ residual, int act, int ch_mod, TOut* __restrict__ out) {
+          const TOut* __restrict__ residual, int act, int ch_mod, TOut* __restrict__ out, const TcHeadEpi hp = TcHeadEpi()) {
   using Cfg = TcCfg<BN, ST>;
   constexpr int S = Cfg::STAGES;
   constexpr int BKE = 128 / (int)sizeof(TIn);   // channels per stage row (128 bytes)
@@ -195,7 +210,42 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const TIn* __restrict__ in,
       o = __ldg(out_rows + o);
       if (o < 0) o = n_out;
     }
-    if (BN >= 64 || half == 0) {
+    if (EPI == 1) {
+      // (staging the rows through shared memory for coalesced block writes was measured slower: 212 against 199 us per step)
+      if (half == 0) {
+        uint32_t v[32];
+        if (nstage > 0) {
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16), v);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0u;
+        }
+        if (o < n_out) {
+          float f[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = (__uint_as_float(v[j]) + s_epi[j]) * s_epi[BN + j] + s_epi[2 * BN + j];
+          const float hscale = hp.scale ? __ldg(hp.scale) : 1.f;
+          const float ctr = f[0];
+          hp.centerness[o] = ctr;
+          const float sc = 1.f / (1.f + expf(-ctr));
+          float mlogit = -INFINITY, mscore = -INFINITY;
+          const int c0 = 1 + hp.n_reg, c1 = c0 + hp.n_cls;
+#pragma unroll
+          for (int j = 1; j < 32; ++j) {
+            if (j < c0) {
+              const int k = j - 1;
+              hp.bbox_pred[(long long)o * hp.n_reg + k] = (k < 6) ? expf(hscale * f[j]) : f[j];
+            } else if (j < c1) {
+              mlogit = fmaxf(mlogit, f[j]);
+              mscore = fmaxf(mscore, (1.f / (1.f + expf(-f[j]))) * sc);
+              hp.cls[(long long)o * hp.n_cls + (j - c0)] = f[j];
+            }
+          }
+          hp.prune_score[o] = mlogit;
+          if (hp.max_score) hp.max_score[o] = mscore;
+        }
+      }
+    } else if (BN >= 64 || half == 0) {
       for (int cc = half * CPW; cc < half * CPW + CPW; cc += 32) {
         uint32_t v[32];
         if (nstage > 0) {
@@ -329,7 +379,7 @@ static int launch_tc_g(const void* in, const void* wt, const int* nbr, long long
   dim3 grid(b2_div_up(n_out, TC_BM), cout / BN);
   kern<<<grid, CT_THREADS, Cfg::SMEM, st>>>(map_b, (const __nv_bfloat16*)in, nbr, (int)ld, tile_mask, out_rows,
                                             (int)n_out, cin, cout, kvol, bias, scale, shift, (const TOut*)residual, act,
-                                            ch_mod, (TOut*)out);
+                                            ch_mod, (TOut*)out, TcHeadEpi());
   B2_LAUNCH_CHECK();
   return B2_OK;
 }
@@ -362,7 +412,33 @@ static int launch_tf32(const void* in, const void* wt, const int* nbr, long long
   if (rc) return rc;
   dim3 grid(b2_div_up(n_out, TC_BM), cout / BN);
   kern<<<grid, CT_THREADS, Cfg::SMEM, st>>>(map_b, (const float*)in, nbr, (int)ld, tile_mask, out_rows, (int)n_out, cin, cout,
-                                            kvol, bias, scale, shift, (const float*)residual, act, ch_mod, (float*)out);
+                                            kvol, bias, scale, shift, (const float*)residual, act, ch_mod, (float*)out, TcHeadEpi());
+  B2_LAUNCH_CHECK();
+  return B2_OK;
+}
+
+// The three 1x1 heads as one 128 -> 32-column GEMM whose epilogue is the head post-processing (see TcHeadEpi)
+extern "C" int b2_head_fused(const void* in_bf16, long long n, const void* wt_bf16, int cin, int cols, const float* bias,
+                             int n_reg, int n_cls, const float* level_scale, float* centerness, float* bbox_pred, float* cls,
+                             float* prune_score, float* max_score, void* stream) {
+  B2_CHECK_ARG(cin % TC_BK == 0 && cin > 0, "b2_head_fused needs cin %% 64 == 0 (got %d)", cin);
+  B2_CHECK_ARG(cols == 32 && 1 + n_reg + n_cls <= 32 && n_reg >= 6 && n_cls >= 1,
+               "b2_head_fused: 1 + n_reg + n_cls (%d) must fit the 32 padded head columns", 1 + n_reg + n_cls);
+  if (n == 0) return B2_OK;
+  B2_CHECK_ARG(in_bf16 && wt_bf16 && centerness && bbox_pred && cls && prune_score, "b2_head_fused: null pointer");
+  using Cfg = TcCfg<32, 4>;
+  auto kern = k_conv_tc<32, 4, float, 2, __nv_bfloat16, 1>;
+  static unsigned long long configured = 0;
+  if (int rc0 = b2_optin_smem((const void*)kern, Cfg::SMEM, &configured)) return rc0;
+  CUtensorMap map_b;
+  const int rc = b2_make_bf16_map(&map_b, wt_bf16, cols, cin, 32);
+  if (rc) return rc;
+  TcHeadEpi hp;
+  hp.centerness = centerness, hp.bbox_pred = bbox_pred, hp.cls = cls, hp.prune_score = prune_score, hp.max_score = max_score;
+  hp.scale = level_scale, hp.n_reg = n_reg, hp.n_cls = n_cls;
+  kern<<<dim3(b2_div_up(n, TC_BM), 1), CT_THREADS, Cfg::SMEM, (cudaStream_t)stream>>>(
+      map_b, (const __nv_bfloat16*)in_bf16, nullptr, 0, nullptr, nullptr, (int)n, cin, cols, 1, bias, nullptr, nullptr, nullptr,
+      B2_ACT_NONE, 0, nullptr, hp);
   B2_LAUNCH_CHECK();
   return B2_OK;
 }

@@ -694,8 +694,6 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
     CK(r.kernel_map(key, key, 3, &ko));
     void* o;
     CK(r.conv(e.out_block[i], f, r.dt, n, ko, n, nullptr, B2_ACT_ELU, 0, r.dt, &o));
-    void* h;
-    CK(r.conv(e.head, o, r.dt, n, nullptr, n, nullptr, B2_ACT_NONE, 0, 0, &h));
     Level& l = lv[i];
     l.map = key;
     l.centerness = (float*)r.take((size_t)(n > 0 ? n : 1) * 4);
@@ -704,8 +702,16 @@ static int infer(Engine& e, Run& r, const float* const* points, const long long*
     l.prune = (float*)r.take((size_t)(n > 0 ? n : 1) * 4);
     l.max_score = (float*)r.take((size_t)(n > 0 ? n : 1) * 4);
     if (!l.centerness || !l.bbox || !l.cls || !l.prune || !l.max_score) return B2_ERR_WS;
-    FK(b2_head_post((const float*)h, n, e.head_cols, e.n_reg, e.n_cls, e.level_scale[i], l.centerness, l.bbox, l.cls, l.prune,
-                    l.max_score, r.stv));
+    if (r.dt == 1 && e.head.wt && e.head_cols == 32 && e.head.cin % 64 == 0 && 1 + e.n_reg + e.n_cls <= 32) {
+      // head GEMM with the head post-processing as its epilogue: the [n, 32] logits never go to memory
+      FK(b2_head_fused(o, n, e.head.wt, e.head.cin, e.head_cols, e.head.bias, e.n_reg, e.n_cls, e.level_scale[i], l.centerness,
+                       l.bbox, l.cls, l.prune, l.max_score, r.stv));
+    } else {
+      void* h;
+      CK(r.conv(e.head, o, r.dt, n, nullptr, n, nullptr, B2_ACT_NONE, 0, 0, &h));
+      FK(b2_head_post((const float*)h, n, e.head_cols, e.n_reg, e.n_cls, e.level_scale[i], l.centerness, l.bbox, l.cls, l.prune,
+                      l.max_score, r.stv));
+    }
   }
 
   // ---- tail: per (scene, level) top-k -> decode -> per (scene, class) BEV NMS (fcaf3d_neck_with_head.py:205-253,332-374)

@@ -348,8 +348,10 @@ class Fcaf3DNeckWithHead(nn.Module):
         pos_bbox_preds = bbox_preds[pos_inds]
         pos_scene = scene_of[pos_inds]
         pos_ct = centerness_targets[pos_inds]
-        denorm = torch.clamp(reduce_mean(torch.zeros(S, device=pos_ct.device).index_add_(0, pos_scene, pos_ct)),
-                             min=1e-6)
+        # per-scene sum of the positives' centerness targets, in a FIXED order (index_add_ adds with atomics: its last bits
+        # change from run to run, and through the bf16 activations that reaches every gradient of the step)
+        per_scene = (torch.nn.functional.one_hot(pos_scene, S).to(pos_ct.dtype) * pos_ct.unsqueeze(1)).sum(0)
+        denorm = torch.clamp(reduce_mean(per_scene), min=1e-6)
         if len(pos_inds) > 0:
             loss_centerness = self.loss_centerness(pos_centerness, pos_ct.unsqueeze(1),
                                                    weight=w_scene[pos_scene].unsqueeze(1), avg_factor=1.0)
@@ -455,10 +457,13 @@ class Fcaf3DNeckWithHead(nn.Module):
             km = cm.kernel_map(key, key, conv.kernel_size, conv.dilation)
             o = conv_bn_act(conv, bn, f, km, cm.size(key), ops.ACT_ELU)
             w, b, wt = self._head_weights()
-            h = ops.sparse_conv(o, w, None, o.shape[0], wt_bf16=wt, bias=b, out_dtype=torch.float32,
-                                wt_tf32=self._head_weights_tf32())
-            ctr, bbox, cls, prune, mx = ops.head_post(h, self.n_reg_outs, self.n_classes,
-                                                      self.scales[i].scale.detach().reshape(1), want_max_score)
+            lscale = self.scales[i].scale.detach().reshape(1)
+            if ops.head_fused_ok(o, wt, self.n_reg_outs, self.n_classes):
+                ctr, bbox, cls, prune, mx = ops.head_fused(o, wt, b, self.n_reg_outs, self.n_classes, lscale, want_max_score)
+            else:
+                h = ops.sparse_conv(o, w, None, o.shape[0], wt_bf16=wt, bias=b, out_dtype=torch.float32,
+                                    wt_tf32=self._head_weights_tf32())
+                ctr, bbox, cls, prune, mx = ops.head_post(h, self.n_reg_outs, self.n_classes, lscale, want_max_score)
             prev = dict(key=key, centerness=ctr, bbox_pred=bbox, cls=cls, prune=prune, max_score=mx)
             levels[i] = prev
         return levels

@@ -543,6 +543,31 @@ def head_post(feat, n_reg, n_cls, scale, want_max_score=False):
     return centerness, bbox_pred, cls, prune, mx
 
 
+def head_fused(x, wt_bf16, bias, n_reg, n_cls, scale, want_max_score=False):
+    """x [n, cin] bf16, wt_bf16 [1, 32, cin], bias [32]: head GEMM + head_post in one launch (b2_head_fused); returns what
+    head_post returns."""
+    n = int(x.shape[0])
+    dev = x.device
+    f32 = torch.float32
+    centerness = torch.empty((n, 1), dtype=f32, device=dev)
+    bbox_pred = torch.empty((n, n_reg), dtype=f32, device=dev)
+    cls = torch.empty((n, n_cls), dtype=f32, device=dev)
+    prune = torch.empty((n, 1), dtype=f32, device=dev)
+    mx = torch.empty((n,), dtype=f32, device=dev) if want_max_score else None
+    t0 = _prof_start()
+    call("b2_head_fused", ptr(x), n, ptr(wt_bf16), int(x.shape[1]), int(wt_bf16.shape[1]), ptr(bias), n_reg, n_cls, ptr(scale),
+         ptr(centerness), ptr(bbox_pred), ptr(cls), ptr(prune), ptr(mx))
+    if t0 is not None:
+        cin = int(x.shape[1])
+        _prof_stop(t0, "conv_tc", 2.0 * n * cin * 32, 2.0 * n * cin + 4.0 * n * (3 + n_reg + n_cls))
+    return centerness, bbox_pred, cls, prune, mx
+
+
+def head_fused_ok(x, wt_bf16, n_reg, n_cls):
+    return (_TC_ENABLED and x.dtype == torch.bfloat16 and x.shape[1] % 64 == 0 and wt_bf16 is not None
+            and wt_bf16.shape[1] == 32 and 1 + n_reg + n_cls <= 32)
+
+
 YAW_MODES = {"none": 0, "naive": 1, "sin-cos": 2, "fcaf3d": 3}
 
 

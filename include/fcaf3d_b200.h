@@ -180,6 +180,12 @@ int b2_topk_mask_n(const float* scores, const int* seg_off, int nseg, int k, lon
  * max_score[n] = max_c sigmoid(cls_c)*sigmoid(centerness) (optional) */
 int b2_head_post(const float* feat, long long n, int feat_ld, int n_reg, int n_cls, const float* scale,
                  float* centerness, float* bbox_pred, float* cls, float* prune_score, float* max_score, void* stream);
+/* forward_single (fcaf3d_neck_with_head.py:256-279) in ONE launch for bf16 rows: the three 1x1 head convolutions as one tcgen05
+ * GEMM [n, cin] x wt_bf16 [cols = 32 (padded), cin] + bias [32] whose epilogue writes what b2_head_post writes (bit-identical):
+ * no [n, 32] logit tensor goes to memory. */
+int b2_head_fused(const void* in_bf16, long long n, const void* wt_bf16, int cin, int cols, const float* bias, int n_reg,
+                  int n_cls, const float* level_scale, float* centerness, float* bbox_pred, float* cls, float* prune_score,
+                  float* max_score, void* stream);
 /* yaw_mode: 0 axis-aligned, 1 naive, 2 sin-cos, 3 fcaf3d (Mobius); out [n,7] */
 int b2_decode_boxes(const float* points, const float* bbox_pred, long long n, int n_reg, int yaw_mode, float* out,
                     void* stream);

@@ -75,3 +75,22 @@ def test_head_post(dev):
     assert torch.equal(prune.cpu()[:, 0], f[:, 1 + n_reg:].max(1).values)
     want = (torch.sigmoid(f[:, 1 + n_reg:]) * torch.sigmoid(f[:, :1])).max(1).values
     assert torch.allclose(mx.cpu(), want, atol=1e-6)
+
+
+@pytest.mark.parametrize("n_reg,n_cls,n", [(6, 18, 70001), (8, 10, 3000), (6, 5, 129), (8, 23, 5)])
+def test_fused_head_equals_gemm_then_head_post(dev, n_reg, n_cls, n):
+    """b2_head_fused (head GEMM whose epilogue is the head post-processing) against the two-launch path b2_conv_tc ->
+    b2_head_post on the same bf16 rows and weights: every output bit-identical (same accumulator, same expressions)."""
+    g = torch.Generator().manual_seed(n)
+    cols = 1 + n_reg + n_cls
+    x = (torch.randn(n, 128, generator=g) * 0.7).to(dev).to(torch.bfloat16)
+    w = torch.nn.functional.pad(torch.randn(128, cols, generator=g) * 0.05, (0, 32 - cols)).unsqueeze(0).to(dev).contiguous()
+    b = torch.nn.functional.pad(torch.randn(cols, generator=g) * 0.1, (0, 32 - cols)).to(dev).contiguous()
+    wt = w.transpose(1, 2).contiguous().to(torch.bfloat16)
+    scale = torch.tensor([1.07], device=dev)
+    assert ops.head_fused_ok(x, wt, n_reg, n_cls)
+    got = ops.head_fused(x, wt, b, n_reg, n_cls, scale, want_max_score=True)
+    h = ops.sparse_conv(x, w, None, n, wt_bf16=wt, bias=b, out_dtype=torch.float32)
+    want = ops.head_post(h, n_reg, n_cls, scale, want_max_score=True)
+    for a, e, name in zip(got, want, ("centerness", "bbox_pred", "cls", "prune", "max_score")):
+        assert a.shape == e.shape and torch.equal(a, e), name
