@@ -16,6 +16,7 @@ Prints ONE JSON line (rank 0).  See DESIGN.md §Measurement for every field.
 import argparse
 import atexit
 import ctypes
+import gc
 import json
 import os
 import statistics
@@ -282,6 +283,8 @@ def bench_infer(ctx, args, workload, dtype_name, steps, warmup, clk=None, brief=
     # EXACTLY `steps` steps inside ONE bracket (barrier + synchronize on both sides, CUDA events on the launching stream);
     # L2 is flushed before every step INSIDE the bracket (256 MB write > 126 MB L2: ~45 us per step counted against us),
     # so the host may run ahead of the GPU across steps as it does in a real serving loop.
+    gc.collect()
+    gc.disable()                # a generation-2 collection (several ms of host time) inside a 100 ms bracket is noise, not signal
     ctx.barrier()
     torch.cuda.synchronize()
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -297,6 +300,7 @@ def bench_infer(ctx, args, workload, dtype_name, steps, warmup, clk=None, brief=
         wait_ready(d)
     e.record()
     torch.cuda.synchronize()
+    gc.enable()
     ctx.barrier()
     ms = ctx.max_over_ranks(s.elapsed_time(e)) / steps
     launches = lib.b2_launch_count() - launches0  # kernels of libfcaf3d_b200.so inside the timed region
@@ -625,6 +629,9 @@ def main():
                                   "calibrated on the batch",
                        "l2": "256 MB flush write before every step, inside the one timed bracket over all steps"
                              if args.mode == "infer" else "activations of one step (GBs) exceed L2",
+                       "pipelining": "steps overlap: executor lanes x (coordinate, feature, tail) streams; python gc is off "
+                                     "inside the device-resident bracket only (on in the end-to-end bracket)"
+                                     if args.mode == "infer" else "maps of batch i+1 built between forward and backward of i",
                        "sharding": "whole scenes per GPU, no collective" if args.mode == "infer" else
                                    "data parallel, 8 scenes per GPU, DDP gradient all-reduce over NCCL"},
             "clocks": head.get("clocks"), "e2e": head["e2e"], "gpu_launches": head["gpu_launches"],
