@@ -14,11 +14,11 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ_DIR = os.path.join(HERE, "build")
 LIB_PATH = os.path.join(HERE, "libfcaf3d_b200.so")
-SOURCES = ["api.cu", "coord_map.cu", "sparse_ops.cu", "conv_tc.cu", "tc_map.cu", "head_ops.cu", "nms.cu", "train_ops.cu", "loss_ops.cu", "wgrad_tc.cu", "kmap_sort.cu", "data_ops.cu", "bn_ops.cu", "engine.cu", "optim_ops.cu"]
+SOURCES = ["api.cu", "coord_map.cu", "sparse_ops.cu", "conv_tc.cu", "conv_tcp.cu", "tc_map.cu", "head_ops.cu", "nms.cu", "train_ops.cu", "loss_ops.cu", "wgrad_tc.cu", "kmap_sort.cu", "data_ops.cu", "bn_ops.cu", "engine.cu", "optim_ops.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr",
-]
+] + os.environ.get("B2_NVCC_EXTRA", "").split()   # e.g. -DB2_TC_DBG (timing experiments of tools/bench_conv.py)
 
 
 def _nvcc():

@@ -53,6 +53,34 @@ struct TcHeadEpi {
   int n_reg = 0, n_cls = 0;
 };
 
+#ifdef B2_TC_DBG
+// timing experiments only (results are wrong with any bit set): 1 = no gathers, 2 = weight tiles only for the first S stages,
+// 4 = no MMA, 8 = every neighbour absent (zero-fill copies only), 16 = no proxy fence before the MMAs, 32 = one arrival per
+// producer warp instead of one per thread, 64 = no neighbour-table staging, 128 = no epilogue loads / stores, 256 = no TMEM read
+__device__ int g_tc_dbg = 0;
+extern "C" int b2_tc_debug(int v) { return cudaMemcpyToSymbol(g_tc_dbg, &v, sizeof(int)) == cudaSuccess ? 0 : -1; }
+#define TC_DBG(bit) (dbg & (bit))
+// cycle counters summed over CTAs: 0 CTAs, 1 stages, 2 prologue, 3 MMA thread waiting for full, 4 MMA thread issuing,
+// 5 producer thread 0 waiting for empty, 6 producer thread 0 issuing, 7 weight thread waiting for empty,
+// 8 waiting for the accumulator (producer thread 0, after its last stage), 9 epilogue, 10 CTA lifetime
+__device__ unsigned long long g_tc_stat[16];
+extern "C" int b2_tc_debug_stats(unsigned long long* out16, int reset) {
+  if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+  if (cudaMemcpyFromSymbol(out16, g_tc_stat, sizeof(g_tc_stat)) != cudaSuccess) return -1;
+  if (reset) {
+    unsigned long long z[16] = {0};
+    if (cudaMemcpyToSymbol(g_tc_stat, z, sizeof(z)) != cudaSuccess) return -1;
+  }
+  return 0;
+}
+#define TC_CLK() clock64()
+#define TC_STAT(i, v) atomicAdd(&g_tc_stat[i], (unsigned long long)(v))
+#else
+#define TC_CLK() 0ll
+#define TC_STAT(i, v)
+#define TC_DBG(bit) false
+#endif
+
 // TIn = __nv_bfloat16 (kind::f16, 64 channels per 128-byte stage row) or float (kind::tf32: fp32 rows and weights read as
 // TF32 operands, 32 channels per stage row, fp32 accumulation - the fp32-storage mode of the tensor-core path).
 template <int BN, int ST, typename TOut, int GRP, typename TIn = __nv_bfloat16, int EPI = 0>
@@ -76,6 +104,10 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const TIn* __restrict__ in,
   float* s_epi = reinterpret_cast<float*>(smem + S * Cfg::STAGE_BYTES + 256 + Cfg::NBR_BYTES);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+#ifdef B2_TC_DBG
+  const int dbg = g_tc_dbg;
+#endif
+  const long long t_start = TC_CLK();
   // sorted tables put the tiles with the most offsets last: walk them first so that the heavy tiles do not form the tail
   const int tile = (out_rows != nullptr) ? (int)(gridDim.x - 1 - blockIdx.x) : (int)blockIdx.x;
   const int row0 = tile * TC_BM, col0 = blockIdx.y * BN;
@@ -85,7 +117,7 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const TIn* __restrict__ in,
 
   if (tid == 0) {
     for (int s = 0; s < S; ++s) {
-      mbar_init(&full_bar[s], TC_PRODUCERS / GRP + 1);  // one group's cp.async arrivals + the weight tile's expect_tx
+      mbar_init(&full_bar[s], (TC_DBG(32) ? TC_PRODUCERS / GRP / 32 : TC_PRODUCERS / GRP) + 1);  // one group's cp.async arrivals + the weight tile's expect_tx
       mbar_init(&empty_bar[s], 1);
     }
     mbar_init(accum_bar, 1);
@@ -98,7 +130,7 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const TIn* __restrict__ in,
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   // stage the tile's neighbour rows in shared memory once (coalesced, independent loads in flight)
-  if (nbr != nullptr) {
+  if (nbr != nullptr && !TC_DBG(64)) {
     const int total = kvol * TC_BM;
     for (int i0 = tid; i0 < total; i0 += CT_THREADS * 4) {
       int v[4];
@@ -126,6 +158,11 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const TIn* __restrict__ in,
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (tid == 0) {
+    TC_STAT(0, 1);
+    TC_STAT(1, nstage);
+    TC_STAT(2, TC_CLK() - t_start);
+  }
 
   if (warp < TC_PRODUCERS / 32) {
     // ===================== producers ======================================================
@@ -136,6 +173,7 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const TIn* __restrict__ in,
       const TIn* in_thr = in + chunk16 * CH16;
       const uint32_t smem_base = smem_u32(smem);
       int it = 0;
+      long long t_pw = 0, t_pi = 0;
       for (int k = 0; k < kvol; ++k) {
         if (!((kmask >> k) & 1u)) continue;
         const int mine = it + ((it & 1) != group);   // this group's first stage of the offset
@@ -150,17 +188,27 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const TIn* __restrict__ in,
         for (int p = 0; p < TC_BM / 16; ++p) {
           const int r = nb[p * 16];
           src[p] = in_thr + (r >= 0 ? (long long)r * cin : 0ll);
-          nbytes[p] = r >= 0 ? 16u : 0u;
+          nbytes[p] = (r >= 0 && !TC_DBG(8)) ? 16u : 0u;
         }
         for (int c = 0; c < chunks; ++c, ++it) {
           if ((it & 1) != group) continue;
           const int s = it % S;
+          const long long t0 = TC_CLK();
           mbar_wait(&empty_bar[s], ((uint32_t)(it / S) & 1u) ^ 1u);
+          const long long t1 = TC_CLK();
+          t_pw += t1 - t0;
           const uint32_t a_dst = smem_base + s * Cfg::STAGE_BYTES + dst_off;
+          if (!TC_DBG(1)) {
 #pragma unroll
           for (int p = 0; p < TC_BM / 16; ++p) cp_async16(a_dst + p * 2048, src[p] + c * BKE, nbytes[p]);
-          cp_async_arrive_noinc(&full_bar[s]);
+          }
+          if (!TC_DBG(32) || lane == 0) cp_async_arrive_noinc(&full_bar[s]);
+          t_pi += TC_CLK() - t1;
         }
+      }
+      if (tid == 0) {
+        TC_STAT(5, t_pw);
+        TC_STAT(6, t_pi);
       }
     } else {
     const int chunk16 = tid & 7, rsub = tid >> 3;  // rsub 0..31
@@ -198,10 +246,13 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const TIn* __restrict__ in,
     }
 
     // ===================== epilogue: TMEM -> registers -> global ===========================
+    const long long t_e0 = TC_CLK();
     if (nstage > 0) {
       mbar_wait(accum_bar, 0);
       tc_fence_after();
     }
+    const long long t_e1 = TC_CLK();
+    if (tid == 0) TC_STAT(8, t_e1 - t_e0);
     const int q = warp & 3, half = warp >> 2;          // TMEM lane quarter, column half
     constexpr int CPW = (BN >= 64) ? BN / 2 : BN;       // columns per warp
     // tile position -> output row (identity, or the permutation of a sparsity-sorted neighbour table, kmap_sort.cu)
@@ -245,10 +296,10 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const TIn* __restrict__ in,
           if (hp.max_score) hp.max_score[o] = mscore;
         }
       }
-    } else if (BN >= 64 || half == 0) {
+    } else if ((BN >= 64 || half == 0) && !TC_DBG(128)) {
       for (int cc = half * CPW; cc < half * CPW + CPW; cc += 32) {
         uint32_t v[32];
-        if (nstage > 0) {
+        if (nstage > 0 && !TC_DBG(256)) {
           tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)cc, v);
         } else {
 #pragma unroll
@@ -313,6 +364,7 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const TIn* __restrict__ in,
       }
     }
     tc_fence_before();
+    if (tid == 0) TC_STAT(9, TC_CLK() - t_e1);
   } else if (warp == TC_PRODUCERS / 32 + 1) {
     // ===================== weight tiles (GRP == 2): one thread, one TMA tile load per stage ===
     if (GRP == 2 && lane == 0) {
@@ -322,7 +374,13 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const TIn* __restrict__ in,
         if (!((kmask >> k) & 1u)) continue;
         for (int c = 0; c < chunks; ++c, ++it) {
           const int s = it % S;
+          const long long t0 = TC_CLK();
           mbar_wait(&empty_bar[s], ((uint32_t)(it / S) & 1u) ^ 1u);
+          TC_STAT(7, TC_CLK() - t0);
+          if (TC_DBG(2) && it >= S) {
+            mbar_arrive(&full_bar[s]);
+            continue;
+          }
           mbar_expect_tx(&full_bar[s], (uint32_t)Cfg::B_BYTES);
           tma_tile_2d(smem_base + s * Cfg::STAGE_BYTES + Cfg::A_BYTES, &map_b, &full_bar[s], c * BKE, k * cout + col0);
         }
@@ -330,35 +388,56 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const TIn* __restrict__ in,
     }
     __syncwarp();
   } else {
-    // ===================== MMA issuer (one thread) ==========================================
-    if (lane == 0 && nstage > 0) {
+    // ===================== MMA issuer (one elected thread; the warp waits together) ==========
+    if (nstage > 0) {
       // instruction descriptor: D = F32; A / B format 1 = BF16 (kind::f16) or 2 = TF32 (kind::tf32); N >> 3; M >> 4
       constexpr uint32_t fmt = sizeof(TIn) == 2 ? 1u : 2u;
       constexpr uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((128u >> 4) << 24);
-      const uint32_t smem_base = smem_u32(smem);
+      // shared-memory descriptors differ only in their 14-bit (address >> 4) field: one descriptor, then additions
+      // (no carry out of the field: shared addresses stay below 256 KB)
+      const uint64_t desc0 = umma_desc_sw128(smem_u32(smem));
+      const bool leader = elect_one();
+      long long t_mw = 0, t_mi = 0;
+      int s = 0;
+      uint32_t phase = 0;
       for (int it = 0; it < nstage; ++it) {
-        const int s = it % S;
-        mbar_wait(&full_bar[s], (uint32_t)(it / S) & 1u);
-        fence_async_smem();  // cp.async wrote through the generic proxy, tcgen05.mma reads through the async proxy
+        const long long t0 = TC_CLK();
+        mbar_wait(&full_bar[s], phase);
+        const long long t1 = TC_CLK();
+        t_mw += t1 - t0;
+        if (!TC_DBG(16)) fence_async_smem();  // cp.async wrote through the generic proxy, tcgen05.mma reads through the async proxy
         tc_fence_after();
-        const uint32_t a_base = smem_base + s * Cfg::STAGE_BYTES;
-        const uint32_t b_base = a_base + Cfg::A_BYTES;
+        if (leader) {
+          const uint64_t da = desc0 + (uint64_t)((s * Cfg::STAGE_BYTES) >> 4);
+          const uint64_t db = da + (uint64_t)(Cfg::A_BYTES >> 4);
+          if (!TC_DBG(4) || it == 0) {
 #pragma unroll
-        for (int kk = 0; kk < TC_BK / 16; ++kk) {
-          const uint64_t da = umma_desc_sw128(a_base + kk * 32);
-          const uint64_t db = umma_desc_sw128(b_base + kk * 32);
-          if (sizeof(TIn) == 2)
-            umma_bf16(tmem_base, da, db, idesc, (it > 0 || kk > 0) ? 1u : 0u);
-          else
-            umma_tf32(tmem_base, da, db, idesc, (it > 0 || kk > 0) ? 1u : 0u);
+            for (int kk = 0; kk < TC_BK / 16; ++kk) {
+              if (sizeof(TIn) == 2)
+                umma_bf16(tmem_base, da + 2 * kk, db + 2 * kk, idesc, (it > 0 || kk > 0) ? 1u : 0u);
+              else
+                umma_tf32(tmem_base, da + 2 * kk, db + 2 * kk, idesc, (it > 0 || kk > 0) ? 1u : 0u);
+            }
+          }
+          umma_commit(&empty_bar[s]);  // frees the smem stage once these MMAs have read it
         }
-        umma_commit(&empty_bar[s]);  // frees the smem stage once these MMAs have read it
+        __syncwarp();
+        t_mi += TC_CLK() - t1;
+        if (++s == S) {
+          s = 0;
+          phase ^= 1u;
+        }
       }
-      umma_commit(accum_bar);
+      if (leader) {
+        umma_commit(accum_bar);
+        TC_STAT(3, t_mw);
+        TC_STAT(4, t_mi);
+      }
     }
     __syncwarp();
   }
   __syncthreads();
+  if (tid == 0) TC_STAT(10, TC_CLK() - t_start);
   if (warp == TC_PRODUCERS / 32) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)BN) : "memory");
@@ -482,6 +561,12 @@ extern "C" int b2_conv_tc(const void* in_bf16, long long n_in, const void* wt_bf
   B2_CHECK_ARG(out_rows == nullptr || nbr != nullptr, "a row permutation needs a neighbour table");
   if (n_out == 0) return B2_OK;
   cudaStream_t st = (cudaStream_t)stream;
+  if (out_dtype == 1) {
+    int taken = 0;
+    const int rc = b2_conv_tcp_dispatch(in_bf16, wt_bf16, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale,
+                                        shift, residual, act, ch_mod, out, st, &taken);
+    if (rc != B2_OK || taken) return rc;
+  }
   const bool wide = (cout % 128 == 0);
   const bool mid = (cout % 64 == 0);
 #define TC_GO(BN, T)                                                                                               \

@@ -45,6 +45,17 @@ __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.a
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
+// true in exactly one lane of a converged warp (the compiler then knows the guarded region runs in one thread: tcgen05.mma /
+// TMA instructions inside it are issued without a per-lane serialisation loop)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                : "memory");
@@ -115,5 +126,10 @@ __device__ __forceinline__ void tma_tile_2d(uint32_t dst, const CUtensorMap* map
 // host (tc_map.cu): 2-D tensor maps [rows, cols], box [box_rows x 128 bytes], 128B swizzle, zero fill
 int b2_make_bf16_map(CUtensorMap* map, const void* base, long long rows, int cols, int box_rows);
 int b2_make_tf32_map(CUtensorMap* map, const void* base, long long rows, int cols, int box_rows);
+// host (conv_tcp.cu): the persistent kernel for bf16 layers with many row tiles; *taken = 0 when the layer is not one of its
+int b2_conv_tcp_dispatch(const void* in, const void* wt, const int* nbr, long long ld, const unsigned int* tile_mask,
+                         const int* out_rows, long long n_out, int cin, int cout, int kvol, const float* bias,
+                         const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
+                         cudaStream_t st, int* taken);
 // host: opt-in of one kernel to `bytes` of dynamic shared memory on the CURRENT device, once per device
 int b2_optin_smem(const void* func, int bytes, unsigned long long* done);

@@ -52,6 +52,42 @@ for name in levels:
     gather = pairs * cin * 2 + (n + 127) // 128 * 27 * cin * cout * 2 * (1 if cout <= 128 else cout // 128)
     print("%-6s rows=%7d pairs=%9d (%.1f/row) C=%d->%d : %8.1f us  %7.1f TFLOP/s  L2->SM %6.0f GB/s" %
           (name, n, pairs, pairs / n, cin, cout, ms * 1000, flops / ms / 1e9, gather / ms / 1e6))
+    if os.environ.get("TC_DBG"):
+        # timing experiments of a -DB2_TC_DBG build (B2_NVCC_EXTRA=-DB2_TC_DBG python -m fcaf3d_b200.build): see conv_tc.cu
+        from fcaf3d_b200._lib import lib
+        import ctypes
+        raw = ctypes.CDLL(lib()._name) if hasattr(lib(), "_name") else lib()
+        for v in [int(t) for t in os.environ["TC_DBG"].split(",")]:
+            raw.b2_tc_debug(ctypes.c_int(v))
+            if hasattr(raw, "b2_tc_debug_stats"):
+                raw.b2_tc_debug_stats((ctypes.c_ulonglong * 16)(), 1)
+                raw.b2_tcp_debug_stats((ctypes.c_ulonglong * 16)(), 1)
+            for _ in range(2):
+                ops.sparse_conv(f, w, km, n, wt_bf16=wt)
+            torch.cuda.synchronize()
+            s.record()
+            for _ in range(iters):
+                ops.sparse_conv(f, w, km, n, wt_bf16=wt)
+            e.record()
+            torch.cuda.synchronize()
+            print("%-6s   dbg=%2d : %8.1f us" % (name, v, s.elapsed_time(e) / iters * 1000))
+            if hasattr(raw, "b2_tc_debug_stats"):
+                st = (ctypes.c_ulonglong * 16)()
+                raw.b2_tc_debug_stats(st, 1)
+                c = max(1, st[0])
+                names = ["ctas", "stages", "prologue", "mma_wait_full", "mma_issue", "prod_wait_empty", "prod_issue",
+                         "wt_wait_empty", "accum_wait", "epilogue", "lifetime"]
+                if st[0]:
+                    print("         per CTA (cycles): " + "  ".join("%s=%.0f" % (names[i], st[i] / c) for i in range(1, 11)))
+                raw.b2_tcp_debug_stats(st, 1)
+                if st[0]:
+                    c = st[0]
+                    names = ["ctas", "stages", "tiles", "mma_wait_full", "mma_issue", "mma_wait_acc", "prod_stage_nbr",
+                             "prod_wait_empty", "prod_issue", "epi_wait", "epi", "lifetime", "prologue", "lifetime_ns"]
+                    print("         persistent, per CTA: " + "  ".join("%s=%.0f" % (names[i], st[i] / c) for i in range(1, 14)) +
+                          "  longest_ns=%d longest_cycles=%d" % (st[14], st[15]))
+        raw.b2_tc_debug(ctypes.c_int(0))
+        continue
     if ops.SORT_MIN_ROWS and km.sorted is not None:
         import copy
         ts_ = []
