@@ -15,7 +15,7 @@
 #include "tc_common.cuh"
 #include <stdlib.h>
 
-// 8 producer / epilogue warps, the MMA warp, and (GRP == 2) the warp whose lane 0 issues the weight-tile TMA loads
+// 8 producer / epilogue warps, the MMA warp, and the warp whose lane 0 issues the weight-tile TMA loads
 #define CT_THREADS 320
 
 template <int BN, int ST>
@@ -43,15 +43,6 @@ struct TcCfg {
 // directly (forward_single, fcaf3d_neck_with_head.py:256-279: centerness, exp(scale * distances), class logits, row max for
 // the pruning score; and max_c sigmoid(cls) * sigmoid(centerness) for the candidate top-k, :237-238).  Same expressions as
 // k_head_post_tiled, hence bit-identical values.
-struct TcHeadEpi {
-  float* centerness = nullptr;
-  float* bbox_pred = nullptr;
-  float* cls = nullptr;
-  float* prune_score = nullptr;
-  float* max_score = nullptr;
-  const float* scale = nullptr;
-  int n_reg = 0, n_cls = 0;
-};
 
 #ifdef B2_TC_DBG
 // timing experiments only (results are wrong with any bit set): 1 = no gathers, 2 = weight tiles only for the first S stages,
@@ -113,11 +104,13 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const TIn* __restrict__ in,
   const int row0 = tile * TC_BM, col0 = blockIdx.y * BN;
   const unsigned int kmask = (nbr != nullptr) ? tile_mask[tile] : 1u;
   const int chunks = cin / BKE;
+  // the staged neighbour table holds 16-byte units (row * row bytes / 16, -1 = absent), see tc_produce
+  const int row_units = cin * (int)sizeof(TIn) / 16;
   const int nstage = __popc(kmask & ((1u << kvol) - 1u)) * chunks;
 
   if (tid == 0) {
     for (int s = 0; s < S; ++s) {
-      mbar_init(&full_bar[s], (TC_DBG(32) ? TC_PRODUCERS / GRP / 32 : TC_PRODUCERS / GRP) + 1);  // one group's cp.async arrivals + the weight tile's expect_tx
+      mbar_init(&full_bar[s], TC_PRODUCERS / 2 + 1);  // one group's cp.async arrivals + the weight tile's expect_tx
       mbar_init(&empty_bar[s], 1);
     }
     mbar_init(accum_bar, 1);
@@ -142,10 +135,10 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const TIn* __restrict__ in,
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u)
-        if (i0 + u * CT_THREADS < total) s_nbr[i0 + u * CT_THREADS] = v[u];
+        if (i0 + u * CT_THREADS < total) s_nbr[i0 + u * CT_THREADS] = v[u] >= 0 ? v[u] * row_units : -1;
     }
   } else {
-    for (int r = tid; r < TC_BM; r += CT_THREADS) s_nbr[r] = (row0 + r < n_out) ? row0 + r : -1;
+    for (int r = tid; r < TC_BM; r += CT_THREADS) s_nbr[r] = (row0 + r < n_out) ? (row0 + r) * row_units : -1;
   }
   for (int j = tid; j < BN; j += CT_THREADS) {
     const int n = col0 + j;
@@ -166,83 +159,22 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const TIn* __restrict__ in,
 
   if (warp < TC_PRODUCERS / 32) {
     // ===================== producers ======================================================
-    if (GRP == 2) {
+    {
       const int group = warp >> 2, gt = tid & 127;
       const int chunk16 = gt & 7, rsub = gt >> 3;  // rsub 0..15; rows rsub + 16 p keep (row & 7) == (rsub & 7)
       const uint32_t dst_off = (uint32_t)(rsub * 128 + ((chunk16 ^ (rsub & 7)) << 4));  // + 2048 per pass (16 rows)
-      const TIn* in_thr = in + chunk16 * CH16;
-      const uint32_t smem_base = smem_u32(smem);
+      const uint4* in_thr = reinterpret_cast<const uint4*>(in) + chunk16;
+      const unsigned int km = kmask & ((1u << kvol) - 1u);
       int it = 0;
-      long long t_pw = 0, t_pi = 0;
-      for (int k = 0; k < kvol; ++k) {
-        if (!((kmask >> k) & 1u)) continue;
-        const int mine = it + ((it & 1) != group);   // this group's first stage of the offset
-        if (mine >= it + chunks) {
-          it += chunks;
-          continue;
-        }
-        const int* nb = s_nbr + k * TC_BM + rsub;
-        const TIn* src[TC_BM / 16];
-        uint32_t nbytes[TC_BM / 16];
-#pragma unroll
-        for (int p = 0; p < TC_BM / 16; ++p) {
-          const int r = nb[p * 16];
-          src[p] = in_thr + (r >= 0 ? (long long)r * cin : 0ll);
-          nbytes[p] = (r >= 0 && !TC_DBG(8)) ? 16u : 0u;
-        }
-        for (int c = 0; c < chunks; ++c, ++it) {
-          if ((it & 1) != group) continue;
-          const int s = it % S;
-          const long long t0 = TC_CLK();
-          mbar_wait(&empty_bar[s], ((uint32_t)(it / S) & 1u) ^ 1u);
-          const long long t1 = TC_CLK();
-          t_pw += t1 - t0;
-          const uint32_t a_dst = smem_base + s * Cfg::STAGE_BYTES + dst_off;
-          if (!TC_DBG(1)) {
-#pragma unroll
-          for (int p = 0; p < TC_BM / 16; ++p) cp_async16(a_dst + p * 2048, src[p] + c * BKE, nbytes[p]);
-          }
-          if (!TC_DBG(32) || lane == 0) cp_async_arrive_noinc(&full_bar[s]);
-          t_pi += TC_CLK() - t1;
-        }
-      }
-      if (tid == 0) {
-        TC_STAT(5, t_pw);
-        TC_STAT(6, t_pi);
-      }
-    } else {
-    const int chunk16 = tid & 7, rsub = tid >> 3;  // rsub 0..31
-    const uint32_t dst_off = (uint32_t)(rsub * 128 + ((chunk16 ^ (rsub & 7)) << 4));  // + 4096 per pass (32 rows)
-    const TIn* in_thr = in + chunk16 * CH16;
-    const uint32_t smem_base = smem_u32(smem);
-    int it = 0;
-    for (int k = 0; k < kvol; ++k) {
-      if (!((kmask >> k) & 1u)) continue;
-      const int* nb = s_nbr + k * TC_BM + rsub;
-      const TIn* src[TC_BM / 32];
-      uint32_t nbytes[TC_BM / 32];
-#pragma unroll
-      for (int p = 0; p < TC_BM / 32; ++p) {
-        const int r = nb[p * 32];
-        src[p] = in_thr + (r >= 0 ? (long long)r * cin : 0ll);
-        nbytes[p] = r >= 0 ? 16u : 0u;
-      }
-      for (int c = 0; c < chunks; ++c, ++it) {
-        const int s = it % S;
-        mbar_wait(&empty_bar[s], ((uint32_t)(it / S) & 1u) ^ 1u);
-        const uint32_t a_dst = smem_base + s * Cfg::STAGE_BYTES + dst_off;
-        const uint32_t b_dst = smem_base + s * Cfg::STAGE_BYTES + Cfg::A_BYTES;
-#pragma unroll
-        for (int p = 0; p < TC_BM / 32; ++p) cp_async16(a_dst + p * 4096, src[p] + c * BKE, nbytes[p]);
-        // the weight slice W_k^T[col0 : col0+BN, c*64 : c*64+64] is ONE TMA tile load (completion counted in bytes)
-        if (tid == 0) {
-          mbar_expect_tx(&full_bar[s], (uint32_t)Cfg::B_BYTES);
-          tma_tile_2d(b_dst, &map_b, &full_bar[s], c * BKE, k * cout + col0);
-        }
-        // asynchronous completion: nobody waits here, so all S stages can be in flight
-        cp_async_arrive_noinc(&full_bar[s]);
-      }
-    }
+      if (chunks == 1)
+        tc_produce<S, Cfg::STAGE_BYTES, 1>(km, 1, group, s_nbr + rsub, in_thr, smem_u32(smem) + dst_off, full_bar, empty_bar, it);
+      else if (chunks == 2)
+        tc_produce<S, Cfg::STAGE_BYTES, 2>(km, 2, group, s_nbr + rsub, in_thr, smem_u32(smem) + dst_off, full_bar, empty_bar, it);
+      else if (chunks == 4)
+        tc_produce<S, Cfg::STAGE_BYTES, 4>(km, 4, group, s_nbr + rsub, in_thr, smem_u32(smem) + dst_off, full_bar, empty_bar, it);
+      else
+        tc_produce<S, Cfg::STAGE_BYTES, 0>(km, chunks, group, s_nbr + rsub, in_thr, smem_u32(smem) + dst_off, full_bar,
+                                           empty_bar, it);
     }
 
     // ===================== epilogue: TMEM -> registers -> global ===========================
@@ -275,25 +207,7 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const TIn* __restrict__ in,
           float f[32];
 #pragma unroll
           for (int j = 0; j < 32; ++j) f[j] = (__uint_as_float(v[j]) + s_epi[j]) * s_epi[BN + j] + s_epi[2 * BN + j];
-          const float hscale = hp.scale ? __ldg(hp.scale) : 1.f;
-          const float ctr = f[0];
-          hp.centerness[o] = ctr;
-          const float sc = 1.f / (1.f + expf(-ctr));
-          float mlogit = -INFINITY, mscore = -INFINITY;
-          const int c0 = 1 + hp.n_reg, c1 = c0 + hp.n_cls;
-#pragma unroll
-          for (int j = 1; j < 32; ++j) {
-            if (j < c0) {
-              const int k = j - 1;
-              hp.bbox_pred[(long long)o * hp.n_reg + k] = (k < 6) ? expf(hscale * f[j]) : f[j];
-            } else if (j < c1) {
-              mlogit = fmaxf(mlogit, f[j]);
-              mscore = fmaxf(mscore, (1.f / (1.f + expf(-f[j]))) * sc);
-              hp.cls[(long long)o * hp.n_cls + (j - c0)] = f[j];
-            }
-          }
-          hp.prune_score[o] = mlogit;
-          if (hp.max_score) hp.max_score[o] = mscore;
+          tc_head_row(f, (long long)o, hp);
         }
       }
     } else if ((BN >= 64 || half == 0) && !TC_DBG(128)) {
@@ -367,7 +281,7 @@ k_conv_tc(const __grid_constant__ CUtensorMap map_b, const TIn* __restrict__ in,
     if (tid == 0) TC_STAT(9, TC_CLK() - t_e1);
   } else if (warp == TC_PRODUCERS / 32 + 1) {
     // ===================== weight tiles (GRP == 2): one thread, one TMA tile load per stage ===
-    if (GRP == 2 && lane == 0) {
+    if (lane == 0) {
       const uint32_t smem_base = smem_u32(smem);
       int it = 0;
       for (int k = 0; k < kvol; ++k) {
@@ -463,17 +377,11 @@ static int launch_tc_g(const void* in, const void* wt, const int* nbr, long long
   return B2_OK;
 }
 
-// producer organisation: 2 = two groups on alternate stages + a weight-loader warp, 1 = all eight warps on every stage
-// (B2_TC_GROUPS=1 / 2 for A/B runs)
 template <int BN, int ST, typename TOut>
 static int launch_tc(const void* in, const void* wt, const int* nbr, long long ld, const unsigned int* tile_mask,
                      const int* out_rows, long long n_out, int cin, int cout, int kvol, const float* bias, const float* scale,
                      const float* shift, const void* residual, int act, int ch_mod, void* out, cudaStream_t st) {
-  static const int groups = getenv("B2_TC_GROUPS") ? atoi(getenv("B2_TC_GROUPS")) : 2;
-  if (groups == 2)
-    return launch_tc_g<BN, ST, TOut, 2>(in, wt, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, shift,
-                                        residual, act, ch_mod, out, st);
-  return launch_tc_g<BN, ST, TOut, 1>(in, wt, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, shift,
+  return launch_tc_g<BN, ST, TOut, 2>(in, wt, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, shift,
                                       residual, act, ch_mod, out, st);
 }
 
@@ -515,6 +423,11 @@ extern "C" int b2_head_fused(const void* in_bf16, long long n, const void* wt_bf
   TcHeadEpi hp;
   hp.centerness = centerness, hp.bbox_pred = bbox_pred, hp.cls = cls, hp.prune_score = prune_score, hp.max_score = max_score;
   hp.scale = level_scale, hp.n_reg = n_reg, hp.n_cls = n_cls;
+  {
+    int taken = 0;
+    const int rcp = b2_head_tcp_dispatch(in_bf16, n, wt_bf16, cin, bias, hp, (cudaStream_t)stream, &taken);
+    if (rcp != B2_OK || taken) return rcp;
+  }
   kern<<<dim3(b2_div_up(n, TC_BM), 1), CT_THREADS, Cfg::SMEM, (cudaStream_t)stream>>>(
       map_b, (const __nv_bfloat16*)in_bf16, nullptr, 0, nullptr, nullptr, (int)n, cin, cols, 1, bias, nullptr, nullptr, nullptr,
       B2_ACT_NONE, 0, nullptr, hp);
@@ -528,7 +441,7 @@ extern "C" int b2_conv_tc_tf32(const void* in_f32, long long n_in, const void* w
                                const unsigned int* tile_mask, const int* out_rows, long long n_out, int cin, int cout,
                                int kvol, const float* bias, const float* scale, const float* shift, const void* residual,
                                int act, int ch_mod, void* out, void* stream) {
-  (void)n_in;
+  B2_CHECK_ARG(n_in * (cin / 4) < (1ll << 31), "b2_conv_tc_tf32: input of %lld rows x %d channels exceeds 2^31 16-byte units", n_in, cin);
   B2_CHECK_ARG(cin % 32 == 0 && cin > 0, "b2_conv_tc_tf32 needs cin %% 32 == 0 (got %d)", cin);
   B2_CHECK_ARG(cout % 32 == 0 && cout > 0, "b2_conv_tc_tf32 needs cout %% 32 == 0 (got %d)", cout);
   B2_CHECK_ARG(nbr != nullptr || kvol == 1, "identity map requires kernel volume 1");
@@ -553,6 +466,7 @@ extern "C" int b2_conv_tc(const void* in_bf16, long long n_in, const void* wt_bf
                           const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
                           int out_dtype, void* stream) {
   B2_CHECK_ARG(cin % TC_BK == 0 && cin > 0, "b2_conv_tc needs cin %% 64 == 0 (got %d)", cin);
+  B2_CHECK_ARG(n_in * (cin / 8) < (1ll << 31), "b2_conv_tc: input of %lld rows x %d channels exceeds 2^31 16-byte units", n_in, cin);
   B2_CHECK_ARG(cout % 32 == 0 && cout > 0, "b2_conv_tc needs cout %% 32 == 0 (got %d)", cout);
   B2_CHECK_ARG(nbr != nullptr || kvol == 1, "identity map requires kernel volume 1");
   B2_CHECK_ARG(nbr == nullptr || (tile_mask != nullptr && kvol <= 27 && ld % TC_BM == 0),

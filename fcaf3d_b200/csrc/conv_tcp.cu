@@ -109,54 +109,15 @@ __device__ __forceinline__ int tcp_tile(int i, int c, int G, int n_tiles, bool r
   return idx < n_tiles ? (rev ? n_tiles - 1 - idx : idx) : -1;
 }
 
-// 64-bit address of 16-byte unit `unit` behind `base` in one instruction (kept opaque so that the compiler holds the eight
-// row addresses of an offset in registers instead of rebuilding them for every stage)
-__device__ __forceinline__ const uint4* tcp_unit_ptr(const uint4* base, int unit) {
-  unsigned long long a;
-  asm("mad.wide.u32 %0, %1, 16, %2;" : "=l"(a) : "r"((unsigned int)unit), "l"((unsigned long long)base));
-  return reinterpret_cast<const uint4*>(a);
-}
-
-// One producer thread's part of a tile: for every used offset the group's stages (alternate stages of the global counter
-// `it`), 8 rows x 16 bytes per stage.  CH = channel slices per offset (cin / 64) when known at compile time, 0 = `chunks`.
-// Per row and offset: shared load, clamp, address; per row and stage: sign test + cp.async.
-template <int S, int STAGE_BYTES, int CH>
-__device__ __forceinline__ void tcp_produce(unsigned int kmask, int chunks, int group, const int* nb0, const uint4* in_thr,
-                                            uint32_t a_dst0, uint64_t* full_bar, uint64_t* empty_bar, int& it) {
-  const int nch = CH > 0 ? CH : chunks;
-  for (unsigned int m = kmask; m != 0u; m &= m - 1u) {
-    const int k = __ffs((int)m) - 1;
-    if (nch == 1 && (it & 1) != group) {  // the other group's offset
-      ++it;
-      continue;
-    }
-    const int* nb = nb0 + k * TC_BM;
-    int r[TC_BM / 16];
-    const uint4* src[TC_BM / 16];
-#pragma unroll
-    for (int p = 0; p < TC_BM / 16; ++p) r[p] = nb[p * 16];
-#pragma unroll
-    for (int p = 0; p < TC_BM / 16; ++p) src[p] = tcp_unit_ptr(in_thr, max(r[p], 0));
-#pragma unroll(CH > 0 ? CH : 1)
-    for (int c = 0; c < nch; ++c, ++it) {
-      if ((it & 1) != group) continue;
-      const int s = it % S;
-      mbar_wait(&empty_bar[s], ((uint32_t)(it / S) & 1u) ^ 1u);
-      const uint32_t a_dst = a_dst0 + s * STAGE_BYTES;
-#pragma unroll
-      for (int p = 0; p < TC_BM / 16; ++p) cp_async16(a_dst + p * 2048, src[p] + c * 8, r[p] >= 0 ? 16u : 0u);
-      cp_async_arrive_noinc(&full_bar[s]);
-    }
-  }
-}
-
-template <int BN, int ST>
+// EPI == 1 (BN == 32): the fused head GEMM, whose epilogue writes the head outputs (TcHeadEpi) instead of `out`.
+// nbr == nullptr: identity map (dense GEMM over consecutive rows: generative transposes, heads), one stage per 64 channels.
+template <int BN, int ST, int EPI = 0>
 __global__ void __launch_bounds__(TCP_THREADS, 2)
 k_conv_tcp(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __restrict__ in, const int* __restrict__ nbr,
            int ld, const unsigned int* __restrict__ tile_mask, const int* __restrict__ out_rows, int n_out, int n_tiles,
            int cin, int cout, int kvol, const float* __restrict__ bias, const float* __restrict__ scale,
            const float* __restrict__ shift, const __nv_bfloat16* __restrict__ residual, int act, int ch_mod,
-           __nv_bfloat16* __restrict__ out) {
+           __nv_bfloat16* __restrict__ out, const TcHeadEpi hp) {
   using Cfg = TcpCfg<BN, ST>;
   constexpr int S = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
@@ -177,6 +138,7 @@ k_conv_tcp(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __res
   const int col0 = blockIdx.y * BN;
   const int chunks = cin / TC_BK;
   const unsigned int kvalid = (1u << kvol) - 1u;
+  const bool dense = nbr == nullptr;   // every tile has the one offset of the identity map
   const bool rev = out_rows != nullptr;   // sorted tables put the tiles with the most offsets last: walk them first
   const int step = gridDim.x;
 
@@ -214,7 +176,7 @@ k_conv_tcp(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __res
   }
 
   int t = tcp_tile(0, blockIdx.x, step, n_tiles, rev);   // (every CTA has one: the grid is at most n_tiles wide)
-  unsigned int kmask = t >= 0 ? (__ldg(tile_mask + t) & kvalid) : 0u;
+  unsigned int kmask = t >= 0 ? (dense ? 1u : (__ldg(tile_mask + t) & kvalid)) : 0u;
 
   if (warp < 8) {
     // ===================== producers: neighbour rows of the tile, then cp.async gathers ===================
@@ -231,10 +193,12 @@ k_conv_tcp(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __res
     for (int i = 0; t >= 0; ++i) {
       const int row0 = t * TC_BM;
       const int tn = tcp_tile(i + 1, blockIdx.x, step, n_tiles, rev);
-      const unsigned int knext = tn >= 0 ? (__ldg(tile_mask + tn) & kvalid) : 0u;
+      const unsigned int knext = tn >= 0 ? (dense ? 1u : (__ldg(tile_mask + tn) & kvalid)) : 0u;
       const long long t_s0 = TCP_CLK();
       tcp_bar_producers();  // every producer has finished with the previous tile's rows
-      {
+      if (dense) {
+        if (tid < TC_BM) s_nbr[tid] = (row0 + tid < n_out) ? (row0 + tid) * row_units : -1;
+      } else {
         const int r = tid & (TC_BM - 1), kh = tid >> 7;   // offsets kh, kh + 2, ...
 #pragma unroll
         for (int k0 = 0; k0 < 28; k0 += 14) {
@@ -254,11 +218,11 @@ k_conv_tcp(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __res
       tcp_bar_producers();
       t_ps += TCP_CLK() - t_s0;
       if (chunks == 1)
-        tcp_produce<S, Cfg::STAGE_BYTES, 1>(kmask, 1, group, s_nbr + rsub, in_thr, smem_base + dst_off, full_bar, empty_bar, it);
+        tc_produce<S, Cfg::STAGE_BYTES, 1>(kmask, 1, group, s_nbr + rsub, in_thr, smem_base + dst_off, full_bar, empty_bar, it);
       else if (chunks == 2)
-        tcp_produce<S, Cfg::STAGE_BYTES, 2>(kmask, 2, group, s_nbr + rsub, in_thr, smem_base + dst_off, full_bar, empty_bar, it);
+        tc_produce<S, Cfg::STAGE_BYTES, 2>(kmask, 2, group, s_nbr + rsub, in_thr, smem_base + dst_off, full_bar, empty_bar, it);
       else
-        tcp_produce<S, Cfg::STAGE_BYTES, 0>(kmask, chunks, group, s_nbr + rsub, in_thr, smem_base + dst_off, full_bar, empty_bar,
+        tc_produce<S, Cfg::STAGE_BYTES, 0>(kmask, chunks, group, s_nbr + rsub, in_thr, smem_base + dst_off, full_bar, empty_bar,
                                             it);
       kmask = knext;
       t = tn;
@@ -274,7 +238,7 @@ k_conv_tcp(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __res
     long long t_mw = 0, t_mi = 0, t_ma = 0;
     for (int j = 0; t >= 0; ++j) {
       const int tn = tcp_tile(j + 1, blockIdx.x, step, n_tiles, rev);
-      const unsigned int knext = tn >= 0 ? (__ldg(tile_mask + tn) & kvalid) : 0u;
+      const unsigned int knext = tn >= 0 ? (dense ? 1u : (__ldg(tile_mask + tn) & kvalid)) : 0u;
       const int nstage = __popc(kmask) * chunks;
       const int b = j & 1;
       const long long t_a0 = TCP_CLK();
@@ -326,7 +290,7 @@ k_conv_tcp(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __res
     uint32_t phase = 0;
     for (int i = 0; t >= 0; ++i) {
       const int tn = tcp_tile(i + 1, blockIdx.x, step, n_tiles, rev);
-      const unsigned int knext = tn >= 0 ? (__ldg(tile_mask + tn) & kvalid) : 0u;
+      const unsigned int knext = tn >= 0 ? (dense ? 1u : (__ldg(tile_mask + tn) & kvalid)) : 0u;
       for (int k = 0; k < kvol; ++k) {
         if (!((kmask >> k) & 1u)) continue;
         for (int c = 0; c < chunks; ++c) {
@@ -350,7 +314,7 @@ k_conv_tcp(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __res
     const int q = warp & 3;
     for (int j = 0; t >= 0; ++j) {
       const int tn = tcp_tile(j + 1, blockIdx.x, step, n_tiles, rev);
-      const unsigned int knext = tn >= 0 ? (__ldg(tile_mask + tn) & kvalid) : 0u;
+      const unsigned int knext = tn >= 0 ? (dense ? 1u : (__ldg(tile_mask + tn) & kvalid)) : 0u;
       const int row0 = t * TC_BM;
       int o = row0 + q * 32 + lane;
       if (out_rows != nullptr) {
@@ -372,7 +336,16 @@ k_conv_tcp(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __res
 #pragma unroll
           for (int e = 0; e < 32; ++e) v[e] = 0u;
         }
-        if (o < n_out) tcp_store_chunk(v, s_epi, BN, cc, residual, out, (long long)o * cout + col0 + cc, act);
+        if (EPI == 1) {
+          if (o < n_out) {
+            float f[32];
+#pragma unroll
+            for (int e = 0; e < 32; ++e) f[e] = (__uint_as_float(v[e]) + s_epi[e]) * s_epi[BN + e] + s_epi[2 * BN + e];
+            tc_head_row(f, (long long)o, hp);
+          }
+        } else {
+          if (o < n_out) tcp_store_chunk(v, s_epi, BN, cc, residual, out, (long long)o * cout + col0 + cc, act);
+        }
       }
       tc_fence_before();
       mbar_arrive(&acc_empty[b]);
@@ -408,7 +381,7 @@ static int launch_tcp(const void* in, const void* wt, const int* nbr, long long 
                       const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
                       int ctas, cudaStream_t st) {
   using Cfg = TcpCfg<BN, ST>;
-  auto kern = k_conv_tcp<BN, ST>;
+  auto kern = k_conv_tcp<BN, ST, 0>;
   static unsigned long long configured = 0;  // per template instance, one bit per device
   if (int rc0 = b2_optin_smem((const void*)kern, Cfg::SMEM, &configured)) return rc0;
   CUtensorMap map_b;
@@ -419,7 +392,7 @@ static int launch_tcp(const void* in, const void* wt, const int* nbr, long long 
   dim3 grid((unsigned)std::min(n_tiles, std::max(1, ctas / gy)), (unsigned)gy);
   kern<<<grid, TCP_THREADS, Cfg::SMEM, st>>>(map_b, (const __nv_bfloat16*)in, nbr, (int)ld, tile_mask, out_rows, (int)n_out,
                                              n_tiles, cin, cout, kvol, bias, scale, shift, (const __nv_bfloat16*)residual, act,
-                                             ch_mod, (__nv_bfloat16*)out);
+                                             ch_mod, (__nv_bfloat16*)out, TcHeadEpi());
   B2_LAUNCH_CHECK();
   return B2_OK;
 }
@@ -434,7 +407,8 @@ int b2_conv_tcp_dispatch(const void* in, const void* wt, const int* nbr, long lo
   *taken = 0;
   static const int enabled = getenv("B2_TC_PERSIST") ? atoi(getenv("B2_TC_PERSIST")) : 1;
   static const int min_env = getenv("B2_TC_PERSIST_MIN_TILES") ? atoi(getenv("B2_TC_PERSIST_MIN_TILES")) : 0;
-  if (!enabled || nbr == nullptr || (cout != 64 && cout != 128)) return B2_OK;
+  const bool dense = nbr == nullptr;   // identity map: any multiple of 128 output columns (column tiles on grid.y)
+  if (!enabled || (dense ? (cout % 128 != 0 || kvol != 1) : (cout != 64 && cout != 128))) return B2_OK;
   static int sms[64] = {0};
   int dev = 0;
   B2_CUDA(cudaGetDevice(&dev));
@@ -442,7 +416,7 @@ int b2_conv_tcp_dispatch(const void* in, const void* wt, const int* nbr, long lo
   if (sms[dev] == 0) B2_CUDA(cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev));
   static const int ctas_env = getenv("B2_TC_PERSIST_CTAS") ? atoi(getenv("B2_TC_PERSIST_CTAS")) : 0;
   const int ctas = ctas_env > 0 ? ctas_env : 2 * sms[dev];
-  const long long tiles = b2_div_up(n_out, TC_BM);
+  const long long tiles = b2_div_up(n_out, TC_BM) * (dense ? cout / 128 : 1);
   if (tiles < (min_env > 0 ? min_env : 4 * sms[dev])) return B2_OK;
   *taken = 1;
   if (cout == 64)
@@ -450,4 +424,33 @@ int b2_conv_tcp_dispatch(const void* in, const void* wt, const int* nbr, long lo
                              ch_mod, out, ctas, st);
   return launch_tcp<128, 3>(in, wt, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, shift, residual, act,
                             ch_mod, out, ctas, st);
+}
+
+// The fused head GEMM (b2_head_fused) on the persistent kernel: 32 head columns, epilogue = head post-processing.
+int b2_head_tcp_dispatch(const void* in, long long n, const void* wt, int cin, const float* bias, const TcHeadEpi& hp,
+                         cudaStream_t st, int* taken) {
+  *taken = 0;
+  static const int enabled = getenv("B2_TC_PERSIST") ? atoi(getenv("B2_TC_PERSIST")) : 1;
+  static const int min_env = getenv("B2_TC_PERSIST_MIN_TILES") ? atoi(getenv("B2_TC_PERSIST_MIN_TILES")) : 0;
+  if (!enabled) return B2_OK;
+  static int sms[64] = {0};
+  int dev = 0;
+  B2_CUDA(cudaGetDevice(&dev));
+  if (dev >= 64) return B2_OK;
+  if (sms[dev] == 0) B2_CUDA(cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev));
+  const int n_tiles = (int)b2_div_up(n, TC_BM);
+  if (n_tiles < (min_env > 0 ? min_env : 4 * sms[dev])) return B2_OK;
+  *taken = 1;
+  using Cfg = TcpCfg<32, 4>;
+  auto kern = k_conv_tcp<32, 4, 1>;
+  static unsigned long long configured = 0;
+  if (int rc0 = b2_optin_smem((const void*)kern, Cfg::SMEM, &configured)) return rc0;
+  CUtensorMap map_b;
+  const int rc = b2_make_bf16_map(&map_b, wt, 32, cin, 32);
+  if (rc) return rc;
+  kern<<<dim3((unsigned)std::min(n_tiles, 2 * sms[dev]), 1), TCP_THREADS, Cfg::SMEM, st>>>(
+      map_b, (const __nv_bfloat16*)in, nullptr, 0, nullptr, nullptr, (int)n, n_tiles, cin, 32, 1, bias, nullptr, nullptr,
+      nullptr, B2_ACT_NONE, 0, nullptr, hp);
+  B2_LAUNCH_CHECK();
+  return B2_OK;
 }

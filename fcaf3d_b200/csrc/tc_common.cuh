@@ -103,6 +103,83 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
 }
 
 
+// outputs of the fused head epilogue (EPI == 1 of k_conv_tc / k_conv_tcp; see conv_tc.cu)
+struct TcHeadEpi {
+  float* centerness = nullptr;
+  float* bbox_pred = nullptr;
+  float* cls = nullptr;
+  float* prune_score = nullptr;
+  float* max_score = nullptr;
+  const float* scale = nullptr;
+  int n_reg = 0, n_cls = 0;
+};
+
+// Head epilogue of one row (forward_single, fcaf3d_neck_with_head.py:256-279, :237-238): f = the row's 32 head columns after
+// bias / scale / shift.  Same expressions as k_head_post_tiled, hence bit-identical values.
+__device__ __forceinline__ void tc_head_row(const float* f, long long o, const TcHeadEpi& hp) {
+  const float hscale = hp.scale ? __ldg(hp.scale) : 1.f;
+  const float ctr = f[0];
+  hp.centerness[o] = ctr;
+  const float sc = 1.f / (1.f + expf(-ctr));
+  float mlogit = -INFINITY, mscore = -INFINITY;
+  const int c0 = 1 + hp.n_reg, c1 = c0 + hp.n_cls;
+#pragma unroll
+  for (int j = 1; j < 32; ++j) {
+    if (j < c0) {
+      const int k = j - 1;
+      hp.bbox_pred[o * hp.n_reg + k] = (k < 6) ? expf(hscale * f[j]) : f[j];
+    } else if (j < c1) {
+      mlogit = fmaxf(mlogit, f[j]);
+      mscore = fmaxf(mscore, (1.f / (1.f + expf(-f[j]))) * sc);
+      hp.cls[o * hp.n_cls + (j - c0)] = f[j];
+    }
+  }
+  hp.prune_score[o] = mlogit;
+  if (hp.max_score) hp.max_score[o] = mscore;
+}
+
+// ---- producer side of the gathers (shared by k_conv_tc and k_conv_tcp) ------------------------------------------
+// 64-bit address of 16-byte unit `unit` behind `base` in one instruction (kept opaque so that the compiler holds the eight
+// row addresses of an offset in registers instead of rebuilding them for every stage)
+__device__ __forceinline__ const uint4* tc_unit_ptr(const uint4* base, int unit) {
+  unsigned long long a;
+  asm("mad.wide.u32 %0, %1, 16, %2;" : "=l"(a) : "r"((unsigned int)unit), "l"((unsigned long long)base));
+  return reinterpret_cast<const uint4*>(a);
+}
+
+// One producer thread's part of a tile: for every used offset the group's stages (alternate stages of the global counter
+// `it`), 8 rows x 16 bytes per stage.  CH = channel slices per offset (cin / 64) when known at compile time, 0 = `chunks`.
+// Per row and offset: shared load, clamp, address; per row and stage: sign test + cp.async.
+template <int S, int STAGE_BYTES, int CH>
+__device__ __forceinline__ void tc_produce(unsigned int kmask, int chunks, int group, const int* nb0, const uint4* in_thr,
+                                            uint32_t a_dst0, uint64_t* full_bar, uint64_t* empty_bar, int& it) {
+  const int nch = CH > 0 ? CH : chunks;
+  for (unsigned int m = kmask; m != 0u; m &= m - 1u) {
+    const int k = __ffs((int)m) - 1;
+    if (nch == 1 && (it & 1) != group) {  // the other group's offset
+      ++it;
+      continue;
+    }
+    const int* nb = nb0 + k * TC_BM;
+    int r[TC_BM / 16];
+    const uint4* src[TC_BM / 16];
+#pragma unroll
+    for (int p = 0; p < TC_BM / 16; ++p) r[p] = nb[p * 16];
+#pragma unroll
+    for (int p = 0; p < TC_BM / 16; ++p) src[p] = tc_unit_ptr(in_thr, max(r[p], 0));
+#pragma unroll(CH > 0 ? CH : 1)
+    for (int c = 0; c < nch; ++c, ++it) {
+      if ((it & 1) != group) continue;
+      const int s = it % S;
+      mbar_wait(&empty_bar[s], ((uint32_t)(it / S) & 1u) ^ 1u);
+      const uint32_t a_dst = a_dst0 + s * STAGE_BYTES;
+#pragma unroll
+      for (int p = 0; p < TC_BM / 16; ++p) cp_async16(a_dst + p * 2048, src[p] + c * 8, r[p] >= 0 ? 16u : 0u);
+      cp_async_arrive_noinc(&full_bar[s]);
+    }
+  }
+}
+
 // ---- TMA (cp.async.bulk.tensor) helpers --------------------------------------------------------------------
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
@@ -130,6 +207,8 @@ int b2_make_tf32_map(CUtensorMap* map, const void* base, long long rows, int col
 int b2_conv_tcp_dispatch(const void* in, const void* wt, const int* nbr, long long ld, const unsigned int* tile_mask,
                          const int* out_rows, long long n_out, int cin, int cout, int kvol, const float* bias,
                          const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
+                         cudaStream_t st, int* taken);
+int b2_head_tcp_dispatch(const void* in, long long n, const void* wt, int cin, const float* bias, const TcHeadEpi& hp,
                          cudaStream_t st, int* taken);
 // host: opt-in of one kernel to `bytes` of dynamic shared memory on the CURRENT device, once per device
 int b2_optin_smem(const void* func, int bytes, unsigned long long* done);
