@@ -408,6 +408,8 @@ def bench_train(ctx, args, workload, dtype_name, steps, warmup, brief=False):
             last = float(pending[0][0])
         return last
 
+    host_ms = [None]
+
     def timed(e2e, k, warm, nosync=False):
         guard = module.no_sync() if (nosync and world > 1) else contextlib.nullcontext()
         with guard:
@@ -417,7 +419,9 @@ def bench_train(ctx, args, workload, dtype_name, steps, warmup, brief=False):
             torch.cuda.synchronize()
             s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             s.record()
+            t0 = time.perf_counter()
             out = run_steps(e2e, k)
+            host_ms[0] = (time.perf_counter() - t0) * 1e3 / k   # host time to enqueue a step (incl. its blocking reads)
             e.record()
             torch.cuda.synchronize()
         return ctx.max_over_ranks(s.elapsed_time(e)) / k, out
@@ -436,6 +440,7 @@ def bench_train(ctx, args, workload, dtype_name, steps, warmup, brief=False):
     torch.cuda.synchronize()
     launches0 = lib.b2_launch_count()
     ms, _ = timed(False, steps, 0)
+    host_enqueue_ms = host_ms[0]
     launches = lib.b2_launch_count() - launches0   # kernels of libfcaf3d_b200.so only (torch's own are not counted)
     ms_e2e, loss = timed(True, max(2, steps // 2), 1)
     n = len(scenes)
@@ -444,7 +449,7 @@ def bench_train(ctx, args, workload, dtype_name, steps, warmup, brief=False):
            "workload": desc.replace(" incl. axis-aligned 3D(BEV) NMS", "").replace(" incl. rotated BEV NMS", "").replace(
                "inference", "training step (fwd+bwd+allreduce+clip+AdamW)"),
            "value": world * n * 1000.0 / ms, "unit": "scenes/s", "ms_per_step": ms, "dtype": dtype_name,
-           "scenes_per_gpu": n, "gpu_launches": launches,
+           "scenes_per_gpu": n, "gpu_launches": launches, "host_ms_per_step": host_enqueue_ms,
            "loss": "focal + centerness BCE + %s IoU" % ("rotated" if det.neck_with_head.loss_bbox.with_yaw else "axis-aligned"),
            "optimizer": "AdamW lr 1e-3 wd 1e-4, clip 10", "last_loss": loss,
            "e2e": {"value": world * n * 1000.0 / ms_e2e, "unit": "scenes/s",

@@ -9,8 +9,11 @@
 // Rows are read 8 channels (16 or 32 bytes) per thread; C % 8 == 0, C <= 2048.  HBM-bound: forward 2 reads + 1 write of
 // [N, C], backward 6 reads + 1..2 writes.
 #include "common.cuh"
+#include <algorithm>
 
 #define BN_PARTS 592  // partial CTAs = 4 per SM
+// at least ~128 rows per partial CTA: small layers (the deep levels) otherwise spend their time on the partial sums' traffic
+static inline int bn_parts(long long n) { return (int)std::max(1ll, std::min((long long)BN_PARTS, n / 128)); }
 
 template <typename T>
 __device__ __forceinline__ void load8(const T* p, float v[8]);
@@ -79,7 +82,38 @@ __global__ void __launch_bounds__(256) k_bn_partial(const T* __restrict__ x, con
         i8[i] = invstd[tl * 8 + i];
       }
     }
-    for (long long r = a + rl; r < b; r += rows_par) {
+    // U rows per trip with all their loads issued first (one row per trip left ~2 MB in flight on the whole GPU: latency
+    // bound at ~40 % of HBM); the sums are still accumulated row by row in the same order
+    constexpr int U = MODE == 0 ? 4 : 1;   // (two rows per trip in the backward sums cost occupancy: 1.26 -> 1.45 ms per step)
+    long long r = a + rl;
+    for (; r + (long long)(U - 1) * rows_par < b; r += (long long)U * rows_par) {
+      float v[U][8], g[U][8], o[U][8];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long off = (r + (long long)u * rows_par) * c + tl * 8;
+        load8<T>(x + off, v[u]);
+        if (MODE == 1) {
+          load8<T>(dy + off, g[u]);
+          if (act != 0) load8<T>(y + off, o[u]);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          if (MODE == 0) {
+            const float d = v[u][i] - k8[i];
+            s1[i] += d;
+            s2[i] += d * d;
+          } else {
+            const float dz = act != 0 ? g[u][i] * act_grad_from_output(o[u][i], act) : g[u][i];
+            s1[i] += dz;
+            s2[i] += dz * ((v[u][i] - m8[i]) * i8[i]);
+          }
+        }
+      }
+    }
+    for (; r < b; r += rows_par) {
       float v[8];
       load8<T>(x + r * c + tl * 8, v);
       if (MODE == 0) {
@@ -192,33 +226,54 @@ __global__ void __launch_bounds__(256) k_bn_bwd_finalize(const float* __restrict
   sums[c + ch] = (float)s2;  // d weight
 }
 
-template <typename T>
+template <typename T, int VPT>
 __global__ void __launch_bounds__(256) k_bn_bwd_apply(const T* __restrict__ x, const T* __restrict__ dy,
                                                       const T* __restrict__ y, long long n, int c, int act,
                                                       const float* __restrict__ mean, const float* __restrict__ invstd,
                                                       const float* __restrict__ weight, const float* __restrict__ sums,
                                                       T* __restrict__ dx, T* __restrict__ dres) {
+  // VPT vectors of 8 channels per thread, 256 vectors apart (coalesced per pass; the same channels when 256 % lanes == 0,
+  // which the launcher guarantees for VPT > 1), all loads issued before the arithmetic
   const int lanes = c >> 3;
-  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= n * lanes) return;
-  const long long r = t / lanes;
-  const int ch0 = (int)(t - r * lanes) * 8;
-  float v[8], g[8], o[8], dz[8], out[8];
-  load8<T>(x + r * c + ch0, v);
-  load8<T>(dy + r * c + ch0, g);
-  if (act != 0) load8<T>(y + r * c + ch0, o);
+  const long long total = n * lanes;
+  const long long t0 = (long long)blockIdx.x * (256 * VPT) + threadIdx.x;
+  if (t0 >= total) return;
+  const int ch0 = (int)(t0 % lanes) * 8;
+  float v[VPT][8], g[VPT][8], o[VPT][8];
+#pragma unroll
+  for (int u = 0; u < VPT; ++u) {
+    const long long t = t0 + u * 256;
+    if (t < total) {
+      load8<T>(x + t * 8, v[u]);
+      load8<T>(dy + t * 8, g[u]);
+      if (act != 0) load8<T>(y + t * 8, o[u]);
+    }
+  }
   const float inv_n = 1.f / (float)n;
+  float is8[8], mean8[8], w8[8], sb8[8], sw8[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int ch = ch0 + i;
-    dz[i] = act != 0 ? g[i] * act_grad_from_output(o[i], act) : g[i];
-    const float is = invstd[ch];
-    const float xhat = (v[i] - mean[ch]) * is;
-    const float w = weight ? weight[ch] : 1.f;
-    out[i] = (w * is) * (dz[i] - sums[ch] * inv_n - xhat * (sums[c + ch] * inv_n));
+    is8[i] = invstd[ch];
+    mean8[i] = mean[ch];
+    w8[i] = weight ? weight[ch] : 1.f;
+    sb8[i] = sums[ch] * inv_n;
+    sw8[i] = sums[c + ch] * inv_n;
   }
-  store8<T>(dx + r * c + ch0, out);
-  if (dres) store8<T>(dres + r * c + ch0, dz);
+#pragma unroll
+  for (int u = 0; u < VPT; ++u) {
+    const long long t = t0 + u * 256;
+    if (t >= total) break;
+    float dz[8], out[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      dz[i] = act != 0 ? g[u][i] * act_grad_from_output(o[u][i], act) : g[u][i];
+      const float xhat = (v[u][i] - mean8[i]) * is8[i];
+      out[i] = (w8[i] * is8[i]) * (dz[i] - sb8[i] - xhat * sw8[i]);
+    }
+    store8<T>(dx + t * 8, out);
+    if (dres) store8<T>(dres + t * 8, dz);
+  }
 }
 
 extern "C" {
@@ -239,7 +294,7 @@ int b2_bn_train_stats(const void* x, int dtype, long long n, int c, const float*
   }
   cudaStream_t st = (cudaStream_t)stream;
   float* partial = (float*)ws;
-  const int parts = (int)(n < BN_PARTS ? n : BN_PARTS);
+  const int parts = bn_parts(n);
   if (dtype == 0) {
     k_bn_partial<float, 0><<<parts, 256, 0, st>>>((const float*)x, nullptr, nullptr, n, c, 0, nullptr, nullptr, partial);
     k_bn_finalize<float><<<b2_div_up(c, 8), 256, 0, st>>>(partial, parts, n, c, (const float*)x, weight, bias,
@@ -270,21 +325,28 @@ int b2_bn_act_bwd(const void* x, const void* dy, const void* y, int dtype, long 
   }
   cudaStream_t st = (cudaStream_t)stream;
   float* partial = (float*)ws;
-  const int parts = (int)(n < BN_PARTS ? n : BN_PARTS);
+  const int parts = bn_parts(n);
   const int G = b2_div_up(n * (c / 8), 256);
+  const bool vpt2 = 256 % (c / 8) == 0;   // two vectors per thread share their channels
+  const int G2 = b2_div_up(n * (c / 8), 512);
   if (dtype == 0) {
     k_bn_partial<float, 1><<<parts, 256, 0, st>>>((const float*)x, (const float*)dy, (const float*)y, n, c, act, mean,
                                                   invstd, partial);
     k_bn_bwd_finalize<<<b2_div_up(c, 8), 256, 0, st>>>(partial, parts, c, sums);
-    k_bn_bwd_apply<float><<<G, 256, 0, st>>>((const float*)x, (const float*)dy, (const float*)y, n, c, act, mean, invstd,
-                                             weight, sums, (float*)dx, (float*)dres);
+    k_bn_bwd_apply<float, 1><<<G, 256, 0, st>>>((const float*)x, (const float*)dy, (const float*)y, n, c, act, mean, invstd,
+                                                weight, sums, (float*)dx, (float*)dres);
   } else {
     k_bn_partial<__nv_bfloat16, 1><<<parts, 256, 0, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)dy,
                                                          (const __nv_bfloat16*)y, n, c, act, mean, invstd, partial);
     k_bn_bwd_finalize<<<b2_div_up(c, 8), 256, 0, st>>>(partial, parts, c, sums);
-    k_bn_bwd_apply<__nv_bfloat16><<<G, 256, 0, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)dy,
-                                                     (const __nv_bfloat16*)y, n, c, act, mean, invstd, weight, sums,
-                                                     (__nv_bfloat16*)dx, (__nv_bfloat16*)dres);
+    if (vpt2)
+      k_bn_bwd_apply<__nv_bfloat16, 2><<<G2, 256, 0, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)dy,
+                                                          (const __nv_bfloat16*)y, n, c, act, mean, invstd, weight, sums,
+                                                          (__nv_bfloat16*)dx, (__nv_bfloat16*)dres);
+    else
+      k_bn_bwd_apply<__nv_bfloat16, 1><<<G, 256, 0, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)dy,
+                                                          (const __nv_bfloat16*)y, n, c, act, mean, invstd, weight, sums,
+                                                          (__nv_bfloat16*)dx, (__nv_bfloat16*)dres);
   }
   b2_count_launches(2);
   B2_LAUNCH_CHECK();

@@ -397,6 +397,14 @@ static int launch_tcp(const void* in, const void* wt, const int* nbr, long long 
   return B2_OK;
 }
 
+// 0 = by size (default), 1 = never, 2 = whenever the layer shape allows it (tests compare the two kernels bit for bit)
+static int g_persist_mode = 0;
+extern "C" int b2_tc_persist_mode(int mode) {
+  const int old = g_persist_mode;
+  if (mode >= 0 && mode <= 2) g_persist_mode = mode;
+  return old;
+}
+
 // Called by b2_conv_tc for bf16 -> bf16 layers with a neighbour table.  *taken = 0: not a layer for the persistent kernel
 // (few tiles, or more than 128 output columns) - the caller goes on to k_conv_tc.  B2_TC_PERSIST=0 switches it off,
 // B2_TC_PERSIST_MIN_TILES (default: 2 resident CTAs x SMs x 2) is the smallest number of row tiles it takes.
@@ -408,7 +416,8 @@ int b2_conv_tcp_dispatch(const void* in, const void* wt, const int* nbr, long lo
   static const int enabled = getenv("B2_TC_PERSIST") ? atoi(getenv("B2_TC_PERSIST")) : 1;
   static const int min_env = getenv("B2_TC_PERSIST_MIN_TILES") ? atoi(getenv("B2_TC_PERSIST_MIN_TILES")) : 0;
   const bool dense = nbr == nullptr;   // identity map: any multiple of 128 output columns (column tiles on grid.y)
-  if (!enabled || (dense ? (cout % 128 != 0 || kvol != 1) : (cout != 64 && cout != 128))) return B2_OK;
+  if (!enabled || g_persist_mode == 1 || (dense ? (cout % 128 != 0 || kvol != 1) : (cout != 64 && cout != 128)))
+    return B2_OK;
   static int sms[64] = {0};
   int dev = 0;
   B2_CUDA(cudaGetDevice(&dev));
@@ -417,7 +426,7 @@ int b2_conv_tcp_dispatch(const void* in, const void* wt, const int* nbr, long lo
   static const int ctas_env = getenv("B2_TC_PERSIST_CTAS") ? atoi(getenv("B2_TC_PERSIST_CTAS")) : 0;
   const int ctas = ctas_env > 0 ? ctas_env : 2 * sms[dev];
   const long long tiles = b2_div_up(n_out, TC_BM) * (dense ? cout / 128 : 1);
-  if (tiles < (min_env > 0 ? min_env : 4 * sms[dev])) return B2_OK;
+  if (g_persist_mode != 2 && tiles < (min_env > 0 ? min_env : 4 * sms[dev])) return B2_OK;
   *taken = 1;
   if (cout == 64)
     return launch_tcp<64, 4>(in, wt, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, shift, residual, act,
@@ -432,14 +441,14 @@ int b2_head_tcp_dispatch(const void* in, long long n, const void* wt, int cin, c
   *taken = 0;
   static const int enabled = getenv("B2_TC_PERSIST") ? atoi(getenv("B2_TC_PERSIST")) : 1;
   static const int min_env = getenv("B2_TC_PERSIST_MIN_TILES") ? atoi(getenv("B2_TC_PERSIST_MIN_TILES")) : 0;
-  if (!enabled) return B2_OK;
+  if (!enabled || g_persist_mode == 1) return B2_OK;
   static int sms[64] = {0};
   int dev = 0;
   B2_CUDA(cudaGetDevice(&dev));
   if (dev >= 64) return B2_OK;
   if (sms[dev] == 0) B2_CUDA(cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev));
   const int n_tiles = (int)b2_div_up(n, TC_BM);
-  if (n_tiles < (min_env > 0 ? min_env : 4 * sms[dev])) return B2_OK;
+  if (g_persist_mode != 2 && n_tiles < (min_env > 0 ? min_env : 4 * sms[dev])) return B2_OK;
   *taken = 1;
   using Cfg = TcpCfg<32, 4>;
   auto kern = k_conv_tcp<32, 4, 1>;

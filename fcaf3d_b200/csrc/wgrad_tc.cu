@@ -201,37 +201,41 @@ k_wgrad_tc(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict
     }
     tc_fence_before();
   } else {
-    // ===================== MMA issuer (one thread) ==========================================
-    if (lane == 0) {
+    // ===================== MMA issuer (one elected thread; the warp waits together) ==========
+    {
       // bf16 x bf16 -> f32, A and B both MN-major (bits 15, 16), N = BN, M = 128
       constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) |
                                  ((uint32_t)(BN >> 3) << 17) | ((128u >> 4) << 24);
       // descriptors differ from stage to stage only in the 14-bit start-address field: add (byte offset >> 4)
       const uint64_t da0 = umma_desc_mn_sw128(smem_base, WG_SUB_BYTES);
       const uint64_t db0 = umma_desc_mn_sw128(smem_base + Cfg::A_BYTES, WG_SUB_BYTES);
+      const bool leader = elect_one();  // (tcgen05.mma under `lane == 0` compiles to a per-lane serialisation loop)
       int s = 0;
       uint32_t ph = 0;
       for (int it = 0; it < nstage; ++it) {
         mbar_wait(&full_bar[s], ph);
         fence_async_smem();  // cp.async wrote through the generic proxy, tcgen05.mma reads through the async proxy
         tc_fence_after();
-        const uint64_t so = (uint64_t)((s * Cfg::STAGE_BYTES) >> 4);
+        if (leader) {
+          const uint64_t so = (uint64_t)((s * Cfg::STAGE_BYTES) >> 4);
 #pragma unroll
-        for (int kk = 0; kk < WG_KR / 16; ++kk) {
-          if (kk == 1 && (dbg & 8)) break;
-          const uint64_t db = db0 + so + (uint64_t)((kk * 2048) >> 4);
-          for (int j = 0; j < ((dbg & 1) ? 0 : nmt); ++j) {
-            const uint64_t da = da0 + so + (uint64_t)((j * 2 * WG_SUB_BYTES + kk * 2048) >> 4);
-            umma_bf16(tmem_base + (uint32_t)(j * BN), da, db, idesc, (it > 0 || kk > 0) ? 1u : 0u);
+          for (int kk = 0; kk < WG_KR / 16; ++kk) {
+            if (kk == 1 && (dbg & 8)) break;
+            const uint64_t db = db0 + so + (uint64_t)((kk * 2048) >> 4);
+            for (int j = 0; j < ((dbg & 1) ? 0 : nmt); ++j) {
+              const uint64_t da = da0 + so + (uint64_t)((j * 2 * WG_SUB_BYTES + kk * 2048) >> 4);
+              umma_bf16(tmem_base + (uint32_t)(j * BN), da, db, idesc, (it > 0 || kk > 0) ? 1u : 0u);
+            }
           }
+          umma_commit(&empty_bar[s]);  // frees the smem stage once these MMAs have read it
         }
-        umma_commit(&empty_bar[s]);  // frees the smem stage once these MMAs have read it
+        __syncwarp();
         if (++s == S) {
           s = 0;
           ph ^= 1u;
         }
       }
-      umma_commit(accum_bar);
+      if (leader) umma_commit(accum_bar);
     }
     __syncwarp();
   }

@@ -123,6 +123,10 @@ int b2_conv_tc(const void* in_bf16, long long n_in, const void* wt_bf16, const i
                const unsigned int* tile_mask, const int* out_rows,
                long long n_out, int cin, int cout, int kvol, const float* bias, const float* scale, const float* shift,
                const void* residual, int act, int ch_mod, void* out, int out_dtype, void* stream);
+/* b2_conv_tc / b2_head_fused run layers with many row tiles (>= 4 x SMs) on a persistent variant of the kernel
+ * (csrc/conv_tcp.cu: CTAs stay resident and walk tiles, results bit-identical).  mode 0 = by size (default), 1 = never,
+ * 2 = whenever the layer shape allows it; returns the previous mode (any other value only queries). */
+int b2_tc_persist_mode(int mode);
 /* The same kernel on fp32 rows and fp32 weights wt_f32 [kvol, cout, cin], read by the tensor cores as TF32 operands
  * (products of 10-bit mantissas, fp32 accumulation), fp32 output: the fp32-storage mode of the tensor-core path (ME's own
  * arithmetic is fp32 cuBLAS SGEMM; tolerance against it 1e-3 of the output's max, stated in tests/test_conv_gpu.py).

@@ -120,6 +120,54 @@ def test_sparsity_sorted_walk_is_bit_identical(dev, cin, cout, stride, out_dtype
     assert km.sorted is None and torch.equal(y_sorted, y_plain)
 
 
+@pytest.mark.parametrize("cin,cout,stride,dense", [(64, 64, 1, False), (128, 128, 1, False), (64, 128, 2, False),
+                                                   (128, 64, 1, False), (64, 256, 1, True)])
+def test_persistent_kernel_is_bit_identical(dev, cin, cout, stride, dense, monkeypatch):
+    """csrc/conv_tcp.cu (CTAs walk tiles, two TMEM accumulators, epilogue warps one tile behind) against k_conv_tc on
+    the same layer: equal bit for bit, with and without the sparsity-sorted table, fused epilogue + residual, a row count
+    that is not a multiple of 128 and more tiles than resident CTAs (so that CTAs take several tiles); the identity map
+    (generative transposes) with column tiles and ch_mod."""
+    from fcaf3d_b200._lib import lib
+    from util import surface_coords
+    c = torch.from_numpy(surface_coords(60000, 3, seed=5)).to(dev)
+    x0 = ME.SparseTensor(torch.zeros(len(c), 1, device=dev), coordinates=c)
+    cm, key = x0.coordinate_manager, x0.coordinate_map_key
+    okey = key if stride == 1 else cm.stride(key, stride)
+    n_in, n_out = cm.size(key), cm.size(okey)
+    assert n_out > 300 * 128 or stride > 1
+    torch.manual_seed(1)
+    f = torch.randn(n_in, cin, device=dev).to(torch.bfloat16)
+    kvol = 1 if dense else 27
+    w = torch.randn(kvol, cin, cout, device=dev) * 0.05
+    wt = w.transpose(1, 2).contiguous().to(torch.bfloat16)
+    ch = 64 if dense else cout
+    scale, shift = torch.rand(ch, device=dev) + .5, torch.randn(ch, device=dev)
+    res = torch.randn(n_out, cout, device=dev).to(torch.bfloat16)
+    outs = {}
+    for mode in (1, 2):
+        old = lib().b2_tc_persist_mode(mode)
+        try:
+            if dense:
+                outs[mode] = (ops.sparse_conv(f, w, None, n_in, wt_bf16=wt, scale=scale, shift=shift, act=ops.ACT_ELU,
+                                              ch_mod=64, out_dtype=torch.bfloat16),)
+            else:
+                km = cm.kernel_map(key, okey, 3)
+                km.sorted = None
+                kw = dict(wt_bf16=wt, scale=scale, shift=shift, residual=res, act=ops.ACT_RELU, out_dtype=torch.bfloat16)
+                monkeypatch.setattr(ops, "SORT_MIN_ROWS", 0)
+                plain = ops.sparse_conv(f, w, km, n_out, **kw)
+                monkeypatch.setattr(ops, "SORT_MIN_ROWS", 1)
+                monkeypatch.setattr(ops, "SORT_MIN_USES", 1)
+                outs[mode] = (plain, ops.sparse_conv(f, w, km, n_out, **kw))
+                assert km.sorted is not None
+        finally:
+            lib().b2_tc_persist_mode(old)
+    for a, b in zip(outs[1], outs[2]):
+        assert torch.equal(a, b)
+    if not dense:
+        assert torch.equal(outs[2][0], outs[2][1])
+
+
 def test_conv_tcgen05_wide_tiles(dev):
     """cout % 256 == 0 on a map with >= 74 row tiles takes the 256-column tile (one CTA per SM); same checks as above:
     against the CUDA-core kernel on the same bf16-rounded operands (5e-4) with the fused epilogue."""

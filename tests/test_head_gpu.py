@@ -94,3 +94,13 @@ def test_fused_head_equals_gemm_then_head_post(dev, n_reg, n_cls, n):
     want = ops.head_post(h, n_reg, n_cls, scale, want_max_score=True)
     for a, e, name in zip(got, want, ("centerness", "bbox_pred", "cls", "prune", "max_score")):
         assert a.shape == e.shape and torch.equal(a, e), name
+    # the persistent kernel (taken by size for >= 4 x SMs row tiles: the 70001-row case has 547) gives the same bits
+    from fcaf3d_b200._lib import lib
+    for mode in (1, 2):
+        old = lib().b2_tc_persist_mode(mode)
+        try:
+            again = ops.head_fused(x, wt, b, n_reg, n_cls, scale, want_max_score=True)
+        finally:
+            lib().b2_tc_persist_mode(old)
+        for a, e, name in zip(again, want, ("centerness", "bbox_pred", "cls", "prune", "max_score")):
+            assert torch.equal(a, e), (mode, name)
