@@ -151,7 +151,7 @@ def kernel_digest():
     """sha256 of the tcgen05 convolution source the built library came from (ties profiles/conv_tc_traffic.json to it)"""
     import hashlib
     h = hashlib.sha256()
-    for f in ("conv_tc.cu", "tc_common.cuh"):
+    for f in ("conv_tc.cu", "conv_tcp.cu", "tc_common.cuh"):
         h.update(open(os.path.join(ROOT, "fcaf3d_b200", "csrc", f), "rb").read())
     return h.hexdigest()[:16]
 

@@ -121,7 +121,8 @@ def test_sparsity_sorted_walk_is_bit_identical(dev, cin, cout, stride, out_dtype
 
 
 @pytest.mark.parametrize("cin,cout,stride,dense", [(64, 64, 1, False), (128, 128, 1, False), (64, 128, 2, False),
-                                                   (128, 64, 1, False), (64, 256, 1, True)])
+                                                   (128, 64, 1, False), (256, 128, 1, False), (512, 128, 2, False),
+                                                   (64, 256, 1, True), (256, 128, 1, True)])
 def test_persistent_kernel_is_bit_identical(dev, cin, cout, stride, dense, monkeypatch):
     """csrc/conv_tcp.cu (CTAs walk tiles, two TMEM accumulators, epilogue warps one tile behind) against k_conv_tc on
     the same layer: equal bit for bit, with and without the sparsity-sorted table, fused epilogue + residual, a row count

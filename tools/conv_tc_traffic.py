@@ -45,7 +45,7 @@ def main(raw, out_csv, note):
         w.writerows(out)
     n = len(out)
     from bench import kernel_digest       # bench.py refuses a capture taken from another version of the kernel source
-    js = {"kernel": "k_conv_tc (all instantiations)", "kernel_digest": kernel_digest(), "launches": n, "dram_bytes_read": tot["rd"], "dram_bytes_write": tot["wr"],
+    js = {"kernel": "k_conv_tc + k_conv_tcp (all instantiations)", "kernel_digest": kernel_digest(), "launches": n, "dram_bytes_read": tot["rd"], "dram_bytes_write": tot["wr"],
           "dram_bytes_per_launch": (tot["rd"] + tot["wr"]) / n, "lts_bytes_per_launch": tot["lts"] / n,
           "time_us_cold": round(tot["t"], 2), "tensor_pipe_active_pct_time_weighted": tot["tw"] / tot["t"],
           "source": "ncu --set full --clock-control none -k regex:k_conv_tc, one inference step (BENCH_PROFILE=1 python bench.py); "
