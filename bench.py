@@ -276,6 +276,12 @@ def bench_infer(ctx, args, workload, dtype_name, steps, warmup, clk=None, brief=
 
     for _ in range(max(warmup, 2 * int(getattr(det, "lanes", 1)) + 1)):   # every executor lane sees both of its arenas
         step_device()
+    # det.submit: one host thread per executor lane (the executor's call blocks on row-count reads of its coordinate stream;
+    # from a single thread the host needed as long to enqueue a step as the GPU to run one).  B2_ASYNC=0: synchronous calls.
+    use_submit = os.environ.get("B2_ASYNC", "1") != "0" and getattr(det, "lanes", 1) > 1 and not det.training
+    if use_submit:
+        for h in [det.submit(dev_pts, read=False, inputs_ready=True) for _ in range(2 * det.lanes)]:
+            wait_ready(h.dets())
     torch.cuda.synchronize()
     launches0 = lib.b2_launch_count()
     if clk is not None:
@@ -293,8 +299,11 @@ def bench_infer(ctx, args, workload, dtype_name, steps, warmup, clk=None, brief=
     recent = []
     for _ in range(steps):
         ctx.flush.fill_(1)
-        dets = step_device()
+        dets = det.submit(dev_pts, read=False, inputs_ready=True) if use_submit else step_device()
         recent = (recent + [dets])[-4:]
+    if use_submit:
+        recent = [h.dets() for h in recent]
+        dets = recent[-1]
     host_ms = 1000.0 * (time.perf_counter() - h0) / steps      # time the host needed to ENQUEUE a step (incl. its reads)
     for d in recent:            # the last steps' work runs on the executor's own streams: the bracket closes behind them
         wait_ready(d)
@@ -313,7 +322,10 @@ def bench_infer(ctx, args, workload, dtype_name, steps, warmup, clk=None, brief=
         # (fcaf3d_b200.data.ScenePrefetcher) and overlaps the compute of step i; L2 is flushed inside the loop.
         k_e2e = max(5, steps)
         for pts in ScenePrefetcher((host_pts for _ in range(5)), dev):       # warm-up through the SAME path
-            DetectionRead(det.simple_test_fused(pts, to_host=False), batch).finish()
+            if use_submit:
+                det.submit(pts, read=True).result()
+            else:
+                DetectionRead(det.simple_test_fused(pts, to_host=False), batch).finish()
         ctx.barrier()
         torch.cuda.synchronize()
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -322,11 +334,15 @@ def bench_infer(ctx, args, workload, dtype_name, steps, warmup, clk=None, brief=
         depth = max(1, int(getattr(det, "lanes", 1)))
         for pts in ScenePrefetcher((host_pts for _ in range(k_e2e)), dev):
             ctx.flush.fill_(1)
-            pending.append(DetectionRead(det.simple_test_fused(pts, to_host=False), batch))   # async packed copy, side stream
+            if use_submit:
+                pending.append(det.submit(pts, read=True))       # lane thread: executor call + async packed read-back
+            else:
+                pending.append(DetectionRead(det.simple_test_fused(pts, to_host=False), batch))   # async packed copy, side stream
             if len(pending) > depth:
-                pending.pop(0).finish()             # an earlier step's detections, read while the later ones run
+                r_ = pending.pop(0)                 # an earlier step's detections, read while the later ones run
+                r_.result() if use_submit else r_.finish()
         for r_ in pending:
-            r_.finish()
+            r_.result() if use_submit else r_.finish()
         e.record()
         torch.cuda.synchronize()
         ms_e2e = ctx.max_over_ranks(s.elapsed_time(e)) / k_e2e
@@ -634,8 +650,9 @@ def main():
                                   "calibrated on the batch",
                        "l2": "256 MB flush write before every step, inside the one timed bracket over all steps"
                              if args.mode == "infer" else "activations of one step (GBs) exceed L2",
-                       "pipelining": "steps overlap: executor lanes x (coordinate, feature, tail) streams; python gc is off "
-                                     "inside the device-resident bracket only (on in the end-to-end bracket)"
+                       "pipelining": "steps overlap: executor lanes (one host thread each, detector.submit) x (coordinate, "
+                                     "feature, tail) streams; python gc is off inside the device-resident bracket only "
+                                     "(on in the end-to-end bracket); host_ms_per_step = the submitting thread's time"
                                      if args.mode == "infer" else "maps of batch i+1 built between forward and backward of i",
                        "sharding": "whole scenes per GPU, no collective" if args.mode == "infer" else
                                    "data parallel, 8 scenes per GPU, DDP gradient all-reduce over NCCL"},

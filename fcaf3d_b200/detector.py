@@ -15,6 +15,8 @@ reference's own three files, loaded unmodified on this package's surfaces by `fc
 """
 import math
 import os
+import queue
+import threading
 
 import torch
 import torch.nn as nn
@@ -583,27 +585,28 @@ class DetectionRead:
     stream behind the step's last kernel, so the caller can enqueue the NEXT step before it looks at the result
     (`finish()`); the GPU never waits for the host between two steps.
 
-    Staging: per (device, box width, count dtype) a ring of SLOTS pinned buffers; read k uses slot k % SLOTS, so up to
-    SLOTS reads may be in flight before a buffer is reused, and `finish()` hands out a copy, never the pinned rows."""
-    SLOTS = 4
+    Staging: per (device, box width, count dtype) a pool of pinned buffers; a read takes a free one (or allocates one: the
+    pool grows to the largest number of reads ever outstanding) and `finish()` hands out a copy, never the pinned rows,
+    and puts the buffer back."""
     CAP = 16384
     _streams = {}      # device index -> side stream
-    _rings = {}        # (device index, box width, count dtype) -> [slots, next read number]
+    _pools = {}        # (device index, box width, count dtype) -> free (rows, count) pinned buffers
+    _lock = threading.Lock()   # reads may be started from the detector's lane threads (submit)
 
     def __init__(self, dets, num_scenes):
         self.dets, self.num_scenes, self.d = dets, num_scenes, dets["box_dim"]
         dev = dets["boxes"].device
         di = dev.index if dev.index is not None else torch.cuda.current_device()
-        stream = DetectionRead._streams.get(di)
-        if stream is None:
-            stream = DetectionRead._streams[di] = torch.cuda.Stream(device=dev)
-        ring = DetectionRead._rings.setdefault((di, self.d, str(dets["count"].dtype)), [[None] * self.SLOTS, 0])
-        slot = ring[1] % self.SLOTS
-        ring[1] += 1
-        if ring[0][slot] is None:
-            ring[0][slot] = (torch.empty((self.CAP, self.d + 3), dtype=torch.float32).pin_memory(),
-                             torch.empty((1,), dtype=dets["count"].dtype).pin_memory())
-        full, self.count_host = ring[0][slot]
+        with DetectionRead._lock:
+            stream = DetectionRead._streams.get(di)
+            if stream is None:
+                stream = DetectionRead._streams[di] = torch.cuda.Stream(device=dev)
+            self._pool = DetectionRead._pools.setdefault((di, self.d, str(dets["count"].dtype)), [])
+            self._buf = self._pool.pop() if self._pool else None
+        if self._buf is None:
+            self._buf = (torch.empty((self.CAP, self.d + 3), dtype=torch.float32).pin_memory(),
+                         torch.empty((1,), dtype=dets["count"].dtype).pin_memory())
+        full, self.count_host = self._buf
         done = torch.cuda.Event()
         done.record()
         cap = min(self.CAP, int(dets["boxes"].shape[0]))
@@ -622,11 +625,73 @@ class DetectionRead:
             self._keep = packed
 
     def finish(self):
+        if self._buf is None:                 # a second call: the staging buffer has gone back to the pool
+            return self._out
         self.event.synchronize()
         n = int(self.count_host[0])
-        if n > self.cap:                      # more detections than the staged rows: fall back to the blocking read
-            return split_detections(self.dets, self.num_scenes)
-        return _split_packed(self.host[:n].clone(), self.d, self.num_scenes)
+        out = None if n > self.cap else _split_packed(self.host[:n].clone(), self.d, self.num_scenes)
+        if self._buf is not None:             # the staging buffer goes back to the pool (once)
+            with DetectionRead._lock:
+                self._pool.append(self._buf)
+            self._buf = None
+        if out is None:                       # more detections than the staged rows: fall back to the blocking read
+            out = split_detections(self.dets, self.num_scenes)
+        self._out = out
+        return out
+
+
+class PendingDetections:
+    """Handle of a step handed to a lane thread (SingleStageSparse3DDetector.submit)."""
+
+    def __init__(self, num_scenes, read):
+        self.num_scenes, self.read = num_scenes, read
+        self._done = threading.Event()
+        self._dets = self._reader = self._error = None
+
+    def dets(self):
+        """device-side result dict (blocks until the lane thread has ENQUEUED the step; see wait_ready for its completion)"""
+        self._done.wait()
+        if self._error is not None:
+            raise self._error
+        return self._dets
+
+    def result(self):
+        """per-scene detections on the host (list of (boxes, scores, labels)), like simple_test_fused(to_host=True)"""
+        d = self.dets()
+        return self._reader.finish() if self._reader is not None else split_detections(d, self.num_scenes)
+
+
+class _LaneWorker(threading.Thread):
+    """One host thread per executor lane: the executor's call blocks on row-count reads from ITS coordinate stream (the GIL
+    is released inside the library call), so with one thread for all lanes the host needed as long to enqueue a step as
+    the GPU to run one; with a thread per lane the enqueues of consecutive steps overlap."""
+
+    def __init__(self, engine, stream, dev):
+        super().__init__(daemon=True)
+        self.engine, self.stream, self.dev = engine, stream, dev
+        self.jobs = queue.Queue(maxsize=1)     # one step being enqueued + one waiting per lane
+        self.start()
+
+    def run(self):
+        torch.cuda.set_device(self.dev)
+        while True:
+            job = self.jobs.get()
+            if job is None:
+                return
+            points, inputs_ready, after, pending = job
+            try:
+                with torch.no_grad(), torch.cuda.stream(self.stream):
+                    self.stream.wait_event(after)       # whatever the caller queued before submit() comes first
+                    dets = self.engine(points, inputs_ready=inputs_ready)
+                    if "ready" not in dets:
+                        dets["ready"] = torch.cuda.Event()
+                        dets["ready"].record(self.stream)
+                    pending._dets = dets
+                    if pending.read:
+                        pending._reader = DetectionRead(dets, pending.num_scenes)
+            except BaseException as exc:            # handed to the caller of dets() / result()
+                pending._error = exc
+            pending._done.set()
 
 
 # =============================================================================================== detector
@@ -649,6 +714,7 @@ class SingleStageSparse3DDetector(nn.Module):
         # levels run 84 - 99 CTAs on 148 SMs, every layer ends in a partial wave).  Results carry a `ready` event.
         self.lanes = int(os.environ.get("B2_LANES", "2"))      # measured: 5.29 -> 4.88 ms per step with 2, no more with 3
         self._lane_engines, self._lane_streams, self._lane_next = [], [], 0
+        self._lane_workers = []                                # host threads of submit(), one per lane
         self.init_weights()
 
     def init_weights(self, pretrained=None):
@@ -690,12 +756,42 @@ class SingleStageSparse3DDetector(nn.Module):
         dets = self.neck_with_head.get_bboxes_fused(levels, x.coordinate_manager)
         return split_detections(dets, len(points)) if to_host else dets
 
-    def _run_on_lane(self, points, inputs_ready):
-        from . import engine as E
+    def submit(self, points, read=True, inputs_ready=None):
+        """Asynchronous form of simple_test_fused for serving loops: the step is handed to the next lane's host thread and a
+        PendingDetections handle comes back at once; `handle.result()` gives the per-scene detections (read back through
+        DetectionRead when `read`), `handle.dets()` the device-side dict.  Steps submitted from one thread are executed in
+        order on alternating lanes; at most two steps per lane are outstanding (submit blocks beyond that).  Without the
+        native executor (training mode, profiling, ...) the step runs synchronously in the caller's thread."""
+        pending = PendingDetections(len(points), read)
+        if not (self._engine_ok() and self.lanes > 1):
+            pending._dets = self.simple_test_fused(points, to_host=False, inputs_ready=inputs_ready)
+            if read:
+                pending._reader = DetectionRead(pending._dets, len(points))
+            pending._done.set()
+            return pending
         dev = points[0].device
+        self._make_lanes(dev)
+        while len(self._lane_workers) < self.lanes:
+            i = len(self._lane_workers)
+            self._lane_workers.append(_LaneWorker(self._lane_engines[i], self._lane_streams[i], dev))
+        lane = self._lane_next % self.lanes
+        self._lane_next += 1
+        after = torch.cuda.Event()
+        after.record(torch.cuda.current_stream(dev))
+        if inputs_ready is None:
+            inputs_ready = getattr(points, "ready", None)
+        self._lane_workers[lane].jobs.put((points, inputs_ready, after, pending))
+        return pending
+
+    def _make_lanes(self, dev):
+        from . import engine as E
         while len(self._lane_engines) < self.lanes:
             self._lane_engines.append(self._engine if not self._lane_engines else E.InferenceEngine(self))
             self._lane_streams.append(torch.cuda.Stream(device=dev))
+
+    def _run_on_lane(self, points, inputs_ready):
+        dev = points[0].device
+        self._make_lanes(dev)
         lane = self._lane_next % self.lanes
         self._lane_next += 1
         s = self._lane_streams[lane]

@@ -158,7 +158,7 @@ def test_two_detection_reads_in_flight_from_a_cold_start(dev):
     """the pinned staging ring of DetectionRead must hand every in-flight read its own buffer from the first
     call on, and finish() must return rows that a later read cannot overwrite."""
     from fcaf3d_b200.detector import DetectionRead, split_detections
-    DetectionRead._rings.clear()                           # cold start: no staging buffer exists yet
+    DetectionRead._pools.clear()                           # cold start: no staging buffer exists yet
     g, det, pts = _load("fcaf3d_tiny_scannet.npz", "scannet", dev)
     with torch.no_grad():
         d1 = det.simple_test_fused(pts, to_host=False)

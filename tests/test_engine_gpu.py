@@ -80,3 +80,36 @@ def test_tf32_mode_engine_equals_python_and_tracks_fp32(dev):
         for k in ("centerness", "bbox_pred", "cls"):
             worst = max(worst, ((a[k] - b[k]).abs() / b[k].abs().max(0).values.clamp(min=1e-6)).max().item())
     assert 0 < worst < 2e-2, worst
+
+
+def test_submit_on_lane_threads_equals_the_synchronous_calls(dev):
+    """detector.submit: steps handed to the lanes' host threads give, in submission order, exactly what simple_test_fused
+    gives for the same inputs - with read-back (DetectionRead inside the lane thread) and without, with several steps
+    outstanding, from a cold start; an error inside a lane thread is raised by the handle."""
+    det = deterministic_init(build_fcaf3d("scannet", depth=14), 0, cls_bias=0.0).to(dev).eval()
+    assert det.lanes >= 2
+    ME.set_compute_dtype(torch.bfloat16)
+    try:
+        batches = [[torch.from_numpy(make_scene("tiny", 10 * b + s, 3000)[0]).to(dev) for s in (1, 2)] for b in range(3)]
+        handles = [det.submit(batches[i % 3], read=True) for i in range(7)]          # cold start, > 2 x lanes outstanding
+        got = [h.result() for h in handles]
+        raw = [det.submit(batches[i % 3], read=False) for i in range(3)]
+        raw = [wait_ready(h.dets()) for h in raw]
+        want = [det.simple_test_fused(b, to_host=True) for b in batches]
+        assert len(det._lane_workers) == det.lanes
+        for i, g in enumerate(got):
+            w = want[i % 3]
+            assert len(g) == len(w) == 2
+            for (gb, gs, gl), (wb, ws, wl) in zip(g, w):
+                assert gb.shape[0] > 0 and torch.equal(gb, wb) and torch.equal(gs, ws) and torch.equal(gl, wl)
+        for i, d in enumerate(raw):
+            n = int(d["count"].item())
+            assert n == sum(b.shape[0] for b, _, _ in want[i])
+            assert torch.equal(d["boxes"][:n, :d["box_dim"]].cpu(), torch.cat([b for b, _, _ in want[i]]))
+        bad = det.submit([batches[0][0], batches[0][1].cpu()], read=True)      # refused by the executor, inside the lane thread
+        with pytest.raises(Exception):
+            bad.result()
+        ok = det.submit(batches[0], read=True).result()                             # the lane thread survives the error
+        assert torch.equal(ok[0][0], want[0][0][0])
+    finally:
+        ME.set_compute_dtype(torch.float32)
