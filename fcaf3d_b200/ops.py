@@ -4,8 +4,8 @@ Tensors are torch CUDA tensors used purely as device memory; every op enqueues o
 stream.  No op has a CPU path.
 """
 import ctypes
-
 import os
+import threading
 
 import torch
 
@@ -32,18 +32,19 @@ def alloc_table(n, device):
     return torch.empty(cap * 16, dtype=torch.uint8, device=device), cap
 
 
-_PINNED = {"bufs": [], "next": 0}
+_PINNED = threading.local()     # one ring per host thread (map building from a thread of its own must not share slots)
 
 
 def _pinned_ints(n):
-    """Small pinned int32 staging buffers, reused round-robin (64 outstanding reads at most)."""
-    if not _PINNED["bufs"]:
-        _PINNED["bufs"] = [torch.empty((256,), dtype=I32).pin_memory() for _ in range(64)]
+    """Small pinned int32 staging buffers, reused round-robin (64 outstanding reads per thread at most)."""
+    if not hasattr(_PINNED, "bufs"):
+        _PINNED.bufs = [torch.empty((256,), dtype=I32).pin_memory() for _ in range(64)]
+        _PINNED.next = 0
     if n > 256:
         return torch.empty((n,), dtype=I32).pin_memory()
-    i = _PINNED["next"]
-    _PINNED["next"] = (i + 1) % len(_PINNED["bufs"])
-    return _PINNED["bufs"][i][:n]
+    i = _PINNED.next
+    _PINNED.next = (i + 1) % len(_PINNED.bufs)
+    return _PINNED.bufs[i][:n]
 
 
 class HostRead:
