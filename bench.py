@@ -652,7 +652,8 @@ def main():
                              if args.mode == "infer" else "activations of one step (GBs) exceed L2",
                        "pipelining": "steps overlap: executor lanes (one host thread each, detector.submit) x (coordinate, "
                                      "feature, tail) streams; python gc is off inside the device-resident bracket only "
-                                     "(on in the end-to-end bracket); host_ms_per_step = the submitting thread's time"
+                                     "(on in the end-to-end bracket); host_ms_per_step = the submitting thread's time per step, which includes waiting for a free lane slot "
+                                     "(back-pressure: two steps per lane outstanding at most)"
                                      if args.mode == "infer" else "maps of batch i+1 built between forward and backward of i",
                        "sharding": "whole scenes per GPU, no collective" if args.mode == "infer" else
                                    "data parallel, 8 scenes per GPU, DDP gradient all-reduce over NCCL"},
