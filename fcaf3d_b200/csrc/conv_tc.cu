@@ -451,6 +451,12 @@ extern "C" int b2_conv_tc_tf32(const void* in_f32, long long n_in, const void* w
   B2_CHECK_ARG(out_rows == nullptr || nbr != nullptr, "a row permutation needs a neighbour table");
   if (n_out == 0) return B2_OK;
   cudaStream_t st = (cudaStream_t)stream;
+  {
+    int taken = 0;
+    const int rc = b2_conv_tcp_dispatch(in_f32, wt_f32, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, shift,
+                                        residual, act, ch_mod, out, 1, st, &taken);
+    if (rc != B2_OK || taken) return rc;
+  }
   if (cout % 128 == 0)
     return launch_tf32<128, 3>(in_f32, wt_f32, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, shift,
                                residual, act, ch_mod, out, st);
@@ -478,7 +484,7 @@ extern "C" int b2_conv_tc(const void* in_bf16, long long n_in, const void* wt_bf
   if (out_dtype == 1) {
     int taken = 0;
     const int rc = b2_conv_tcp_dispatch(in_bf16, wt_bf16, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale,
-                                        shift, residual, act, ch_mod, out, st, &taken);
+                                        shift, residual, act, ch_mod, out, 0, st, &taken);
     if (rc != B2_OK || taken) return rc;
   }
   const bool wide = (cout % 128 == 0);

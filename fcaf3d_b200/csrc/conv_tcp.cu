@@ -62,43 +62,62 @@ __device__ __forceinline__ unsigned long long tcp_ns() {
 
 __device__ __forceinline__ void tcp_bar_producers() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
-// one 32-column chunk of a row: (acc + bias) * scale + shift (+ residual), activation, bf16 store
+// one 32-column chunk of a row: (acc + bias) * scale + shift (+ residual), activation, store (bf16, or fp32 in the TF32 mode)
+template <typename T>
 __device__ __forceinline__ void tcp_store_chunk(const uint32_t* v, const float* s_epi, int bn, int cc,
-                                                const __nv_bfloat16* __restrict__ residual, __nv_bfloat16* __restrict__ out,
-                                                long long base, int act) {
+                                                const T* __restrict__ residual, T* __restrict__ out, long long base,
+                                                int act) {
   float f[32];
 #pragma unroll
   for (int j = 0; j < 32; ++j) f[j] = (__uint_as_float(v[j]) + s_epi[cc + j]) * s_epi[bn + cc + j] + s_epi[2 * bn + cc + j];
   if (residual) {
-    const uint4* rp = reinterpret_cast<const uint4*>(residual + base);
+    if (sizeof(T) == 2) {
+      const uint4* rp = reinterpret_cast<const uint4*>(residual + base);
 #pragma unroll
-    for (int qq = 0; qq < 4; ++qq) {
-      const uint4 u = __ldg(rp + qq);
-      const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
+      for (int qq = 0; qq < 4; ++qq) {
+        const uint4 u = __ldg(rp + qq);
+        const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        f[qq * 8 + e * 2] += __uint_as_float(w4[e] << 16);
-        f[qq * 8 + e * 2 + 1] += __uint_as_float(w4[e] & 0xFFFF0000u);
+        for (int e = 0; e < 4; ++e) {
+          f[qq * 8 + e * 2] += __uint_as_float(w4[e] << 16);
+          f[qq * 8 + e * 2 + 1] += __uint_as_float(w4[e] & 0xFFFF0000u);
+        }
+      }
+    } else {
+      const float4* rp = reinterpret_cast<const float4*>(residual + base);
+#pragma unroll
+      for (int qq = 0; qq < 8; ++qq) {
+        const float4 u = __ldg(rp + qq);
+        f[qq * 4] += u.x;
+        f[qq * 4 + 1] += u.y;
+        f[qq * 4 + 2] += u.z;
+        f[qq * 4 + 3] += u.w;
       }
     }
   }
-  if (act == B2_ACT_ELU) {
+  if (sizeof(T) == 2 && act == B2_ACT_ELU) {
 #pragma unroll
     for (int j = 0; j < 32; ++j) f[j] = b2_elu_bf16(f[j]);
   } else {
 #pragma unroll
     for (int j = 0; j < 32; ++j) f[j] = b2_apply_act(f[j], act);
   }
-  uint4* op = reinterpret_cast<uint4*>(out + base);
+  if (sizeof(T) == 2) {
+    uint4* op = reinterpret_cast<uint4*>(out + base);
 #pragma unroll
-  for (int qq = 0; qq < 4; ++qq) {
-    uint32_t w4[4];
+    for (int qq = 0; qq < 4; ++qq) {
+      uint32_t w4[4];
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const __nv_bfloat162 h = __floats2bfloat162_rn(f[qq * 8 + e * 2], f[qq * 8 + e * 2 + 1]);
-      w4[e] = *reinterpret_cast<const uint32_t*>(&h);
+      for (int e = 0; e < 4; ++e) {
+        const __nv_bfloat162 h = __floats2bfloat162_rn(f[qq * 8 + e * 2], f[qq * 8 + e * 2 + 1]);
+        w4[e] = *reinterpret_cast<const uint32_t*>(&h);
+      }
+      op[qq] = make_uint4(w4[0], w4[1], w4[2], w4[3]);
     }
-    op[qq] = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+  } else {
+    float4* op = reinterpret_cast<float4*>(out + base);
+#pragma unroll
+    for (int qq = 0; qq < 8; ++qq) op[qq] = make_float4(f[qq * 4], f[qq * 4 + 1], f[qq * 4 + 2], f[qq * 4 + 3]);
   }
 }
 
@@ -111,13 +130,15 @@ __device__ __forceinline__ int tcp_tile(int i, int c, int G, int n_tiles, bool r
 
 // EPI == 1 (BN == 32): the fused head GEMM, whose epilogue writes the head outputs (TcHeadEpi) instead of `out`.
 // nbr == nullptr: identity map (dense GEMM over consecutive rows: generative transposes, heads), one stage per 64 channels.
-template <int BN, int ST, int EPI = 0>
+// T = __nv_bfloat16 (kind::f16) or float (kind::tf32: fp32 rows and weights as TF32 operands, 32 channels per stage row,
+// fp32 output - the persistent form of b2_conv_tc_tf32).
+template <int BN, int ST, int EPI = 0, typename T = __nv_bfloat16>
 __global__ void __launch_bounds__(TCP_THREADS, 2)
-k_conv_tcp(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __restrict__ in, const int* __restrict__ nbr,
+k_conv_tcp(const __grid_constant__ CUtensorMap map_b, const T* __restrict__ in, const int* __restrict__ nbr,
            int ld, const unsigned int* __restrict__ tile_mask, const int* __restrict__ out_rows, int n_out, int n_tiles,
            int cin, int cout, int kvol, const float* __restrict__ bias, const float* __restrict__ scale,
-           const float* __restrict__ shift, const __nv_bfloat16* __restrict__ residual, int act, int ch_mod,
-           __nv_bfloat16* __restrict__ out, const TcHeadEpi hp) {
+           const float* __restrict__ shift, const T* __restrict__ residual, int act, int ch_mod,
+           T* __restrict__ out, const TcHeadEpi hp) {
   using Cfg = TcpCfg<BN, ST>;
   constexpr int S = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
@@ -136,7 +157,8 @@ k_conv_tcp(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __res
   const unsigned long long ns_start = tcp_ns();
 #endif
   const int col0 = blockIdx.y * BN;
-  const int chunks = cin / TC_BK;
+  constexpr int BKE = 128 / (int)sizeof(T);   // channels per stage row (128 bytes)
+  const int chunks = cin / BKE;
   const unsigned int kvalid = (1u << kvol) - 1u;
   const bool dense = nbr == nullptr;   // every tile has the one offset of the identity map
   const bool rev = out_rows != nullptr;   // sorted tables put the tiles with the most offsets last: walk them first
@@ -186,7 +208,7 @@ k_conv_tcp(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __res
     // the staged neighbour table holds 16-byte units (row * cin / 8, -1 = absent): the multiplication is done once per entry
     // at staging time and a producer needs three instructions per row (load, sign test, 64-bit address)
     const uint4* in_thr = reinterpret_cast<const uint4*>(in) + chunk16;
-    const int row_units = cin >> 3;
+    const int row_units = cin * (int)sizeof(T) / 16;
     const uint32_t smem_base = smem_u32(smem);
     int it = 0;
     long long t_ps = 0;
@@ -221,6 +243,8 @@ k_conv_tcp(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __res
         tc_produce<S, Cfg::STAGE_BYTES, 1>(kmask, 1, group, s_nbr + rsub, in_thr, smem_base + dst_off, full_bar, empty_bar, it);
       else if (chunks == 2)
         tc_produce<S, Cfg::STAGE_BYTES, 2>(kmask, 2, group, s_nbr + rsub, in_thr, smem_base + dst_off, full_bar, empty_bar, it);
+      else if (chunks == 4)
+        tc_produce<S, Cfg::STAGE_BYTES, 4>(kmask, 4, group, s_nbr + rsub, in_thr, smem_base + dst_off, full_bar, empty_bar, it);
       else
         tc_produce<S, Cfg::STAGE_BYTES, 0>(kmask, chunks, group, s_nbr + rsub, in_thr, smem_base + dst_off, full_bar, empty_bar,
                                             it);
@@ -230,7 +254,8 @@ k_conv_tcp(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __res
     if (tid == 0) TCP_STAT(6, t_ps);
   } else if (warp == 8) {
     // ===================== MMA issuer (one elected thread; the warp waits together) =======================
-    constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((128u >> 4) << 24);
+    constexpr uint32_t fmt = sizeof(T) == 2 ? 1u : 2u;   // A / B format: BF16 or TF32
+    constexpr uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((128u >> 4) << 24);
     const uint64_t desc0 = umma_desc_sw128(smem_u32(smem));
     const bool leader = elect_one();
     int s = 0;
@@ -261,8 +286,12 @@ k_conv_tcp(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __res
           const uint64_t da = desc0 + (uint64_t)((s * Cfg::STAGE_BYTES) >> 4);
           const uint64_t db = da + (uint64_t)(Cfg::A_BYTES >> 4);
 #pragma unroll
-          for (int kk = 0; kk < TC_BK / 16; ++kk)
-            umma_bf16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (i > 0 || kk > 0) ? 1u : 0u);
+          for (int kk = 0; kk < TC_BK / 16; ++kk) {
+            if (sizeof(T) == 2)
+              umma_bf16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (i > 0 || kk > 0) ? 1u : 0u);
+            else
+              umma_tf32(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (i > 0 || kk > 0) ? 1u : 0u);
+          }
           umma_commit(&empty_bar[s]);  // frees the smem stage once these MMAs have read it
         }
         __syncwarp();
@@ -297,7 +326,7 @@ k_conv_tcp(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __res
           mbar_wait(&empty_bar[s], phase ^ 1u);
           if (leader) {
             mbar_expect_tx(&full_bar[s], (uint32_t)Cfg::B_BYTES);
-            tma_tile_2d(smem_base + s * Cfg::STAGE_BYTES + Cfg::A_BYTES, &map_b, &full_bar[s], c * TC_BK, k * cout + col0);
+            tma_tile_2d(smem_base + s * Cfg::STAGE_BYTES + Cfg::A_BYTES, &map_b, &full_bar[s], c * BKE, k * cout + col0);
           }
           __syncwarp();
           if (++s == S) {
@@ -344,7 +373,7 @@ k_conv_tcp(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __res
             tc_head_row(f, (long long)o, hp);
           }
         } else {
-          if (o < n_out) tcp_store_chunk(v, s_epi, BN, cc, residual, out, (long long)o * cout + col0 + cc, act);
+          if (o < n_out) tcp_store_chunk<T>(v, s_epi, BN, cc, residual, out, (long long)o * cout + col0 + cc, act);
         }
       }
       tc_fence_before();
@@ -375,24 +404,25 @@ k_conv_tcp(const __grid_constant__ CUtensorMap map_b, const __nv_bfloat16* __res
   }
 }
 
-template <int BN, int ST>
+template <int BN, int ST, typename T>
 static int launch_tcp(const void* in, const void* wt, const int* nbr, long long ld, const unsigned int* tile_mask,
                       const int* out_rows, long long n_out, int cin, int cout, int kvol, const float* bias,
                       const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
                       int ctas, cudaStream_t st) {
   using Cfg = TcpCfg<BN, ST>;
-  auto kern = k_conv_tcp<BN, ST, 0>;
+  auto kern = k_conv_tcp<BN, ST, 0, T>;
   static unsigned long long configured = 0;  // per template instance, one bit per device
   if (int rc0 = b2_optin_smem((const void*)kern, Cfg::SMEM, &configured)) return rc0;
   CUtensorMap map_b;
-  const int rc = b2_make_bf16_map(&map_b, wt, (long long)kvol * cout, cin, BN);
+  const int rc = sizeof(T) == 2 ? b2_make_bf16_map(&map_b, wt, (long long)kvol * cout, cin, BN)
+                                : b2_make_tf32_map(&map_b, wt, (long long)kvol * cout, cin, BN);
   if (rc) return rc;
   const int n_tiles = (int)b2_div_up(n_out, TC_BM);
   const int gy = cout / BN;
   dim3 grid((unsigned)std::min(n_tiles, std::max(1, ctas / gy)), (unsigned)gy);
-  kern<<<grid, TCP_THREADS, Cfg::SMEM, st>>>(map_b, (const __nv_bfloat16*)in, nbr, (int)ld, tile_mask, out_rows, (int)n_out,
-                                             n_tiles, cin, cout, kvol, bias, scale, shift, (const __nv_bfloat16*)residual, act,
-                                             ch_mod, (__nv_bfloat16*)out, TcHeadEpi());
+  kern<<<grid, TCP_THREADS, Cfg::SMEM, st>>>(map_b, (const T*)in, nbr, (int)ld, tile_mask, out_rows, (int)n_out, n_tiles, cin,
+                                             cout, kvol, bias, scale, shift, (const T*)residual, act, ch_mod, (T*)out,
+                                             TcHeadEpi());
   B2_LAUNCH_CHECK();
   return B2_OK;
 }
@@ -411,7 +441,7 @@ extern "C" int b2_tc_persist_mode(int mode) {
 int b2_conv_tcp_dispatch(const void* in, const void* wt, const int* nbr, long long ld, const unsigned int* tile_mask,
                          const int* out_rows, long long n_out, int cin, int cout, int kvol, const float* bias,
                          const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
-                         cudaStream_t st, int* taken) {
+                         int tf32, cudaStream_t st, int* taken) {
   *taken = 0;
   static const int enabled = getenv("B2_TC_PERSIST") ? atoi(getenv("B2_TC_PERSIST")) : 1;
   static const int min_env = getenv("B2_TC_PERSIST_MIN_TILES") ? atoi(getenv("B2_TC_PERSIST_MIN_TILES")) : 0;
@@ -428,11 +458,18 @@ int b2_conv_tcp_dispatch(const void* in, const void* wt, const int* nbr, long lo
   const long long tiles = b2_div_up(n_out, TC_BM) * (dense ? cout / 128 : 1);
   if (g_persist_mode != 2 && tiles < (min_env > 0 ? min_env : 4 * sms[dev])) return B2_OK;
   *taken = 1;
+  if (tf32) {   // fp32 rows / weights / output (b2_conv_tc_tf32)
+    if (cout == 64)
+      return launch_tcp<64, 4, float>(in, wt, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, shift,
+                                      residual, act, ch_mod, out, ctas, st);
+    return launch_tcp<128, 3, float>(in, wt, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, shift,
+                                     residual, act, ch_mod, out, ctas, st);
+  }
   if (cout == 64)
-    return launch_tcp<64, 4>(in, wt, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, shift, residual, act,
-                             ch_mod, out, ctas, st);
-  return launch_tcp<128, 3>(in, wt, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, shift, residual, act,
-                            ch_mod, out, ctas, st);
+    return launch_tcp<64, 4, __nv_bfloat16>(in, wt, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, shift,
+                                            residual, act, ch_mod, out, ctas, st);
+  return launch_tcp<128, 3, __nv_bfloat16>(in, wt, nbr, ld, tile_mask, out_rows, n_out, cin, cout, kvol, bias, scale, shift,
+                                           residual, act, ch_mod, out, ctas, st);
 }
 
 // The fused head GEMM (b2_head_fused) on the persistent kernel: 32 head columns, epilogue = head post-processing.

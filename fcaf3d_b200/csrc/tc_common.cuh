@@ -207,7 +207,7 @@ int b2_make_tf32_map(CUtensorMap* map, const void* base, long long rows, int col
 int b2_conv_tcp_dispatch(const void* in, const void* wt, const int* nbr, long long ld, const unsigned int* tile_mask,
                          const int* out_rows, long long n_out, int cin, int cout, int kvol, const float* bias,
                          const float* scale, const float* shift, const void* residual, int act, int ch_mod, void* out,
-                         cudaStream_t st, int* taken);
+                         int tf32, cudaStream_t st, int* taken);
 int b2_head_tcp_dispatch(const void* in, long long n, const void* wt, int cin, const float* bias, const TcHeadEpi& hp,
                          cudaStream_t st, int* taken);
 // host: opt-in of one kernel to `bytes` of dynamic shared memory on the CURRENT device, once per device

@@ -331,3 +331,40 @@ def test_conv_tf32_tensor_core_path(dev, cin, cout, ksize, stride):
     assert 0 < err < 1e-3, err                          # > 0: the tensor-core path really ran
     z = ops.sparse_conv(torch.zeros_like(f), w, km, n_out, wt_tf32=wt, out_dtype=torch.float32)
     assert float(z.abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("cin,cout,stride", [(64, 64, 1), (128, 128, 1), (64, 128, 2), (256, 128, 1)])
+def test_persistent_kernel_tf32_is_bit_identical(dev, cin, cout, stride, monkeypatch):
+    """The TF32 form of the persistent kernel (fp32 rows, weights and output) against k_conv_tc<..., float> on the same
+    layer: equal bit for bit, plain and sparsity-sorted table, fused epilogue with ELU and an fp32 residual."""
+    from fcaf3d_b200._lib import lib
+    from util import surface_coords
+    c = torch.from_numpy(surface_coords(60000, 3, seed=7)).to(dev)
+    x0 = ME.SparseTensor(torch.zeros(len(c), 1, device=dev), coordinates=c)
+    cm, key = x0.coordinate_manager, x0.coordinate_map_key
+    okey = key if stride == 1 else cm.stride(key, stride)
+    n_in, n_out = cm.size(key), cm.size(okey)
+    torch.manual_seed(3)
+    f = torch.randn(n_in, cin, device=dev)
+    w = torch.randn(27, cin, cout, device=dev) * 0.05
+    wt = w.transpose(1, 2).contiguous()
+    scale, shift = torch.rand(cout, device=dev) + .5, torch.randn(cout, device=dev)
+    res = torch.randn(n_out, cout, device=dev)
+    kw = dict(wt_tf32=wt, scale=scale, shift=shift, residual=res, act=ops.ACT_ELU, out_dtype=torch.float32)
+    outs = {}
+    for mode in (1, 2):
+        old = lib().b2_tc_persist_mode(mode)
+        try:
+            km = cm.kernel_map(key, okey, 3)
+            km.sorted = None
+            monkeypatch.setattr(ops, "SORT_MIN_ROWS", 0)
+            plain = ops.sparse_conv(f, w, km, n_out, **kw)
+            monkeypatch.setattr(ops, "SORT_MIN_ROWS", 1)
+            monkeypatch.setattr(ops, "SORT_MIN_USES", 1)
+            outs[mode] = (plain, ops.sparse_conv(f, w, km, n_out, **kw))
+        finally:
+            lib().b2_tc_persist_mode(old)
+    assert torch.equal(outs[1][0], outs[2][0]) and torch.equal(outs[1][1], outs[2][1])
+    assert torch.equal(outs[2][0], outs[2][1]) and float(outs[2][0].abs().max()) > 0
+    y_cc = ops.sparse_conv(f, w, km, n_out, scale=scale, shift=shift, residual=res, act=ops.ACT_ELU, out_dtype=torch.float32)
+    assert ((outs[2][0] - y_cc).abs().max() / y_cc.abs().max()).item() < 1e-3
