@@ -721,6 +721,13 @@ class SingleStageSparse3DDetector(nn.Module):
         self.backbone.init_weights()
         self.neck_with_head.init_weights()
 
+    def __getstate__(self):
+        """copy.deepcopy / pickle of the module: executors, their streams and lane threads are per-process run-time state
+        (library handles, CUDA streams, threads) and are rebuilt on first use"""
+        state = dict(self.__dict__)
+        state.update(_engine=None, _lane_engines=[], _lane_streams=[], _lane_workers=[], _lane_next=0)
+        return state
+
     def _input_tensor(self, points):
         coords, feats = ops.quantize_points([p.contiguous() for p in points], self.voxel_size, 255.0)
         stem = self.backbone.conv1[0]
